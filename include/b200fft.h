@@ -1,0 +1,108 @@
+/* include/b200fft.h -- the thin C-ABI between the plain-C host side (csrc/fftw_api.c, the
+ * drop-in replacement of the reference's fftw/fftw_api.c public layer) and the CUDA engine
+ * (csrc/engine.cu: kernel-configuration selector + hand-written sm_100a kernels).
+ *
+ * Plain pointers and sizes only; no C++ or torch types.  One shared object is built per
+ * precision (like the reference: FFTW_SINGLE is a compile-time switch, fftw/fftw3.h:65-82),
+ * so "real" below means float in lib/fp32 and double in lib/fp64.
+ *
+ * What each entry point replaces in the reference:
+ *   b2fft_plan_create   <- fftw_mkproblem_dft_d / fftw_mkproblem_rdft2_d_3pointers +
+ *                          fftw_mkapiplan (fftw/fftw_api.c:4110, 9358, 317-407): geometry in,
+ *                          executable plan out.  The recursive planner (fftw_api.c:14745-15710)
+ *                          is replaced by a deterministic selector.
+ *   b2fft_execute       <- fftw_execute / fftw_dft_solve / fftw_rdft2_solve
+ *                          (fftw/fftw_api.c:428-454, 4589, 10577)
+ *   b2fft_plan_destroy  <- fftw_destroy_plan (fftw/fftw_api.c:409-422)
+ *   b2fft_malloc/free   <- fftw_malloc / fftw_free (fftw/fftw_api.c:234-256, 14448)
+ *   b2fft_slab_*        <- fftw/mpi: local_size_guru (mpi/api.c:248-346), default_block
+ *                          (mpi/block.c:39-50), dft-rank-geq2-transposed.c:47-198,
+ *                          transpose-alltoall.c:49-104 (MPI_Alltoall -> NCCL over NVLink)
+ */
+#ifndef B200FFT_H
+#define B200FFT_H
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2FFT_MAXRANK 8
+
+enum { B2FFT_C2C = 0, B2FFT_R2C = 1, B2FFT_C2R = 2 };
+
+/* One loop dimension.  Strides are in ELEMENTS of the array they index: complex elements for
+ * a complex array, reals for a real array (the public "many" convention, fftw_api.c:655-661;
+ * the reference's internal doubling of complex strides, fftw_api.c:842-861, is not exposed). */
+typedef struct { ptrdiff_t n, is, os; } b2fft_dim;
+
+typedef struct {
+    int kind;                       /* B2FFT_C2C / R2C / C2R */
+    int sign;                       /* -1 forward, +1 backward (C2C only; R2C is -1, C2R +1) */
+    int rank;                       /* transform dims, outermost first; n = LOGICAL size */
+    b2fft_dim dims[B2FFT_MAXRANK];
+    int vrank;                      /* batch ("howmany") dims */
+    b2fft_dim vdims[B2FFT_MAXRANK];
+    int in_place;                   /* in == out at plan time */
+    unsigned flags;                 /* FFTW_* planner flags, passed through */
+} b2fft_geom;
+
+typedef struct b2fft_plan_s b2fft_plan;
+
+/* NULL when the geometry is unsupported or the device cannot be initialised; the reason is
+ * then available from b2fft_last_error(). */
+b2fft_plan *b2fft_plan_create(const b2fft_geom *g);
+void        b2fft_plan_destroy(b2fft_plan *p);
+
+/* Synchronous execute.  in/out may each be a host pointer (copied over PCIe inside the call)
+ * or a device/managed pointer (transformed in HBM).  Returns 0, or a CUDA error code. */
+int b2fft_execute(b2fft_plan *p, void *in, void *out);
+/* Asynchronous execute on a caller-provided cudaStream_t (device pointers only). */
+int b2fft_execute_async(b2fft_plan *p, void *in, void *out, void *cuda_stream);
+
+/* Introspection: the selected kernel configurations ("passes"). */
+int    b2fft_plan_num_passes(const b2fft_plan *p);     /* kernels launched per execute */
+int    b2fft_plan_num_hbm_sweeps(const b2fft_plan *p); /* full read+write sweeps over the data */
+size_t b2fft_plan_scratch_bytes(const b2fft_plan *p);
+int    b2fft_plan_describe(const b2fft_plan *p, char *buf, size_t buflen); /* snprintf-like */
+double b2fft_plan_flops(const b2fft_plan *p);          /* 5 N log2 N (c2c), 2.5 N log2 N (real) */
+unsigned long long b2fft_launch_count(void);           /* kernels launched so far (process) */
+
+/* Pinned host memory (what fftw_malloc hands out) and device memory helpers. */
+void *b2fft_malloc(size_t nbytes);
+void  b2fft_free(void *p);
+void *b2fft_device_malloc(size_t nbytes);
+void  b2fft_device_free(void *p);
+
+int         b2fft_device_count(void);       /* 0 => no usable GPU: plans are NULL */
+int         b2fft_set_device(int ordinal);  /* default: $FFTW_CUDA_DEVICE, $LOCAL_RANK or 0 */
+const char *b2fft_last_error(void);
+void        b2fft_cleanup(void);            /* drops cached twiddle tables / workspaces */
+const char *b2fft_precision(void);          /* "fp32" or "fp64" */
+
+/* ---- slab-distributed 3-D c2c (fftw_mpi_plan_dft_3d form), one process per GPU --------- */
+typedef struct b2fft_comm_s b2fft_comm;
+
+/* ceil(n/P) block distribution, exactly fftw/mpi/block.c:39-50. */
+ptrdiff_t b2fft_slab_local_size_3d_transposed(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2,
+                                              int n_pes, int my_pe,
+                                              ptrdiff_t *local_n0, ptrdiff_t *local_0_start,
+                                              ptrdiff_t *local_n1, ptrdiff_t *local_1_start);
+
+int         b2fft_nccl_unique_id(void *id128);                 /* fills 128 bytes */
+b2fft_comm *b2fft_comm_create(const void *id128, int n_pes, int my_pe);
+b2fft_comm *b2fft_comm_self(void);                             /* single-rank communicator */
+void        b2fft_comm_destroy(b2fft_comm *c);
+int         b2fft_comm_rank(const b2fft_comm *c);
+int         b2fft_comm_size(const b2fft_comm *c);
+
+b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
+                                   b2fft_comm *c, int sign, int transposed_in,
+                                   int transposed_out, unsigned flags);
+/* device time (ms) of the last slab execute split into local FFT / exchange / local FFT */
+int b2fft_slab_last_times(const b2fft_plan *p, float *ms_fft1, float *ms_exchange, float *ms_fft2);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200FFT_H */
