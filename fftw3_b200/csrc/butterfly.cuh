@@ -1,0 +1,193 @@
+// csrc/butterfly.cuh -- register-resident radix-R DFT butterflies (forward sign, natural
+// order in, natural order out, unnormalised).  These hand-written routines take the place
+// of the reference's generated no-twiddle / twiddle codelets n1_* and t1_*
+// (fftw/dft_scalar/codelets/n1_4.c:94-132, t1_4.c:125-187, fftw/dft_simd/common/*.c): a
+// GPU thread keeps the R points in registers; the twiddle multiply is done by the caller.
+// The backward transform is obtained, as in the reference (fftw_extract_reim,
+// fftw/fftw_api.c:14555-14564), by swapping re/im on the way in and out.
+#pragma once
+#include "b2_common.h"
+
+template <int R, typename T> struct Bf;
+
+template <typename T> struct Bf<1, T> {
+    static B2_HD void run(cpx<T> *v) { (void)v; }
+};
+
+template <typename T> struct Bf<2, T> {
+    static B2_HD void run(cpx<T> *v) {
+        cpx<T> a = v[0];
+        v[0] = cadd(a, v[1]);
+        v[1] = csub(a, v[1]);
+    }
+};
+
+template <typename T> struct Bf<4, T> {
+    static B2_HD void run(cpx<T> *v) {
+        cpx<T> s0 = cadd(v[0], v[2]), d0 = csub(v[0], v[2]);
+        cpx<T> s1 = cadd(v[1], v[3]), d1 = cmul_mi(csub(v[1], v[3]));
+        v[0] = cadd(s0, s1);
+        v[2] = csub(s0, s1);
+        v[1] = cadd(d0, d1);
+        v[3] = csub(d0, d1);
+    }
+};
+
+template <typename T> struct Bf<8, T> {
+    static B2_HD void run(cpx<T> *v) {
+        const T h = (T)0.70710678118654752440;
+        cpx<T> e[4] = {v[0], v[2], v[4], v[6]};
+        cpx<T> o[4] = {v[1], v[3], v[5], v[7]};
+        Bf<4, T>::run(e);
+        Bf<4, T>::run(o);
+        cpx<T> o1 = cpx<T>{(o[1].x + o[1].y) * h, (o[1].y - o[1].x) * h};
+        cpx<T> o2 = cmul_mi(o[2]);
+        cpx<T> o3 = cpx<T>{(o[3].y - o[3].x) * h, -(o[3].x + o[3].y) * h};
+        v[0] = cadd(e[0], o[0]);
+        v[4] = csub(e[0], o[0]);
+        v[1] = cadd(e[1], o1);
+        v[5] = csub(e[1], o1);
+        v[2] = cadd(e[2], o2);
+        v[6] = csub(e[2], o2);
+        v[3] = cadd(e[3], o3);
+        v[7] = csub(e[3], o3);
+    }
+};
+
+// 16 = 4 x 4: four radix-4 butterflies over the stride-4 sub-sequences, the w16^(j2*k1)
+// twiddles, then four radix-4 butterflies; X[k1 + 4 k2].
+template <typename T> struct Bf<16, T> {
+    static B2_HD void run(cpx<T> *v) {
+        const T h = (T)0.70710678118654752440;
+        const T c1 = (T)0.92387953251128675613, s1 = (T)0.38268343236508977173;
+        cpx<T> b[4][4];  // b[j2][k1]
+#pragma unroll
+        for (int j2 = 0; j2 < 4; ++j2) {
+            b[j2][0] = v[j2];
+            b[j2][1] = v[4 + j2];
+            b[j2][2] = v[8 + j2];
+            b[j2][3] = v[12 + j2];
+            Bf<4, T>::run(b[j2]);
+        }
+        // twiddles w16^(j2*k1)
+        b[1][1] = cmul(b[1][1], cpx<T>{c1, -s1});
+        b[1][2] = cpx<T>{(b[1][2].x + b[1][2].y) * h, (b[1][2].y - b[1][2].x) * h};  // w^2
+        b[1][3] = cmul(b[1][3], cpx<T>{s1, -c1});                                      // w^3
+        b[2][1] = cpx<T>{(b[2][1].x + b[2][1].y) * h, (b[2][1].y - b[2][1].x) * h};  // w^2
+        b[2][2] = cmul_mi(b[2][2]);                                                    // w^4
+        b[2][3] = cpx<T>{(b[2][3].y - b[2][3].x) * h, -(b[2][3].x + b[2][3].y) * h}; // w^6
+        b[3][1] = cmul(b[3][1], cpx<T>{s1, -c1});                                      // w^3
+        b[3][2] = cpx<T>{(b[3][2].y - b[3][2].x) * h, -(b[3][2].x + b[3][2].y) * h}; // w^6
+        b[3][3] = cmul(b[3][3], cpx<T>{-c1, s1});                                      // w^9
+#pragma unroll
+        for (int k1 = 0; k1 < 4; ++k1) {
+            cpx<T> r[4] = {b[0][k1], b[1][k1], b[2][k1], b[3][k1]};
+            Bf<4, T>::run(r);
+            v[k1] = r[0];
+            v[k1 + 4] = r[1];
+            v[k1 + 8] = r[2];
+            v[k1 + 12] = r[3];
+        }
+    }
+};
+
+// Odd primes: X[k] = a0 + sum_{j=1..(P-1)/2} (a_j + a_{P-j}) cos(2 pi jk/P)
+//                                          - i (a_j - a_{P-j}) sin(2 pi jk/P)
+template <int P> struct PrimeTab;
+template <> struct PrimeTab<3> {
+    static B2_HD double c(int m) { const double t[3] = {1, -0.5, -0.5}; return t[m]; }
+    static B2_HD double s(int m) { const double t[3] = {0, 0.86602540378443864676, -0.86602540378443864676}; return t[m]; }
+};
+template <> struct PrimeTab<5> {
+    static B2_HD double c(int m) {
+        const double t[5] = {1, 0.30901699437494742410, -0.80901699437494742410, -0.80901699437494742410, 0.30901699437494742410};
+        return t[m];
+    }
+    static B2_HD double s(int m) {
+        const double t[5] = {0, 0.95105651629515357212, 0.58778525229247312917, -0.58778525229247312917, -0.95105651629515357212};
+        return t[m];
+    }
+};
+template <> struct PrimeTab<7> {
+    static B2_HD double c(int m) {
+        const double t[7] = {1, 0.62348980185873353053, -0.22252093395631440429, -0.90096886790241912624,
+                             -0.90096886790241912624, -0.22252093395631440429, 0.62348980185873353053};
+        return t[m];
+    }
+    static B2_HD double s(int m) {
+        const double t[7] = {0, 0.78183148246802980871, 0.97492791218182360702, 0.43388373911755812048,
+                             -0.43388373911755812048, -0.97492791218182360702, -0.78183148246802980871};
+        return t[m];
+    }
+};
+template <> struct PrimeTab<11> {
+    static B2_HD double c(int m) {
+        const double t[11] = {1, 0.84125353283118116886, 0.41541501300188642553, -0.14231483827328514044,
+                              -0.65486073394528506406, -0.95949297361449738989, -0.95949297361449738989,
+                              -0.65486073394528506406, -0.14231483827328514044, 0.41541501300188642553,
+                              0.84125353283118116886};
+        return t[m];
+    }
+    static B2_HD double s(int m) {
+        const double t[11] = {0, 0.54064081745559758211, 0.90963199535451837141, 0.98982144188093273238,
+                              0.75574957435425828377, 0.28173255684142969771, -0.28173255684142969771,
+                              -0.75574957435425828377, -0.98982144188093273238, -0.90963199535451837141,
+                              -0.54064081745559758211};
+        return t[m];
+    }
+};
+template <> struct PrimeTab<13> {
+    static B2_HD double c(int m) {
+        const double t[13] = {1, 0.88545602565320989590, 0.56806474673115580251, 0.12053668025532305335,
+                              -0.35460488704253562597, -0.74851074817110109863, -0.97094181742605202716,
+                              -0.97094181742605202716, -0.74851074817110109863, -0.35460488704253562597,
+                              0.12053668025532305335, 0.56806474673115580251, 0.88545602565320989590};
+        return t[m];
+    }
+    static B2_HD double s(int m) {
+        const double t[13] = {0, 0.46472317204376854566, 0.82298386589365639458, 0.99270887409805399280,
+                              0.93501624268541482344, 0.66312265824079520238, 0.23931566428755776715,
+                              -0.23931566428755776715, -0.66312265824079520238, -0.93501624268541482344,
+                              -0.99270887409805399280, -0.82298386589365639458, -0.46472317204376854566};
+        return t[m];
+    }
+};
+
+template <int P, typename T> struct BfPrime {
+    static B2_HD void run(cpx<T> *v) {
+        constexpr int H = (P - 1) / 2;
+        cpx<T> sp[H], sm[H];
+#pragma unroll
+        for (int j = 1; j <= H; ++j) {
+            sp[j - 1] = cadd(v[j], v[P - j]);
+            sm[j - 1] = csub(v[j], v[P - j]);
+        }
+        cpx<T> a0 = v[0];
+        cpx<T> dc = a0;
+#pragma unroll
+        for (int j = 0; j < H; ++j) dc = cadd(dc, sp[j]);
+        v[0] = dc;
+#pragma unroll
+        for (int k = 1; k <= H; ++k) {
+            cpx<T> re = a0;            // sum of cos terms
+            cpx<T> im = cpx<T>{0, 0};  // sum of sin terms (to be multiplied by -i)
+#pragma unroll
+            for (int j = 1; j <= H; ++j) {
+                const int m = (j * k) % P;
+                const T c = (T)PrimeTab<P>::c(m), s = (T)PrimeTab<P>::s(m);
+                re.x += sp[j - 1].x * c;
+                re.y += sp[j - 1].y * c;
+                im.x += sm[j - 1].x * s;
+                im.y += sm[j - 1].y * s;
+            }
+            cpx<T> t = cmul_mi(im);
+            v[k] = cadd(re, t);
+            v[P - k] = csub(re, t);
+        }
+    }
+};
+template <typename T> struct Bf<3, T> : BfPrime<3, T> {};
+template <typename T> struct Bf<5, T> : BfPrime<5, T> {};
+template <typename T> struct Bf<7, T> : BfPrime<7, T> {};
+template <typename T> struct Bf<11, T> : BfPrime<11, T> {};
+template <typename T> struct Bf<13, T> : BfPrime<13, T> {};

@@ -1,0 +1,160 @@
+// csrc/device_rt.h -- the only place that talks to the CUDA runtime (or, in the TEST-ONLY
+// -DB2_EMULATE build, to malloc/memcpy).  Everything above it (selector, plans, C-ABI) is
+// identical in both builds, which is what lets the CPU tests exercise the selector and the
+// kernels' index arithmetic without a GPU.  The product build has no CPU execution path:
+// with no CUDA device every plan is NULL and b2fft_last_error() says why.
+#pragma once
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+
+#include "b2_common.h"
+
+namespace b2 {
+
+inline std::string &last_error() {
+    static thread_local std::string e;
+    return e;
+}
+inline void set_error(const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    last_error() = buf;
+    if (getenv("FFTW_B200_VERBOSE")) fprintf(stderr, "[b200fft] %s\n", buf);
+}
+
+inline unsigned long long &launch_counter() {
+    static unsigned long long n = 0;
+    return n;
+}
+
+#if B2_CUDA
+typedef cudaStream_t stream_t;
+#define B2_CK(expr)                                                                      \
+    do {                                                                                 \
+        cudaError_t e_ = (expr);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            b2::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, \
+                          __LINE__);                                                     \
+            return (int)e_;                                                              \
+        }                                                                                \
+    } while (0)
+
+inline int &device_ordinal() {
+    static int d = -1;
+    return d;
+}
+// 0 when a usable device is selected
+inline int ensure_device() {
+    static int state = 0;  // 0 unknown, 1 ok, -1 none
+    if (state == 1) {
+        cudaSetDevice(device_ordinal());
+        return 0;
+    }
+    if (state == -1) return -1;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        set_error("no CUDA device available (%s): the B200 engine has no CPU fallback",
+                  e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+        state = -1;
+        return -1;
+    }
+    int d = device_ordinal();
+    if (d < 0) {
+        const char *s = getenv("FFTW_CUDA_DEVICE");
+        if (!s) s = getenv("LOCAL_RANK");
+        d = s ? atoi(s) : 0;
+        if (d < 0 || d >= n) d = d % n;
+    }
+    device_ordinal() = d;
+    if (cudaSetDevice(d) != cudaSuccess) {
+        set_error("cudaSetDevice(%d) failed", d);
+        state = -1;
+        return -1;
+    }
+    state = 1;
+    return 0;
+}
+inline void *dev_malloc(size_t bytes) {
+    void *p = nullptr;
+    if (bytes == 0) bytes = 16;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) {
+        set_error("cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    return p;
+}
+inline void dev_free(void *p) {
+    if (p) cudaFree(p);
+}
+inline int dev_upload(void *dst, const void *src, size_t bytes) {
+    B2_CK(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+    return 0;
+}
+inline void *host_malloc(size_t bytes) {
+    void *p = nullptr;
+    if (bytes == 0) bytes = 16;
+    if (ensure_device() != 0) return nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+        set_error("cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    return p;
+}
+inline void host_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+// 1 if p is device-accessible memory (device or managed), 0 if plain/pinned host memory
+inline int is_device_ptr(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+inline int max_smem_optin() {
+    static int v = 0;
+    if (!v) {
+        cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device_ordinal());
+        if (v <= 0) v = 227 * 1024;
+    }
+    return v;
+}
+inline int sm_count() {
+    static int v = 0;
+    if (!v) {
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device_ordinal());
+        if (v <= 0) v = 148;
+    }
+    return v;
+}
+#else  // ---------------------------------------------------------------- emulation
+typedef void *stream_t;
+#define B2_CK(expr)                 \
+    do {                            \
+        int e_ = (expr);            \
+        if (e_ != 0) return e_;     \
+    } while (0)
+inline int ensure_device() { return 0; }
+inline void *dev_malloc(size_t bytes) { return malloc(bytes ? bytes : 16); }
+inline void dev_free(void *p) { free(p); }
+inline int dev_upload(void *dst, const void *src, size_t bytes) {
+    memcpy(dst, src, bytes);
+    return 0;
+}
+inline void *host_malloc(size_t bytes) { return malloc(bytes ? bytes : 16); }
+inline void host_free(void *p) { free(p); }
+inline int is_device_ptr(const void *) { return 1; }  // emulation: "device" memory is the heap
+inline int max_smem_optin() { return 227 * 1024; }
+inline int sm_count() { return 148; }
+#endif
+
+}  // namespace b2

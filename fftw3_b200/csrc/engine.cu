@@ -1,0 +1,257 @@
+// csrc/engine.cu -- the CUDA engine behind include/b200fft.h: builds plans with the selector,
+// launches the sm_100a kernels, stages host arrays over PCIe when the caller passes host
+// pointers.  Compiled by nvcc for the product; compiled by g++ -DB2_EMULATE (-x c++) into the
+// test-only emulation library.  There is deliberately no CPU execution path in the product
+// build: without a CUDA device b2fft_plan_create returns NULL.
+#include <mutex>
+
+#include "b200fft.h"
+#include "generic_kernel.cuh"
+#include "plan_build_real.h"
+#include "realpp_kernel.cuh"
+#include "tile_kernel.cuh"
+
+using namespace b2;
+
+struct b2fft_plan_s {
+    PlanCore pc;
+    real_t *scr = nullptr;
+    // device staging for host-pointer executes (allocated on first use)
+    real_t *dev_in = nullptr, *dev_out = nullptr;
+    stream_t stream = nullptr;
+    bool own_stream = false;
+    struct SlabPlan *slab = nullptr;
+};
+
+void b2_slab_destroy(b2fft_plan *p);
+int b2_slab_execute(b2fft_plan *p, void *in, void *out);
+
+// ------------------------------------------------------------------------- launching
+static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream_t stream) {
+    // host loops over the line dims that did not fit in the kernel descriptor
+    std::vector<long long> idx(s.outer.size(), 0);
+    for (;;) {
+        long long so = 0, dof = 0;
+        for (size_t i = 0; i < s.outer.size(); ++i) {
+            so += idx[i] * s.outer[i].s;
+            dof += idx[i] * s.outer[i].d;
+        }
+        const real_t *sp = src + so;
+        real_t *dp = dst + dof;
+        PassParams pp = s.pp;
+        if (s.kind == SK_PASS) {
+            // vector access needs 2-real alignment of the actual base addresses
+            if (((uintptr_t)sp % sizeof(cpx_t)) != 0) pp.vec_ld = 0;
+            if (((uintptr_t)dp % sizeof(cpx_t)) != 0) pp.vec_st = 0;
+        }
+        const long long maxgrid = 1ll << 30;
+        for (long long b0 = 0; b0 < s.nblocks; b0 += maxgrid) {
+            const long long nb = std::min(maxgrid, s.nblocks - b0);
+#if B2_CUDA
+            if (s.kind == SK_PASS) {
+                if (s.fast_id >= 0 && pp.vec_ld == s.pp.vec_ld && pp.vec_st == s.pp.vec_st) {
+                    int rc = b2_launch_tile_kernel(s.fast_id, pp, sp, dp, b0, nb, s.nthreads, s.smem, stream);
+                    if (rc) return rc;
+                } else {
+                    const size_t smem = b2_generic_smem_bytes(pp.C, pp.lstride);
+                    b2_generic_pass_kernel<<<(unsigned)nb, s.gen_threads, smem, stream>>>(pp, sp, dp, b0);
+                }
+            } else {
+                b2_realpp_kernel<<<(unsigned)nb, s.nthreads, 0, stream>>>(s.rp, s.kind == SK_RPOST, sp, dp, b0);
+            }
+            ++launch_counter();
+            B2_CK(cudaGetLastError());
+#else
+            (void)stream;
+            if (s.kind == SK_PASS) {
+                if (s.fast_id >= 0 && pp.vec_ld == s.pp.vec_ld && pp.vec_st == s.pp.vec_st) {
+                    int rc = b2_launch_tile_kernel(s.fast_id, pp, sp, dp, b0, nb, s.nthreads, s.smem, stream);
+                    if (rc) return rc;
+                } else {
+                    std::vector<char> smem(b2_generic_smem_bytes(pp.C, pp.lstride) + 64);
+                    for (long long b = 0; b < nb; ++b)
+                        b2_generic_pass_body(pp, sp, dp, b0 + b, smem.data(), s.gen_threads);
+                }
+            } else {
+                for (long long b = 0; b < nb; ++b)
+                    b2_realpp_body(s.rp, s.kind == SK_RPOST, sp, dp, b0 + b, s.nthreads);
+            }
+            ++launch_counter();
+#endif
+        }
+        size_t i = 0;
+        for (; i < idx.size(); ++i) {
+            if (++idx[i] < s.outer[i].n) break;
+            idx[i] = 0;
+        }
+        if (i == idx.size()) break;
+    }
+    return 0;
+}
+
+static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
+    real_t *buf[3] = {in, out, p->scr};
+    for (const StepPlan &s : p->pc.steps) {
+        int rc = launch_step(s, buf[s.src], buf[s.dst], stream);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------- plan create
+#if B2_CUDA
+static void init_kernel_attrs() {
+    static std::once_flag once;
+    std::call_once(once, [] {
+        cudaFuncSetAttribute(b2_generic_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             max_smem_optin());
+        b2_init_tile_kernels();
+    });
+}
+#endif
+
+extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
+    if (!g) return nullptr;
+    if (ensure_device() != 0) return nullptr;
+#if B2_CUDA
+    init_kernel_attrs();
+#endif
+    if (g->rank < 0 || g->rank > B2FFT_MAXRANK || g->vrank < 0 || g->vrank > B2FFT_MAXRANK) {
+        set_error("rank out of range");
+        return nullptr;
+    }
+    b2fft_plan *p = new b2fft_plan_s();
+    p->pc.g = *g;
+    p->pc.in_place = g->in_place != 0;
+    bool ok = (g->kind == B2FFT_C2C) ? build_c2c(p->pc) : build_real(p->pc);
+    if (ok) {
+        for (StepPlan &s : p->pc.steps) {
+            s.gen_threads = s.nthreads;
+            if (s.kind == SK_PASS) b2_select_tile_kernel(s);
+        }
+        if (p->pc.scr_reals > 0) {
+            p->scr = (real_t *)dev_malloc((size_t)p->pc.scr_reals * sizeof(real_t));
+            if (!p->scr) ok = false;
+        }
+    }
+    if (!ok) {
+        delete p;
+        return nullptr;
+    }
+    std::string d;
+    static const char *bn[] = {"in", "out", "scratch"};
+    for (size_t i = 0; i < p->pc.steps.size(); ++i) {
+        const StepPlan &s = p->pc.steps[i];
+        d += "  pass " + std::to_string(i) + ": " + s.desc + " [" + bn[s.src] + "->" + bn[s.dst] + "]\n";
+    }
+    p->pc.desc = d;
+    return p;
+}
+
+extern "C" void b2fft_plan_destroy(b2fft_plan *p) {
+    if (!p) return;
+    if (p->slab) b2_slab_destroy(p);
+    dev_free(p->scr);
+    dev_free(p->dev_in);
+    dev_free(p->dev_out);
+#if B2_CUDA
+    if (p->own_stream && p->stream) cudaStreamDestroy(p->stream);
+#endif
+    delete p;
+}
+
+// ------------------------------------------------------------------------- execute
+extern "C" int b2fft_execute_async(b2fft_plan *p, void *in, void *out, void *stream) {
+    if (!p) return -1;
+    if (p->pc.empty) return 0;
+    if (ensure_device() != 0) return -1;
+    return run_steps(p, (real_t *)in, (real_t *)out, (stream_t)stream);
+}
+
+extern "C" int b2fft_execute(b2fft_plan *p, void *in, void *out) {
+    if (!p) return -1;
+    if (p->slab) return b2_slab_execute(p, in, out);
+    if (p->pc.empty) return 0;
+    if (ensure_device() != 0) return -1;
+    const bool same = (in == out);
+    if (same != p->pc.in_place) {
+        set_error("execute: in-place-ness differs from the plan (reference contract, fftw_api.c:434-440)");
+        return -2;
+    }
+#if B2_CUDA
+    const bool din = is_device_ptr(in), dout = is_device_ptr(out);
+    real_t *ri = (real_t *)in, *ro = (real_t *)out;
+    const size_t ib = (size_t)p->pc.in_reals * sizeof(real_t), ob = (size_t)p->pc.out_reals * sizeof(real_t);
+    if (!dout) {
+        if (!p->dev_out) p->dev_out = (real_t *)dev_malloc(std::max(ob, same ? ib : (size_t)0));
+        if (!p->dev_out) return -3;
+        ro = p->dev_out;
+        // keep whatever lives in the gaps of a strided / embedded output
+        if (!same && p->pc.out_dense != p->pc.out_reals) B2_CK(cudaMemcpyAsync(ro, out, ob, cudaMemcpyHostToDevice, 0));
+    }
+    if (!din) {
+        if (same)
+            ri = ro;
+        else {
+            if (!p->dev_in) p->dev_in = (real_t *)dev_malloc(ib);
+            if (!p->dev_in) return -3;
+            ri = p->dev_in;
+        }
+        B2_CK(cudaMemcpyAsync(ri, in, ib, cudaMemcpyHostToDevice, 0));
+    } else if (same)
+        ri = ro;
+    int rc = run_steps(p, ri, ro, 0);
+    if (rc) return rc;
+    if (!dout) B2_CK(cudaMemcpyAsync(out, ro, std::max(ob, same ? ib : (size_t)0), cudaMemcpyDeviceToHost, 0));
+    B2_CK(cudaStreamSynchronize(0));
+    return 0;
+#else
+    return run_steps(p, (real_t *)in, (real_t *)out, nullptr);
+#endif
+}
+
+// ------------------------------------------------------------------------- introspection
+extern "C" int b2fft_plan_num_passes(const b2fft_plan *p) { return p ? (int)p->pc.steps.size() : 0; }
+extern "C" int b2fft_plan_num_hbm_sweeps(const b2fft_plan *p) { return p ? (int)p->pc.steps.size() : 0; }
+extern "C" size_t b2fft_plan_scratch_bytes(const b2fft_plan *p) {
+    return p ? (size_t)p->pc.scr_reals * sizeof(real_t) : 0;
+}
+extern "C" int b2fft_plan_describe(const b2fft_plan *p, char *buf, size_t n) {
+    if (!p) return 0;
+    return snprintf(buf, n, "b200fft %s plan, %zu kernel pass(es), scratch %zu bytes\n%s", B2_PREC_NAME,
+                    p->pc.steps.size(), (size_t)p->pc.scr_reals * sizeof(real_t), p->pc.desc.c_str());
+}
+extern "C" double b2fft_plan_flops(const b2fft_plan *p) { return p ? p->pc.flops : 0.0; }
+extern "C" unsigned long long b2fft_launch_count(void) { return launch_counter(); }
+
+extern "C" void *b2fft_malloc(size_t n) { return host_malloc(n); }
+extern "C" void b2fft_free(void *p) { host_free(p); }
+extern "C" void *b2fft_device_malloc(size_t n) {
+    if (ensure_device() != 0) return nullptr;
+    return dev_malloc(n);
+}
+extern "C" void b2fft_device_free(void *p) { dev_free(p); }
+extern "C" int b2fft_device_count(void) {
+#if B2_CUDA
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+#else
+    return 1;
+#endif
+}
+extern "C" int b2fft_set_device(int d) {
+#if B2_CUDA
+    device_ordinal() = d;
+    return cudaSetDevice(d) == cudaSuccess ? 0 : -1;
+#else
+    (void)d;
+    return 0;
+#endif
+}
+extern "C" const char *b2fft_last_error(void) { return last_error().c_str(); }
+extern "C" void b2fft_cleanup(void) { twiddles().clear(); }
+extern "C" const char *b2fft_precision(void) { return B2_PREC_NAME; }

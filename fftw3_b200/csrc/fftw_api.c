@@ -1,0 +1,473 @@
+/* csrc/fftw_api.c -- plain-C host side of the B200 FFT engine: the public fftw3.h entry
+ * points.  It is the drop-in counterpart of the API layer of the reference
+ * (fftw/fftw_api.c:21-1517): same names, same argument meaning, same NULL-plan error
+ * behaviour; but instead of building problem/tensor objects for a recursive planner
+ * (fftw_mkproblem_dft_d :4110, fftw_mkapiplan :317-407) it fills a flat geometry descriptor
+ * and hands it to the CUDA engine through the C-ABI of include/b200fft.h.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "b200fft.h"
+#include "fftw3.h"
+
+struct fftw_plan_s {
+    b2fft_plan *bp;
+    void *in, *out; /* the arrays given at plan time (reference: problem_dft.ri.., api.h:1874) */
+    int kind;
+    b2fft_geom g;
+};
+
+const char fftw_version[] = "b200fft-0.1 (fftw3.h ABI, sm_100a)";
+const char fftw_cc[] = "nvcc -gencode arch=compute_100a,code=sm_100a";
+const char fftw_codelet_optim[] = "";
+
+/* same validity rule as fftw_many_kosherp (reference fftw_api.c:863-877) */
+static int kosher(int rank, const int *n, int howmany) {
+    int i;
+    if (rank < 0 || rank > B2FFT_MAXRANK || howmany < 0) return 0;
+    for (i = 0; i < rank; ++i)
+        if (n[i] <= 0) return 0;
+    return 1;
+}
+
+static fftw_plan finish(b2fft_geom *g, void *in, void *out, unsigned flags) {
+    fftw_plan p;
+    b2fft_plan *bp;
+    /* the reference answers WISDOM_ONLY with NULL when it has no wisdom (fftw_api.c:332-337);
+     * this engine keeps no wisdom, every plan is computed by the selector. */
+    if (flags & FFTW_WISDOM_ONLY) return 0;
+    g->flags = flags;
+    g->in_place = (in == out);
+    bp = b2fft_plan_create(g);
+    if (!bp) return 0;
+    p = (fftw_plan)malloc(sizeof *p);
+    if (!p) {
+        b2fft_plan_destroy(bp);
+        return 0;
+    }
+    p->bp = bp;
+    p->in = in;
+    p->out = out;
+    p->kind = g->kind;
+    p->g = *g;
+    return p;
+}
+
+/* row-major strides inside an embedding array, like fftw_mktensor_rowmajor (fftw_api.c:842-861)
+ * but in elements rather than in reals */
+static void rowmajor(b2fft_geom *g, int rank, const int *n, const int *ie, const int *oe, ptrdiff_t is,
+                     ptrdiff_t os) {
+    int i;
+    g->rank = rank;
+    if (rank <= 0) return;
+    g->dims[rank - 1].n = n[rank - 1];
+    g->dims[rank - 1].is = is;
+    g->dims[rank - 1].os = os;
+    for (i = rank - 1; i > 0; --i) {
+        g->dims[i - 1].n = n[i - 1];
+        g->dims[i - 1].is = g->dims[i].is * ie[i];
+        g->dims[i - 1].os = g->dims[i].os * oe[i];
+    }
+}
+
+/* ------------------------------------------------------------------ complex DFT */
+fftw_plan fftw_plan_many_dft(int rank, const int *n, int howmany, FFTW_COMPLEX *in, const int *inembed,
+                             int istride, int idist, FFTW_COMPLEX *out, const int *onembed, int ostride,
+                             int odist, int sign, unsigned flags) {
+    b2fft_geom g;
+    if (!kosher(rank, n, howmany)) return 0;
+    memset(&g, 0, sizeof g);
+    g.kind = B2FFT_C2C;
+    g.sign = sign < 0 ? -1 : +1;
+    rowmajor(&g, rank, n, inembed ? inembed : n, onembed ? onembed : n, istride, ostride);
+    g.vrank = 1;
+    g.vdims[0].n = howmany;
+    g.vdims[0].is = idist;
+    g.vdims[0].os = odist;
+    return finish(&g, in, out, flags);
+}
+
+fftw_plan fftw_plan_dft(int rank, const int *n, FFTW_COMPLEX *in, FFTW_COMPLEX *out, int sign, unsigned flags) {
+    return fftw_plan_many_dft(rank, n, 1, in, 0, 1, 1, out, 0, 1, 1, sign, flags);
+}
+fftw_plan fftw_plan_dft_1d(int n, FFTW_COMPLEX *in, FFTW_COMPLEX *out, int sign, unsigned flags) {
+    return fftw_plan_dft(1, &n, in, out, sign, flags);
+}
+fftw_plan fftw_plan_dft_2d(int n0, int n1, FFTW_COMPLEX *in, FFTW_COMPLEX *out, int sign, unsigned flags) {
+    int n[2];
+    n[0] = n0;
+    n[1] = n1;
+    return fftw_plan_dft(2, n, in, out, sign, flags);
+}
+fftw_plan fftw_plan_dft_3d(int n0, int n1, int n2, FFTW_COMPLEX *in, FFTW_COMPLEX *out, int sign,
+                           unsigned flags) {
+    int n[3];
+    n[0] = n0;
+    n[1] = n1;
+    n[2] = n2;
+    return fftw_plan_dft(3, n, in, out, sign, flags);
+}
+
+/* ------------------------------------------------------------------ real DFT */
+/* default embedding of the last dimension, the rule of fftw_rdft2_pad (fftw_api.c:774-788):
+ * complex side n/2+1; real side 2(n/2+1) when in place, n otherwise */
+static void pad_embed(int rank, const int *n, const int *embed, int inplace, int cmplx, int *tmp,
+                      const int **res) {
+    if (!embed && rank > 0) {
+        memcpy(tmp, n, sizeof(int) * (size_t)rank);
+        if (inplace || cmplx) tmp[rank - 1] = (n[rank - 1] / 2 + 1) * (cmplx ? 1 : 2);
+        *res = tmp;
+    } else
+        *res = embed;
+}
+
+fftw_plan fftw_plan_many_dft_r2c(int rank, const int *n, int howmany, FFTW_REAL_TYPE *in, const int *inembed,
+                                 int istride, int idist, FFTW_COMPLEX *out, const int *onembed, int ostride,
+                                 int odist, unsigned flags) {
+    b2fft_geom g;
+    int ti[B2FFT_MAXRANK], to[B2FFT_MAXRANK];
+    const int *ie, *oe;
+    const int inplace = ((void *)in == (void *)out);
+    if (!kosher(rank, n, howmany)) return 0;
+    memset(&g, 0, sizeof g);
+    g.kind = B2FFT_R2C;
+    g.sign = -1;
+    pad_embed(rank, n, inembed, inplace, 0, ti, &ie);
+    pad_embed(rank, n, onembed, inplace, 1, to, &oe);
+    rowmajor(&g, rank, n, ie, oe, istride, ostride);
+    g.vrank = 1;
+    g.vdims[0].n = howmany;
+    g.vdims[0].is = idist;
+    g.vdims[0].os = odist;
+    return finish(&g, in, out, flags);
+}
+
+fftw_plan fftw_plan_many_dft_c2r(int rank, const int *n, int howmany, FFTW_COMPLEX *in, const int *inembed,
+                                 int istride, int idist, FFTW_REAL_TYPE *out, const int *onembed, int ostride,
+                                 int odist, unsigned flags) {
+    b2fft_geom g;
+    int ti[B2FFT_MAXRANK], to[B2FFT_MAXRANK];
+    const int *ie, *oe;
+    const int inplace = ((void *)in == (void *)out);
+    if (!kosher(rank, n, howmany)) return 0;
+    /* out-of-place c2r may overwrite its input, as in the reference (fftw_api.c:684-685) */
+    if (!inplace) flags |= FFTW_DESTROY_INPUT;
+    memset(&g, 0, sizeof g);
+    g.kind = B2FFT_C2R;
+    g.sign = +1;
+    pad_embed(rank, n, inembed, inplace, 1, ti, &ie);
+    pad_embed(rank, n, onembed, inplace, 0, to, &oe);
+    rowmajor(&g, rank, n, ie, oe, istride, ostride);
+    g.vrank = 1;
+    g.vdims[0].n = howmany;
+    g.vdims[0].is = idist;
+    g.vdims[0].os = odist;
+    return finish(&g, in, out, flags);
+}
+
+fftw_plan fftw_plan_dft_r2c(int rank, const int *n, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out, unsigned flags) {
+    return fftw_plan_many_dft_r2c(rank, n, 1, in, 0, 1, 1, out, 0, 1, 1, flags);
+}
+fftw_plan fftw_plan_dft_r2c_1d(int n, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out, unsigned flags) {
+    return fftw_plan_dft_r2c(1, &n, in, out, flags);
+}
+fftw_plan fftw_plan_dft_r2c_2d(int n0, int n1, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out, unsigned flags) {
+    int n[2];
+    n[0] = n0;
+    n[1] = n1;
+    return fftw_plan_dft_r2c(2, n, in, out, flags);
+}
+fftw_plan fftw_plan_dft_r2c_3d(int n0, int n1, int n2, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out, unsigned flags) {
+    int n[3];
+    n[0] = n0;
+    n[1] = n1;
+    n[2] = n2;
+    return fftw_plan_dft_r2c(3, n, in, out, flags);
+}
+fftw_plan fftw_plan_dft_c2r(int rank, const int *n, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out, unsigned flags) {
+    return fftw_plan_many_dft_c2r(rank, n, 1, in, 0, 1, 1, out, 0, 1, 1, flags);
+}
+fftw_plan fftw_plan_dft_c2r_1d(int n, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out, unsigned flags) {
+    return fftw_plan_dft_c2r(1, &n, in, out, flags);
+}
+fftw_plan fftw_plan_dft_c2r_2d(int n0, int n1, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out, unsigned flags) {
+    int n[2];
+    n[0] = n0;
+    n[1] = n1;
+    return fftw_plan_dft_c2r(2, n, in, out, flags);
+}
+fftw_plan fftw_plan_dft_c2r_3d(int n0, int n1, int n2, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out, unsigned flags) {
+    int n[3];
+    n[0] = n0;
+    n[1] = n1;
+    n[2] = n2;
+    return fftw_plan_dft_c2r(3, n, in, out, flags);
+}
+
+/* ------------------------------------------------------------------ guru (interleaved) */
+/* The guru interface hands over the loop nest directly (reference fftw_api.c:1172-1517);
+ * it maps one to one onto the geometry descriptor.  Split-array variants are not on the hot
+ * path: they return NULL, which callers such as the reference's bench treat as "cannot do"
+ * (fftw/tests/fftw-bench.c:180-198). */
+#define GURU_BODY(KIND, SIGN)                                                         \
+    b2fft_geom g;                                                                     \
+    int i;                                                                            \
+    if (rank < 0 || rank > B2FFT_MAXRANK || howmany_rank < 0 ||                       \
+        howmany_rank > B2FFT_MAXRANK)                                                 \
+        return 0;                                                                     \
+    memset(&g, 0, sizeof g);                                                          \
+    g.kind = (KIND);                                                                  \
+    g.sign = (SIGN) < 0 ? -1 : +1;                                                    \
+    g.rank = rank;                                                                    \
+    for (i = 0; i < rank; ++i) {                                                      \
+        if (dims[i].n <= 0) return 0;                                                 \
+        g.dims[i].n = dims[i].n;                                                      \
+        g.dims[i].is = dims[i].is;                                                    \
+        g.dims[i].os = dims[i].os;                                                    \
+    }                                                                                 \
+    g.vrank = howmany_rank;                                                           \
+    for (i = 0; i < howmany_rank; ++i) {                                              \
+        if (howmany_dims[i].n < 0) return 0;                                          \
+        g.vdims[i].n = howmany_dims[i].n;                                             \
+        g.vdims[i].is = howmany_dims[i].is;                                           \
+        g.vdims[i].os = howmany_dims[i].os;                                           \
+    }
+
+fftw_plan fftw_plan_guru_dft(int rank, const fftw_iodim *dims, int howmany_rank, const fftw_iodim *howmany_dims,
+                             FFTW_COMPLEX *in, FFTW_COMPLEX *out, int sign, unsigned flags) {
+    GURU_BODY(B2FFT_C2C, sign)
+    return finish(&g, in, out, flags);
+}
+fftw_plan fftw_plan_guru64_dft(int rank, const fftw_iodim64 *dims, int howmany_rank,
+                               const fftw_iodim64 *howmany_dims, FFTW_COMPLEX *in, FFTW_COMPLEX *out, int sign,
+                               unsigned flags) {
+    GURU_BODY(B2FFT_C2C, sign)
+    return finish(&g, in, out, flags);
+}
+fftw_plan fftw_plan_guru_dft_r2c(int rank, const fftw_iodim *dims, int howmany_rank,
+                                 const fftw_iodim *howmany_dims, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out,
+                                 unsigned flags) {
+    GURU_BODY(B2FFT_R2C, -1)
+    if (rank < 1) return 0;
+    return finish(&g, in, out, flags);
+}
+fftw_plan fftw_plan_guru64_dft_r2c(int rank, const fftw_iodim64 *dims, int howmany_rank,
+                                   const fftw_iodim64 *howmany_dims, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out,
+                                   unsigned flags) {
+    GURU_BODY(B2FFT_R2C, -1)
+    if (rank < 1) return 0;
+    return finish(&g, in, out, flags);
+}
+fftw_plan fftw_plan_guru_dft_c2r(int rank, const fftw_iodim *dims, int howmany_rank,
+                                 const fftw_iodim *howmany_dims, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out,
+                                 unsigned flags) {
+    GURU_BODY(B2FFT_C2R, +1)
+    if (rank < 1) return 0;
+    return finish(&g, in, out, flags);
+}
+fftw_plan fftw_plan_guru64_dft_c2r(int rank, const fftw_iodim64 *dims, int howmany_rank,
+                                   const fftw_iodim64 *howmany_dims, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out,
+                                   unsigned flags) {
+    GURU_BODY(B2FFT_C2R, +1)
+    if (rank < 1) return 0;
+    return finish(&g, in, out, flags);
+}
+
+#define UNUSED_GURU (void)rank, (void)dims, (void)howmany_rank, (void)howmany_dims, (void)flags
+fftw_plan fftw_plan_guru_split_dft(int rank, const fftw_iodim *dims, int howmany_rank,
+                                   const fftw_iodim *howmany_dims, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii,
+                                   FFTW_REAL_TYPE *ro, FFTW_REAL_TYPE *io, unsigned flags) {
+    UNUSED_GURU, (void)ri, (void)ii, (void)ro, (void)io;
+    return 0;
+}
+fftw_plan fftw_plan_guru64_split_dft(int rank, const fftw_iodim64 *dims, int howmany_rank,
+                                     const fftw_iodim64 *howmany_dims, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii,
+                                     FFTW_REAL_TYPE *ro, FFTW_REAL_TYPE *io, unsigned flags) {
+    UNUSED_GURU, (void)ri, (void)ii, (void)ro, (void)io;
+    return 0;
+}
+fftw_plan fftw_plan_guru_split_dft_r2c(int rank, const fftw_iodim *dims, int howmany_rank,
+                                       const fftw_iodim *howmany_dims, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *ro,
+                                       FFTW_REAL_TYPE *io, unsigned flags) {
+    UNUSED_GURU, (void)in, (void)ro, (void)io;
+    return 0;
+}
+fftw_plan fftw_plan_guru_split_dft_c2r(int rank, const fftw_iodim *dims, int howmany_rank,
+                                       const fftw_iodim *howmany_dims, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii,
+                                       FFTW_REAL_TYPE *out, unsigned flags) {
+    UNUSED_GURU, (void)ri, (void)ii, (void)out;
+    return 0;
+}
+fftw_plan fftw_plan_guru64_split_dft_r2c(int rank, const fftw_iodim64 *dims, int howmany_rank,
+                                         const fftw_iodim64 *howmany_dims, FFTW_REAL_TYPE *in,
+                                         FFTW_REAL_TYPE *ro, FFTW_REAL_TYPE *io, unsigned flags) {
+    UNUSED_GURU, (void)in, (void)ro, (void)io;
+    return 0;
+}
+fftw_plan fftw_plan_guru64_split_dft_c2r(int rank, const fftw_iodim64 *dims, int howmany_rank,
+                                         const fftw_iodim64 *howmany_dims, FFTW_REAL_TYPE *ri,
+                                         FFTW_REAL_TYPE *ii, FFTW_REAL_TYPE *out, unsigned flags) {
+    UNUSED_GURU, (void)ri, (void)ii, (void)out;
+    return 0;
+}
+
+/* ------------------------------------------------------------------ r2r: not on the hot path */
+fftw_plan fftw_plan_many_r2r(int rank, const int *n, int howmany, FFTW_REAL_TYPE *in, const int *inembed,
+                             int istride, int idist, FFTW_REAL_TYPE *out, const int *onembed, int ostride,
+                             int odist, const fftw_r2r_kind *kind, unsigned flags) {
+    (void)rank, (void)n, (void)howmany, (void)in, (void)inembed, (void)istride, (void)idist, (void)out;
+    (void)onembed, (void)ostride, (void)odist, (void)kind, (void)flags;
+    return 0;
+}
+fftw_plan fftw_plan_r2r(int rank, const int *n, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out,
+                        const fftw_r2r_kind *kind, unsigned flags) {
+    (void)rank, (void)n, (void)in, (void)out, (void)kind, (void)flags;
+    return 0;
+}
+fftw_plan fftw_plan_r2r_1d(int n, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out, fftw_r2r_kind kind, unsigned flags) {
+    (void)n, (void)in, (void)out, (void)kind, (void)flags;
+    return 0;
+}
+fftw_plan fftw_plan_r2r_2d(int n0, int n1, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out, fftw_r2r_kind kind0,
+                           fftw_r2r_kind kind1, unsigned flags) {
+    (void)n0, (void)n1, (void)in, (void)out, (void)kind0, (void)kind1, (void)flags;
+    return 0;
+}
+fftw_plan fftw_plan_r2r_3d(int n0, int n1, int n2, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out,
+                           fftw_r2r_kind kind0, fftw_r2r_kind kind1, fftw_r2r_kind kind2, unsigned flags) {
+    (void)n0, (void)n1, (void)n2, (void)in, (void)out, (void)kind0, (void)kind1, (void)kind2, (void)flags;
+    return 0;
+}
+fftw_plan fftw_plan_guru_r2r(int rank, const fftw_iodim *dims, int howmany_rank, const fftw_iodim *howmany_dims,
+                             FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out, const fftw_r2r_kind *kind,
+                             unsigned flags) {
+    UNUSED_GURU, (void)in, (void)out, (void)kind;
+    return 0;
+}
+fftw_plan fftw_plan_guru64_r2r(int rank, const fftw_iodim64 *dims, int howmany_rank,
+                               const fftw_iodim64 *howmany_dims, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out,
+                               const fftw_r2r_kind *kind, unsigned flags) {
+    UNUSED_GURU, (void)in, (void)out, (void)kind;
+    return 0;
+}
+
+/* ------------------------------------------------------------------ execution */
+static void run(const fftw_plan p, void *in, void *out) {
+    int rc;
+    if (!p || !p->bp) return;
+    rc = b2fft_execute(p->bp, in, out);
+    if (rc != 0) {
+        /* fftw_execute has no error channel (returns void, reference fftw_api.c:428-431);
+         * say so loudly rather than leave stale output unnoticed */
+        fprintf(stderr, "b200fft: fftw_execute failed (%d): %s\n", rc, b2fft_last_error());
+    }
+}
+void fftw_execute(const fftw_plan p) {
+    if (p) run(p, p->in, p->out);
+}
+void fftw_execute_dft(const fftw_plan p, FFTW_COMPLEX *in, FFTW_COMPLEX *out) { run(p, in, out); }
+void fftw_execute_dft_r2c(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out) { run(p, in, out); }
+void fftw_execute_dft_c2r(const fftw_plan p, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out) { run(p, in, out); }
+void fftw_execute_split_dft(const fftw_plan p, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii, FFTW_REAL_TYPE *ro,
+                            FFTW_REAL_TYPE *io) {
+    (void)p, (void)ri, (void)ii, (void)ro, (void)io; /* split plans are never created */
+}
+void fftw_execute_split_dft_r2c(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *ro, FFTW_REAL_TYPE *io) {
+    (void)p, (void)in, (void)ro, (void)io;
+}
+void fftw_execute_split_dft_c2r(const fftw_plan p, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii, FFTW_REAL_TYPE *out) {
+    (void)p, (void)ri, (void)ii, (void)out;
+}
+void fftw_execute_r2r(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out) {
+    (void)p, (void)in, (void)out;
+}
+
+/* ------------------------------------------------------------------ lifecycle */
+void fftw_destroy_plan(fftw_plan p) {
+    if (!p) return; /* NULL is legal (reference fftw_api.c:410) */
+    b2fft_plan_destroy(p->bp);
+    free(p);
+}
+void fftw_cleanup(void) { b2fft_cleanup(); }
+void fftw_forget_wisdom(void) {}
+void fftw_set_timelimit(double t) { (void)t; }
+
+/* The reference keeps these four in its threads library (fftw/threads/api.c:39-86).  A GPU
+ * plan has no host worker threads; they are accepted so that threaded callers still link. */
+int fftw_init_threads(void) { return 1; }
+void fftw_plan_with_nthreads(int nthreads) { (void)nthreads; }
+void fftw_cleanup_threads(void) { fftw_cleanup(); }
+void fftw_make_planner_thread_safe(void) {}
+
+/* wisdom: nothing to remember -- the selector is deterministic.  Export writes an empty but
+ * well-formed wisdom list; import accepts anything and reports success. */
+static const char empty_wisdom[] = "(b200fft_wisdom)\n";
+char *fftw_export_wisdom_to_string(void) {
+    char *s = (char *)malloc(sizeof empty_wisdom);
+    if (s) memcpy(s, empty_wisdom, sizeof empty_wisdom);
+    return s;
+}
+void fftw_export_wisdom_to_file(FILE *f) {
+    if (f) fputs(empty_wisdom, f);
+}
+int fftw_export_wisdom_to_filename(const char *filename) {
+    FILE *f = fopen(filename, "w");
+    if (!f) return 0;
+    fputs(empty_wisdom, f);
+    return fclose(f) == 0;
+}
+void fftw_export_wisdom(fftw_write_char_func write_char, void *data) {
+    const char *c;
+    if (!write_char) return;
+    for (c = empty_wisdom; *c; ++c) write_char(*c, data);
+}
+int fftw_import_system_wisdom(void) { return 0; }
+int fftw_import_wisdom_from_filename(const char *filename) {
+    FILE *f = fopen(filename, "r");
+    if (!f) return 0;
+    fclose(f);
+    return 1;
+}
+int fftw_import_wisdom_from_file(FILE *f) { return f != 0; }
+int fftw_import_wisdom_from_string(const char *s) { return s != 0; }
+int fftw_import_wisdom(fftw_read_char_func read_char, void *data) {
+    (void)data;
+    return read_char != 0;
+}
+
+/* plan printing: the selected kernel configurations (reference prints its solver tree,
+ * fftw_api.c:1046-1078) */
+char *fftw_sprint_plan(const fftw_plan p) {
+    int n;
+    char *s;
+    if (!p) return 0;
+    n = b2fft_plan_describe(p->bp, 0, 0);
+    s = (char *)malloc((size_t)n + 1);
+    if (s) b2fft_plan_describe(p->bp, s, (size_t)n + 1);
+    return s;
+}
+void fftw_fprint_plan(const fftw_plan p, FILE *f) {
+    char *s = fftw_sprint_plan(p);
+    if (s && f) fputs(s, f);
+    free(s);
+}
+void fftw_print_plan(const fftw_plan p) { fftw_fprint_plan(p, stdout); }
+
+/* memory: pinned host memory, so that fftw_execute can DMA it at full PCIe speed */
+void *fftw_malloc(size_t n) { return b2fft_malloc(n); }
+FFTW_REAL_TYPE *fftw_alloc_real(size_t n) { return (FFTW_REAL_TYPE *)b2fft_malloc(n * sizeof(FFTW_REAL_TYPE)); }
+FFTW_COMPLEX *fftw_alloc_complex(size_t n) { return (FFTW_COMPLEX *)b2fft_malloc(n * sizeof(FFTW_COMPLEX)); }
+void fftw_free(void *p) { b2fft_free(p); }
+
+/* 5 N log2 N convention (fftw/libbench2/mflops.c:6-31), split evenly between adds and muls */
+void fftw_flops(const fftw_plan p, double *add, double *mul, double *fmas) {
+    double f = p ? b2fft_plan_flops(p->bp) : 0.0;
+    if (add) *add = 0.6 * f;
+    if (mul) *mul = 0.4 * f;
+    if (fmas) *fmas = 0.0;
+}
+double fftw_estimate_cost(const fftw_plan p) { return p ? b2fft_plan_flops(p->bp) : 0.0; }
+double fftw_cost(const fftw_plan p) { return p ? b2fft_plan_flops(p->bp) : 0.0; }
+int fftw_alignment_of(FFTW_REAL_TYPE *p) { return (int)(((uintptr_t)p) % 16); } /* fftw_api.c:14530 */

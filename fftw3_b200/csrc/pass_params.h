@@ -1,0 +1,41 @@
+// csrc/pass_params.h -- the descriptor of one "axis pass": batched length-n DFTs along one
+// axis of a strided array, a tile of C lines per CTA.  It plays the role of the reference's
+// problem_dft {sz, vecsz} after canonicalisation (fftw/fftw_api.h:1871-1875, tensor/iodim
+// fftw_api.h:472-487) for ONE solver step (ct / direct / rank>=2 / vrank>=1 glue,
+// fftw/fftw_api.c:2079-2102, 3160-3187, 4435-4445, 4627-4638 all collapse into it).
+#pragma once
+#include "b2_common.h"
+
+#define B2_MAXPASS 14
+#define B2_MAXLD 4
+
+enum { RM_C2C = 0, RM_R2C_HALF = 1, RM_C2R_HALF = 2, RM_R2C_FULL = 3, RM_C2R_FULL = 4 };
+
+struct PassParams {
+    // ---- transform ----
+    int n;       // logical length along the axis
+    int m;       // complex FFT length computed on chip: n, or n/2 in the half-length real modes
+    int npass;   // radix passes, m = prod radix[]
+    int radix[B2_MAXPASS];
+    int rmode;   // RM_*
+    int C;       // lines per CTA tile
+    int lstride; // smem line stride, complex elements
+    int nload, nstore;  // points per line read from / written to global memory
+    int swap_in, swap_out;  // backward transform = swap re/im going in and coming out
+    // ---- addressing, all in units of REALS ----
+    long long s_axis, s_pair;  // src: point-to-point stride along the axis; re->im distance
+    long long d_axis, d_pair;  // dst: same
+    int nld;                   // line dims; dim 0 is the tile dim
+    long long ln[B2_MAXLD], ls[B2_MAXLD], ld[B2_MAXLD];
+    long long tiles0;          // ceil(ln[0] / C)
+    int ld_col, st_col;        // 1: consecutive threads walk the tile dim first (column tile)
+    int vec_ld, vec_st;        // 1: (re,im) adjacent and aligned -> one vector access
+    // ---- twiddles ----
+    const cpx_t *tw;   // exp(-2 pi i j / m), j < m
+    const cpx_t *twr;  // exp(-2 pi i k / n), k <= n/2 (half-length real modes)
+    // ---- four-step epilogue: dst[k][i2] *= w_N^(i2*k), i2 = coordinate along line dim epi_dim
+    int epi_dim;           // -1: none
+    int epi_shift;         // exponent e = (hi << epi_shift) | lo
+    const cpx_t *epi_lo;   // w_N^lo
+    const cpx_t *epi_hi;   // w_N^(hi << shift)
+};

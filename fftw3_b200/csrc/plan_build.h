@@ -1,0 +1,282 @@
+// csrc/plan_build.h -- geometry -> list of kernel steps.  This is where the reference's
+// solver tree (rank>=2 splitting fftw/fftw_api.c:4508-4558, vrank>=1 :4712-4755, Cooley-Tukey
+// ct_mkplan :2158-2270, rdft2-ct ct_hc2c_mkplan :5661-5788, rank>=2 rdft2 :10219-10282) is
+// re-expressed as a flat list: one step per axis (two for a four-step axis), each step one
+// kernel launch that sweeps the data once.
+#pragma once
+#include <math.h>
+
+#include "b200fft.h"
+#include "selector.h"
+
+struct b2fft_comm_s;
+
+namespace b2 {
+
+struct StepPlan : Step {
+    int src_fixed = -1;            // -1: wherever the data currently is
+    std::vector<int> dst_allowed;  // candidate destination buffers
+};
+
+struct PlanCore {
+    b2fft_geom g;
+    std::vector<StepPlan> steps;
+    bool in_place = false;
+    bool empty = false;         // howmany == 0: a legal no-op
+    long long in_reals = 0;     // extent of the user's arrays, in reals
+    long long out_reals = 0;
+    long long in_dense = 0, out_dense = 0;  // reals actually touched
+    long long scr_reals = 0;
+    double flops = 0;
+    std::string desc;
+};
+
+struct GDim {
+    long long n, is, os;
+};
+
+// four-step split n = n1 * n2 (n1: strided/column pass with twiddle epilogue, n2: row pass)
+inline bool split_four_step(long long n, long long *n1o, long long *n2o) {
+    const Caps c = caps();
+    long long best = -1;
+    double bestd = 1e300;
+    for (long long a = 2; a * a <= n * (long long)c.col; ++a) {
+        if (a > c.col) break;
+        if (n % a) continue;
+        long long b = n / a;
+        if (b > c.col || !factorable(a) || !factorable(b)) continue;
+        double d = fabs(log((double)a) - log((double)b));
+        if (d < bestd) {
+            bestd = d;
+            best = a;
+        }
+    }
+    if (best < 0) return false;
+    long long a = best, b = n / best;
+    if (a < b) std::swap(a, b);  // larger factor to the column pass, shorter rows for pass B tiles
+    *n1o = a;
+    *n2o = b;
+    return true;
+}
+
+inline long long dst_extent(const StepPlan &s) {
+    if (s.kind != SK_PASS) {
+        long long e = (long long)s.rp.m * s.rp.d_axis + 2;
+        for (int d = 0; d < s.rp.nld; ++d) e += (s.rp.ln[d] - 1) * s.rp.ld[d];
+        return e;
+    }
+    const PassParams &p = s.pp;
+    long long e = (long long)(p.nstore - 1) * p.d_axis + p.d_pair + 1;
+    for (int d = 0; d < p.nld; ++d) e += (p.ln[d] - 1) * p.ld[d];
+    for (const LDim &o : s.outer) e += (o.n - 1) * o.d;
+    return e;
+}
+
+inline bool lines_same(const std::vector<LDim> &L) {
+    for (const LDim &d : L)
+        if (d.s != d.d) return false;
+    return true;
+}
+
+// Append the step(s) for one complex axis.  `lines` carry (src, dst) strides in reals.
+// first/last: whether the backward swap is applied on the way in / out.
+inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long d_axis,
+                         const std::vector<LDim> &lines, bool swap_in, bool swap_out,
+                         const std::vector<int> &dst_allowed) {
+    const Caps c = caps();
+    const bool row = (s_axis <= 2 && d_axis <= 2);
+    const long long cap = row ? c.row : c.col;
+    if (n <= cap) {
+        AxisSpec a;
+        a.n = (int)n;
+        a.s_axis = s_axis;
+        a.d_axis = d_axis;
+        a.lines = lines;
+        a.swap_in = swap_in;
+        a.swap_out = swap_out;
+        StepPlan st;
+        if (!make_pass_step(st, a)) return false;
+        st.inplace_ok = (s_axis == d_axis) && lines_same(lines);
+        st.dst_allowed = dst_allowed;
+        pc.steps.push_back(st);
+        return true;
+    }
+    long long n1, n2;
+    if (!split_four_step(n, &n1, &n2)) {
+        set_error("length %lld: no four-step split with factors <= %d", n, c.col);
+        return false;
+    }
+    {  // pass A: n2 interleaved sub-sequences of length n1, twiddle w_n^(i2*k1) on the way out
+        AxisSpec a;
+        a.n = (int)n1;
+        a.s_axis = s_axis * n2;
+        a.d_axis = d_axis * n2;
+        a.lines = lines;
+        a.lines.push_back(LDim{n2, s_axis, d_axis, true});
+        a.swap_in = swap_in;
+        a.epi_N = n;
+        StepPlan st;
+        if (!make_pass_step(st, a)) return false;
+        st.inplace_ok = (s_axis == d_axis) && lines_same(lines);
+        st.dst_allowed = dst_allowed;
+        pc.steps.push_back(st);
+    }
+    {  // pass B: length-n2 rows for each k1, written transposed: X[k1 + n1*k2]
+        AxisSpec a;
+        a.n = (int)n2;
+        a.s_axis = d_axis;
+        a.d_axis = d_axis * n1;
+        for (const LDim &l : lines) a.lines.push_back(LDim{l.n, l.d, l.d, false});
+        a.lines.push_back(LDim{n1, d_axis * n2, d_axis, false});
+        a.swap_out = swap_out;
+        StepPlan st;
+        if (!make_pass_step(st, a)) return false;
+        st.inplace_ok = false;
+        st.dst_allowed = dst_allowed;
+        pc.steps.push_back(st);
+    }
+    return true;
+}
+
+// Decide which buffer every step writes.  Exhaustive over <= 2^steps choices.
+inline bool assign_buffers(PlanCore &pc) {
+    const int ns = (int)pc.steps.size();
+    if (ns == 0) return true;
+    auto norm = [&](int b) { return (pc.in_place && b == B_IN) ? B_OUT : b; };
+    std::vector<int> best, cur(ns);
+    double bestc = 1e300;
+    // iterative DFS
+    std::vector<int> choice(ns, 0);
+    std::vector<std::vector<int>> allowed(ns);
+    for (int i = 0; i < ns; ++i) {
+        for (int b : pc.steps[i].dst_allowed) {
+            int nb = norm(b);
+            if (std::find(allowed[i].begin(), allowed[i].end(), nb) == allowed[i].end())
+                allowed[i].push_back(nb);
+        }
+        if (allowed[i].empty()) return false;
+    }
+    long long combos = 1;
+    for (int i = 0; i < ns; ++i) combos *= (long long)allowed[i].size();
+    for (long long code = 0; code < combos; ++code) {
+        long long c = code;
+        int state = norm(B_IN);
+        double cost = 0;
+        bool ok = true;
+        for (int i = 0; i < ns && ok; ++i) {
+            int dst = allowed[i][c % allowed[i].size()];
+            c /= allowed[i].size();
+            const StepPlan &s = pc.steps[i];
+            if (s.src_fixed >= 0 && norm(s.src_fixed) != state) ok = false;
+            if (dst == state && !s.inplace_ok) ok = false;
+            if (dst == B_IN && !pc.in_place && state != B_IN &&
+                std::find(s.dst_allowed.begin(), s.dst_allowed.end(), (int)B_IN) == s.dst_allowed.end())
+                ok = false;
+            if (dst != state && s.inplace_ok) cost += 1.0;
+            if (dst == B_SCR) cost += 0.25;
+            cur[i] = dst;
+            state = dst;
+        }
+        if (!ok || state != B_OUT) continue;
+        if (cost < bestc) {
+            bestc = cost;
+            best = cur;
+        }
+    }
+    if (best.empty()) {
+        set_error("no valid buffer assignment for this plan");
+        return false;
+    }
+    int state = norm(B_IN);
+    pc.scr_reals = 0;
+    for (int i = 0; i < ns; ++i) {
+        pc.steps[i].src = state;
+        pc.steps[i].dst = best[i];
+        state = best[i];
+        if (best[i] == B_SCR) pc.scr_reals = std::max(pc.scr_reals, dst_extent(pc.steps[i]));
+    }
+    return true;
+}
+
+inline long long extent_of(const std::vector<GDim> &dims, bool in, long long unit) {
+    long long e = 1;
+    for (const GDim &d : dims) {
+        if (d.n == 0) return 0;
+        e += (d.n - 1) * (in ? d.is : d.os);
+    }
+    return e * unit;
+}
+
+inline bool build_c2c(PlanCore &pc) {
+    const b2fft_geom &g = pc.g;
+    std::vector<GDim> T, V;
+    double N = 1, H = 1;
+    for (int i = 0; i < g.rank; ++i) {
+        if (g.dims[i].n <= 0) {
+            set_error("non-positive transform size");
+            return false;
+        }
+        N *= (double)g.dims[i].n;
+        T.push_back(GDim{g.dims[i].n, g.dims[i].is, g.dims[i].os});
+    }
+    for (int i = 0; i < g.vrank; ++i) {
+        if (g.vdims[i].n < 0) {
+            set_error("negative howmany");
+            return false;
+        }
+        H *= (double)g.vdims[i].n;
+        V.push_back(GDim{g.vdims[i].n, g.vdims[i].is, g.vdims[i].os});
+    }
+    std::vector<GDim> all = T;
+    all.insert(all.end(), V.begin(), V.end());
+    pc.in_reals = extent_of(all, true, 2);
+    pc.out_reals = extent_of(all, false, 2);
+    pc.in_dense = pc.out_dense = (long long)(N * H * 2);
+    pc.flops = 5.0 * N * (N > 1 ? log2(N) : 0) * H;
+    if (H == 0) {
+        pc.empty = true;
+        return true;
+    }
+    for (const GDim &d : all)
+        if (d.is < 0 || d.os < 0) {
+            set_error("negative strides are not supported");
+            return false;
+        }
+    if (pc.in_place)
+        for (const GDim &d : all)
+            if (d.n > 1 && d.is != d.os) {
+                set_error("in-place transform with different input and output strides");
+                return false;
+            }
+    // axes: smallest output stride first
+    std::vector<int> order;
+    for (int i = 0; i < (int)T.size(); ++i)
+        if (T[i].n > 1) order.push_back(i);
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return T[a].os < T[b].os; });
+    const bool bwd = g.sign > 0;
+    if (order.empty()) {
+        // all transform dims have length 1: a (strided) copy, done by a length-1 "pass"
+        AxisSpec a;
+        a.n = 1;
+        for (const GDim &d : all) a.lines.push_back(LDim{d.n, 2 * d.is, 2 * d.os, false});
+        StepPlan st;
+        if (!make_pass_step(st, a)) return false;
+        st.inplace_ok = lines_same(a.lines);
+        st.dst_allowed = {B_OUT, B_SCR};
+        pc.steps.push_back(st);
+    }
+    for (size_t oi = 0; oi < order.size(); ++oi) {
+        const int ax = order[oi];
+        const bool first = (oi == 0), last = (oi + 1 == order.size());
+        std::vector<LDim> lines;
+        for (int i = 0; i < (int)T.size(); ++i)
+            if (i != ax) lines.push_back(LDim{T[i].n, 2 * (first ? T[i].is : T[i].os), 2 * T[i].os, false});
+        for (const GDim &d : V) lines.push_back(LDim{d.n, 2 * (first ? d.is : d.os), 2 * d.os, false});
+        if (!add_c2c_axis(pc, T[ax].n, 2 * (first ? T[ax].is : T[ax].os), 2 * T[ax].os, lines,
+                          bwd && first, bwd && last, {B_OUT, B_SCR}))
+            return false;
+    }
+    return assign_buffers(pc);
+}
+
+}  // namespace b2

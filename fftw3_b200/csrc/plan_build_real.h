@@ -1,0 +1,349 @@
+// csrc/plan_build_real.h -- r2c / c2r geometries -> kernel steps.  The reference reaches
+// these through problem_rdft2 (fftw/fftw_api.c:9298-9379) and the solvers rdft2-ct
+// (ct_hc2c_mkplan :5661-5788: half-length complex FFT + hc2c twiddle pass), rdft2 direct
+// leaves (:7139-7157) and rank>=2 rdft2 (:10111-10139, 10219-10282: real transform on the last
+// dimension, complex transforms on the others).  Here: the last-dimension real transform is a
+// length-n/2 complex FFT with the Hermitian split / merge fused into the same kernel.
+#pragma once
+#include "plan_build.h"
+
+namespace b2 {
+
+inline void fill_realpp(StepPlan &st, int post, int m, long long n_real, long long s_axis,
+                        long long d_axis, const std::vector<LDim> &lines, bool use_src_for_both) {
+    st.kind = post ? SK_RPOST : SK_RPRE;
+    RealPPParams &r = st.rp;
+    memset(&r, 0, sizeof r);
+    r.m = m;
+    r.s_axis = s_axis;
+    r.d_axis = d_axis;
+    r.nld = 0;
+    st.outer.clear();
+    for (const LDim &l : lines) {
+        if (l.n <= 1) continue;
+        LDim x = l;
+        if (use_src_for_both) x.d = x.s;
+        if (r.nld < B2_MAXLD) {
+            r.ln[r.nld] = x.n;
+            r.ls[r.nld] = x.s;
+            r.ld[r.nld] = x.d;
+            ++r.nld;
+        } else
+            st.outer.push_back(x);
+    }
+    r.twr = twiddles().get((unsigned long long)n_real, (unsigned long long)m / 2 + 1, 1);
+    st.nthreads = 256;
+    long long nb = (m / 2 + 1 + 255) / 256;
+    for (int d = 0; d < r.nld; ++d) nb *= r.ln[d];
+    st.nblocks = nb;
+    st.smem = 0;
+    char buf[128];
+    snprintf(buf, sizeof buf, "%s n=%lld ctas=%lld", post ? "hermitian-split" : "hermitian-merge",
+             n_real, nb);
+    st.desc = buf;
+}
+
+// compact scratch layout for the lines of a big real transform: [lines...][m] complex
+inline std::vector<long long> compact_strides(const std::vector<LDim> &lines, long long m) {
+    std::vector<long long> cs(lines.size());
+    long long s = 2 * m;
+    for (size_t i = 0; i < lines.size(); ++i) {
+        cs[i] = s;
+        s *= lines[i].n;
+    }
+    return cs;
+}
+
+inline bool build_real(PlanCore &pc) {
+    const b2fft_geom &g = pc.g;
+    const bool r2c = (g.kind == B2FFT_R2C);
+    if (g.rank < 1) {
+        set_error("real transforms need rank >= 1");
+        return false;
+    }
+    // is: strides of the INPUT array in its own elements, os: of the OUTPUT array.
+    // r2c: input real, output complex; c2r: input complex, output real.
+    std::vector<GDim> T, V;
+    double N = 1, H = 1;
+    for (int i = 0; i < g.rank; ++i) {
+        if (g.dims[i].n <= 0) {
+            set_error("non-positive transform size");
+            return false;
+        }
+        N *= (double)g.dims[i].n;
+        T.push_back(GDim{g.dims[i].n, g.dims[i].is, g.dims[i].os});
+    }
+    for (int i = 0; i < g.vrank; ++i) {
+        if (g.vdims[i].n < 0) {
+            set_error("negative howmany");
+            return false;
+        }
+        H *= (double)g.vdims[i].n;
+        V.push_back(GDim{g.vdims[i].n, g.vdims[i].is, g.vdims[i].os});
+    }
+    const int L = g.rank - 1;
+    const long long nl = T[L].n, hc = nl / 2 + 1;
+    const long long ru = 1, cu = 2;                // reals per element of a real / complex array
+    const long long iu = r2c ? ru : cu, ou = r2c ? cu : ru;
+    {   // extents: the last dim holds nl reals on the real side and hc complex on the other
+        long long ei = 1, eo = 1, di = 1, dn = 1;
+        for (int i = 0; i < g.rank; ++i) {
+            long long ni = (i == L) ? (r2c ? nl : hc) : T[i].n;
+            long long no = (i == L) ? (r2c ? hc : nl) : T[i].n;
+            ei += (ni - 1) * T[i].is;
+            eo += (no - 1) * T[i].os;
+            di *= ni;
+            dn *= no;
+        }
+        bool zero = false;
+        for (const GDim &d : V) {
+            if (d.n == 0) zero = true;
+            ei += (d.n - 1) * d.is;
+            eo += (d.n - 1) * d.os;
+            di *= d.n;
+            dn *= d.n;
+        }
+        pc.in_reals = zero ? 0 : ei * iu;
+        pc.out_reals = zero ? 0 : eo * ou;
+        pc.in_dense = di * iu;
+        pc.out_dense = dn * ou;
+    }
+    pc.flops = 2.5 * N * (N > 1 ? log2(N) : 0) * H;
+    if (H == 0) {
+        pc.empty = true;
+        return true;
+    }
+    for (const GDim &d : T)
+        if (d.is < 0 || d.os < 0) {
+            set_error("negative strides are not supported");
+            return false;
+        }
+    for (const GDim &d : V)
+        if (d.is < 0 || d.os < 0) {
+            set_error("negative strides are not supported");
+            return false;
+        }
+    if (pc.in_place) {
+        // same bytes: stride in reals on the real side == 2 * stride in complex on the other
+        bool ok = true;
+        for (int i = 0; i < g.rank; ++i) {
+            if (i == L || T[i].n == 1) continue;
+            if (T[i].is * iu != T[i].os * ou) ok = false;
+        }
+        for (const GDim &d : V)
+            if (d.n > 1 && d.is * iu != d.os * ou) ok = false;
+        if (!ok) {
+            set_error("in-place real transform: input and output rows do not coincide");
+            return false;
+        }
+    }
+    const Caps c = caps();
+    const bool even = (nl % 2 == 0);
+    const long long m = even ? nl / 2 : nl;
+    const bool unit_rows = r2c ? (T[L].is == 1 && T[L].os == 1) : (T[L].is == 1 && T[L].os == 1);
+    const long long cap = unit_rows ? c.row : c.col;
+
+    // lines of the last-dimension real step, (src, dst) strides in reals
+    std::vector<LDim> rl;
+    for (int i = 0; i < L; ++i) rl.push_back(LDim{T[i].n, T[i].is * iu, T[i].os * ou, false});
+    for (const GDim &d : V) rl.push_back(LDim{d.n, d.is * iu, d.os * ou, false});
+    bool evens_src = true, evens_dst = true;  // all complex-side offsets even -> vector access
+    for (const LDim &l : rl) {
+        if (l.s & 1) evens_src = false;
+        if (l.d & 1) evens_dst = false;
+    }
+
+    auto leading_axes = [&](bool on_input) -> bool {
+        // complex transforms over dims 0..L-1 with hc columns; r2c: forward in place on OUT,
+        // c2r: backward on IN (the reference destroys multi-dim c2r input too)
+        std::vector<int> order;
+        for (int i = 0; i < L; ++i)
+            if (T[i].n > 1) order.push_back(i);
+        auto st_of = [&](int i) { return 2 * (on_input ? T[i].is : T[i].os); };
+        std::sort(order.begin(), order.end(), [&](int a, int b) { return st_of(a) < st_of(b); });
+        for (size_t oi = 0; oi < order.size(); ++oi) {
+            const int ax = order[oi];
+            std::vector<LDim> lines;
+            for (int i = 0; i < g.rank; ++i) {
+                if (i == ax) continue;
+                long long n = (i == L) ? hc : T[i].n;
+                lines.push_back(LDim{n, st_of(i), st_of(i), false});
+            }
+            for (const GDim &d : V) {
+                long long s = 2 * (on_input ? d.is : d.os);
+                lines.push_back(LDim{d.n, s, s, false});
+            }
+            const bool bwd = !r2c;
+            std::vector<int> allowed = on_input ? std::vector<int>{B_IN, B_SCR} : std::vector<int>{B_OUT, B_SCR};
+            if (!add_c2c_axis(pc, T[ax].n, st_of(ax), st_of(ax), lines, bwd && oi == 0,
+                              bwd && oi + 1 == order.size(), allowed))
+                return false;
+        }
+        return true;
+    };
+
+    if (!r2c && !leading_axes(true)) return false;
+    const size_t first_real_step = pc.steps.size();
+
+    if (even && m <= cap) {
+        AxisSpec a;
+        a.n = (int)nl;
+        a.rmode = r2c ? RM_R2C_HALF : RM_C2R_HALF;
+        if (r2c) {
+            a.s_axis = 2 * T[L].is;
+            a.s_pair = T[L].is;
+            a.d_axis = 2 * T[L].os;
+            a.d_pair = 1;
+            a.src_vec = (T[L].is == 1) && evens_src;
+            a.dst_vec = evens_dst;
+        } else {
+            a.s_axis = 2 * T[L].is;
+            a.s_pair = 1;
+            a.d_axis = 2 * T[L].os;
+            a.d_pair = T[L].os;
+            a.src_vec = evens_src;
+            a.dst_vec = (T[L].os == 1) && evens_dst;
+            a.swap_out = true;
+        }
+        a.lines = rl;
+        StepPlan st;
+        if (!make_pass_step(st, a)) return false;
+        st.inplace_ok = pc.in_place;  // row-for-row overlap was verified above
+        if (pc.in_place && (st.pp.ld_col || st.pp.st_col || (T[L].is != 1 && T[L].n > 1))) {
+            // a CTA must own whole rows for the in-place real step to be race-free
+            if (T[L].is != 1 || T[L].os != 1) {
+                set_error("in-place real transform with a strided last dimension");
+                return false;
+            }
+        }
+        st.dst_allowed = {B_OUT};
+        pc.steps.push_back(st);
+    } else if (!even) {
+        if (nl > cap) {
+            set_error("odd real length %lld > %lld is not supported", nl, cap);
+            return false;
+        }
+        AxisSpec a;
+        a.n = (int)nl;
+        a.rmode = r2c ? RM_R2C_FULL : RM_C2R_FULL;
+        if (r2c) {
+            a.s_axis = T[L].is;
+            a.d_axis = 2 * T[L].os;
+            a.dst_vec = evens_dst;
+        } else {
+            a.s_axis = 2 * T[L].is;
+            a.d_axis = T[L].os;
+            a.src_vec = evens_src;
+            a.swap_out = true;
+        }
+        a.lines = rl;
+        StepPlan st;
+        if (!make_pass_step(st, a)) return false;
+        st.inplace_ok = pc.in_place;
+        if (pc.in_place && (T[L].is != 1 || T[L].os != 1)) {
+            set_error("in-place real transform with a strided last dimension");
+            return false;
+        }
+        st.dst_allowed = {B_OUT};
+        pc.steps.push_back(st);
+    } else {
+        // ---- four-step half-length complex transform through a compact scratch ----
+        long long n1, n2;
+        if (!split_four_step(m, &n1, &n2)) {
+            set_error("real length %lld: no four-step split", nl);
+            return false;
+        }
+        std::vector<LDim> nz;
+        for (const LDim &l : rl)
+            if (l.n > 1) nz.push_back(l);
+        const std::vector<long long> cs = compact_strides(nz, m);
+        if (r2c) {
+            {   // A: IN (pairs of reals) -> SCR compact, column pass + twiddle
+                AxisSpec a;
+                a.n = (int)n1;
+                a.s_axis = 2 * T[L].is * n2;
+                a.s_pair = T[L].is;
+                a.d_axis = 2 * n2;
+                a.src_vec = (T[L].is == 1) && evens_src;
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, nz[i].s, cs[i], false});
+                a.lines.push_back(LDim{n2, 2 * T[L].is, 2, true});
+                a.epi_N = m;
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.dst_allowed = {B_SCR};
+                pc.steps.push_back(st);
+            }
+            {   // B: SCR -> OUT rows (Z[k] at complex position k), transposed store
+                AxisSpec a;
+                a.n = (int)n2;
+                a.s_axis = 2;
+                a.d_axis = 2 * T[L].os * n1;
+                a.dst_vec = evens_dst;
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, cs[i], nz[i].d, false});
+                a.lines.push_back(LDim{n1, 2 * n2, 2 * T[L].os, false});
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.src_fixed = B_SCR;
+                st.dst_allowed = {B_OUT};
+                pc.steps.push_back(st);
+            }
+            {   // Hermitian split, in place on OUT
+                StepPlan st;
+                std::vector<LDim> ol;
+                for (const LDim &l : nz) ol.push_back(LDim{l.n, l.d, l.d, false});
+                fill_realpp(st, 1, (int)m, nl, 2 * T[L].os, 2 * T[L].os, ol, false);
+                if (!st.rp.twr) return false;
+                st.inplace_ok = true;
+                st.src_fixed = B_OUT;
+                st.dst_allowed = {B_OUT};
+                pc.steps.push_back(st);
+            }
+        } else {
+            {   // Hermitian merge: IN -> SCR compact (swapped for the backward transform)
+                StepPlan st;
+                std::vector<LDim> ol;
+                for (size_t i = 0; i < nz.size(); ++i) ol.push_back(LDim{nz[i].n, nz[i].s, cs[i], false});
+                fill_realpp(st, 0, (int)m, nl, 2 * T[L].is, 2, ol, false);
+                if (!st.rp.twr) return false;
+                st.dst_allowed = {B_SCR};
+                pc.steps.push_back(st);
+            }
+            {   // A: in place on SCR
+                AxisSpec a;
+                a.n = (int)n1;
+                a.s_axis = 2 * n2;
+                a.d_axis = 2 * n2;
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, cs[i], cs[i], false});
+                a.lines.push_back(LDim{n2, 2, 2, true});
+                a.epi_N = m;
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.inplace_ok = true;
+                st.src_fixed = B_SCR;
+                st.dst_allowed = {B_SCR};
+                pc.steps.push_back(st);
+            }
+            {   // B: SCR -> OUT as pairs of reals, transposed store, un-swap
+                AxisSpec a;
+                a.n = (int)n2;
+                a.s_axis = 2;
+                a.d_axis = 2 * T[L].os * n1;
+                a.d_pair = T[L].os;
+                a.dst_vec = (T[L].os == 1) && evens_dst;
+                a.swap_out = true;
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, cs[i], nz[i].d, false});
+                a.lines.push_back(LDim{n1, 2 * n2, 2 * T[L].os, false});
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.src_fixed = B_SCR;
+                st.dst_allowed = {B_OUT};
+                pc.steps.push_back(st);
+            }
+        }
+    }
+    (void)first_real_step;
+    if (r2c && !leading_axes(false)) return false;
+    return assign_buffers(pc);
+}
+
+}  // namespace b2
