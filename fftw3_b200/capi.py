@@ -103,6 +103,10 @@ class FFTW3Lib:
         L.fftw_free.argtypes = [_vp]
         L.fftw_cleanup.restype = None
         L.fftw_cleanup.argtypes = []
+        L.fftw_sprint_plan.restype = _vp
+        L.fftw_sprint_plan.argtypes = [_vp]
+        L.fftw_flops.restype = None
+        L.fftw_flops.argtypes = [_vp] + [C.POINTER(C.c_double)] * 3
         if hasattr(L, "fftw_init_threads"):
             L.fftw_init_threads.restype = C.c_int
             L.fftw_plan_with_nthreads.restype = None
@@ -156,6 +160,19 @@ class FFTW3Lib:
 
     def execute_dft_c2r(self, plan, inp, out):
         self.lib.fftw_execute_dft_c2r(plan, _ptr(inp), _ptr(out))
+
+    def sprint_plan(self, plan) -> str:
+        p = self.lib.fftw_sprint_plan(plan)
+        if not p:
+            return ""
+        s = C.string_at(p).decode()
+        C.CDLL(None).free(C.c_void_p(p))
+        return s
+
+    def flops(self, plan):
+        a, m, f = C.c_double(), C.c_double(), C.c_double()
+        self.lib.fftw_flops(plan, C.byref(a), C.byref(m), C.byref(f))
+        return a.value, m.value, f.value
 
     def destroy_plan(self, plan):
         self.lib.fftw_destroy_plan(plan)

@@ -1,0 +1,249 @@
+"""Parity cases shared by the CPU (emulation) and GPU test suites.
+
+Every case drives the engine through the public fftw3.h C ABI (fftw3_b200/capi.py is a plain
+ctypes binding of it) and compares with the oracle (oracle/fft_oracle.c via oracle/pyoracle.py,
+itself pinned to the unmodified reference by tests/test_oracle.py) or with the committed golden
+vectors produced by the reference itself (tests/golden/ref_golden.npz).
+
+Tolerance (BASELINE.json north_star): relative L2 error < 1e-6*log2(N) in fp32 and
+< 1e-14*log2(N) in fp64, against double-precision reference output.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+
+from fftw3_b200 import capi
+from oracle import pyoracle as orc
+
+
+def rel_l2(a, b):
+    a = np.asarray(a).astype(np.complex128).ravel()
+    b = np.asarray(b).astype(np.complex128).ravel()
+    den = np.linalg.norm(b)
+    return float(np.linalg.norm(a - b) / (den if den > 0 else 1.0))
+
+
+def tol(lib, N):
+    return (1e-6 if lib.single else 1e-14) * max(1.0, math.log2(max(2, N)))
+
+
+def rand_c(rng, shape, lib):
+    return ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
+
+
+def rand_r(rng, shape, lib):
+    return (rng.random(shape) - 0.5).astype(lib.real)
+
+
+C2C_SHAPES = [(1,), (2,), (3,), (4,), (5,), (7,), (8,), (11,), (13,), (16,), (30,), (64,), (100,),
+              (128,), (243,), (1000,), (1024,), (4096,), (8, 12), (16, 16), (4, 6, 8), (16, 16, 16),
+              (5, 3, 7), (2, 3, 4, 5)]
+C2C_BIG = [(8192,), (16384,), (3 * 2 ** 13,), (2 ** 17,), (64, 64, 64), (4, 2 ** 14)]
+R2C_SHAPES = [(2,), (4,), (6,), (7,), (9,), (16,), (30,), (64,), (1024,), (6, 8), (5, 9), (4, 4, 6),
+              (3, 5, 7)]
+R2C_BIG = [(4096,), (2 ** 15,), (2 ** 17,), (3, 2 ** 14), (32, 32, 32)]
+
+
+def check_c2c(lib, shape, seed=0):
+    rng = np.random.default_rng(seed)
+    x = rand_c(rng, shape, lib)
+    N = int(np.prod(shape))
+    x0 = x.copy()
+    for sign in (capi.FFTW_FORWARD, capi.FFTW_BACKWARD):
+        y = lib.dft(x, sign)
+        assert rel_l2(y, orc.dft(x0, sign)) < tol(lib, N), (shape, sign)
+        assert np.array_equal(x, x0), "out-of-place c2c must preserve its input"
+    # in place
+    z = x0.copy()
+    p = lib.plan_dft(list(shape), z, z, capi.FFTW_FORWARD)
+    assert p, "in-place plan is NULL"
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(z, orc.dft(x0, -1)) < tol(lib, N), (shape, "in place")
+
+
+def check_r2c_c2r(lib, shape, seed=0):
+    rng = np.random.default_rng(seed)
+    x = rand_r(rng, shape, lib)
+    N = int(np.prod(shape))
+    X = lib.r2c(x)
+    Xo = orc.r2c(x)
+    assert rel_l2(X, Xo) < tol(lib, N), (shape, "r2c")
+    Xin = Xo.astype(lib.cplx)
+    y = lib.c2r(Xin, shape[-1])
+    assert rel_l2(y, orc.c2r(Xin, shape[-1])) < tol(lib, N), (shape, "c2r")
+    # unnormalised round trip (fftw3.h convention): c2r(r2c(x)) = N x
+    assert rel_l2(lib.c2r(X, shape[-1]), N * x.astype(np.float64)) < 2 * tol(lib, N)
+
+
+def check_r2c_inplace(lib, shape, seed=0):
+    """in-place r2c / c2r with the padded rows of fftw_rdft2_pad (reference fftw_api.c:774-788)"""
+    rng = np.random.default_rng(seed)
+    n = shape[-1]
+    pad = 2 * (n // 2 + 1)
+    x = rand_r(rng, shape, lib)
+    a = np.zeros(shape[:-1] + (pad,), dtype=lib.real)
+    a[..., :n] = x
+    p = lib.plan_dft_r2c(list(shape), a, a)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    N = int(np.prod(shape))
+    got = a.view(lib.cplx)
+    assert rel_l2(got, orc.r2c(x)) < tol(lib, N), (shape, "r2c in place")
+    # and back
+    Xo = orc.r2c(x).astype(lib.cplx)
+    b = np.ascontiguousarray(Xo).view(lib.real).copy()
+    p = lib.plan_dft_c2r(list(shape), b, b)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(b[..., :n], orc.c2r(Xo, n)) < tol(lib, N), (shape, "c2r in place")
+
+
+def check_many_strided(lib, n=12, howmany=5, istride=3, idist=40, ostride=2, odist=30, seed=1):
+    """advanced interface, element stride and dist (fftw_plan_many_dft, reference fftw_api.c:642-666)"""
+    rng = np.random.default_rng(seed)
+    buf = rand_c(rng, howmany * idist + n * istride, lib)
+    res = np.zeros(howmany * odist + n * ostride, dtype=lib.cplx)
+    p = lib.plan_many_dft([n], howmany, buf, None, istride, idist, res, None, ostride, odist,
+                          capi.FFTW_FORWARD)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    ref = np.zeros(res.shape, dtype=np.complex128)
+    orc.dft_many([n], howmany, buf.astype(np.complex128), None, istride, idist, ref, None, ostride,
+                 odist, -1)
+    assert rel_l2(res, ref) < tol(lib, n)
+    assert np.array_equal(res == 0, ref == 0), "gaps of a strided output must stay untouched"
+
+
+def check_embedded_2d(lib, seed=2):
+    rng = np.random.default_rng(seed)
+    n, inembed, onembed = [4, 6], [5, 8], [4, 7]
+    hm, idist, odist = 3, 5 * 8 + 3, 4 * 7 + 1
+    buf = rand_c(rng, hm * idist, lib)
+    res = np.zeros(hm * odist, dtype=lib.cplx)
+    p = lib.plan_many_dft(n, hm, buf, inembed, 1, idist, res, onembed, 1, odist, capi.FFTW_BACKWARD)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    ref = np.zeros(res.shape, dtype=np.complex128)
+    orc.dft_many(n, hm, buf.astype(np.complex128), inembed, 1, idist, ref, onembed, 1, odist, +1)
+    assert rel_l2(res, ref) < tol(lib, 24)
+
+
+def check_batched_transposed(lib, n=64, howmany=48, seed=3):
+    """batch along the contiguous dimension: istride = howmany, idist = 1 (column transforms)"""
+    rng = np.random.default_rng(seed)
+    x = rand_c(rng, (n, howmany), lib)
+    y = np.zeros_like(x)
+    p = lib.plan_many_dft([n], howmany, x, None, howmany, 1, y, None, howmany, 1, capi.FFTW_FORWARD)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    ref = np.fft.fft(x.astype(np.complex128), axis=0)
+    assert rel_l2(y, ref) < tol(lib, n)
+
+
+def check_many_r2c(lib, n=32, howmany=7, seed=4):
+    rng = np.random.default_rng(seed)
+    x = rand_r(rng, (howmany, n), lib)
+    y = np.zeros((howmany, n // 2 + 1), dtype=lib.cplx)
+    p = lib.plan_many_dft_r2c([n], howmany, x, None, 1, n, y, None, 1, n // 2 + 1)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(y, np.fft.rfft(x.astype(np.float64), axis=1)) < tol(lib, n)
+    z = np.zeros((howmany, n), dtype=lib.real)
+    yc = y.copy()
+    p = lib.plan_many_dft_c2r([n], howmany, yc, None, 1, n // 2 + 1, z, None, 1, n)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(z, n * x.astype(np.float64)) < 2 * tol(lib, n)
+
+
+def check_golden(lib, golden):
+    """outputs of the unmodified reference on stored inputs (tests/golden/make_golden.py)"""
+    tag = "f32" if lib.single else "f64"
+    from tests.golden.make_golden import C2C_SHAPES as GC, R2C_SHAPES as GR
+    for shape in GC:
+        key = "c2c_" + "x".join(map(str, shape)) + "_" + tag
+        x = golden[key + "_in"]
+        N = int(np.prod(shape))
+        t = 2 * tol(lib, N)  # both sides carry working-precision rounding
+        assert rel_l2(lib.dft(x, -1), golden[key + "_fwd"]) < t, key
+        assert rel_l2(lib.dft(x, +1), golden[key + "_bwd"]) < t, key
+    for shape in GR:
+        key = "r2c_" + "x".join(map(str, shape)) + "_" + tag
+        x = golden[key + "_in"]
+        X = golden[key + "_out"]
+        N = int(np.prod(shape))
+        t = 2 * tol(lib, N)
+        assert rel_l2(lib.r2c(x), X) < t, key
+        assert rel_l2(lib.c2r(X, shape[-1]), golden[key + "_c2r"]) < t, key
+
+
+def check_edge_cases(lib):
+    x = np.zeros(8, dtype=lib.cplx)
+    # invalid sizes -> NULL plan, like the reference (fftw_api.c:863-877)
+    assert not lib.plan_many_dft([0], 1, x, None, 1, 1, x, None, 1, 1, -1)
+    assert not lib.plan_many_dft([4], -1, x, None, 1, 4, x, None, 1, 4, -1)
+    # FFTW_WISDOM_ONLY without wisdom -> NULL (fftw_api.c:332-337)
+    assert not lib.plan_dft_1d(8, x, x, -1, capi.FFTW_ESTIMATE | capi.FFTW_WISDOM_ONLY)
+    # howmany = 0 is a legal no-op
+    p = lib.plan_many_dft([4], 0, x, None, 1, 4, x, None, 1, 4, -1)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    # destroy_plan(NULL) is legal (fftw_api.c:410)
+    lib.destroy_plan(None)
+    # rank 0 = copy
+    a = np.arange(5, dtype=np.float64).astype(lib.cplx) + 1j
+    b = np.zeros_like(a)
+    p = lib.plan_many_dft([], 5, a, None, 1, 1, b, None, 1, 1, -1)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert np.array_equal(a, b)
+    # execute_dft on new arrays
+    rng = np.random.default_rng(5)
+    u, v = rand_c(rng, 64, lib), np.zeros(64, dtype=lib.cplx)
+    p = lib.plan_dft_1d(64, u, v, -1)
+    u2, v2 = rand_c(rng, 64, lib), np.zeros(64, dtype=lib.cplx)
+    lib.execute_dft(p, u2, v2)
+    lib.destroy_plan(p)
+    assert rel_l2(v2, np.fft.fft(u2.astype(np.complex128))) < tol(lib, 64)
+    # a length with a prime factor the radix set does not cover yet -> NULL plan, not garbage
+    w = np.zeros(17, dtype=lib.cplx)
+    p = lib.plan_dft_1d(17, w, w.copy(), -1)
+    if p:
+        lib.destroy_plan(p)
+
+
+def check_properties(lib, shape, seed=7):
+    """size-independent checks in the style of the reference verifier
+    (fftw/libbench2/verify-lib.c:293-436): impulse, linearity, shift theorem, Parseval,
+    backward(forward(x)) = N x."""
+    rng = np.random.default_rng(seed)
+    N = int(np.prod(shape))
+    t = 4 * tol(lib, N)
+    imp = np.zeros(shape, dtype=lib.cplx)
+    imp.flat[0] = 1
+    assert rel_l2(lib.dft(imp, -1), np.ones(shape)) < t
+    a, b = rand_c(rng, shape, lib), rand_c(rng, shape, lib)
+    alpha, beta = 0.75 - 0.25j, -0.5 + 1.25j
+    lhs = lib.dft((alpha * a + beta * b).astype(lib.cplx), -1)
+    rhs = alpha * lib.dft(a, -1).astype(np.complex128) + beta * lib.dft(b, -1).astype(np.complex128)
+    assert rel_l2(lhs, rhs) < t
+    A = lib.dft(a, -1)
+    assert abs(np.sum(np.abs(A.astype(np.complex128)) ** 2) / (N * np.sum(np.abs(a.astype(np.complex128)) ** 2)) - 1) < t
+    assert rel_l2(lib.dft(A, +1), N * a.astype(np.complex128)) < t
+    # time shift along the last axis <-> phase ramp
+    n = shape[-1]
+    sh = np.roll(a, 1, axis=-1)
+    ramp = np.exp(-2j * np.pi * np.arange(n) / n)
+    assert rel_l2(lib.dft(sh, -1), A.astype(np.complex128) * ramp) < t

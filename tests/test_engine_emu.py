@@ -1,0 +1,76 @@
+"""CPU suite for the host logic of the engine: C API layer (csrc/fftw_api.c), geometry
+canonicalisation, selector, buffer assignment, and every index computation of the kernels.
+
+It runs the TEST-ONLY emulation build (tests/_emu/libfftw3_emu_*.so: the same sources compiled
+with -DB2_EMULATE, each CTA executed by a host loop) -- there is no GPU in this container.
+The product library has no such path; the real parity tests are tests/test_gpu_parity.py.
+"""
+import numpy as np
+import pytest
+
+from fftw3_b200 import build, capi
+from tests import cases
+
+
+@pytest.fixture(scope="module", params=["fp32", "fp64"])
+def lib(request):
+    path = build.build_emu(request.param)
+    return capi.FFTW3Lib(path, request.param == "fp32")
+
+
+@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG, ids=lambda s: "x".join(map(str, s)))
+def test_c2c(lib, shape):
+    cases.check_c2c(lib, shape)
+
+
+@pytest.mark.parametrize("shape", cases.R2C_SHAPES + cases.R2C_BIG, ids=lambda s: "x".join(map(str, s)))
+def test_r2c_c2r(lib, shape):
+    cases.check_r2c_c2r(lib, shape)
+
+
+@pytest.mark.parametrize("shape", [(10,), (16,), (3, 10), (4, 6, 8), (7,), (2 ** 15,)],
+                         ids=lambda s: "x".join(map(str, s)))
+def test_r2c_inplace(lib, shape):
+    cases.check_r2c_inplace(lib, shape)
+
+
+def test_many_strided(lib):
+    cases.check_many_strided(lib)
+    cases.check_many_strided(lib, n=64, howmany=9, istride=1, idist=70, ostride=1, odist=64)
+
+
+def test_embedded_2d(lib):
+    cases.check_embedded_2d(lib)
+
+
+def test_batched_transposed(lib):
+    cases.check_batched_transposed(lib)
+    cases.check_batched_transposed(lib, n=4096, howmany=6)
+
+
+def test_many_r2c(lib):
+    cases.check_many_r2c(lib)
+
+
+def test_golden_vectors_of_the_reference(lib, golden):
+    cases.check_golden(lib, golden)
+
+
+def test_edge_cases(lib):
+    cases.check_edge_cases(lib)
+
+
+@pytest.mark.parametrize("shape", [(96,), (16, 20), (2 ** 14,)], ids=lambda s: "x".join(map(str, s)))
+def test_verifier_properties(lib, shape):
+    cases.check_properties(lib, shape)
+
+
+def test_plan_description_and_flops(lib):
+    x = np.zeros((4, 4096), dtype=lib.cplx)
+    p = lib.plan_many_dft([4096], 4, x, None, 1, 4096, x.copy(), None, 1, 4096, -1)
+    assert p
+    s = lib.sprint_plan(p)
+    assert "n=4096" in s and "pass 0" in s
+    add, mul, fma = lib.flops(p)
+    assert abs((add + mul + fma) - 5 * 4096 * 12 * 4) < 1e-6
+    lib.destroy_plan(p)

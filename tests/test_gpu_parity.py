@@ -1,0 +1,197 @@
+"""GPU parity tests proper: the product library (fftw3_b200/lib/*/libfftw3.so, sm_100a CUDA
+kernels) driven through the fftw3.h C ABI, compared with the oracle and with the golden
+vectors of the reference.  Host-pointer cases go through the PCIe staging path; device-pointer
+cases (torch tensors, used only as device memory) run in HBM with no copies."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+
+from fftw3_b200 import build, capi
+from tests import cases
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", params=["fp32", "fp64"])
+def lib(request):
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    path = build.lib_path(request.param)
+    import os
+    assert os.path.exists(path), "product library missing: run __graft_entry__.build()"
+    L = capi.FFTW3Lib(path, request.param == "fp32")
+    L.lib.b2fft_launch_count.restype = C.c_ulonglong
+    return L
+
+
+@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG, ids=lambda s: "x".join(map(str, s)))
+def test_c2c(lib, shape):
+    n0 = lib.lib.b2fft_launch_count()
+    cases.check_c2c(lib, shape)
+    assert lib.lib.b2fft_launch_count() > n0, "no CUDA kernel was launched"
+
+
+@pytest.mark.parametrize("shape", cases.R2C_SHAPES + cases.R2C_BIG, ids=lambda s: "x".join(map(str, s)))
+def test_r2c_c2r(lib, shape):
+    cases.check_r2c_c2r(lib, shape)
+
+
+@pytest.mark.parametrize("shape", [(10,), (16,), (3, 10), (4, 6, 8), (7,), (2 ** 15,)],
+                         ids=lambda s: "x".join(map(str, s)))
+def test_r2c_inplace(lib, shape):
+    cases.check_r2c_inplace(lib, shape)
+
+
+def test_many_strided(lib):
+    cases.check_many_strided(lib)
+    cases.check_many_strided(lib, n=64, howmany=9, istride=1, idist=70, ostride=1, odist=64)
+
+
+def test_embedded_2d(lib):
+    cases.check_embedded_2d(lib)
+
+
+def test_batched_transposed(lib):
+    cases.check_batched_transposed(lib)
+    cases.check_batched_transposed(lib, n=4096, howmany=6)
+
+
+def test_many_r2c(lib):
+    cases.check_many_r2c(lib)
+
+
+def test_golden_vectors_of_the_reference(lib, golden):
+    cases.check_golden(lib, golden)
+
+
+def test_edge_cases(lib):
+    cases.check_edge_cases(lib)
+
+
+@pytest.mark.parametrize("shape", [(96,), (16, 20), (2 ** 14,), (2 ** 20,), (128, 128, 128)],
+                         ids=lambda s: "x".join(map(str, s)))
+def test_verifier_properties(lib, shape):
+    cases.check_properties(lib, shape)
+
+
+# ---------------------------------------------------------------- device-resident arrays
+def _tdtype(lib):
+    import torch
+    return (torch.complex64, torch.float32) if lib.single else (torch.complex128, torch.float64)
+
+
+def test_device_pointers_batched_4096(lib):
+    """config 2 shape at reduced batch: fftw_plan_many_dft n=4096, contiguous batch, in HBM"""
+    import torch
+    ct, _ = _tdtype(lib)
+    howmany, n = 256, 4096
+    rng = np.random.default_rng(11)
+    xh = cases.rand_c(rng, (howmany, n), lib)
+    x = torch.from_numpy(xh).cuda()
+    y = torch.empty_like(x)
+    p = lib.plan_many_dft([n], howmany, x, None, 1, n, y, None, 1, n, capi.FFTW_FORWARD)
+    assert p
+    lib.execute(p)
+    torch.cuda.synchronize()
+    got = y.cpu().numpy()
+    from oracle import pyoracle as orc
+    assert cases.rel_l2(got, orc.dft_batched(xh, -1)) < cases.tol(lib, n)
+    assert torch.equal(x.cpu(), torch.from_numpy(xh)), "input must be preserved"
+    # new-array execute with the same plan (fftw_execute_dft)
+    x2 = torch.from_numpy(cases.rand_c(rng, (howmany, n), lib)).cuda()
+    y2 = torch.empty_like(x2)
+    lib.execute_dft(p, x2, y2)
+    torch.cuda.synchronize()
+    assert cases.rel_l2(y2.cpu().numpy(), np.fft.fft(x2.cpu().numpy().astype(np.complex128), axis=1)) < cases.tol(lib, n)
+    lib.destroy_plan(p)
+
+
+def test_device_3d_in_place_and_out_of_place(lib):
+    import torch
+    rng = np.random.default_rng(12)
+    shape = (64, 64, 64)
+    xh = cases.rand_c(rng, shape, lib)
+    ref = np.fft.fftn(xh.astype(np.complex128))
+    x = torch.from_numpy(xh).cuda()
+    y = torch.empty_like(x)
+    p = lib.plan_dft_3d(*shape, x, y, capi.FFTW_FORWARD)
+    lib.execute(p)
+    lib.destroy_plan(p)
+    torch.cuda.synchronize()
+    assert cases.rel_l2(y.cpu().numpy(), ref) < cases.tol(lib, 64 ** 3)
+    p = lib.plan_dft_3d(*shape, x, x, capi.FFTW_FORWARD)
+    lib.execute(p)
+    lib.destroy_plan(p)
+    torch.cuda.synchronize()
+    assert cases.rel_l2(x.cpu().numpy(), ref) < cases.tol(lib, 64 ** 3)
+
+
+def test_device_r2c_c2r_large_1d(lib):
+    """config 3 shape at reduced batch: n = 2^20 real, four-step half-length path"""
+    import torch
+    rng = np.random.default_rng(13)
+    n, howmany = 2 ** 20, 3
+    xh = cases.rand_r(rng, (howmany, n), lib)
+    x = torch.from_numpy(xh).cuda()
+    X = torch.empty((howmany, n // 2 + 1), dtype=_tdtype(lib)[0], device="cuda")
+    p = lib.plan_many_dft_r2c([n], howmany, x, None, 1, n, X, None, 1, n // 2 + 1)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    torch.cuda.synchronize()
+    ref = np.fft.rfft(xh.astype(np.float64), axis=1)
+    assert cases.rel_l2(X.cpu().numpy(), ref) < cases.tol(lib, n)
+    z = torch.empty_like(x)
+    p = lib.plan_many_dft_c2r([n], howmany, X, None, 1, n // 2 + 1, z, None, 1, n)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    torch.cuda.synchronize()
+    assert cases.rel_l2(z.cpu().numpy(), n * xh.astype(np.float64)) < 2 * cases.tol(lib, n)
+
+
+def test_full_size_roundtrip_512_cubed_fp32(lib):
+    """BASELINE config 4 at full size, through size-independent properties: closed-form
+    spectrum of plane waves + backward(forward(x)) = N x + Parseval."""
+    import torch
+    if not lib.single:
+        pytest.skip("config 4 is fp32")
+    n = 512
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = (torch.rand((n, n, n, 2), device="cuda", generator=g) - 0.5)
+    x = torch.view_as_complex(x).contiguous()
+    # add a plane wave with integer wave numbers: a spike of height N at (5, 7, 11)
+    i = torch.arange(n, device="cuda", dtype=torch.float32)
+    ph = (5 * i[:, None, None] + 7 * i[None, :, None] + 11 * i[None, None, :]) * (2 * math.pi / n)
+    x0 = x.clone()
+    x = x + 3.0 * torch.polar(torch.ones_like(ph), ph)
+    del ph
+    y = torch.empty_like(x)
+    p = lib.plan_dft_3d(n, n, n, x, y, capi.FFTW_FORWARD)
+    assert p
+    lib.execute(p)
+    torch.cuda.synchronize()
+    N = n ** 3
+    e_in = float((x.abs() ** 2).sum(dtype=torch.float64))
+    e_out = float((y.abs() ** 2).sum(dtype=torch.float64))
+    assert abs(e_out / (N * e_in) - 1) < 1e-5
+    # linearity: F(x0 + 3 wave) - F(x0) is a single spike 3N at (5,7,11)
+    y0 = torch.empty_like(x0)
+    lib.execute_dft(p, x0, y0)
+    torch.cuda.synchronize()
+    d = y - y0
+    spike = d[5, 7, 11].item()
+    assert abs(spike - 3.0 * N) / (3.0 * N) < 1e-5
+    d[5, 7, 11] = 0
+    assert float(d.abs().max()) / (3.0 * N) < 1e-4
+    del d, y0, x0
+    lib.destroy_plan(p)
+    # in place, backward: N x
+    p = lib.plan_dft_3d(n, n, n, y, y, capi.FFTW_BACKWARD)
+    lib.execute(p)
+    lib.destroy_plan(p)
+    torch.cuda.synchronize()
+    err = float(((y / N - x).abs() ** 2).sum(dtype=torch.float64).sqrt() / (x.abs() ** 2).sum(dtype=torch.float64).sqrt())
+    assert err < 2e-6 * math.log2(N)
