@@ -114,3 +114,296 @@ class ClockSampler:
         s = sorted(self.samples)
         return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
                 "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------- reference arm
+def reference_lib(prec):
+    """the UNMODIFIED reference build (oracle/_ref), else None"""
+    path = os.path.join(ROOT, "oracle", "_ref", f"libfftw3_ref_{'f32' if prec == 'fp32' else 'f64'}.so")
+    if not os.path.exists(path):
+        return None
+    return capi.FFTW3Lib(path, prec == "fp32")
+
+
+def cpu_sample_of(w, budget_s=20.0):
+    """a bounded sample of the workload: same transform, fewer of them"""
+    s = dict(w)
+    N = int(np.prod(w["n"]))
+    if w["howmany"] > 1:
+        # ~1.5 GFLOP-conv per repetition keeps a rep well under a second on a few cores
+        s["howmany"] = max(1, min(w["howmany"], int(1.5e9 / (5.0 * N * math.log2(N))) or 1))
+    elif len(w["n"]) == 3 and N > 256 ** 3:
+        s["n"] = [256, 256, 256]
+    return s
+
+
+def run_reference(w, steps, warmup, threads=None, measure=True):
+    """times the reference's own CPU implementation on this host: threads + AVX2 + FFTW_MEASURE
+    (oracle/_ref is built with -DWITH_SLOW_TIMER so MEASURE really measures)"""
+    lib = reference_lib(w["prec"])
+    kind = "reference"
+    cores = threads or (os.cpu_count() or 1)
+    if lib is None:
+        return None
+    lib.lib.fftw_init_threads()
+    lib.plan_with_nthreads(cores)
+    n, hm = w["n"], w["howmany"]
+    N = int(np.prod(n))
+    rng = np.random.default_rng(1)
+    flags = capi.FFTW_MEASURE if measure else capi.FFTW_ESTIMATE
+    lib.lib.fftw_set_timelimit.argtypes = [C.c_double]
+    lib.lib.fftw_set_timelimit(20.0)
+    if w["kind"] == "c2c":
+        x = np.zeros((hm, N), dtype=lib.cplx)
+        y = x if w.get("inplace") else np.zeros_like(x)
+        p = lib.plan_many_dft(n, hm, x, None, 1, N, y, None, 1, N, capi.FFTW_FORWARD, flags)
+        x[:] = ((rng.random(x.shape) - 0.5) + 1j * (rng.random(x.shape) - 0.5)).astype(lib.cplx)
+    elif w["kind"] == "r2c":
+        x = np.zeros((hm, N), dtype=lib.real)
+        y = np.zeros((hm, N // n[-1] * (n[-1] // 2 + 1)), dtype=lib.cplx)
+        p = lib.plan_many_dft_r2c(n, hm, x, None, 1, N, y, None, 1, y.shape[1], flags)
+        x[:] = (rng.random(x.shape) - 0.5).astype(lib.real)
+    else:
+        y = np.zeros((hm, N), dtype=lib.real)
+        x = np.zeros((hm, N // n[-1] * (n[-1] // 2 + 1)), dtype=lib.cplx)
+        p = lib.plan_many_dft_c2r(n, hm, x, None, 1, x.shape[1], y, None, 1, N, flags)
+        x[:] = ((rng.random(x.shape) - 0.5) + 1j * (rng.random(x.shape) - 0.5)).astype(lib.cplx)
+    assert p, "reference plan is NULL"
+    for _ in range(warmup):
+        lib.execute(p)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        lib.execute(p)
+    dt = (time.perf_counter() - t0) / steps
+    lib.destroy_plan(p)
+    flops, _ = workload_numbers(w)
+    return {"value": flops / dt / 1e9, "unit": "GFLOP/s", "cores": cores, "kind": kind,
+            "sample": f"{w['kind']} n={'x'.join(map(str, n))} howmany={hm} {w['prec']}, "
+                      f"{'FFTW_MEASURE' if measure else 'FFTW_ESTIMATE'}, {cores} threads, AVX2",
+            "ms_per_step": dt * 1e3}
+
+
+# ------------------------------------------------------------------------------- GPU arm
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def engine_lib(prec):
+    path = b2build.lib_path(prec)
+    if not os.path.exists(path):
+        path = b2build.build_product(prec)
+    L = capi.FFTW3Lib(path, prec == "fp32")
+    L.lib.b2fft_launch_count.restype = C.c_ulonglong
+    L.lib.b2fft_execute_async.restype = C.c_int
+    L.lib.b2fft_execute_async.argtypes = [C.c_void_p] * 4
+    L.lib.b2fft_last_error.restype = C.c_char_p
+    L.lib.b2fft_plan_num_passes.argtypes = [C.c_void_p]
+    return L
+
+
+def plan_for(lib, w, x, y):
+    n, hm = w["n"], w["howmany"]
+    N = int(np.prod(n))
+    if w["kind"] == "c2c":
+        return lib.plan_many_dft(n, hm, x, None, 1, N, y, None, 1, N, capi.FFTW_FORWARD)
+    hc = N // n[-1] * (n[-1] // 2 + 1)
+    if w["kind"] == "r2c":
+        return lib.plan_many_dft_r2c(n, hm, x, None, 1, N, y, None, 1, hc)
+    return lib.plan_many_dft_c2r(n, hm, x, None, 1, hc, y, None, 1, N)
+
+
+def io_shapes(lib, w):
+    n, hm = w["n"], w["howmany"]
+    N = int(np.prod(n))
+    hc = N // n[-1] * (n[-1] // 2 + 1)
+    if w["kind"] == "c2c":
+        return ((hm, N), lib.cplx), ((hm, N), lib.cplx)
+    if w["kind"] == "r2c":
+        return ((hm, N), lib.real), ((hm, hc), lib.cplx)
+    return ((hm, hc), lib.cplx), ((hm, N), lib.real)
+
+
+def fftw_plan_bp(plan):
+    """struct fftw_plan_s { b2fft_plan *bp; ... }: first member (csrc/fftw_api.c)"""
+    return C.cast(plan, C.POINTER(C.c_void_p))[0]
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    w = WORKLOADS[args.workload]
+    lib = engine_lib(w["prec"])
+    lib.lib.b2fft_set_device(local)
+    flops, nbytes = workload_numbers(w)
+    (ishape, idt), (oshape, odt) = io_shapes(lib, w)
+    tmap = {np.complex64: torch.complex64, np.complex128: torch.complex128,
+            np.float32: torch.float32, np.float64: torch.float64}
+
+    # ---- device-resident arrays: synthetic uniform [-0.5, 0.5) like the reference verifier
+    g = torch.Generator(device="cuda").manual_seed(1 + rank)
+    rdt = torch.float32 if w["prec"] == "fp32" else torch.float64
+    if idt in (np.complex64, np.complex128):
+        x = torch.view_as_complex(torch.rand(ishape + (2,), device="cuda", dtype=rdt, generator=g) - 0.5)
+    else:
+        x = torch.rand(ishape, device="cuda", dtype=rdt, generator=g) - 0.5
+    inplace = bool(w.get("inplace"))
+    y = x if inplace else torch.empty(oshape, device="cuda", dtype=tmap[odt])
+    plan = plan_for(lib, w, x, y)
+    assert plan, "plan is NULL: " + lib.lib.b2fft_last_error().decode()
+    bp = fftw_plan_bp(plan)
+    stream = torch.cuda.current_stream()
+    sp = C.c_void_p(stream.cuda_stream)
+
+    def step_dev():
+        rc = lib.lib.b2fft_execute_async(bp, x.data_ptr(), y.data_ptr(), sp)
+        assert rc == 0, lib.lib.b2fft_last_error()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step_dev()
+    barrier()
+    l0 = lib.lib.b2fft_launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    with ClockSampler(local) as clk:
+        ev[0].record(stream)
+        for i in range(args.steps):
+            step_dev()
+            ev[i + 1].record(stream)
+        barrier()
+    launches = int(lib.lib.b2fft_launch_count() - l0)
+    total_ms = ev[0].elapsed_time(ev[-1])
+    per = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps))
+    if world > 1:
+        t = torch.tensor([total_ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    ms_step = total_ms / args.steps
+    value = world * flops / (ms_step * 1e-3) / 1e9
+    npasses = lib.lib.b2fft_plan_num_passes(bp)
+    peak, peak_src = measured_peak_gbs()
+    achieved = nbytes / (ms_step * 1e-3) / 1e9
+    plan_desc = lib.sprint_plan(plan)
+
+    # ---- end to end: host (pinned) arrays through fftw_execute, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        ib = int(np.prod(ishape)) * np.dtype(idt).itemsize
+        ob = int(np.prod(oshape)) * np.dtype(odt).itemsize
+        hin = lib.malloc(ib)
+        hout = hin if inplace else lib.malloc(ob)
+        assert hin and hout, "fftw_malloc failed"
+        hx = np.ctypeslib.as_array(C.cast(hin, C.POINTER(C.c_byte)), shape=(ib,)).view(idt).reshape(ishape)
+        hx[...] = x.cpu().numpy()
+        hplan = plan_for(lib, w, hin, hout)
+        assert hplan
+        esteps = max(1, min(args.steps, args.e2e_steps))
+        for _ in range(2):
+            lib.execute(hplan)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(esteps):
+            lib.execute(hplan)  # synchronous: returns when the result is in host memory
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / esteps
+        if world > 1:
+            t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e = {"value": world * flops / dt / 1e9, "unit": "GFLOP/s", "h2d_bytes_per_step": ib,
+               "d2h_bytes_per_step": ob, "ms_per_step": dt * 1e3, "steps": esteps}
+        lib.destroy_plan(hplan)
+        lib.free(hin)
+        if not inplace:
+            lib.free(hout)
+    lib.destroy_plan(plan)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        s = cpu_sample_of(w)
+        cpu = run_reference(s, steps=3, warmup=1, measure=True)
+        if cpu:
+            cpu.pop("ms_per_step", None)
+    if rank == 0:
+        line = {
+            "metric": "FFTW-convention GFLOP/s (5 N log2 N / t), fftw_execute",
+            "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if w["prec"] == "fp32" else "f64", "data": "synthetic uniform[-0.5,0.5), seed 1",
+            "config": {"workload": args.workload, "api": "fftw_plan_many_dft + fftw_execute" if w["kind"] == "c2c"
+                       else f"fftw_plan_many_dft_{w['kind']} + fftw_execute",
+                       "n": w["n"], "howmany_per_gpu": w["howmany"], "in_place": inplace,
+                       "l2": "inputs+outputs %.2f GiB per step >> 126 MB L2, no flush needed" % (nbytes / GIB)
+                       if nbytes > 512e6 else "working set fits L2 (latency-bound config)",
+                       "global_passes": int(npasses), "sharding": "batch split across ranks, no collective"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_step": nbytes, "kernels_per_step": launches / args.steps,
+                         "median_step_ms": per[len(per) // 2], "min_step_ms": per[0]},
+            "clocks": clk.summary(),
+            "gpu_launches": launches,
+            "plan": plan_desc.strip().split("\n"),
+        }
+        if e2e:
+            line["e2e"] = e2e
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    w = WORKLOADS[args.workload]
+    s = cpu_sample_of(w)
+    r = run_reference(s, steps=max(1, args.steps), warmup=max(1, min(args.warmup, 3)), measure=True)
+    if r is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (run __graft_entry__.build() where /root/reference exists)"}))
+        return
+    line = {"impl": "reference", "metric": "FFTW-convention GFLOP/s (5 N log2 N / t), fftw_execute",
+            "value": r["value"], "unit": "GFLOP/s", "n_gpus": int(os.environ.get("WORLD_SIZE", 1)),
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if w["prec"] == "fp32" else "f64", "data": "synthetic uniform[-0.5,0.5), seed 1",
+            "config": {"workload": args.workload, "n": w["n"], "howmany_per_gpu": w["howmany"]},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -174,6 +174,9 @@ class FFTW3Lib:
         self.lib.fftw_flops(plan, C.byref(a), C.byref(m), C.byref(f))
         return a.value, m.value, f.value
 
+    def plan_with_nthreads(self, n):
+        self.lib.fftw_plan_with_nthreads(int(n))
+
     def destroy_plan(self, plan):
         self.lib.fftw_destroy_plan(plan)
 
