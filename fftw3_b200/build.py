@@ -62,7 +62,7 @@ def build_product(prec: str, force: bool = False, verbose: bool = False) -> str:
     jobs = []
     for s in CU_SOURCES:
         o = os.path.join(od, s + ".o")
-        jobs.append((["nvcc", "-O3", "-std=c++17", "-lineinfo", *ARCH, "-Xcompiler", "-fPIC,-O3,-fno-gnu-unique",
+        jobs.append((["nvcc", "-O3", "-std=c++17", "-lineinfo", "--expt-relaxed-constexpr", *ARCH, "-Xcompiler", "-fPIC,-O3,-fno-gnu-unique",
                       *(["-Xptxas", "-v"] if verbose else []), *defs, "-I", INC, "-I", CSRC,
                       "-c", os.path.join(CSRC, s), "-o", o], o))
     for s in csrc:

@@ -9,7 +9,7 @@
 #include "generic_kernel.cuh"
 #include "plan_build_real.h"
 #include "realpp_kernel.cuh"
-#include "tile_kernel.cuh"
+#include "tile_dispatch.cuh"
 
 using namespace b2;
 
@@ -38,45 +38,39 @@ static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream
         }
         const real_t *sp = src + so;
         real_t *dp = dst + dof;
-        PassParams pp = s.pp;
-        if (s.kind == SK_PASS) {
-            // vector access needs 2-real alignment of the actual base addresses
-            if (((uintptr_t)sp % sizeof(cpx_t)) != 0) pp.vec_ld = 0;
-            if (((uintptr_t)dp % sizeof(cpx_t)) != 0) pp.vec_st = 0;
-        }
+        bool fast = s.kind == SK_PASS && s.fast_id >= 0;
+        bool al_s = ((uintptr_t)sp % sizeof(cpx_t)) == 0, al_d = ((uintptr_t)dp % sizeof(cpx_t)) == 0;
+        if (!al_s || !al_d) fast = false;  // vector access needs 2-real alignment of the base addresses
+        PassParams pp = fast ? s.pp : s.gen_pp;
+        if (!al_s) pp.vec_ld = 0;
+        if (!al_d) pp.vec_st = 0;
+        const long long nblocks = (s.kind == SK_PASS && !fast) ? s.gen_nblocks : s.nblocks;
         const long long maxgrid = 1ll << 30;
-        for (long long b0 = 0; b0 < s.nblocks; b0 += maxgrid) {
-            const long long nb = std::min(maxgrid, s.nblocks - b0);
+        for (long long b0 = 0; b0 < nblocks; b0 += maxgrid) {
+            const long long nb = std::min(maxgrid, nblocks - b0);
+            if (s.kind == SK_PASS && fast) {
+                int rc = b2_launch_tile_kernel(s.fast_id, pp, sp, dp, b0, nb, s.nthreads, s.smem, stream);
+                if (rc) return rc;
+            } else if (s.kind == SK_PASS) {
+                const size_t smem = b2_generic_smem_bytes(pp.C, pp.lstride);
 #if B2_CUDA
-            if (s.kind == SK_PASS) {
-                if (s.fast_id >= 0 && pp.vec_ld == s.pp.vec_ld && pp.vec_st == s.pp.vec_st) {
-                    int rc = b2_launch_tile_kernel(s.fast_id, pp, sp, dp, b0, nb, s.nthreads, s.smem, stream);
-                    if (rc) return rc;
-                } else {
-                    const size_t smem = b2_generic_smem_bytes(pp.C, pp.lstride);
-                    b2_generic_pass_kernel<<<(unsigned)nb, s.gen_threads, smem, stream>>>(pp, sp, dp, b0);
-                }
+                b2_generic_pass_kernel<<<(unsigned)nb, s.gen_threads, smem, stream>>>(pp, sp, dp, b0);
+#else
+                std::vector<char> sm(smem + 64);
+                for (long long b = 0; b < nb; ++b) b2_generic_pass_body(pp, sp, dp, b0 + b, sm.data(), s.gen_threads);
+#endif
             } else {
+#if B2_CUDA
                 b2_realpp_kernel<<<(unsigned)nb, s.nthreads, 0, stream>>>(s.rp, s.kind == SK_RPOST, sp, dp, b0);
+#else
+                for (long long b = 0; b < nb; ++b) b2_realpp_body(s.rp, s.kind == SK_RPOST, sp, dp, b0 + b, s.nthreads);
+#endif
             }
             ++launch_counter();
+#if B2_CUDA
             B2_CK(cudaGetLastError());
 #else
             (void)stream;
-            if (s.kind == SK_PASS) {
-                if (s.fast_id >= 0 && pp.vec_ld == s.pp.vec_ld && pp.vec_st == s.pp.vec_st) {
-                    int rc = b2_launch_tile_kernel(s.fast_id, pp, sp, dp, b0, nb, s.nthreads, s.smem, stream);
-                    if (rc) return rc;
-                } else {
-                    std::vector<char> smem(b2_generic_smem_bytes(pp.C, pp.lstride) + 64);
-                    for (long long b = 0; b < nb; ++b)
-                        b2_generic_pass_body(pp, sp, dp, b0 + b, smem.data(), s.gen_threads);
-                }
-            } else {
-                for (long long b = 0; b < nb; ++b)
-                    b2_realpp_body(s.rp, s.kind == SK_RPOST, sp, dp, b0 + b, s.nthreads);
-            }
-            ++launch_counter();
 #endif
         }
         size_t i = 0;
@@ -127,6 +121,8 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
     if (ok) {
         for (StepPlan &s : p->pc.steps) {
             s.gen_threads = s.nthreads;
+            s.gen_pp = s.pp;
+            s.gen_nblocks = s.nblocks;
             if (s.kind == SK_PASS) b2_select_tile_kernel(s);
         }
         if (p->pc.scr_reals > 0) {

@@ -149,6 +149,7 @@ inline bool build_real(PlanCore &pc) {
     for (const GDim &d : V) rl.push_back(LDim{d.n, d.is * iu, d.os * ou, false});
     bool evens_src = true, evens_dst = true;  // all complex-side offsets even -> vector access
     for (const LDim &l : rl) {
+        if (l.n <= 1) continue;
         if (l.s & 1) evens_src = false;
         if (l.d & 1) evens_dst = false;
     }

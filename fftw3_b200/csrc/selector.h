@@ -41,7 +41,9 @@ struct Step {
     bool reads_input_layout = false;
     long long nblocks = 0;
     int nthreads = 0;
-    int gen_threads = 0;        // launch width of the generic kernel for this step
+    int gen_threads = 0;        // launch shape of the generic kernel for this step (fallback when
+    PassParams gen_pp;          // the arrays given to execute are not vector-aligned)
+    long long gen_nblocks = 0;
     size_t smem = 0;
     int fast_id = -1;           // >= 0: specialised tile kernel
     std::vector<LDim> outer;    // extra line dims looped on the host

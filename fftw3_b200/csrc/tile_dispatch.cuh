@@ -1,0 +1,122 @@
+// csrc/tile_dispatch.cuh -- table of instantiated tile kernels and the rule that picks one
+// for a step (the "selector over kernel configurations" for the hot geometries).
+#pragma once
+#include "tile_kernel.cuh"
+
+struct TileEntry {
+    int n, e, mode, epi, c, threads;
+    size_t smem;
+    int (*launch)(const PassParams &, const real_t *, real_t *, long long, long long, int, size_t, b2::stream_t);
+    void (*init)();
+};
+
+template <int N, int E, int MODE, bool EPI, int C>
+struct TileInst {
+    static constexpr int THREADS = C * (N / E);
+    static constexpr int MINB = THREADS <= 128 ? 6 : THREADS <= 256 ? 3 : THREADS <= 512 ? 2 : 1;
+    static int launch(const PassParams &p, const real_t *src, real_t *dst, long long b0, long long nb,
+                      int threads, size_t smem, b2::stream_t st) {
+#if B2_CUDA
+        b2_tile_kernel<N, E, MODE, EPI, THREADS, MINB><<<(unsigned)nb, threads, smem, st>>>(p, src, dst, b0);
+        return 0;
+#else
+        (void)st;
+        std::vector<char> sm(smem + 64);
+        for (long long b = 0; b < nb; ++b) TileFFT<N, E, MODE, EPI>::run(p, src, dst, b0 + b, sm.data(), threads);
+        return 0;
+#endif
+    }
+    static void init() {
+#if B2_CUDA
+        cudaFuncSetAttribute(b2_tile_kernel<N, E, MODE, EPI, THREADS, MINB>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)TileFFT<N, E, MODE, EPI>::smem_bytes(C));
+#endif
+    }
+    static TileEntry entry() {
+        return TileEntry{N, E, MODE, EPI ? 1 : 0, C, THREADS, TileFFT<N, E, MODE, EPI>::smem_bytes(C), &launch, &init};
+    }
+};
+
+#define B2_TILE_ALLMODES(N, E, CROW, CCOL)                 \
+    TileInst<N, E, MODE_ROW, false, CROW>::entry(),        \
+    TileInst<N, E, MODE_COL, false, CCOL>::entry(),        \
+    TileInst<N, E, MODE_COL, true, CCOL>::entry(),         \
+    TileInst<N, E, MODE_ROW2COL, false, CCOL>::entry()
+
+inline const std::vector<TileEntry> &b2_tile_table() {
+    static const std::vector<TileEntry> tab = {
+#if defined(FFTW_SINGLE)
+        B2_TILE_ALLMODES(64, 8, 32, 16),
+        B2_TILE_ALLMODES(128, 8, 16, 16),
+        B2_TILE_ALLMODES(256, 16, 16, 16),
+        B2_TILE_ALLMODES(512, 16, 8, 16),
+        B2_TILE_ALLMODES(1024, 16, 4, 16),
+        B2_TILE_ALLMODES(2048, 16, 2, 8),
+        TileInst<4096, 16, MODE_ROW, false, 1>::entry(),
+        TileInst<8192, 16, MODE_ROW, false, 1>::entry(),
+#else
+        B2_TILE_ALLMODES(64, 8, 32, 8),
+        B2_TILE_ALLMODES(128, 8, 16, 8),
+        B2_TILE_ALLMODES(256, 8, 8, 8),
+        B2_TILE_ALLMODES(512, 8, 4, 8),
+        B2_TILE_ALLMODES(1024, 8, 2, 8),
+        TileInst<2048, 8, MODE_ROW, false, 1>::entry(),
+        TileInst<4096, 8, MODE_ROW, false, 1>::entry(),
+#endif
+    };
+    return tab;
+}
+
+inline void b2_init_tile_kernels() {
+    for (const TileEntry &e : b2_tile_table()) e.init();
+}
+
+inline void b2_select_tile_kernel(b2::StepPlan &s) {
+    s.fast_id = -1;
+    if (getenv("FFTW_B200_GENERIC_ONLY")) return;
+    PassParams &p = s.pp;
+    if (s.kind != b2::SK_PASS || p.rmode != RM_C2C || !p.vec_ld || !p.vec_st) return;
+    if ((p.s_axis | p.d_axis) & 1) return;
+    for (int d = 0; d < p.nld; ++d)
+        if ((p.ls[d] | p.ld[d]) & 1) return;
+    for (const b2::LDim &o : s.outer)
+        if ((o.s | o.d) & 1) return;
+    int mode;
+    if (p.s_axis == 2 && p.d_axis == 2)
+        mode = MODE_ROW;
+    else if (p.s_axis != 2 && p.d_axis != 2 && p.ls[0] == 2 && p.ld[0] == 2 && p.ln[0] > 1)
+        mode = MODE_COL;
+    else if (p.s_axis == 2 && p.d_axis != 2 && p.ld[0] == 2 && p.ln[0] > 1)
+        mode = MODE_ROW2COL;
+    else
+        return;
+    const int epi = p.epi_dim >= 0 ? 1 : 0;
+    if (epi && mode != MODE_COL) return;
+    const std::vector<TileEntry> &tab = b2_tile_table();
+    for (size_t i = 0; i < tab.size(); ++i) {
+        const TileEntry &e = tab[i];
+        if (e.n != p.m || e.mode != mode || e.epi != epi) continue;
+        s.fast_id = (int)i;
+        p.C = e.c;
+        p.tiles0 = (p.ln[0] + p.C - 1) / p.C;
+        long long nb = p.tiles0;
+        for (int d = 1; d < p.nld; ++d) nb *= p.ln[d];
+        s.nblocks = nb;
+        s.nthreads = e.threads;
+        s.smem = e.smem;
+        static const char *mn[] = {"row", "col", "row->col"};
+        char buf[256];
+        std::string rs;
+        for (int i2 = 0; i2 < p.npass; ++i2) rs += (i2 ? "x" : "") + std::to_string(p.radix[i2]);
+        snprintf(buf, sizeof buf, "c2c n=%d tile-kernel[%s%s] E=%d regs-resident, tile=%dx%d ctas=%lld threads=%d smem=%zuB",
+                 p.m, mn[mode], epi ? "+twiddle" : "", e.e, p.C, p.m, nb, e.threads, e.smem);
+        s.desc = buf;
+        return;
+    }
+}
+
+inline int b2_launch_tile_kernel(int id, const PassParams &p, const real_t *src, real_t *dst, long long b0,
+                                 long long nb, int threads, size_t smem, b2::stream_t st) {
+    return b2_tile_table()[id].launch(p, src, dst, b0, nb, threads, smem, st);
+}

@@ -1,11 +1,268 @@
-// csrc/tile_kernel.cuh -- specialised register-resident tile kernels for the hot geometries
-// (selected per step by b2_select_tile_kernel; anything not matched runs the generic kernel).
+// csrc/tile_kernel.cuh -- specialised tile kernels for power-of-two lengths: the hot path.
+//
+// One CTA transforms a tile of C lines of N points.  Each thread keeps E points of one line
+// in registers across ALL radix passes (compile-time schedule, radices <= E); between passes
+// the points are exchanged through padded shared memory (Stockham auto-sort), the first pass
+// reads global memory straight into registers and the last pass writes registers straight
+// back, so a line costs exactly one HBM read and one HBM write however many radix passes it
+// needs.  Twiddles: one accurate table value per butterfly (fp64-generated, rounded once),
+// the other R-2 by a short product tree.
+//
+//   MODE_ROW     lines contiguous in src and dst (batched 1-D, last axis of N-D)
+//   MODE_COL     lines strided, neighbouring lines contiguous (other axes of N-D, four-step
+//                pass A): a warp walks C neighbouring lines -> C*sizeof(complex) segments
+//   MODE_ROW2COL contiguous lines in, transposed out (four-step pass B)
+//
+// These replace the reference's twiddle codelets t1*/t2*/t3* and q1* (fftw/dft_simd/common/
+// t3fv_32.c:482, q1fv_8.c:542; drivers dftw_direct_apply fftw/fftw_api.c:2315-2324,
+// dftw_directsq_apply :2613) and leaf codelets n1*/n2* (n1fv_128.c:1851; direct_apply :3183).
+// Anything these kernels do not cover runs in the generic kernel (generic_kernel.cuh).
 #pragma once
+#include "butterfly.cuh"
 #include "plan_build.h"
 
-inline void b2_select_tile_kernel(b2::StepPlan &s) { s.fast_id = -1; }
-inline void b2_init_tile_kernels() {}
-inline int b2_launch_tile_kernel(int, const PassParams &, const real_t *, real_t *, long long, long long,
-                                 int, size_t, b2::stream_t) {
-    return -1;
+enum { MODE_ROW = 0, MODE_COL = 1, MODE_ROW2COL = 2 };
+
+constexpr int b2_ilog2(int v) { return v <= 1 ? 0 : 1 + b2_ilog2(v / 2); }
+
+template <int N, int E> struct TileSched {
+    static constexpr int LOGN = b2_ilog2(N), LOGE = b2_ilog2(E);
+    static constexpr int NP = (LOGN + LOGE - 1) / LOGE;
+    static constexpr int bits(int i) { return (LOGN + (NP - 1 - i)) / NP; }
+    static constexpr int radix(int i) { return 1 << bits(i); }
+    static constexpr int ns(int i) { return i == 0 ? 1 : ns(i - 1) * radix(i - 1); }
+};
+
+#if B2_CUDA
+#define B2_TREGS(ctx) (ctx.vbase)
+#else
+#define B2_TREGS(ctx) (ctx.vbase + (size_t)tid * E)
+#endif
+
+struct TileCtx {
+    const PassParams *p;
+    const real_t *src;
+    real_t *dst;
+    cpx_t *sm;
+    cpx_t *vbase;
+    long long l0;         // first line of the tile along the tile dim
+    long long sbase, dbase;
+    int nlines;
+    int i2base;
+    int nthreads;
+};
+
+template <int PADSHIFT> B2_HD int b2_pad(int o) { return o + (o >> PADSHIFT); }
+
+// w[k] = w1^k, k = 1..R-1, by a product tree of depth <= log2(R)
+template <int R> B2_D void b2_twiddle_powers(cpx_t w1, cpx_t *w) {
+    w[1] = w1;
+#pragma unroll
+    for (int k = 2; k < R; ++k) {
+        if ((k & 1) == 0)
+            w[k] = cmul(w[k / 2], w[k / 2]);
+        else
+            w[k] = cmul(w[k - 1], w1);
+    }
 }
+
+template <int N, int E, int MODE, bool EPI> struct TileFFT {
+    typedef TileSched<N, E> S;
+    static constexpr int T = N / E;  // threads per line
+    static constexpr int PADSHIFT = sizeof(real_t) == 4 ? 4 : 3;
+    static constexpr bool COLMAP = (MODE == MODE_COL);
+    // smem line stride (complex): row-mapped passes pad inside the line; any kernel that walks
+    // neighbouring lines with neighbouring lanes needs an odd stride
+    static constexpr int LSRAW = COLMAP ? N : (N + (N >> PADSHIFT));
+    static constexpr int LS = (MODE == MODE_ROW) ? LSRAW : (LSRAW | 1);
+
+    static B2_HD int phys(int o) { return COLMAP ? o : b2_pad<PADSHIFT>(o); }
+    static B2_HD size_t smem_bytes(int C) { return (size_t)C * LS * sizeof(cpx_t); }
+
+    // thread -> (line c, slot t)
+    static B2_HD void map(int tid, int C, int &c, int &t) {
+        if (COLMAP) {
+            c = tid % C;
+            t = tid / C;
+        } else {
+            c = tid / T;
+            t = tid - c * T;
+        }
+    }
+
+    template <int P> static B2_D void butterflies(const TileCtx &x, cpx_t *v, int c, int t, bool active) {
+        constexpr int R = S::radix(P), NS = S::ns(P), NB = E / R;
+        constexpr bool LAST = (P == S::NP - 1);
+        const cpx_t *tw = x.p->tw;
+        cpx_t *line = x.sm + (size_t)c * LS;
+#pragma unroll
+        for (int m = 0; m < NB; ++m) {
+            const int j = t + m * T;
+            cpx_t a[R];
+#pragma unroll
+            for (int k = 0; k < R; ++k) a[k] = v[m + k * NB];
+            const int jm = j & (NS - 1);
+            if (NS > 1) {
+                cpx_t w[R];
+                b2_twiddle_powers<R>(tw[jm * (N / (NS * R))], w);
+#pragma unroll
+                for (int k = 1; k < R; ++k) a[k] = cmul(a[k], w[k]);
+            }
+            Bf<R, real_t>::run(a);
+            if (LAST) {
+#pragma unroll
+                for (int k = 0; k < R; ++k) v[m + k * NB] = a[k];
+            } else if (active) {
+                const int o = (j - jm) * R + jm;  // (j / NS) * NS * R + jm
+#pragma unroll
+                for (int k = 0; k < R; ++k) line[phys(o + k * NS)] = a[k];
+            }
+        }
+    }
+
+    template <int P> static B2_D void passes_from(TileCtx &x) {
+        // exchange: everybody has written pass P-1's outputs; read this pass's inputs
+        const int b2_nthreads = x.nthreads;
+        (void)b2_nthreads;
+        B2_SYNC();
+        B2_FOR_THREADS {
+            cpx_t *v = B2_TREGS(x);
+            int c, t;
+            map(tid, x.p->C, c, t);
+            const cpx_t *line = x.sm + (size_t)c * LS;
+#pragma unroll
+            for (int q = 0; q < E; ++q) v[q] = line[phys(t + q * T)];
+        }
+        if (P < S::NP - 1) B2_SYNC();  // the next write must not overtake a neighbour's read
+        B2_FOR_THREADS {
+            cpx_t *v = B2_TREGS(x);
+            int c, t;
+            map(tid, x.p->C, c, t);
+            butterflies<P>(x, v, c, t, true);
+        }
+        if constexpr (P + 1 < S::NP) passes_from<P + 1>(x);
+    }
+
+    static B2_D void run(const PassParams &p, const real_t *B2_RESTRICT src, real_t *B2_RESTRICT dst,
+                         long long bid, char *smem, int b2_nthreads) {
+        (void)b2_nthreads;
+        TileCtx x;
+        x.p = &p;
+        x.src = src;
+        x.dst = dst;
+        x.sm = reinterpret_cast<cpx_t *>(smem);
+        x.nthreads = B2_NTHREADS;
+        B2_REGS(cpx_t, vreg, E);
+#if B2_CUDA
+        x.vbase = vreg;
+#else
+        x.vbase = vreg_store.data();
+#endif
+        const int C = p.C;
+        const long long t0 = bid % p.tiles0;
+        long long rest = bid / p.tiles0;
+        x.l0 = t0 * C;
+        x.nlines = (int)((p.ln[0] - x.l0 < C) ? (p.ln[0] - x.l0) : C);
+        x.sbase = 0;
+        x.dbase = 0;
+        x.i2base = 0;
+        for (int d = 1; d < p.nld; ++d) {
+            const long long cc = rest % p.ln[d];
+            rest /= p.ln[d];
+            x.sbase += cc * p.ls[d];
+            x.dbase += cc * p.ld[d];
+            if (d == p.epi_dim) x.i2base = (int)cc;
+        }
+        const cpx_t *csrc = reinterpret_cast<const cpx_t *>(src);
+        cpx_t *cdst = reinterpret_cast<cpx_t *>(dst);
+
+        // ---- load (global -> registers) + first radix pass ----
+        B2_FOR_THREADS {
+            cpx_t *v = B2_TREGS(x);
+            int c, t;
+            map(tid, C, c, t);
+            const bool active = c < x.nlines;
+            if (active) {
+                // all strides are in reals and even here (vector access was checked by the selector)
+                const long long base = (x.sbase + (x.l0 + c) * p.ls[0]) / 2;
+                const long long as = p.s_axis / 2;
+#pragma unroll
+                for (int q = 0; q < E; ++q) {
+                    cpx_t a = csrc[base + (long long)(t + q * T) * as];
+                    v[q] = p.swap_in ? cswap(a) : a;
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < E; ++q) v[q] = cpx_t{0, 0};
+            }
+            butterflies<0>(x, v, c, t, active);
+        }
+        if constexpr (S::NP > 1) passes_from<1>(x);
+
+        // ---- store (registers -> global), v[q] holds output index t + q*T ----
+        if (MODE != MODE_ROW2COL) {
+            B2_FOR_THREADS {
+                cpx_t *v = B2_TREGS(x);
+                int c, t;
+                map(tid, C, c, t);
+                if (c < x.nlines) {
+                    const long long base = (x.dbase + (x.l0 + c) * p.ld[0]) / 2;
+                    const long long ds = p.d_axis / 2;
+                    if (EPI) {
+                        // w_Nbig^(i2*k), k = t + q*T: base * step^q, both from the two-level table
+                        const unsigned long long i2 = (p.epi_dim == 0) ? (unsigned long long)(x.l0 + c)
+                                                                       : (unsigned long long)x.i2base;
+                        const unsigned long long mask = (1ull << p.epi_shift) - 1;
+                        const unsigned long long e0 = i2 * (unsigned long long)t, e1 = i2 * (unsigned long long)T;
+                        const cpx_t wb = cmul(p.epi_hi[e0 >> p.epi_shift], p.epi_lo[e0 & mask]);
+                        const cpx_t ws = cmul(p.epi_hi[e1 >> p.epi_shift], p.epi_lo[e1 & mask]);
+                        cpx_t wq[E];
+                        wq[0] = cpx_t{1, 0};
+                        b2_twiddle_powers<E>(ws, wq);
+#pragma unroll
+                        for (int q = 0; q < E; ++q) v[q] = cmul(v[q], q ? cmul(wb, wq[q]) : wb);
+                    }
+#pragma unroll
+                    for (int q = 0; q < E; ++q) {
+                        cpx_t a = p.swap_out ? cswap(v[q]) : v[q];
+                        cdst[base + (long long)(t + q * T) * ds] = a;
+                    }
+                }
+            }
+        } else {
+            // transposed exit: through shared memory, then neighbouring lanes walk the lines
+            B2_SYNC();
+            B2_FOR_THREADS {
+                cpx_t *v = B2_TREGS(x);
+                int c, t;
+                map(tid, C, c, t);
+                cpx_t *line = x.sm + (size_t)c * LS;
+#pragma unroll
+                for (int q = 0; q < E; ++q) line[phys(t + q * T)] = v[q];
+            }
+            B2_SYNC();
+            B2_FOR_THREADS {
+                const int nl = x.nlines;
+                const long long ds = p.d_axis / 2;
+                const long long base = (x.dbase + x.l0 * p.ld[0]) / 2;
+                const long long lstep = p.ld[0] / 2;
+                for (int idx = tid; idx < nl * N; idx += B2_NTHREADS) {
+                    const int k = idx / nl, c = idx - k * nl;
+                    cpx_t a = x.sm[(size_t)c * LS + phys(k)];
+                    if (p.swap_out) a = cswap(a);
+                    cdst[base + (long long)c * lstep + (long long)k * ds] = a;
+                }
+            }
+        }
+    }
+};
+
+#if B2_CUDA
+template <int N, int E, int MODE, bool EPI, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB)
+    b2_tile_kernel(const __grid_constant__ PassParams p, const real_t *B2_RESTRICT src,
+                   real_t *B2_RESTRICT dst, long long bid0) {
+    extern __shared__ __align__(16) char b2_smem[];
+    TileFFT<N, E, MODE, EPI>::run(p, src, dst, bid0 + blockIdx.x, b2_smem, blockDim.x);
+}
+#endif
