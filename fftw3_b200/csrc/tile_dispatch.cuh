@@ -3,6 +3,9 @@
 #pragma once
 #include "tile_kernel.cuh"
 
+#ifndef B2_MINB256
+#define B2_MINB256 4
+#endif
 struct TileEntry {
     int n, e, mode, epi, c, threads;
     size_t smem;
@@ -13,7 +16,7 @@ struct TileEntry {
 template <int N, int E, int MODE, bool EPI, int C>
 struct TileInst {
     static constexpr int THREADS = C * (N / E);
-    static constexpr int MINB = THREADS <= 128 ? 6 : THREADS <= 256 ? 3 : THREADS <= 512 ? 2 : 1;
+    static constexpr int MINB = THREADS <= 128 ? 6 : THREADS <= 256 ? B2_MINB256 : THREADS <= 512 ? 2 : 1;
     static int launch(const PassParams &p, const real_t *src, real_t *dst, long long b0, long long nb,
                       int threads, size_t smem, b2::stream_t st) {
 #if B2_CUDA

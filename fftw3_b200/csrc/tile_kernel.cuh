@@ -77,6 +77,15 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
     static constexpr int LS = (MODE == MODE_ROW) ? LSRAW : (LSRAW | 1);
 
     static B2_HD int phys(int o) { return COLMAP ? o : b2_pad<PADSHIFT>(o); }
+    // phys(o + k*STEP) for k = 0..: when STEP is a multiple of the padding period (or the whole
+    // run stays inside one period) the padding separates and k*STEP' becomes an immediate offset
+    template <int STEP, int SPAN> static B2_HD int phys_k(int o, int po, int k) {
+        constexpr int PER = 1 << PADSHIFT;
+        if (COLMAP) return o + k * STEP;
+        if (STEP % PER == 0) return po + k * (STEP + STEP / PER);
+        if (SPAN > 0 && STEP * SPAN <= PER && (PER % (STEP * (SPAN > 0 ? SPAN : 1))) == 0) return po + k * STEP;  // o is a multiple of STEP*SPAN
+        return b2_pad<PADSHIFT>(o + k * STEP);
+    }
     static B2_HD size_t smem_bytes(int C) { return (size_t)C * LS * sizeof(cpx_t); }
 
     // thread -> (line c, slot t)
@@ -114,8 +123,9 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
                 for (int k = 0; k < R; ++k) v[m + k * NB] = a[k];
             } else if (active) {
                 const int o = (j - jm) * R + jm;  // (j / NS) * NS * R + jm
+                const int po = phys(o);
 #pragma unroll
-                for (int k = 0; k < R; ++k) line[phys(o + k * NS)] = a[k];
+                for (int k = 0; k < R; ++k) line[NS == 1 ? phys_k<1, R>(o, po, k) : phys_k<NS, 0>(o, po, k)] = a[k];
             }
         }
     }
@@ -130,8 +140,9 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
             int c, t;
             map(tid, x.p->C, c, t);
             const cpx_t *line = x.sm + (size_t)c * LS;
+            const int pt = phys(t);
 #pragma unroll
-            for (int q = 0; q < E; ++q) v[q] = line[phys(t + q * T)];
+            for (int q = 0; q < E; ++q) v[q] = line[phys_k<T, 0>(t, pt, q)];
         }
         if (P < S::NP - 1) B2_SYNC();  // the next write must not overtake a neighbour's read
         B2_FOR_THREADS {
@@ -237,8 +248,9 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
                 int c, t;
                 map(tid, C, c, t);
                 cpx_t *line = x.sm + (size_t)c * LS;
+                const int pt = phys(t);
 #pragma unroll
-                for (int q = 0; q < E; ++q) line[phys(t + q * T)] = v[q];
+                for (int q = 0; q < E; ++q) line[phys_k<T, 0>(t, pt, q)] = v[q];
             }
             B2_SYNC();
             B2_FOR_THREADS {
