@@ -44,6 +44,11 @@ WORKLOADS = {
     "c2r_1d_1048576x256_fp32": dict(kind="c2r", n=[1 << 20], howmany=256, prec="fp32"),
     "c2c_3d_512_fp32": dict(kind="c2c", n=[512, 512, 512], howmany=1, prec="fp32"),
     "c2c_3d_512_fp32_inplace": dict(kind="c2c", n=[512, 512, 512], howmany=1, prec="fp32", inplace=True),
+    # slab-distributed 3-D (fftw_mpi_plan_dft_3d, FFTW_MPI_TRANSPOSED_OUT): the WHOLE cube is split
+    # over the ranks (strong scaling); 2048^3 needs >= 2 GPUs
+    "c2c_3d_2048_slab_fp32": dict(kind="slab", n=[2048, 2048, 2048], howmany=1, prec="fp32"),
+    "c2c_3d_1024_slab_fp32": dict(kind="slab", n=[1024, 1024, 1024], howmany=1, prec="fp32"),
+    "c2c_3d_512_slab_fp32": dict(kind="slab", n=[512, 512, 512], howmany=1, prec="fp32"),
 }
 DEFAULT_WORKLOAD = "c2c_1d_4096x65536_fp32"
 
@@ -53,7 +58,7 @@ def workload_numbers(w):
     N = int(np.prod(w["n"]))
     hm = w["howmany"]
     rb = 4 if w["prec"] == "fp32" else 8
-    if w["kind"] == "c2c":
+    if w["kind"] in ("c2c", "slab"):
         flops = 5.0 * N * math.log2(N) * hm
         nbytes = 2.0 * N * hm * 2 * rb
     else:
@@ -153,7 +158,7 @@ def run_reference(w, steps, warmup, threads=None, measure=True):
     flags = capi.FFTW_MEASURE if measure else capi.FFTW_ESTIMATE
     lib.lib.fftw_set_timelimit.argtypes = [C.c_double]
     lib.lib.fftw_set_timelimit(20.0)
-    if w["kind"] == "c2c":
+    if w["kind"] in ("c2c", "slab"):
         x = np.zeros((hm, N), dtype=lib.cplx)
         y = x if w.get("inplace") else np.zeros_like(x)
         p = lib.plan_many_dft(n, hm, x, None, 1, N, y, None, 1, N, capi.FFTW_FORWARD, flags)
@@ -367,6 +372,106 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+def run_slab(args):
+    """3-D c2c split over the ranks by slabs: local 2-D FFTs, NCCL all-to-all, 1-D FFTs"""
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    w = WORKLOADS[args.workload]
+    lib = engine_lib(w["prec"])
+    L = lib.lib
+    L.b2fft_set_device(local)
+    L.fftw_mpi_comm_from_nccl.restype = C.c_void_p
+    L.fftw_mpi_comm_from_nccl.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    L.fftw_mpi_comm_self.restype = C.c_void_p
+    L.fftw_mpi_plan_dft_3d.restype = C.c_void_p
+    L.fftw_mpi_plan_dft_3d.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] * 3 + [C.c_int, C.c_uint]
+    L.fftw_mpi_local_size_3d_transposed.restype = C.c_ssize_t
+    L.fftw_mpi_local_size_3d_transposed.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] + [C.POINTER(C.c_ssize_t)] * 4
+    L.b2fft_slab_last_times.argtypes = [C.c_void_p] + [C.POINTER(C.c_float)] * 3
+    if world > 1:
+        idt = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            buf = (C.c_char * 128)()
+            assert L.fftw_mpi_nccl_unique_id(buf) == 0, L.b2fft_last_error()
+            idt = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
+        idt = idt.cuda()
+        dist.broadcast(idt, 0)
+        idb = bytes(idt.cpu().numpy().tobytes())
+        comm = L.fftw_mpi_comm_from_nccl(idb, world, rank)
+    else:
+        comm = L.fftw_mpi_comm_self()
+    assert comm, L.b2fft_last_error()
+    n0, n1, n2 = w["n"]
+    v = [C.c_ssize_t() for _ in range(4)]
+    nalloc = L.fftw_mpi_local_size_3d_transposed(n0, n1, n2, comm, *[C.byref(t) for t in v])
+    ln0, s0, ln1, s1 = (t.value for t in v)
+    g = torch.Generator(device="cuda").manual_seed(1 + rank)
+    x = torch.view_as_complex(torch.rand((nalloc, 2), device="cuda", dtype=torch.float32, generator=g) - 0.5)
+    y = torch.empty_like(x)
+    plan = L.fftw_mpi_plan_dft_3d(n0, n1, n2, x.data_ptr(), y.data_ptr(), comm, capi.FFTW_FORWARD,
+                                  capi.FFTW_ESTIMATE | (1 << 30))
+    assert plan, L.b2fft_last_error()
+    bp = fftw_plan_bp(plan)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        lib.execute(plan)
+    barrier()
+    l0 = L.b2fft_launch_count()
+    stage = np.zeros(3)
+    with ClockSampler(local) as clk:
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            lib.execute(plan)  # synchronous on the plan's streams
+            a, b, c = C.c_float(), C.c_float(), C.c_float()
+            L.b2fft_slab_last_times(bp, C.byref(a), C.byref(b), C.byref(c))
+            stage += (a.value, b.value, c.value)
+        barrier()
+        dt = (time.perf_counter() - t0) / args.steps
+    launches = int(L.b2fft_launch_count() - l0)
+    stage /= args.steps
+    if world > 1:
+        t = torch.tensor([dt, *stage], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt, stage = float(t[0]), t[1:].cpu().numpy()
+    flops, nbytes = workload_numbers(w)
+    peak, peak_src = measured_peak_gbs()
+    sent = (n0 * n1 * n2 * 8 / world) * (world - 1) / world  # bytes each GPU sends
+    if rank == 0:
+        line = {
+            "metric": "FFTW-convention GFLOP/s (5 N log2 N / t), fftw_mpi_plan_dft_3d + fftw_execute",
+            "value": flops / dt / 1e9, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic uniform[-0.5,0.5)",
+            "config": {"workload": args.workload, "n": w["n"], "layout": "FFTW_MPI_TRANSPOSED_OUT, slabs over n0",
+                       "timing": "host clock around synchronous fftw_execute, barrier + max over ranks",
+                       "stage_ms": {"local_2d_ffts": float(stage[0]), "exposed_exchange": float(stage[1]),
+                                    "final_1d_ffts": float(stage[2])}},
+            "roofline": {"bound": "hbm", "achieved": nbytes / world / dt / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": nbytes / world / dt / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                         "note": "per GPU: algorithmic bytes of its slab / whole step",
+                         "nvlink_bytes_sent_per_gpu": sent,
+                         "nvlink_min_ms_at_770GBs": sent / 770e9 * 1e3},
+            "clocks": clk.summary(), "gpu_launches": launches,
+            "plan": lib.sprint_plan(plan).strip().split("\n"),
+        }
+        print(json.dumps(line))
+    lib.destroy_plan(plan)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
@@ -401,6 +506,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
+    elif WORKLOADS[args.workload]["kind"] == "slab":
+        run_slab(args)
     else:
         run_gpu(args)
 

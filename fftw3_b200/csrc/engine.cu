@@ -8,23 +8,11 @@
 #include "b200fft.h"
 #include "generic_kernel.cuh"
 #include "plan_build_real.h"
+#include "plan_struct.h"
 #include "realpp_kernel.cuh"
 #include "tile_dispatch.cuh"
 
 using namespace b2;
-
-struct b2fft_plan_s {
-    PlanCore pc;
-    real_t *scr = nullptr;
-    // device staging for host-pointer executes (allocated on first use)
-    real_t *dev_in = nullptr, *dev_out = nullptr;
-    stream_t stream = nullptr;
-    bool own_stream = false;
-    struct SlabPlan *slab = nullptr;
-};
-
-void b2_slab_destroy(b2fft_plan *p);
-int b2_slab_execute(b2fft_plan *p, void *in, void *out);
 
 // ------------------------------------------------------------------------- launching
 static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream_t stream) {

@@ -12,12 +12,7 @@
 #include "b200fft.h"
 #include "fftw3.h"
 
-struct fftw_plan_s {
-    b2fft_plan *bp;
-    void *in, *out; /* the arrays given at plan time (reference: problem_dft.ri.., api.h:1874) */
-    int kind;
-    b2fft_geom g;
-};
+#include "fftw_plan_struct.h"
 
 const char fftw_version[] = "b200fft-0.1 (fftw3.h ABI, sm_100a)";
 const char fftw_cc[] = "nvcc -gencode arch=compute_100a,code=sm_100a";

@@ -1,0 +1,70 @@
+/* csrc/fftw_mpi_api.c -- plain-C host side of the slab-distributed interface: the subset of
+ * the reference's fftw/mpi/api.c named by the hot path (fftw_mpi_plan_dft_3d :638-645 ->
+ * plan_many_dft :592 -> plan_guru_dft :560-590; local sizes :494-516; execute decl
+ * fftw3-mpi.h:192), with MPI_Comm standing for an NCCL communicator (include/fftw3-mpi.h).
+ */
+#include <stdlib.h>
+#include <string.h>
+
+#include "fftw3-mpi.h"
+#include "fftw_plan_struct.h"
+
+void fftw_mpi_init(void) {}
+void fftw_mpi_cleanup(void) { fftw_cleanup(); }
+
+ptrdiff_t fftw_mpi_local_size_3d_transposed(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, MPI_Comm comm,
+                                            ptrdiff_t *local_n0, ptrdiff_t *local_0_start,
+                                            ptrdiff_t *local_n1, ptrdiff_t *local_1_start) {
+    return b2fft_slab_local_size_3d_transposed(n0, n1, n2, b2fft_comm_size(comm), b2fft_comm_rank(comm), local_n0,
+                                               local_0_start, local_n1, local_1_start);
+}
+ptrdiff_t fftw_mpi_local_size_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, MPI_Comm comm, ptrdiff_t *local_n0,
+                                 ptrdiff_t *local_0_start) {
+    ptrdiff_t a, b;
+    return fftw_mpi_local_size_3d_transposed(n0, n1, n2, comm, local_n0, local_0_start, &a, &b);
+}
+
+fftw_plan fftw_mpi_plan_many_dft(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block, ptrdiff_t tblock,
+                                 FFTW_COMPLEX *in, FFTW_COMPLEX *out, MPI_Comm comm, int sign, unsigned flags) {
+    fftw_plan p;
+    b2fft_plan *bp;
+    int P;
+    if (rnk != 3 || !n || !comm) return 0; /* the slab path is 3-D */
+    P = b2fft_comm_size(comm);
+    /* only the default ceil(n/P) blocks (FFTW_MPI_DEFAULT_BLOCK, or the same value spelled out) */
+    if (block != FFTW_MPI_DEFAULT_BLOCK && block != (n[0] + P - 1) / P) return 0;
+    if (tblock != FFTW_MPI_DEFAULT_BLOCK && tblock != (n[1] + P - 1) / P) return 0;
+    /* more blocks than ranks cannot be distributed (reference fftw/mpi/api.c:578-582) */
+    bp = b2fft_slab_plan_dft_3d(n[0], n[1], n[2], howmany, comm, sign, (flags & FFTW_MPI_TRANSPOSED_IN) != 0,
+                                (flags & FFTW_MPI_TRANSPOSED_OUT) != 0, flags);
+    if (!bp) return 0;
+    p = (fftw_plan)malloc(sizeof *p);
+    if (!p) {
+        b2fft_plan_destroy(bp);
+        return 0;
+    }
+    memset(p, 0, sizeof *p);
+    p->bp = bp;
+    p->in = in;
+    p->out = out;
+    p->kind = B2FFT_C2C;
+    return p;
+}
+
+fftw_plan fftw_mpi_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_COMPLEX *in, FFTW_COMPLEX *out,
+                               MPI_Comm comm, int sign, unsigned flags) {
+    ptrdiff_t n[3];
+    n[0] = n0;
+    n[1] = n1;
+    n[2] = n2;
+    return fftw_mpi_plan_many_dft(3, n, 1, FFTW_MPI_DEFAULT_BLOCK, FFTW_MPI_DEFAULT_BLOCK, in, out, comm, sign, flags);
+}
+
+void fftw_mpi_execute_dft(fftw_plan p, FFTW_COMPLEX *in, FFTW_COMPLEX *out) { fftw_execute_dft(p, in, out); }
+
+int fftw_mpi_nccl_unique_id(void *id128) { return b2fft_nccl_unique_id(id128); }
+MPI_Comm fftw_mpi_comm_from_nccl(const void *id128, int n_pes, int my_pe) {
+    return b2fft_comm_create(id128, n_pes, my_pe);
+}
+MPI_Comm fftw_mpi_comm_self(void) { return b2fft_comm_self(); }
+void fftw_mpi_comm_free(MPI_Comm comm) { b2fft_comm_destroy(comm); }

@@ -99,6 +99,13 @@ int         b2fft_comm_size(const b2fft_comm *c);
 b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
                                    b2fft_comm *c, int sign, int transposed_in,
                                    int transposed_out, unsigned flags);
+/* Staged execution, for callers that bring their own transport and for the CPU tests of the
+ * multi-rank path: stage 0 local (n1 x n2) FFTs in -> send buffer; 1 exchange (NCCL); 2 length-n0
+ * FFTs recv buffer -> out; 3 (natural-order output only) exchange back.  b2fft_slab_buffer returns
+ * the send (0) / receive (1) buffer.  b2fft_comm_detached carries (rank, size) without NCCL. */
+int         b2fft_slab_stage(b2fft_plan *p, int stage, void *in, void *out);
+void       *b2fft_slab_buffer(b2fft_plan *p, int which, size_t *bytes);
+b2fft_comm *b2fft_comm_detached(int n_pes, int my_pe);
 /* device time (ms) of the last slab execute split into local FFT / exchange / local FFT */
 int b2fft_slab_last_times(const b2fft_plan *p, float *ms_fft1, float *ms_exchange, float *ms_fft2);
 

@@ -1,0 +1,54 @@
+"""GPU tests of the slab-distributed 3-D transform: one rank (self communicator, device arrays)
+and, when the box has >= 2 GPUs, 2 ranks over NCCL (tests/slab_nccl_worker.py under torchrun)."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from fftw3_b200 import build, capi
+from oracle import pyoracle as orc
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp64"])
+@pytest.mark.parametrize("transposed", [True, False])
+def test_single_rank_device_arrays(prec, transposed):
+    import torch
+    lib = capi.FFTW3Lib(build.lib_path(prec), prec == "fp32")
+    L = lib.lib
+    L.fftw_mpi_comm_self.restype = C.c_void_p
+    L.fftw_mpi_plan_dft_3d.restype = C.c_void_p
+    L.fftw_mpi_plan_dft_3d.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] * 3 + [C.c_int, C.c_uint]
+    comm = L.fftw_mpi_comm_self()
+    shape = (64, 48, 32)
+    rng = np.random.default_rng(3)
+    xh = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
+    x = torch.from_numpy(xh).cuda()
+    y = torch.zeros_like(x)
+    plan = L.fftw_mpi_plan_dft_3d(*shape, x.data_ptr(), y.data_ptr(), comm, -1,
+                                  capi.FFTW_ESTIMATE | ((1 << 30) if transposed else 0))
+    assert plan
+    lib.execute(plan)
+    torch.cuda.synchronize()
+    ref = orc.mpi_dft_3d_local(xh, 1, 0, transposed_out=transposed)
+    got = y.cpu().numpy().reshape(ref.shape)
+    tol = (1e-6 if lib.single else 1e-14) * np.log2(np.prod(shape))
+    assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < tol
+    lib.destroy_plan(plan)
+
+
+@pytest.mark.parametrize("shape", [(48, 40, 32), (50, 30, 16)], ids=lambda s: "x".join(map(str, s)))
+def test_two_ranks_over_nccl(shape):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(29700 + os.getpid() % 200),
+           os.path.join(ROOT, "tests", "slab_nccl_worker.py"), *map(str, shape)]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "SLAB_OK" in r.stdout, r.stdout[-3000:]

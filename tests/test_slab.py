@@ -1,0 +1,186 @@
+"""Slab-distributed 3-D c2c (the fftw_mpi_plan_dft_3d form): geometry, message layout and the
+two local FFT stages, checked on the CPU.
+
+The product exchanges over NCCL, which needs GPUs; here the ranks run the TEST-ONLY emulation
+build with "detached" communicators (rank, size only) and the test moves the messages itself:
+in one process for P = 1..8 (ragged block sizes, empty ranks), and between two real processes
+over torch.distributed/gloo.  The expected result is the reference's own definition of the
+distributed transform: the serial DFT, redistributed (fftw/mpi/mpi-bench.c:236-257;
+oracle_mpi_dft_3d_local)."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from fftw3_b200 import build, capi
+from oracle import pyoracle as orc
+
+TRANSPOSED_OUT = 1 << 30
+
+
+def load(prec="fp64"):
+    lib = capi.FFTW3Lib(build.build_emu(prec), prec == "fp32")
+    L = lib.lib
+    L.b2fft_comm_detached.restype = C.c_void_p
+    L.b2fft_comm_detached.argtypes = [C.c_int, C.c_int]
+    L.b2fft_comm_destroy.argtypes = [C.c_void_p]
+    L.fftw_mpi_plan_dft_3d.restype = C.c_void_p
+    L.fftw_mpi_plan_dft_3d.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] * 3 + [C.c_int, C.c_uint]
+    L.fftw_mpi_local_size_3d_transposed.restype = C.c_ssize_t
+    L.fftw_mpi_local_size_3d_transposed.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] + [C.POINTER(C.c_ssize_t)] * 4
+    L.b2fft_slab_stage.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    L.b2fft_slab_buffer.restype = C.c_void_p
+    L.b2fft_slab_buffer.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_size_t)]
+    return lib
+
+
+def local_sizes(lib, shape, comm):
+    v = [C.c_ssize_t() for _ in range(4)]
+    N = lib.lib.fftw_mpi_local_size_3d_transposed(*shape, comm, *[C.byref(x) for x in v])
+    return (N,) + tuple(x.value for x in v)
+
+
+def buffer_view(lib, plan, which, dtype):
+    nb = C.c_size_t()
+    bp = C.cast(plan, C.POINTER(C.c_void_p))[0]
+    ptr = lib.lib.b2fft_slab_buffer(bp, which, C.byref(nb))
+    return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_byte)), shape=(nb.value,)).view(dtype), bp
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 4, 8])
+@pytest.mark.parametrize("shape", [(8, 6, 4), (10, 6, 5), (16, 16, 16)], ids=lambda s: "x".join(map(str, s)))
+def test_local_sizes_match_the_reference_rule(P, shape):
+    lib = load()
+    for pe in range(P):
+        comm = lib.lib.b2fft_comm_detached(P, pe)
+        assert local_sizes(lib, shape, comm) == orc.mpi_local_size_3d_transposed(*shape, P, pe)
+        lib.lib.b2fft_comm_destroy(comm)
+
+
+@pytest.mark.parametrize("transposed", [True, False], ids=["transposed_out", "natural_out"])
+@pytest.mark.parametrize("P", [1, 2, 3, 4, 8])
+@pytest.mark.parametrize("shape", [(8, 6, 4), (10, 6, 5), (32, 16, 8)], ids=lambda s: "x".join(map(str, s)))
+def test_ranks_simulated_in_one_process(shape, P, transposed):
+    lib = load()
+    n0, n1, n2 = shape
+    rng = np.random.default_rng(P)
+    x = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
+    b0, b1 = -(-n0 // P), -(-n1 // P)
+    ranks = []
+    for pe in range(P):
+        comm = lib.lib.b2fft_comm_detached(P, pe)
+        N, ln0, s0, ln1, s1 = local_sizes(lib, shape, comm)
+        xin = np.zeros(max(N, 1), dtype=lib.cplx)
+        xin[:ln0 * n1 * n2] = x[s0:s0 + ln0].ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = lib.lib.fftw_mpi_plan_dft_3d(n0, n1, n2, xin.ctypes.data, out.ctypes.data, comm, -1,
+                                            capi.FFTW_ESTIMATE | (TRANSPOSED_OUT if transposed else 0))
+        assert plan, "slab plan is NULL"
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        ranks.append(dict(comm=comm, ln0=ln0, s0=s0, ln1=ln1, s1=s1, xin=xin, out=out, plan=plan, bp=bp, S=S, R=R))
+    for r in ranks:
+        assert lib.lib.b2fft_slab_stage(r["bp"], 0, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    # the exchange, spelled out from the documented layout: S = [ln0][n1][n2], R = [n0][ln1][n2]
+    for src in ranks:
+        Sv = src["S"][:src["ln0"] * n1 * n2].reshape(src["ln0"], n1, n2)
+        for dst in ranks:
+            if dst["ln1"] == 0 or src["ln0"] == 0:
+                continue
+            Rv = dst["R"][:n0 * dst["ln1"] * n2].reshape(n0, dst["ln1"], n2)
+            Rv[src["s0"]:src["s0"] + src["ln0"]] = Sv[:, dst["s1"]:dst["s1"] + dst["ln1"], :]
+    for pe, r in enumerate(ranks):
+        assert lib.lib.b2fft_slab_stage(r["bp"], 2, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    if not transposed:  # second exchange, back to [ln0][n1][n2]
+        for src in ranks:
+            if src["ln1"] == 0:
+                continue
+            Rv = src["R"][:n0 * src["ln1"] * n2].reshape(n0, src["ln1"], n2)
+            for dst in ranks:
+                if dst["ln0"] == 0:
+                    continue
+                Ov = dst["out"][:dst["ln0"] * n1 * n2].reshape(dst["ln0"], n1, n2)
+                Ov[:, src["s1"]:src["s1"] + src["ln1"], :] = Rv[dst["s0"]:dst["s0"] + dst["ln0"]]
+    for pe, r in enumerate(ranks):
+        ref = orc.mpi_dft_3d_local(x, P, pe, transposed_out=transposed)
+        got = r["out"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13, (pe, P)
+        lib.destroy_plan(r["plan"])
+        lib.lib.b2fft_comm_destroy(r["comm"])
+
+
+def _gloo_worker(rank, world, port, shape, q):
+    try:
+        import torch
+        import torch.distributed as dist
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        lib = load()
+        n0, n1, n2 = shape
+        rng = np.random.default_rng(5)  # every rank can regenerate the global array
+        x = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
+        comm = lib.lib.b2fft_comm_detached(world, rank)
+        N, ln0, s0, ln1, s1 = local_sizes(lib, shape, comm)
+        xin = np.zeros(max(N, 1), dtype=lib.cplx)
+        xin[:ln0 * n1 * n2] = x[s0:s0 + ln0].ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = lib.lib.fftw_mpi_plan_dft_3d(n0, n1, n2, xin.ctypes.data, out.ctypes.data, comm, -1,
+                                            capi.FFTW_ESTIMATE | TRANSPOSED_OUT)
+        assert plan
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        assert lib.lib.b2fft_slab_stage(bp, 0, xin.ctypes.data, out.ctypes.data) == 0
+        b0, b1 = -(-n0 // world), -(-n1 // world)
+        Sv = S[:ln0 * n1 * n2].reshape(ln0, n1, n2)
+        sends = [torch.from_numpy(np.ascontiguousarray(Sv[:, p * b1:min(n1, (p + 1) * b1), :]).view(np.float64).copy())
+                 for p in range(world)]
+        recvs = [torch.empty((max(0, min(b0, n0 - p * b0)), ln1, n2 * 2), dtype=torch.float64).reshape(-1)
+                 for p in range(world)]
+        sends = [t.reshape(-1) for t in sends]
+        # gloo has no all_to_all: pairwise exchange
+        for p in range(world):
+            if p == rank:
+                recvs[p].copy_(sends[p])
+            elif rank < p:
+                dist.send(sends[p], p)
+                dist.recv(recvs[p], p)
+            else:
+                dist.recv(recvs[p], p)
+                dist.send(sends[p], p)
+        Rv = R[:n0 * ln1 * n2].reshape(n0, ln1, n2)
+        for p in range(world):
+            l0p = max(0, min(b0, n0 - p * b0))
+            if l0p and ln1:
+                Rv[p * b0:p * b0 + l0p] = recvs[p].numpy().view(np.complex128).reshape(l0p, ln1, n2)
+        assert lib.lib.b2fft_slab_stage(bp, 2, xin.ctypes.data, out.ctypes.data) == 0
+        ref = orc.mpi_dft_3d_local(x, world, rank, transposed_out=True)
+        err = np.linalg.norm(out[:ref.size].reshape(ref.shape) - ref) / np.linalg.norm(ref)
+        # and the batch-sharding rule of bench.py: per-rank howmany, whole-job value by max time
+        t = torch.tensor([1.0 + rank])
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.destroy_process_group()
+        q.put((rank, float(err), float(t.item())))
+    except Exception as e:  # pragma: no cover
+        import traceback
+        q.put((rank, "ERR " + traceback.format_exc(), 0.0))
+
+
+def test_two_processes_over_gloo():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, (12, 10, 6), q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, err, tmax in res:
+        assert not isinstance(err, str), err
+        assert err < 1e-13
+        assert tmax == 2.0
