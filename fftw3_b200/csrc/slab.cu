@@ -62,6 +62,8 @@ struct NcclApi {
     int (*CommDestroy)(nccl_comm_t) = nullptr;
     int (*Send)(const void *, size_t, int, int, nccl_comm_t, void *) = nullptr;
     int (*Recv)(void *, size_t, int, int, nccl_comm_t, void *) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, nccl_comm_t, void *) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, nccl_comm_t, void *) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     const char *(*GetErrorString)(int) = nullptr;
@@ -95,6 +97,8 @@ static NcclApi *nccl() {
     B2_NSYM(CommDestroy, "ncclCommDestroy")
     B2_NSYM(Send, "ncclSend")
     B2_NSYM(Recv, "ncclRecv")
+    B2_NSYM(AllGather, "ncclAllGather")
+    B2_NSYM(AllReduce, "ncclAllReduce")
     B2_NSYM(GroupStart, "ncclGroupStart")
     B2_NSYM(GroupEnd, "ncclGroupEnd")
     B2_NSYM(GetErrorString, "ncclGetErrorString")
@@ -199,7 +203,15 @@ struct SlabPlan {
     cudaEvent_t t0 = nullptr, t1 = nullptr, t2 = nullptr, t3 = nullptr;
 #endif
     float ms[3] = {0, 0, 0};
+    // direct peer-memory exchange (CUDA IPC): every rank's S and R mapped into this process
+    bool p2p = false;
+    std::vector<cpx_t *> peerS, peerR;
+    float *flag = nullptr;  // tiny device buffer for the cross-rank barrier
 };
+
+#if B2_CUDA
+static int slab_setup_p2p(SlabPlan &s);
+#endif
 
 static b2fft_plan *make_stage1(const SlabPlan &s, ptrdiff_t planes) {
     if (planes <= 0) return nullptr;
@@ -264,6 +276,14 @@ void b2_slab_destroy(b2fft_plan_s *p) {
     b2fft_plan_destroy(s->p1);
     b2fft_plan_destroy(s->p1_tail);
     b2fft_plan_destroy(s->p2);
+#if B2_CUDA
+    for (int q = 0; q < (int)s->peerS.size(); ++q)
+        if (q != s->pe) {
+            if (s->peerS[q]) cudaIpcCloseMemHandle(s->peerS[q]);
+            if (s->peerR[q]) cudaIpcCloseMemHandle(s->peerR[q]);
+        }
+    if (s->flag) cudaFree(s->flag);
+#endif
     dev_free(s->S);
     dev_free(s->R);
     dev_free(s->dev_in);
@@ -345,6 +365,7 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
         s->ev.resize(s->nchunks + 1);
         for (cudaEvent_t &e : s->ev) ok = ok && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
         for (cudaEvent_t *e : {&s->t0, &s->t1, &s->t2, &s->t3}) ok = ok && cudaEventCreate(e) == cudaSuccess;
+        if (ok) ok = slab_setup_p2p(*s) == 0;
     }
 #endif
     if (!ok) {
@@ -357,10 +378,13 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
     char buf[512];
     snprintf(buf, sizeof buf,
              "  slab 3-D c2c %td x %td x %td over %d ranks (rank %d: planes %td+%td, out rows %td+%td), %s output\n"
-             "  stage 1: %d chunk(s) of %td plane(s), (n1 x n2) FFTs in->send; exchange: ncclSend/Recv per plane and peer\n"
+             "  stage 1: %d chunk(s) of %td plane(s), (n1 x n2) FFTs in->send; exchange: %s\n"
              "  stage 2: length-%td FFTs recv->out\n",
              n0, n1, n2, s->P, s->pe, s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
-             s->nchunks, s->chunk, n0);
+             s->nchunks, s->chunk,
+             s->P == 1 ? "local copy" : s->p2p ? "strided DMA into peer memory (CUDA IPC over NVLink), NCCL barrier"
+                                                : "ncclSend/ncclRecv per plane and peer",
+             n0);
     bp->pc.desc = buf;
     return bp;
 }
@@ -407,6 +431,97 @@ static int slab_exchange(SlabPlan &s, int chunk, cpx_t *sb, cpx_t *rb, bool reve
     return -5;
 #endif
 }
+
+#if B2_CUDA
+// ---- direct exchange through peer memory (CUDA IPC over NVLink) ----------------------------
+// Each rank maps every peer's send/receive buffer once, at plan time.  The exchange of a chunk
+// is then one strided DMA per peer (cudaMemcpy2DAsync straight from the stage-1 output into the
+// peer's receive buffer at its final position): no packing, no SM time, and it overlaps the
+// FFTs of the next chunk.  NCCL is used only for the handle all-gather and as a barrier.
+static int slab_barrier(SlabPlan &s, cudaStream_t st) {
+    if (s.P == 1 || !s.comm->nc) return 0;
+    B2_NCCL(nccl()->AllReduce(s.flag, s.flag, 1, 7, 0, s.comm->nc, st));
+    return 0;
+}
+static int slab_setup_p2p(SlabPlan &s) {
+    s.p2p = false;
+    if (s.P == 1 || !s.comm->nc) return 0;
+    NcclApi *a = nccl();
+    B2_CK(cudaMalloc(&s.flag, 256));
+    B2_CK(cudaMemset(s.flag, 0, 256));
+    struct H {
+        cudaIpcMemHandle_t s, r;
+        int ok;
+    };
+    H mine;
+    memset(&mine, 0, sizeof mine);
+    mine.ok = !getenv("B2FFT_SLAB_SENDRECV") && cudaIpcGetMemHandle(&mine.s, s.S) == cudaSuccess &&
+              cudaIpcGetMemHandle(&mine.r, s.R) == cudaSuccess;
+    cudaGetLastError();
+    H *dev = nullptr;
+    B2_CK(cudaMalloc(&dev, sizeof(H) * s.P));
+    B2_CK(cudaMemcpy(dev + s.pe, &mine, sizeof(H), cudaMemcpyHostToDevice));
+    B2_NCCL(a->AllGather(dev + s.pe, dev, sizeof(H), 0, s.comm->nc, s.sc));
+    B2_CK(cudaStreamSynchronize(s.sc));
+    std::vector<H> all(s.P);
+    B2_CK(cudaMemcpy(all.data(), dev, sizeof(H) * s.P, cudaMemcpyDeviceToHost));
+    cudaFree(dev);
+    bool ok = true;
+    for (int p = 0; p < s.P; ++p) ok = ok && all[p].ok;
+    s.peerS.assign(s.P, nullptr);
+    s.peerR.assign(s.P, nullptr);
+    float good = 1.0f;
+    if (ok)
+        for (int p = 0; p < s.P; ++p) {
+            if (p == s.pe) {
+                s.peerS[p] = s.S;
+                s.peerR[p] = s.R;
+                continue;
+            }
+            if (cudaIpcOpenMemHandle((void **)&s.peerS[p], all[p].s, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+                cudaIpcOpenMemHandle((void **)&s.peerR[p], all[p].r, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                good = 0.0f;
+                break;
+            }
+        }
+    else
+        good = 0.0f;
+    // every rank must take the same path: agree on the minimum
+    float bad = 1.0f - good;
+    B2_CK(cudaMemcpy(s.flag, &bad, sizeof(float), cudaMemcpyHostToDevice));
+    B2_NCCL(a->AllReduce(s.flag, s.flag, 1, 7, 0, s.comm->nc, s.sc));
+    B2_CK(cudaStreamSynchronize(s.sc));
+    B2_CK(cudaMemcpy(&bad, s.flag, sizeof(float), cudaMemcpyDeviceToHost));
+    B2_CK(cudaMemset(s.flag, 0, 256));
+    s.p2p = (bad == 0.0f);
+    return 0;
+}
+static int slab_exchange_p2p(SlabPlan &s, int chunk, bool reverse, cudaStream_t st) {
+    const size_t esz = sizeof(cpx_t);
+    for (int d = 0; d < s.P; ++d) {
+        const int p = (s.pe + d) % s.P;
+        if (!reverse) {
+            // my planes [a,b) of this chunk -> peer p's receive buffer R_p[s0 + i0][*][*]
+            const ptrdiff_t ln1p = blk_len(s.n1, s.b1, p);
+            const ptrdiff_t a = std::min<ptrdiff_t>(s.ln0, chunk * s.chunk), b = std::min<ptrdiff_t>(s.ln0, a + s.chunk);
+            if (ln1p <= 0 || b <= a) continue;
+            B2_CK(cudaMemcpy2DAsync(s.peerR[p] + (size_t)((s.s0 + a) * ln1p) * s.n2, (size_t)ln1p * s.n2 * esz,
+                                    s.S + (size_t)(a * s.n1 + p * s.b1) * s.n2, (size_t)s.n1 * s.n2 * esz,
+                                    (size_t)ln1p * s.n2 * esz, (size_t)(b - a), cudaMemcpyDeviceToDevice, st));
+        } else {
+            // my rows of peer p's planes [a,b) -> peer p's send buffer S_p[i0][s1 + j1][*]
+            const ptrdiff_t ln0p = blk_len(s.n0, s.b0, p);
+            const ptrdiff_t a = std::min<ptrdiff_t>(ln0p, chunk * s.chunk), b = std::min<ptrdiff_t>(ln0p, a + s.chunk);
+            if (s.ln1 <= 0 || b <= a) continue;
+            B2_CK(cudaMemcpy2DAsync(s.peerS[p] + (size_t)(a * s.n1 + s.s1) * s.n2, (size_t)s.n1 * s.n2 * esz,
+                                    s.R + (size_t)((p * s.b0 + a) * s.ln1) * s.n2, (size_t)s.ln1 * s.n2 * esz,
+                                    (size_t)s.ln1 * s.n2 * esz, (size_t)(b - a), cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    return 0;
+}
+#endif
 
 // stage 0: local (n1 x n2) FFTs of chunk k, in -> S
 static int slab_stage1_chunk(SlabPlan &s, int k, cpx_t *in, stream_t st) {
@@ -475,12 +590,22 @@ int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
         dout = s.dev_out;
     }
     B2_CK(cudaEventRecord(s.t0, s.sc));
+    if (s.p2p) {
+        // nobody may still be reading the receive buffer this exchange is about to overwrite
+        int rc = slab_barrier(s, s.sn);
+        if (rc) return rc;
+    }
     for (int k = 0; k < s.nchunks; ++k) {
         int rc = slab_stage1_chunk(s, k, din, s.sc);
         if (rc) return rc;
         B2_CK(cudaEventRecord(s.ev[k], s.sc));
         B2_CK(cudaStreamWaitEvent(s.sn, s.ev[k], 0));
-        rc = slab_exchange(s, k, s.S, s.R, false, s.sn);
+        rc = s.p2p ? slab_exchange_p2p(s, k, false, s.sn) : slab_exchange(s, k, s.S, s.R, false, s.sn);
+        if (rc) return rc;
+    }
+    if (s.p2p) {
+        // all pushes into my receive buffer have landed once every rank has passed this point
+        int rc = slab_barrier(s, s.sn);
         if (rc) return rc;
     }
     B2_CK(cudaEventRecord(s.t1, s.sc));
@@ -491,11 +616,21 @@ int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
         int rc = b2fft_execute_async(s.p2, s.R, s.transposed_out ? (void *)dout : (void *)s.R, s.sc);
         if (rc) return rc;
     }
-    if (!s.transposed_out)
-        for (int k = 0; k < s.nchunks; ++k) {
-            int rc = slab_exchange(s, k, dout, s.R, true, s.sc);
+    if (!s.transposed_out) {
+        if (s.p2p) {
+            for (int k = 0; k < s.nchunks; ++k) {
+                int rc = slab_exchange_p2p(s, k, true, s.sc);
+                if (rc) return rc;
+            }
+            int rc = slab_barrier(s, s.sc);
             if (rc) return rc;
-        }
+            B2_CK(cudaMemcpyAsync(dout, s.S, (size_t)s.ln0 * s.n1 * s.n2 * sizeof(cpx_t), cudaMemcpyDeviceToDevice, s.sc));
+        } else
+            for (int k = 0; k < s.nchunks; ++k) {
+                int rc = slab_exchange(s, k, dout, s.R, true, s.sc);
+                if (rc) return rc;
+            }
+    }
     B2_CK(cudaEventRecord(s.t3, s.sc));
     if (hout) B2_CK(cudaMemcpyAsync(out, dout, out_b, cudaMemcpyDeviceToHost, s.sc));
     B2_CK(cudaStreamSynchronize(s.sc));
