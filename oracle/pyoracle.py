@@ -44,6 +44,19 @@ def build_reference(jobs: int = 8) -> bool:
     return True
 
 
+def build_verifier(jobs: int = 8) -> bool:
+    """Link the reference's own bench/verifier CLI (unmodified objects compiled from
+    /root/reference) against the B200 engine and against the test-only emulation build:
+    oracle/_ref/refbench_{b200,emu}_{f32,f64}.  Needs those libraries to exist already."""
+    names = [f"refbench_{e}_{p}" for e in ("b200", "emu") for p in ("f32", "f64")]
+    if not os.path.isdir(REFERENCE_ROOT):
+        return all(os.path.exists(os.path.join(REF_DIR, n)) for n in names)
+    for prec in ("f64", "f32"):
+        subprocess.check_call(["make", "-s", f"-j{jobs}", f"PREC={prec}", f"REF={REFERENCE_ROOT}", "verifier"],
+                              cwd=os.path.join(HERE, "refbuild"))
+    return True
+
+
 def reference_lib(single: bool):
     """FFTW3Lib bound to the unmodified reference build, or None when it is absent."""
     from fftw3_b200.capi import FFTW3Lib  # generic fftw3.h ctypes binding (no compute)

@@ -1,0 +1,68 @@
+"""The reference's OWN verifier (fftw/libbench2 + fftw/tests/bench.c, compiled unmodified from
+/root/reference by oracle/refbuild/Makefile, target `verifier`) run against the engine.
+
+`bench -y <problem>` performs the property-based self-test of SURVEY.md section 4: impulse and
+constant inputs with closed forms, linearity, time and frequency shift, preserves-input
+(fftw/libbench2/verify-lib.c:260-436), tolerance 1e-3 single / 1e-10 double
+(bench-main.c:70); it exits non-zero on failure.  `bench -a` measures accuracy against its
+160-bit arithmetic (mp.c:609-632).  Problem syntax: i/o = in/out of place, c/r = complex/real,
+f/b = forward/backward, AxBxC dims, *N = howmany (libbench2/problem.c:229-318).
+CPU: the emulation build.  GPU: the product library (host arrays from fftw_malloc)."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref")
+
+PROBLEMS = ["icf1024", "ocf4096", "ocb4096", "orf1024", "orb1024", "irf1024", "icf16x16x16", "ocf64*8",
+            "ib256", "orf30", "ocb100x12", "irf16x10", "obr12x6x4", "ocf13*3", "if7x5x3", "ocf8192",
+            "ocf16384", "orf32768", "ocf64x64x64", "icf256*16", "obr128x64", "ocf3x5x7x2", "ocf1",
+            "orf2", "icb2x2", "ocf1000", "ocf512*12", "ocf2048*3", "irb64x66"]
+
+
+def run(binary, args):
+    path = os.path.join(REF, binary)
+    if not os.path.exists(path):
+        pytest.skip(f"{binary} not built (needs /root/reference once: __graft_entry__.build())")
+    return subprocess.run([path, *args], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+
+
+def check_verify(binary, problem, tol):
+    r = run(binary, ["-v1", "-y", problem])
+    assert r.returncode == 0, r.stdout[-2000:]
+    last = r.stdout.strip().splitlines()[-1].split()
+    assert last[0] == problem, r.stdout
+    errs = [float(v) for v in last[1:4]]  # linearity, impulse, shift
+    assert max(errs) < tol, (problem, errs)
+
+
+@pytest.mark.parametrize("prec,tol", [("f64", 1e-13), ("f32", 1e-5)])
+@pytest.mark.parametrize("problem", PROBLEMS)
+def test_reference_verifier_on_emulation_build(problem, prec, tol):
+    check_verify(f"refbench_emu_{prec}", problem, tol)
+
+
+def test_reference_accuracy_tool_on_emulation_build():
+    r = run("refbench_emu_f64", ["-a", "ocf1024"])
+    assert r.returncode == 0
+    errs = [float(v) for v in r.stdout.split()[-6:]]
+    assert max(errs) < 2e-15  # the reference itself reports 2.0e-16 L2 here
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prec,tol", [("f64", 1e-13), ("f32", 1e-5)])
+@pytest.mark.parametrize("problem", PROBLEMS + ["ocf4096*256", "orf1048576", "ocf128x128x128"])
+def test_reference_verifier_on_b200(problem, prec, tol):
+    check_verify(f"refbench_b200_{prec}", problem, tol)
+
+
+@pytest.mark.gpu
+def test_reference_accuracy_tool_on_b200():
+    r = run("refbench_b200_f64", ["-a", "ocf1024"])
+    assert r.returncode == 0, r.stdout
+    assert max(float(v) for v in r.stdout.split()[-6:]) < 2e-15
+    r = run("refbench_b200_f32", ["-a", "ocf4096"])
+    assert r.returncode == 0, r.stdout
+    assert max(float(v) for v in r.stdout.split()[-6:]) < 2e-6
