@@ -3,7 +3,7 @@
 
 `bench -y <problem>` performs the property-based self-test of SURVEY.md section 4: impulse and
 constant inputs with closed forms, linearity, time and frequency shift, preserves-input
-(fftw/libbench2/verify-lib.c:260-436), tolerance 1e-3 single / 1e-10 double
+(fftw/libbench2/verify-lib.c:260-436), tolerance 1e-3 single / 1e-10 double (here: 1e-4 / 1e-13, relative L-infinity)
 (bench-main.c:70); it exits non-zero on failure.  `bench -a` measures accuracy against its
 160-bit arithmetic (mp.c:609-632).  Problem syntax: i/o = in/out of place, c/r = complex/real,
 f/b = forward/backward, AxBxC dims, *N = howmany (libbench2/problem.c:229-318).
@@ -38,7 +38,7 @@ def check_verify(binary, problem, tol):
     assert max(errs) < tol, (problem, errs)
 
 
-@pytest.mark.parametrize("prec,tol", [("f64", 1e-13), ("f32", 1e-5)])
+@pytest.mark.parametrize("prec,tol", [("f64", 1e-13), ("f32", 1e-4)])
 @pytest.mark.parametrize("problem", PROBLEMS)
 def test_reference_verifier_on_emulation_build(problem, prec, tol):
     check_verify(f"refbench_emu_{prec}", problem, tol)
@@ -52,7 +52,7 @@ def test_reference_accuracy_tool_on_emulation_build():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("prec,tol", [("f64", 1e-13), ("f32", 1e-5)])
+@pytest.mark.parametrize("prec,tol", [("f64", 1e-13), ("f32", 1e-4)])
 @pytest.mark.parametrize("problem", PROBLEMS + ["ocf4096*256", "orf1048576", "ocf128x128x128"])
 def test_reference_verifier_on_b200(problem, prec, tol):
     check_verify(f"refbench_b200_{prec}", problem, tol)
