@@ -92,7 +92,7 @@ inline void *dev_malloc(size_t bytes) {
     return p;
 }
 inline void dev_free(void *p) {
-    if (p) cudaFree(p);
+    if (p && cudaFree(p) != cudaSuccess) cudaGetLastError();  // never leave a stale error behind
 }
 inline int dev_upload(void *dst, const void *src, size_t bytes) {
     B2_CK(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));

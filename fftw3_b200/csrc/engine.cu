@@ -80,6 +80,10 @@ static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
     return 0;
 }
 
+#if B2_CUDA
+static void pipe_destroy(b2fft_plan *p);
+#endif
+
 // ------------------------------------------------------------------------- plan create
 #if B2_CUDA
 static void init_kernel_attrs() {
@@ -135,6 +139,9 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
 extern "C" void b2fft_plan_destroy(b2fft_plan *p) {
     if (!p) return;
     if (p->slab) b2_slab_destroy(p);
+#if B2_CUDA
+    pipe_destroy(p);
+#endif
     dev_free(p->scr);
     dev_free(p->dev_in);
     dev_free(p->dev_out);
@@ -143,6 +150,89 @@ extern "C" void b2fft_plan_destroy(b2fft_plan *p) {
 #endif
     delete p;
 }
+
+// ------------------------------------------------------------------------- host pipeline
+#if B2_CUDA
+static void pipe_destroy(b2fft_plan *p) {
+    HostPipe *hp = p->pipe;
+    if (!hp) return;
+    for (auto &sl : hp->slot) {
+        b2fft_plan_destroy(sl.plan);
+        b2fft_plan_destroy(sl.plan_tail);
+        if (sl.din != sl.dout) dev_free(sl.din);  // in place: one buffer
+        dev_free(sl.dout);
+        if (sl.stream) cudaStreamDestroy(sl.stream);
+    }
+    delete hp;
+    p->pipe = nullptr;
+}
+
+// Decide once whether host executes of this plan can be chunked along a batch dimension.
+static void pipe_setup(b2fft_plan *p) {
+    HostPipe *hp = new HostPipe();
+    p->pipe = hp;
+    hp->state = -1;
+    const PlanCore &pc = p->pc;
+    const b2fft_geom &g = pc.g;
+    if (getenv("FFTW_B200_NO_PIPELINE")) return;
+    // dense arrays only: a chunk of the batch must be one contiguous range on both sides
+    if (pc.in_dense != pc.in_reals || pc.out_dense != pc.out_reals) return;
+    int v = -1;
+    for (int i = 0; i < g.vrank; ++i)
+        if (g.vdims[i].n > 1 && (v < 0 || g.vdims[i].os > g.vdims[v].os)) v = i;
+    if (v < 0 || g.vdims[v].n < 4) return;
+    const long long iu = (g.kind == B2FFT_R2C) ? 1 : 2, ou = (g.kind == B2FFT_C2R) ? 1 : 2;
+    hp->in_step = (long long)g.vdims[v].is * iu;
+    hp->out_step = (long long)g.vdims[v].os * ou;
+    // the batch dim must be the outermost one on both sides
+    if (hp->in_step * g.vdims[v].n != pc.in_reals || hp->out_step * g.vdims[v].n != pc.out_reals) return;
+    const double bytes_per = (double)(hp->in_step + hp->out_step) * sizeof(real_t);
+    long long chunk = (long long)std::max(1.0, (96.0 * (1 << 20)) / bytes_per);
+    chunk = std::min<long long>(chunk, (g.vdims[v].n + 3) / 4);
+    hp->chunk = chunk;
+    hp->nchunks = (g.vdims[v].n + chunk - 1) / chunk;
+    hp->tail = g.vdims[v].n % chunk;
+    hp->vdim = v;
+    for (auto &sl : hp->slot) {
+        b2fft_geom g2 = g;
+        g2.vdims[v].n = chunk;
+        sl.plan = b2fft_plan_create(&g2);
+        if (!sl.plan) return;
+        const size_t ib = (size_t)hp->in_step * chunk * sizeof(real_t), ob = (size_t)hp->out_step * chunk * sizeof(real_t);
+        sl.dout = (real_t *)dev_malloc(pc.in_place ? std::max(ib, ob) : ob);
+        sl.din = pc.in_place ? sl.dout : (real_t *)dev_malloc(ib);
+        if (!sl.din || !sl.dout) return;
+        if (cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking) != cudaSuccess) return;
+    }
+    if (hp->tail) {
+        b2fft_geom g2 = g;
+        g2.vdims[v].n = hp->tail;
+        HostPipe::Slot &sl = hp->slot[(hp->nchunks - 1) % 3];
+        sl.plan_tail = b2fft_plan_create(&g2);
+        if (!sl.plan_tail) return;
+    }
+    hp->state = 1;
+}
+
+static int pipe_execute(b2fft_plan *p, void *in, void *out) {
+    HostPipe *hp = p->pipe;
+    const bool same = p->pc.in_place;
+    for (long long c = 0; c < hp->nchunks; ++c) {
+        HostPipe::Slot &sl = hp->slot[c % 3];
+        const long long cnt = (c == hp->nchunks - 1 && hp->tail) ? hp->tail : hp->chunk;
+        b2fft_plan *sp = (cnt == hp->chunk) ? sl.plan : sl.plan_tail;
+        const size_t ib = (size_t)hp->in_step * cnt * sizeof(real_t), ob = (size_t)hp->out_step * cnt * sizeof(real_t);
+        const real_t *hin = (const real_t *)in + c * hp->chunk * hp->in_step;
+        real_t *hout = (real_t *)out + c * hp->chunk * hp->out_step;
+        B2_CK(cudaMemcpyAsync(sl.din, hin, ib, cudaMemcpyHostToDevice, sl.stream));
+        int rc = run_steps(sp, sl.din, same ? sl.din : sl.dout, sl.stream);
+        if (rc) return rc;
+        B2_CK(cudaMemcpyAsync(hout, same ? sl.din : sl.dout, ob, cudaMemcpyDeviceToHost, sl.stream));
+    }
+    for (auto &sl : hp->slot) B2_CK(cudaStreamSynchronize(sl.stream));
+    return 0;
+}
+#endif
 
 // ------------------------------------------------------------------------- execute
 extern "C" int b2fft_execute_async(b2fft_plan *p, void *in, void *out, void *stream) {
@@ -164,6 +254,10 @@ extern "C" int b2fft_execute(b2fft_plan *p, void *in, void *out) {
     }
 #if B2_CUDA
     const bool din = is_device_ptr(in), dout = is_device_ptr(out);
+    if (!din && !dout) {
+        if (!p->pipe) pipe_setup(p);
+        if (p->pipe->state == 1) return pipe_execute(p, in, out);
+    }
     real_t *ri = (real_t *)in, *ro = (real_t *)out;
     const size_t ib = (size_t)p->pc.in_reals * sizeof(real_t), ob = (size_t)p->pc.out_reals * sizeof(real_t);
     if (!dout) {

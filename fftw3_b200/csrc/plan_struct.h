@@ -3,6 +3,20 @@
 #include "plan_build.h"
 
 struct SlabPlan;
+struct b2fft_plan_s;
+// Host-array executes of a batched plan run as a pipeline over chunks of the batch: H2D copy,
+// kernels and D2H copy of different chunks overlap on separate streams (PCIe is full duplex).
+struct HostPipe {
+    int state = 0;  // 0 not tried, 1 ready, -1 not applicable
+    int vdim = -1;  // batch dim that is chunked
+    long long chunk = 0, nchunks = 0, tail = 0;
+    long long in_step = 0, out_step = 0;  // reals between consecutive batch entries
+    struct Slot {
+        b2fft_plan_s *plan = nullptr, *plan_tail = nullptr;
+        real_t *din = nullptr, *dout = nullptr;
+        b2::stream_t stream = nullptr;
+    } slot[3];
+};
 struct b2fft_plan_s {
     b2::PlanCore pc;
     real_t *scr = nullptr;
@@ -11,6 +25,7 @@ struct b2fft_plan_s {
     b2::stream_t stream = nullptr;
     bool own_stream = false;
     SlabPlan *slab = nullptr;
+    HostPipe *pipe = nullptr;
 };
 void b2_slab_destroy(b2fft_plan_s *p);
 int b2_slab_execute(b2fft_plan_s *p, void *in, void *out);

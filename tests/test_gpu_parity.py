@@ -195,3 +195,31 @@ def test_full_size_roundtrip_512_cubed_fp32(lib):
     torch.cuda.synchronize()
     err = float(((y / N - x).abs() ** 2).sum(dtype=torch.float64).sqrt() / (x.abs() ** 2).sum(dtype=torch.float64).sqrt())
     assert err < 2e-6 * math.log2(N)
+
+
+@pytest.mark.parametrize("howmany", [4, 37, 256])
+def test_host_arrays_go_through_the_chunked_pipeline(lib, howmany):
+    """host arrays + batch: H2D / kernels / D2H of different chunks overlap (engine.cu pipe_*);
+    ragged last chunk, out of place, in place, and r2c"""
+    rng = np.random.default_rng(howmany)
+    n = 1024
+    x = cases.rand_c(rng, (howmany, n), lib)
+    y = np.zeros_like(x)
+    p = lib.plan_many_dft([n], howmany, x, None, 1, n, y, None, 1, n, capi.FFTW_FORWARD)
+    assert p
+    lib.execute(p)
+    lib.execute(p)
+    lib.destroy_plan(p)
+    ref = np.fft.fft(x.astype(np.complex128), axis=1)
+    assert cases.rel_l2(y, ref) < cases.tol(lib, n)
+    z = x.copy()
+    p = lib.plan_many_dft([n], howmany, z, None, 1, n, z, None, 1, n, capi.FFTW_BACKWARD)
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert cases.rel_l2(z, n * np.fft.ifft(x.astype(np.complex128), axis=1)) < cases.tol(lib, n)
+    xr = cases.rand_r(rng, (howmany, n), lib)
+    yr = np.zeros((howmany, n // 2 + 1), dtype=lib.cplx)
+    p = lib.plan_many_dft_r2c([n], howmany, xr, None, 1, n, yr, None, 1, n // 2 + 1)
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert cases.rel_l2(yr, np.fft.rfft(xr.astype(np.float64), axis=1)) < cases.tol(lib, n)
