@@ -10,7 +10,7 @@
 #include "plan_build_real.h"
 #include "plan_struct.h"
 #include "realpp_kernel.cuh"
-#include "tile_dispatch.cuh"
+#include "chain_build.h"
 
 using namespace b2;
 
@@ -26,7 +26,8 @@ static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream
         }
         const real_t *sp = src + so;
         real_t *dp = dst + dof;
-        bool fast = s.kind == SK_PASS && s.fast_id >= 0;
+        // a chain member was re-tiled for the chained launch: on its own it runs the generic kernel
+        bool fast = s.kind == SK_PASS && s.fast_id >= 0 && s.chain_id < 0;
         bool al_s = ((uintptr_t)sp % sizeof(cpx_t)) == 0, al_d = ((uintptr_t)dp % sizeof(cpx_t)) == 0;
         if (!al_s || !al_d) fast = false;  // vector access needs 2-real alignment of the base addresses
         PassParams pp = fast ? s.pp : s.gen_pp;
@@ -71,9 +72,48 @@ static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream
     return 0;
 }
 
+static int run_chain(b2fft_plan *p, const Chain &ch, real_t *const *buf, stream_t stream) {
+    ChainParams cp;
+    memset(&cp, 0, sizeof cp);
+    cp.nsteps = ch.count;
+    cp.lag = ch.lag;
+    cp.G = ch.G;
+    cp.bpg = ch.bpg;
+    cp.counters = ch.counters;
+    cp.errflag = ch.counters + (size_t)ch.count * ch.G;
+    for (int k = 0; k < ch.count; ++k) {
+        const StepPlan &s = p->pc.steps[ch.first + k];
+        ChainStep &c = cp.st[k];
+        c.kind = s.kind;
+        c.tpg = ch.tpg[k];
+        c.nthreads = s.kind == SK_PASS ? s.nthreads : ch.threads;
+        c.src = buf[s.src];
+        c.dst = buf[s.dst];
+        if (s.kind == SK_PASS) {
+            const TileEntry &e = b2_tile_table()[s.fast_id];
+            c.mode = e.mode;
+            c.epi = e.epi;
+            c.pp = s.pp;
+            b2_pp_prepare(c.pp);
+        } else
+            c.rp = s.rp;
+    }
+    return b2_launch_chain(cp, ch.threads, ch.smem, stream);
+}
+
 static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
     real_t *buf[3] = {in, out, p->scr};
-    for (const StepPlan &s : p->pc.steps) {
+    const bool aligned = ((uintptr_t)in % sizeof(cpx_t)) == 0 && ((uintptr_t)out % sizeof(cpx_t)) == 0;
+    const size_t ns = p->pc.steps.size();
+    for (size_t i = 0; i < ns; ++i) {
+        const StepPlan &s = p->pc.steps[i];
+        if (s.chain_id >= 0 && s.chain_pos == 0 && aligned && p->chains) {
+            const Chain &ch = (*p->chains)[s.chain_id];
+            int rc = run_chain(p, ch, buf, stream);
+            if (rc) return rc;
+            i += ch.count - 1;
+            continue;
+        }
         int rc = launch_step(s, buf[s.src], buf[s.dst], stream);
         if (rc) return rc;
     }
@@ -121,6 +161,16 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
             p->scr = (real_t *)dev_malloc((size_t)p->pc.scr_reals * sizeof(real_t));
             if (!p->scr) ok = false;
         }
+        p->chains = new std::vector<Chain>();
+        build_chains(p->pc.steps, *p->chains);
+        for (Chain &ch : *p->chains) {
+            const size_t nb = sizeof(unsigned) * ((size_t)ch.count * ch.G + 1);
+            ch.counters = (unsigned *)dev_malloc(nb);
+            if (!ch.counters) ok = false;
+#if B2_CUDA
+            else if (cudaMemset(ch.counters, 0, nb) != cudaSuccess) ok = false;
+#endif
+        }
     }
     if (!ok) {
         delete p;
@@ -130,7 +180,14 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
     static const char *bn[] = {"in", "out", "scratch"};
     for (size_t i = 0; i < p->pc.steps.size(); ++i) {
         const StepPlan &s = p->pc.steps[i];
-        d += "  pass " + std::to_string(i) + ": " + s.desc + " [" + bn[s.src] + "->" + bn[s.dst] + "]\n";
+        d += "  pass " + std::to_string(i) + ": " + s.desc + " [" + bn[s.src] + "->" + bn[s.dst] + "]";
+        if (s.chain_id >= 0) {
+            const Chain &ch = (*p->chains)[s.chain_id];
+            d += " {chained launch " + std::to_string(s.chain_id) + ", step " + std::to_string(s.chain_pos) + ": " +
+                 std::to_string(ch.G) + " groups x " + std::to_string(ch.tpg[s.chain_pos]) + " tiles, " +
+                 std::to_string(ch.threads) + " threads, lag " + std::to_string(ch.lag) + "}";
+        }
+        d += "\n";
     }
     p->pc.desc = d;
     return p;
@@ -142,6 +199,10 @@ extern "C" void b2fft_plan_destroy(b2fft_plan *p) {
 #if B2_CUDA
     pipe_destroy(p);
 #endif
+    if (p->chains) {
+        for (Chain &ch : *p->chains) dev_free(ch.counters);
+        delete p->chains;
+    }
     dev_free(p->scr);
     dev_free(p->dev_in);
     dev_free(p->dev_out);

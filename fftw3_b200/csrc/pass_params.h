@@ -38,4 +38,27 @@ struct PassParams {
     int epi_shift;         // exponent e = (hi << epi_shift) | lo
     const cpx_t *epi_lo;   // w_N^lo
     const cpx_t *epi_hi;   // w_N^(hi << shift)
+    // ---- tile-kernel decode helpers, filled by b2_pp_prepare() just before a launch ----
+    unsigned dv_m[B2_MAXLD], dv_s[B2_MAXLD];  // exact division by tiles0 (slot 0) and ln[1..] for indices < 2^31
+    int lgC;                                  // log2(C), or -1 when C is not a power of two
 };
+
+// Division by an invariant d for 0 <= n < 2^31 (Granlund-Montgomery): with l = ceil(log2 d) and
+// m = floor(2^(31+l) / d) + 1 (fits 32 bits), floor(n / d) = (n * m) >> (31 + l).
+inline void b2_fastdiv_make(unsigned long long d, unsigned &m, unsigned &s) {
+    unsigned l = 0;
+    while ((1ull << l) < d) ++l;
+    m = (unsigned)((1ull << (31 + l)) / d + 1);  // d < 2^31, so 31 + l <= 62
+    s = 31 + l;
+}
+B2_HD unsigned b2_fastdiv(unsigned n, unsigned m, unsigned s) {
+    return (unsigned)(((unsigned long long)n * m) >> s);
+}
+inline void b2_pp_prepare(PassParams &p) {
+    b2_fastdiv_make((unsigned long long)(p.tiles0 > 0 ? p.tiles0 : 1), p.dv_m[0], p.dv_s[0]);
+    for (int d = 1; d < B2_MAXLD; ++d)
+        b2_fastdiv_make((unsigned long long)(d < p.nld && p.ln[d] > 0 ? p.ln[d] : 1), p.dv_m[d], p.dv_s[d]);
+    p.lgC = -1;
+    for (int l = 0; l < 16; ++l)
+        if ((1 << l) == p.C) p.lgC = l;
+}

@@ -33,7 +33,8 @@ inline void fill_realpp(StepPlan &st, int post, int m, long long n_real, long lo
     }
     r.twr = twiddles().get((unsigned long long)n_real, (unsigned long long)m / 2 + 1, 1);
     st.nthreads = 256;
-    long long nb = (m / 2 + 1 + 255) / 256;
+    r.pts_per_block = 1024;
+    long long nb = (m / 2 + 1 + r.pts_per_block - 1) / r.pts_per_block;
     for (int d = 0; d < r.nld; ++d) nb *= r.ln[d];
     st.nblocks = nb;
     st.smem = 0;

@@ -2,6 +2,10 @@
 #pragma once
 #include "plan_build.h"
 
+namespace b2 {
+struct Chain;
+}
+
 struct SlabPlan;
 struct b2fft_plan_s;
 // Host-array executes of a batched plan run as a pipeline over chunks of the batch: H2D copy,
@@ -26,6 +30,7 @@ struct b2fft_plan_s {
     bool own_stream = false;
     SlabPlan *slab = nullptr;
     HostPipe *pipe = nullptr;
+    std::vector<b2::Chain> *chains = nullptr;
 };
 void b2_slab_destroy(b2fft_plan_s *p);
 int b2_slab_execute(b2fft_plan_s *p, void *in, void *out);

@@ -6,12 +6,13 @@
 // fftw/fftw_api.c:5831-5845).
 #pragma once
 #include "selector.h"
+#include "tile_kernel.cuh"
 
 // grid: x = ceil((m/2+1)/threads) chunks, then lines.  src/dst may alias (in-place split).
 B2_D void b2_realpp_body(const b2::RealPPParams &p, int post, const real_t *src, real_t *dst,
                          long long bid, int b2_nthreads) {
     const int hk = p.m / 2 + 1;
-    const int chunks = (hk + B2_NTHREADS - 1) / B2_NTHREADS;
+    const int chunks = (hk + p.pts_per_block - 1) / p.pts_per_block;
     const int chunk = (int)(bid % chunks);
     long long rest = bid / chunks;
     long long so = 0, dof = 0;
@@ -22,20 +23,20 @@ B2_D void b2_realpp_body(const b2::RealPPParams &p, int post, const real_t *src,
         dof += c * p.ld[d];
     }
     B2_FOR_THREADS {
-        const int k = chunk * B2_NTHREADS + tid;
         const int m = p.m;
-        if (k < hk) {
+        const int kend = (chunk + 1) * p.pts_per_block < hk ? (chunk + 1) * p.pts_per_block : hk;
+        for (int k = chunk * p.pts_per_block + tid; k < kend; k += B2_NTHREADS) {
             const cpx_t *S = reinterpret_cast<const cpx_t *>(src + so);
             // strides are in reals and even for complex arrays
             const long long ss = p.s_axis / 2, ds = p.d_axis / 2;
             cpx_t *D = reinterpret_cast<cpx_t *>(dst + dof);
             if (post) {
                 if (k == 0) {
-                    const cpx_t z0 = S[0];
+                    const cpx_t z0 = b2_ldcg(S);
                     D[0] = cpx_t{z0.x + z0.y, (real_t)0};
                     D[(long long)m * ds] = cpx_t{z0.x - z0.y, (real_t)0};
                 } else {
-                    const cpx_t zk = S[(long long)k * ss], zc = cconj(S[(long long)(m - k) * ss]);
+                    const cpx_t zk = b2_ldcg(S + (long long)k * ss), zc = cconj(b2_ldcg(S + (long long)(m - k) * ss));
                     const cpx_t E = cscale(cadd(zk, zc), (real_t)0.5);
                     const cpx_t O = cmul_mi(cscale(csub(zk, zc), (real_t)0.5));
                     const cpx_t wO = cmul(p.twr[k], O);
@@ -43,7 +44,7 @@ B2_D void b2_realpp_body(const b2::RealPPParams &p, int post, const real_t *src,
                     if (k != m - k) D[(long long)(m - k) * ds] = cconj(csub(E, wO));
                 }
             } else {
-                const cpx_t A = S[(long long)k * ss], B = cconj(S[(long long)(m - k) * ss]);
+                const cpx_t A = b2_ldcg(S + (long long)k * ss), B = cconj(b2_ldcg(S + (long long)(m - k) * ss));
                 const cpx_t sum = cadd(A, B), dif = csub(A, B);
                 const cpx_t Dd = cmul_pi(cmul(cconj(p.twr[k]), dif));
                 const cpx_t zk = cadd(sum, Dd), zmk = cconj(csub(sum, Dd));

@@ -30,6 +30,7 @@ struct RealPPParams {
     int nld;
     long long ln[B2_MAXLD], ls[B2_MAXLD], ld[B2_MAXLD];
     const cpx_t *twr;      // w_n^k, k <= m/2
+    int pts_per_block;     // pairs (k, m-k) handled by one CTA
 };
 
 struct Step {
@@ -46,6 +47,7 @@ struct Step {
     long long gen_nblocks = 0;
     size_t smem = 0;
     int fast_id = -1;           // >= 0: specialised tile kernel
+    int chain_id = -1, chain_pos = 0;  // member of a chained launch (chain_build.h)
     std::vector<LDim> outer;    // extra line dims looped on the host
     std::string desc;
 };

@@ -9,6 +9,7 @@
 struct TileEntry {
     int n, e, mode, epi, c, threads;
     size_t smem;
+    size_t (*smem_for)(int C);
     int (*launch)(const PassParams &, const real_t *, real_t *, long long, long long, int, size_t, b2::stream_t);
     void (*init)();
 };
@@ -29,6 +30,7 @@ struct TileInst {
         return 0;
 #endif
     }
+    static size_t smem_for(int c) { return TileFFT<N, E, MODE, EPI>::smem_bytes(c); }
     static void init() {
 #if B2_CUDA
         cudaFuncSetAttribute(b2_tile_kernel<N, E, MODE, EPI, THREADS, MINB>,
@@ -37,37 +39,37 @@ struct TileInst {
 #endif
     }
     static TileEntry entry() {
-        return TileEntry{N, E, MODE, EPI ? 1 : 0, C, THREADS, TileFFT<N, E, MODE, EPI>::smem_bytes(C), &launch, &init};
+        return TileEntry{N, E, MODE, EPI ? 1 : 0, C, THREADS, TileFFT<N, E, MODE, EPI>::smem_bytes(C), &smem_for, &launch, &init};
     }
 };
 
-#define B2_TILE_ALLMODES(N, E, CROW, CCOL)                 \
-    TileInst<N, E, MODE_ROW, false, CROW>::entry(),        \
-    TileInst<N, E, MODE_COL, false, CCOL>::entry(),        \
-    TileInst<N, E, MODE_COL, true, CCOL>::entry(),         \
-    TileInst<N, E, MODE_ROW2COL, false, CCOL>::entry()
+// X(N, E, MODE, EPI, C): every instantiated tile kernel, in table order
+#define B2_TILE_ALLMODES(X, N, E, CROW, CCOL) \
+    X(N, E, MODE_ROW, false, CROW) X(N, E, MODE_COL, false, CCOL) X(N, E, MODE_COL, true, CCOL) \
+    X(N, E, MODE_ROW2COL, false, CCOL)
+#if defined(FFTW_SINGLE)
+#define B2_TILE_LIST(X)                   \
+    B2_TILE_ALLMODES(X, 64, 8, 32, 16)    \
+    B2_TILE_ALLMODES(X, 128, 8, 16, 16)   \
+    B2_TILE_ALLMODES(X, 256, 16, 16, 16)  \
+    B2_TILE_ALLMODES(X, 512, 16, 8, 16)   \
+    B2_TILE_ALLMODES(X, 1024, 16, 4, 16)  \
+    B2_TILE_ALLMODES(X, 2048, 16, 2, 8)   \
+    X(4096, 16, MODE_ROW, false, 1) X(8192, 16, MODE_ROW, false, 1)
+#else
+#define B2_TILE_LIST(X)                 \
+    B2_TILE_ALLMODES(X, 64, 8, 32, 8)   \
+    B2_TILE_ALLMODES(X, 128, 8, 16, 8)  \
+    B2_TILE_ALLMODES(X, 256, 8, 8, 8)   \
+    B2_TILE_ALLMODES(X, 512, 8, 4, 8)   \
+    B2_TILE_ALLMODES(X, 1024, 8, 2, 8)  \
+    X(2048, 8, MODE_ROW, false, 1) X(4096, 8, MODE_ROW, false, 1)
+#endif
 
 inline const std::vector<TileEntry> &b2_tile_table() {
-    static const std::vector<TileEntry> tab = {
-#if defined(FFTW_SINGLE)
-        B2_TILE_ALLMODES(64, 8, 32, 16),
-        B2_TILE_ALLMODES(128, 8, 16, 16),
-        B2_TILE_ALLMODES(256, 16, 16, 16),
-        B2_TILE_ALLMODES(512, 16, 8, 16),
-        B2_TILE_ALLMODES(1024, 16, 4, 16),
-        B2_TILE_ALLMODES(2048, 16, 2, 8),
-        TileInst<4096, 16, MODE_ROW, false, 1>::entry(),
-        TileInst<8192, 16, MODE_ROW, false, 1>::entry(),
-#else
-        B2_TILE_ALLMODES(64, 8, 32, 8),
-        B2_TILE_ALLMODES(128, 8, 16, 8),
-        B2_TILE_ALLMODES(256, 8, 8, 8),
-        B2_TILE_ALLMODES(512, 8, 4, 8),
-        B2_TILE_ALLMODES(1024, 8, 2, 8),
-        TileInst<2048, 8, MODE_ROW, false, 1>::entry(),
-        TileInst<4096, 8, MODE_ROW, false, 1>::entry(),
-#endif
-    };
+#define B2_X_ENTRY(N, E, MODE, EPI, C) TileInst<N, E, MODE, EPI, C>::entry(),
+    static const std::vector<TileEntry> tab = {B2_TILE_LIST(B2_X_ENTRY)};
+#undef B2_X_ENTRY
     return tab;
 }
 
@@ -105,6 +107,7 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         p.tiles0 = (p.ln[0] + p.C - 1) / p.C;
         long long nb = p.tiles0;
         for (int d = 1; d < p.nld; ++d) nb *= p.ln[d];
+        if (nb >= (1ll << 31)) continue;  // the tile kernels decode a 31-bit tile index
         s.nblocks = nb;
         s.nthreads = e.threads;
         s.smem = e.smem;
@@ -121,5 +124,7 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
 
 inline int b2_launch_tile_kernel(int id, const PassParams &p, const real_t *src, real_t *dst, long long b0,
                                  long long nb, int threads, size_t smem, b2::stream_t st) {
-    return b2_tile_table()[id].launch(p, src, dst, b0, nb, threads, smem, st);
+    PassParams q = p;
+    b2_pp_prepare(q);
+    return b2_tile_table()[id].launch(q, src, dst, b0, nb, threads, smem, st);
 }

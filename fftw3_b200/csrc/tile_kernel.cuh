@@ -54,6 +54,23 @@ struct TileCtx {
 
 template <int PADSHIFT> B2_HD int b2_pad(int o) { return o + (o >> PADSHIFT); }
 
+// Streaming data is read through L2 only (ld.global.cg): it is never reused from L1, and when
+// passes are chained inside one launch the producer may be another SM, whose writes a stale L1
+// line would hide.
+B2_D cpx_t b2_ldcg(const cpx_t *p) {
+#if B2_CUDA
+    if (sizeof(real_t) == 4) {
+        const float2 v = __ldcg(reinterpret_cast<const float2 *>(p));
+        return cpx_t{(real_t)v.x, (real_t)v.y};
+    } else {
+        const double2 v = __ldcg(reinterpret_cast<const double2 *>(p));
+        return cpx_t{(real_t)v.x, (real_t)v.y};
+    }
+#else
+    return *p;
+#endif
+}
+
 // w[k] = w1^k, k = 1..R-1, by a product tree of depth <= log2(R)
 template <int R> B2_D void b2_twiddle_powers(cpx_t w1, cpx_t *w) {
     w[1] = w1;
@@ -88,15 +105,23 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
     }
     static B2_HD size_t smem_bytes(int C) { return (size_t)C * LS * sizeof(cpx_t); }
 
-    // thread -> (line c, slot t)
-    static B2_HD void map(int tid, int C, int &c, int &t) {
+    // thread -> (line c, slot t).  Every thread of the CTA owns a slot: a chained launch, whose
+    // CTAs have the thread count of the widest step, retires its surplus warps before it gets here
+    // (a per-thread "live" guard costs the 64-register kernels 20-80 bytes of spills).
+    static B2_HD bool map(int tid, int C, int lgC, int &c, int &t) {
         if (COLMAP) {
-            c = tid % C;
-            t = tid / C;
+            if (lgC >= 0) {
+                t = tid >> lgC;
+                c = tid & (C - 1);
+            } else {
+                t = tid / C;
+                c = tid - t * C;
+            }
         } else {
             c = tid / T;
             t = tid - c * T;
         }
+        return true;
     }
 
     template <int P> static B2_D void butterflies(const TileCtx &x, cpx_t *v, int c, int t, bool active) {
@@ -138,18 +163,19 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
         B2_FOR_THREADS {
             cpx_t *v = B2_TREGS(x);
             int c, t;
-            map(tid, x.p->C, c, t);
-            const cpx_t *line = x.sm + (size_t)c * LS;
-            const int pt = phys(t);
+            if (map(tid, x.p->C, x.p->lgC, c, t)) {
+                const cpx_t *line = x.sm + (size_t)c * LS;
+                const int pt = phys(t);
 #pragma unroll
-            for (int q = 0; q < E; ++q) v[q] = line[phys_k<T, 0>(t, pt, q)];
+                for (int q = 0; q < E; ++q) v[q] = line[phys_k<T, 0>(t, pt, q)];
+            }
         }
         if (P < S::NP - 1) B2_SYNC();  // the next write must not overtake a neighbour's read
         B2_FOR_THREADS {
             cpx_t *v = B2_TREGS(x);
             int c, t;
-            map(tid, x.p->C, c, t);
-            butterflies<P>(x, v, c, t, true);
+            const bool live = map(tid, x.p->C, x.p->lgC, c, t);
+            butterflies<P>(x, v, c, t, live);
         }
         if constexpr (P + 1 < S::NP) passes_from<P + 1>(x);
     }
@@ -170,18 +196,20 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
         x.vbase = vreg_store.data();
 #endif
         const int C = p.C;
-        const long long t0 = bid % p.tiles0;
-        long long rest = bid / p.tiles0;
-        x.l0 = t0 * C;
+        // tile index -> coordinates: exact multiply-shift divisions (b2_pp_prepare), 31-bit index
+        unsigned rest = b2_fastdiv((unsigned)bid, p.dv_m[0], p.dv_s[0]);
+        const unsigned t0 = (unsigned)bid - rest * (unsigned)p.tiles0;
+        x.l0 = (long long)t0 * C;
         x.nlines = (int)((p.ln[0] - x.l0 < C) ? (p.ln[0] - x.l0) : C);
         x.sbase = 0;
         x.dbase = 0;
         x.i2base = 0;
         for (int d = 1; d < p.nld; ++d) {
-            const long long cc = rest % p.ln[d];
-            rest /= p.ln[d];
-            x.sbase += cc * p.ls[d];
-            x.dbase += cc * p.ld[d];
+            const unsigned qd = b2_fastdiv(rest, p.dv_m[d], p.dv_s[d]);
+            const unsigned cc = rest - qd * (unsigned)p.ln[d];
+            rest = qd;
+            x.sbase += (long long)cc * p.ls[d];
+            x.dbase += (long long)cc * p.ld[d];
             if (d == p.epi_dim) x.i2base = (int)cc;
         }
         const cpx_t *csrc = reinterpret_cast<const cpx_t *>(src);
@@ -191,22 +219,32 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
         B2_FOR_THREADS {
             cpx_t *v = B2_TREGS(x);
             int c, t;
-            map(tid, C, c, t);
-            const bool active = c < x.nlines;
+            const bool live = map(tid, C, p.lgC, c, t);
+            const bool active = live && c < x.nlines;
             if (active) {
                 // all strides are in reals and even here (vector access was checked by the selector)
-                const long long base = (x.sbase + (x.l0 + c) * p.ls[0]) / 2;
                 const long long as = p.s_axis / 2;
+                const cpx_t *pl = csrc + ((x.sbase + (x.l0 + c) * p.ls[0]) / 2 + (long long)t * as);
+                if (as == 1) {  // contiguous lines: the offsets fold into the load instructions
 #pragma unroll
-                for (int q = 0; q < E; ++q) {
-                    cpx_t a = csrc[base + (long long)(t + q * T) * as];
-                    v[q] = p.swap_in ? cswap(a) : a;
+                    for (int q = 0; q < E; ++q) v[q] = b2_ldcg(pl + q * T);
+                } else {
+                    const long long step = (long long)T * as;
+#pragma unroll
+                    for (int q = 0; q < E; ++q) {
+                        v[q] = b2_ldcg(pl);
+                        pl += step;
+                    }
+                }
+                if (p.swap_in) {
+#pragma unroll
+                    for (int q = 0; q < E; ++q) v[q] = cswap(v[q]);
                 }
             } else {
 #pragma unroll
                 for (int q = 0; q < E; ++q) v[q] = cpx_t{0, 0};
             }
-            butterflies<0>(x, v, c, t, active);
+            butterflies<0>(x, v, c, t, live);
         }
         if constexpr (S::NP > 1) passes_from<1>(x);
 
@@ -215,8 +253,8 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
             B2_FOR_THREADS {
                 cpx_t *v = B2_TREGS(x);
                 int c, t;
-                map(tid, C, c, t);
-                if (c < x.nlines) {
+                const bool live = map(tid, C, p.lgC, c, t);
+                if (live && c < x.nlines) {
                     const long long base = (x.dbase + (x.l0 + c) * p.ld[0]) / 2;
                     const long long ds = p.d_axis / 2;
                     if (EPI) {
@@ -233,10 +271,21 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
 #pragma unroll
                         for (int q = 0; q < E; ++q) v[q] = cmul(v[q], q ? cmul(wb, wq[q]) : wb);
                     }
+                    if (p.swap_out) {
 #pragma unroll
-                    for (int q = 0; q < E; ++q) {
-                        cpx_t a = p.swap_out ? cswap(v[q]) : v[q];
-                        cdst[base + (long long)(t + q * T) * ds] = a;
+                        for (int q = 0; q < E; ++q) v[q] = cswap(v[q]);
+                    }
+                    cpx_t *ps = cdst + (base + (long long)t * ds);
+                    if (ds == 1) {
+#pragma unroll
+                        for (int q = 0; q < E; ++q) ps[q * T] = v[q];
+                    } else {
+                        const long long step = (long long)T * ds;
+#pragma unroll
+                        for (int q = 0; q < E; ++q) {
+                            *ps = v[q];
+                            ps += step;
+                        }
                     }
                 }
             }
@@ -246,11 +295,12 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
             B2_FOR_THREADS {
                 cpx_t *v = B2_TREGS(x);
                 int c, t;
-                map(tid, C, c, t);
-                cpx_t *line = x.sm + (size_t)c * LS;
-                const int pt = phys(t);
+                if (map(tid, C, p.lgC, c, t)) {
+                    cpx_t *line = x.sm + (size_t)c * LS;
+                    const int pt = phys(t);
 #pragma unroll
-                for (int q = 0; q < E; ++q) line[phys_k<T, 0>(t, pt, q)] = v[q];
+                    for (int q = 0; q < E; ++q) line[phys_k<T, 0>(t, pt, q)] = v[q];
+                }
             }
             B2_SYNC();
             B2_FOR_THREADS {
@@ -258,11 +308,32 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
                 const long long ds = p.d_axis / 2;
                 const long long base = (x.dbase + x.l0 * p.ld[0]) / 2;
                 const long long lstep = p.ld[0] / 2;
-                for (int idx = tid; idx < nl * N; idx += B2_NTHREADS) {
-                    const int k = idx / nl, c = idx - k * nl;
-                    cpx_t a = x.sm[(size_t)c * LS + phys(k)];
-                    if (p.swap_out) a = cswap(a);
-                    cdst[base + (long long)c * lstep + (long long)k * ds] = a;
+                if (nl == C && p.lgC >= 0 && B2_NTHREADS == C * T) {
+                    // full tile: thread -> (line c, points k0 + q*T), no per-element division
+                    const int c = tid & (C - 1), k0 = tid >> p.lgC;
+                    const cpx_t *sp = x.sm + (size_t)c * LS;
+                    const int pk = phys(k0);
+                    cpx_t *ps = cdst + (base + (long long)c * lstep + (long long)k0 * ds);
+                    const long long step = (long long)T * ds;
+                    cpx_t a[E];
+#pragma unroll
+                    for (int q = 0; q < E; ++q) a[q] = sp[phys_k<T, 0>(k0, pk, q)];
+                    if (p.swap_out) {
+#pragma unroll
+                        for (int q = 0; q < E; ++q) a[q] = cswap(a[q]);
+                    }
+#pragma unroll
+                    for (int q = 0; q < E; ++q) {
+                        *ps = a[q];
+                        ps += step;
+                    }
+                } else {
+                    for (int idx = tid; idx < nl * N; idx += B2_NTHREADS) {
+                        const int k = idx / nl, c = idx - k * nl;
+                        cpx_t a = x.sm[(size_t)c * LS + phys(k)];
+                        if (p.swap_out) a = cswap(a);
+                        cdst[base + (long long)c * lstep + (long long)k * ds] = a;
+                    }
                 }
             }
         }

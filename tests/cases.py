@@ -249,3 +249,51 @@ def check_properties(lib, shape, seed=7):
     sh = np.roll(a, 1, axis=-1)
     ramp = np.exp(-2j * np.pi * np.arange(n) / n)
     assert rel_l2(lib.dft(sh, -1), A.astype(np.complex128) * ramp) < t
+
+
+def check_chained_launch(lib, device=False):
+    """FFTW_B200_CHAIN=1: dependent passes fused into one launch (csrc/chain_kernel.cuh); the plan
+    must say so and the results must not change.  Reference equivalents: rank_geq2_apply
+    fftw_api.c:4435-4445 (3-D), ct_apply_dit :2079-2090 (four-step), ct_hc2c_apply_dit_dft :5579-5590."""
+    import os
+    old = os.environ.get("FFTW_B200_CHAIN")
+    os.environ["FFTW_B200_CHAIN"] = "1"
+    try:
+        rng = np.random.default_rng(11)
+        # 3-D: z and y passes of each plane group
+        x = rand_c(rng, (64, 64, 64), lib)
+        y = np.zeros_like(x)
+        p = lib.plan_dft(list(x.shape), x, y, capi.FFTW_FORWARD)
+        assert p and "chained launch" in lib.sprint_plan(p)
+        lib.execute(p)
+        lib.destroy_plan(p)
+        assert rel_l2(y, np.fft.fftn(x.astype(np.complex128))) < tol(lib, x.size)
+        # batched four-step c2c
+        n, hm = 2 ** 14, 4
+        x = rand_c(rng, (hm, n), lib)
+        y = np.zeros_like(x)
+        p = lib.plan_many_dft([n], hm, x, None, 1, n, y, None, 1, n, capi.FFTW_BACKWARD)
+        assert p and "chained launch" in lib.sprint_plan(p)
+        lib.execute(p)
+        lib.destroy_plan(p)
+        assert rel_l2(y, n * np.fft.ifft(x.astype(np.complex128), axis=1)) < tol(lib, n)
+        # batched long r2c (two passes + Hermitian split) and c2r (merge + two passes)
+        n, hm = 2 ** 15, 6
+        xr = rand_r(rng, (hm, n), lib)
+        yc = np.zeros((hm, n // 2 + 1), dtype=lib.cplx)
+        p = lib.plan_many_dft_r2c([n], hm, xr, None, 1, n, yc, None, 1, n // 2 + 1)
+        assert p and "chained launch" in lib.sprint_plan(p)
+        lib.execute(p)
+        lib.destroy_plan(p)
+        assert rel_l2(yc, np.fft.rfft(xr.astype(np.float64), axis=1)) < tol(lib, n)
+        z = np.zeros_like(xr)
+        p = lib.plan_many_dft_c2r([n], hm, yc, None, 1, n // 2 + 1, z, None, 1, n)
+        assert p and "chained launch" in lib.sprint_plan(p)
+        lib.execute(p)
+        lib.destroy_plan(p)
+        assert rel_l2(z, n * xr.astype(np.float64)) < 2 * tol(lib, n)
+    finally:
+        if old is None:
+            os.environ.pop("FFTW_B200_CHAIN", None)
+        else:
+            os.environ["FFTW_B200_CHAIN"] = old

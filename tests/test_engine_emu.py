@@ -74,3 +74,7 @@ def test_plan_description_and_flops(lib):
     add, mul, fma = lib.flops(p)
     assert abs((add + mul + fma) - 5 * 4096 * 12 * 4) < 1e-6
     lib.destroy_plan(p)
+
+
+def test_chained_launch_opt_in(lib):
+    cases.check_chained_launch(lib)

@@ -223,3 +223,8 @@ def test_host_arrays_go_through_the_chunked_pipeline(lib, howmany):
     lib.execute(p)
     lib.destroy_plan(p)
     assert cases.rel_l2(yr, np.fft.rfft(xr.astype(np.float64), axis=1)) < cases.tol(lib, n)
+
+
+def test_chained_launch_opt_in(lib):
+    """the single-launch chain (acquire/release between CTAs of one grid) gives the same answers"""
+    cases.check_chained_launch(lib)
