@@ -131,6 +131,21 @@ class FFTW3Lib:
                                                _ints(inembed), istride, idist, _ptr(out),
                                                _ints(onembed), ostride, odist, flags)
 
+    def plan_guru_dft(self, dims, howmany_dims, inp, out, sign, flags=FFTW_ESTIMATE):
+        """dims / howmany_dims: lists of (n, is, os) in complex elements (fftw_iodim, fftw3.h)"""
+        class IoDim(C.Structure):
+            _fields_ = [("n", C.c_int), ("is_", C.c_int), ("os", C.c_int)]
+        def arr(ds):
+            a = (IoDim * max(1, len(ds)))()
+            for i, (n, is_, os_) in enumerate(ds):
+                a[i].n, a[i].is_, a[i].os = n, is_, os_
+            return a
+        f = self.lib.fftw_plan_guru_dft
+        f.restype = _vp
+        f.argtypes = [C.c_int, _vp, C.c_int, _vp, _vp, _vp, C.c_int, C.c_uint]
+        d, h = arr(dims), arr(howmany_dims)
+        return f(len(dims), C.cast(d, _vp), len(howmany_dims), C.cast(h, _vp), _ptr(inp), _ptr(out), sign, flags)
+
     def plan_dft(self, n, inp, out, sign, flags=FFTW_ESTIMATE):
         return self.lib.fftw_plan_dft(len(n), _ints(n), _ptr(inp), _ptr(out), sign, flags)
 

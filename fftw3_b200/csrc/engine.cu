@@ -95,6 +95,7 @@ static int run_chain(b2fft_plan *p, const Chain &ch, real_t *const *buf, stream_
             c.epi = e.epi;
             c.pp = s.pp;
             b2_pp_prepare(c.pp);
+            c.pp.pf_ahead = 0;
         } else
             c.rp = s.rp;
     }

@@ -41,6 +41,8 @@ struct PassParams {
     // ---- tile-kernel decode helpers, filled by b2_pp_prepare() just before a launch ----
     unsigned dv_m[B2_MAXLD], dv_s[B2_MAXLD];  // exact division by tiles0 (slot 0) and ln[1..] for indices < 2^31
     int lgC;                                  // log2(C), or -1 when C is not a power of two
+    unsigned pf_ahead;                        // L2 prefetch distance in tiles (0: off)
+    long long nblocks;                        // tiles in the whole pass
 };
 
 // Division by an invariant d for 0 <= n < 2^31 (Granlund-Montgomery): with l = ceil(log2 d) and
@@ -59,6 +61,8 @@ inline void b2_pp_prepare(PassParams &p) {
     for (int d = 1; d < B2_MAXLD; ++d)
         b2_fastdiv_make((unsigned long long)(d < p.nld && p.ln[d] > 0 ? p.ln[d] : 1), p.dv_m[d], p.dv_s[d]);
     p.lgC = -1;
+    p.nblocks = (p.tiles0 > 0 ? p.tiles0 : 1);
+    for (int d = 1; d < p.nld; ++d) p.nblocks *= p.ln[d];
     for (int l = 0; l < 16; ++l)
         if ((1 << l) == p.C) p.lgC = l;
 }

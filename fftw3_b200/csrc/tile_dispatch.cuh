@@ -17,11 +17,30 @@ struct TileEntry {
 template <int N, int E, int MODE, bool EPI, int C>
 struct TileInst {
     static constexpr int THREADS = C * (N / E);
-    static constexpr int MINB = THREADS <= 128 ? 6 : THREADS <= 256 ? B2_MINB256 : THREADS <= 512 ? 2 : 1;
+    static constexpr int MINB = E >= 32 ? (THREADS <= 256 ? 2 : 1)
+                                        : THREADS <= 128 ? 6 : THREADS <= 256 ? B2_MINB256 : THREADS <= 512 ? 2 : 1;
     static int launch(const PassParams &p, const real_t *src, real_t *dst, long long b0, long long nb,
                       int threads, size_t smem, b2::stream_t st) {
 #if B2_CUDA
-        b2_tile_kernel<N, E, MODE, EPI, THREADS, MINB><<<(unsigned)nb, threads, smem, st>>>(p, src, dst, b0);
+        // L2 prefetch distance: the tile whose CTA will take over this CTA's slot (one wave on)
+        static int wave = -1;
+        if (wave < 0) {
+            int occ = 1;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b2_tile_kernel<N, E, MODE, EPI, THREADS, MINB>,
+                                                              threads, smem) != cudaSuccess || occ < 1) {
+                cudaGetLastError();
+                occ = 1;
+            }
+            wave = occ * b2::sm_count();
+            if (const char *e = getenv("FFTW_B200_PF")) wave = atoi(e) < 0 ? 0 : atoi(e);
+        }
+        // Measured on B200 (profiles/r1_axis_probe.md): the hint pays for short rows and for column
+        // tiles with a moderate axis stride (+5..9 %), and costs 2..13 % for long rows and for
+        // strides of MiBs (a TLB miss per hint) -- so it is only switched on where it pays.
+        const bool pays = (MODE == MODE_COL) ? (p.s_axis * (long long)sizeof(real_t) < (1ll << 20)) : (N <= 128);
+        PassParams q = p;
+        q.pf_ahead = (pays || getenv("FFTW_B200_PF")) ? (unsigned)wave : 0u;
+        b2_tile_kernel<N, E, MODE, EPI, THREADS, MINB><<<(unsigned)nb, threads, smem, st>>>(q, src, dst, b0);
         return 0;
 #else
         (void)st;
@@ -47,14 +66,30 @@ struct TileInst {
 #define B2_TILE_ALLMODES(X, N, E, CROW, CCOL) \
     X(N, E, MODE_ROW, false, CROW) X(N, E, MODE_COL, false, CCOL) X(N, E, MODE_COL, true, CCOL) \
     X(N, E, MODE_ROW2COL, false, CCOL)
+// column-tile widths of the long column kernels (lines per CTA); overridable for experiments
+#ifndef B2_CC512
+#define B2_CC512 16
+#endif
+#ifndef B2_CC1024
+#define B2_CC1024 16
+#endif
+#ifndef B2_CC2048
+#define B2_CC2048 8
+#endif
+#ifndef B2_E512
+#define B2_E512 16
+#endif
+#ifndef B2_E1024
+#define B2_E1024 16
+#endif
 #if defined(FFTW_SINGLE)
 #define B2_TILE_LIST(X)                   \
     B2_TILE_ALLMODES(X, 64, 8, 32, 16)    \
     B2_TILE_ALLMODES(X, 128, 8, 16, 16)   \
     B2_TILE_ALLMODES(X, 256, 16, 16, 16)  \
-    B2_TILE_ALLMODES(X, 512, 16, 8, 16)   \
-    B2_TILE_ALLMODES(X, 1024, 16, 4, 16)  \
-    B2_TILE_ALLMODES(X, 2048, 16, 2, 8)   \
+    B2_TILE_ALLMODES(X, 512, B2_E512, 8, B2_CC512)   \
+    B2_TILE_ALLMODES(X, 1024, B2_E1024, 4, B2_CC1024)  \
+    B2_TILE_ALLMODES(X, 2048, 16, 2, B2_CC2048)   \
     X(4096, 16, MODE_ROW, false, 1) X(8192, 16, MODE_ROW, false, 1)
 #else
 #define B2_TILE_LIST(X)                 \
@@ -126,5 +161,6 @@ inline int b2_launch_tile_kernel(int id, const PassParams &p, const real_t *src,
                                  long long nb, int threads, size_t smem, b2::stream_t st) {
     PassParams q = p;
     b2_pp_prepare(q);
+    q.pf_ahead = 0;
     return b2_tile_table()[id].launch(q, src, dst, b0, nb, threads, smem, st);
 }

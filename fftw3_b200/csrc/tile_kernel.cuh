@@ -27,7 +27,8 @@ constexpr int b2_ilog2(int v) { return v <= 1 ? 0 : 1 + b2_ilog2(v / 2); }
 
 template <int N, int E> struct TileSched {
     static constexpr int LOGN = b2_ilog2(N), LOGE = b2_ilog2(E);
-    static constexpr int NP = (LOGN + LOGE - 1) / LOGE;
+    static constexpr int LOGR = LOGE < 4 ? LOGE : 4;  // butterflies up to radix 16 (butterfly.cuh)
+    static constexpr int NP = (LOGN + LOGR - 1) / LOGR;
     static constexpr int bits(int i) { return (LOGN + (NP - 1 - i)) / NP; }
     static constexpr int radix(int i) { return 1 << bits(i); }
     static constexpr int ns(int i) { return i == 0 ? 1 : ns(i - 1) * radix(i - 1); }
@@ -68,6 +69,15 @@ B2_D cpx_t b2_ldcg(const cpx_t *p) {
     }
 #else
     return *p;
+#endif
+}
+
+// L2 prefetch hint for the 128-byte line holding *p
+B2_D void b2_prefetch_l2(const void *p) {
+#if B2_CUDA
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+    (void)p;
 #endif
 }
 
@@ -122,6 +132,27 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
             t = tid - c * T;
         }
         return true;
+    }
+
+    // tile index -> coordinates: exact multiply-shift divisions (b2_pp_prepare), 31-bit index
+    static B2_D void decode(const PassParams &p, unsigned bid, long long &l0, int &nlines, long long &sbase,
+                            long long &dbase, int &i2base) {
+        const int C = p.C;
+        unsigned rest = b2_fastdiv(bid, p.dv_m[0], p.dv_s[0]);
+        const unsigned t0 = bid - rest * (unsigned)p.tiles0;
+        l0 = (long long)t0 * C;
+        nlines = (int)((p.ln[0] - l0 < C) ? (p.ln[0] - l0) : C);
+        sbase = 0;
+        dbase = 0;
+        i2base = 0;
+        for (int d = 1; d < p.nld; ++d) {
+            const unsigned qd = b2_fastdiv(rest, p.dv_m[d], p.dv_s[d]);
+            const unsigned cc = rest - qd * (unsigned)p.ln[d];
+            rest = qd;
+            sbase += (long long)cc * p.ls[d];
+            dbase += (long long)cc * p.ld[d];
+            if (d == p.epi_dim) i2base = (int)cc;
+        }
     }
 
     template <int P> static B2_D void butterflies(const TileCtx &x, cpx_t *v, int c, int t, bool active) {
@@ -196,22 +227,7 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
         x.vbase = vreg_store.data();
 #endif
         const int C = p.C;
-        // tile index -> coordinates: exact multiply-shift divisions (b2_pp_prepare), 31-bit index
-        unsigned rest = b2_fastdiv((unsigned)bid, p.dv_m[0], p.dv_s[0]);
-        const unsigned t0 = (unsigned)bid - rest * (unsigned)p.tiles0;
-        x.l0 = (long long)t0 * C;
-        x.nlines = (int)((p.ln[0] - x.l0 < C) ? (p.ln[0] - x.l0) : C);
-        x.sbase = 0;
-        x.dbase = 0;
-        x.i2base = 0;
-        for (int d = 1; d < p.nld; ++d) {
-            const unsigned qd = b2_fastdiv(rest, p.dv_m[d], p.dv_s[d]);
-            const unsigned cc = rest - qd * (unsigned)p.ln[d];
-            rest = qd;
-            x.sbase += (long long)cc * p.ls[d];
-            x.dbase += (long long)cc * p.ld[d];
-            if (d == p.epi_dim) x.i2base = (int)cc;
-        }
+        decode(p, (unsigned)bid, x.l0, x.nlines, x.sbase, x.dbase, x.i2base);
         const cpx_t *csrc = reinterpret_cast<const cpx_t *>(src);
         cpx_t *cdst = reinterpret_cast<cpx_t *>(dst);
 
@@ -221,6 +237,31 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
             int c, t;
             const bool live = map(tid, C, p.lgC, c, t);
             const bool active = live && c < x.nlines;
+            // While a tile is being transformed nothing of its CTA is in flight to HBM: ask L2 now
+            // for the tile that the CTA taking over this slot will load (pf_ahead tiles on), one
+            // hint per 128-byte line of that tile.
+            if (p.pf_ahead > 0 && (unsigned long long)bid + p.pf_ahead < (unsigned long long)p.nblocks) {
+                long long nl0, nsb, ndb;
+                int nnl, ni2;
+                decode(p, (unsigned)bid + p.pf_ahead, nl0, nnl, nsb, ndb, ni2);
+                constexpr int PER = 128 / (int)sizeof(cpx_t);  // points per 128-byte line
+                const cpx_t *nb = csrc + (nsb + nl0 * p.ls[0]) / 2;
+                if (COLMAP) {
+                    const int spr = (nnl + PER - 1) / PER;  // 128-byte lines per point row, usually 1
+                    const long long as = p.s_axis / 2;
+                    for (int s = tid; s < N * spr; s += B2_NTHREADS) {
+                        const int k = spr == 1 ? s : s / spr, j = s - k * spr;
+                        b2_prefetch_l2(nb + (long long)k * as + j * PER);
+                    }
+                } else {
+                    constexpr int SPL = N / PER;  // 128-byte lines per (contiguous) line of the tile
+                    const long long lstep = p.ls[0] / 2;
+                    for (int s = tid; s < nnl * SPL; s += B2_NTHREADS) {
+                        const int c2 = s / SPL, j = s - c2 * SPL;
+                        b2_prefetch_l2(nb + (long long)c2 * lstep + j * PER);
+                    }
+                }
+            }
             if (active) {
                 // all strides are in reals and even here (vector access was checked by the selector)
                 const long long as = p.s_axis / 2;
@@ -315,17 +356,21 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
                     const int pk = phys(k0);
                     cpx_t *ps = cdst + (base + (long long)c * lstep + (long long)k0 * ds);
                     const long long step = (long long)T * ds;
-                    cpx_t a[E];
+                    constexpr int H = E / 2;  // two half batches: 16 values in flight would spill
 #pragma unroll
-                    for (int q = 0; q < E; ++q) a[q] = sp[phys_k<T, 0>(k0, pk, q)];
-                    if (p.swap_out) {
+                    for (int h = 0; h < 2; ++h) {
+                        cpx_t a[H];
 #pragma unroll
-                        for (int q = 0; q < E; ++q) a[q] = cswap(a[q]);
-                    }
+                        for (int q = 0; q < H; ++q) a[q] = sp[phys_k<T, 0>(k0, pk, h * H + q)];
+                        if (p.swap_out) {
 #pragma unroll
-                    for (int q = 0; q < E; ++q) {
-                        *ps = a[q];
-                        ps += step;
+                            for (int q = 0; q < H; ++q) a[q] = cswap(a[q]);
+                        }
+#pragma unroll
+                        for (int q = 0; q < H; ++q) {
+                            *ps = a[q];
+                            ps += step;
+                        }
                     }
                 } else {
                     for (int idx = tid; idx < nl * N; idx += B2_NTHREADS) {
