@@ -10,6 +10,7 @@
 #include "plan_build_real.h"
 #include "plan_struct.h"
 #include "realpp_kernel.cuh"
+#include "blue_kernel.cuh"
 #include "chain_build.h"
 
 using namespace b2;
@@ -47,6 +48,12 @@ static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream
 #else
                 std::vector<char> sm(smem + 64);
                 for (long long b = 0; b < nb; ++b) b2_generic_pass_body(pp, sp, dp, b0 + b, sm.data(), s.gen_threads);
+#endif
+            } else if (s.kind == SK_BLUE) {
+#if B2_CUDA
+                b2_blue_kernel<<<(unsigned)nb, s.nthreads, 0, stream>>>(s.bp, sp, dp, b0);
+#else
+                for (long long b = 0; b < nb; ++b) b2_blue_body(s.bp, sp, dp, b0 + b, s.nthreads);
 #endif
             } else {
 #if B2_CUDA
@@ -103,7 +110,7 @@ static int run_chain(b2fft_plan *p, const Chain &ch, real_t *const *buf, stream_
 }
 
 static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
-    real_t *buf[3] = {in, out, p->scr};
+    real_t *buf[B_NBUF] = {in, out, p->scr, p->wrk};
     const bool aligned = ((uintptr_t)in % sizeof(cpx_t)) == 0 && ((uintptr_t)out % sizeof(cpx_t)) == 0;
     const size_t ns = p->pc.steps.size();
     for (size_t i = 0; i < ns; ++i) {
@@ -162,6 +169,10 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
             p->scr = (real_t *)dev_malloc((size_t)p->pc.scr_reals * sizeof(real_t));
             if (!p->scr) ok = false;
         }
+        if (ok && p->pc.wrk_reals > 0) {
+            p->wrk = (real_t *)dev_malloc((size_t)p->pc.wrk_reals * sizeof(real_t));
+            if (!p->wrk) ok = false;
+        }
         p->chains = new std::vector<Chain>();
         build_chains(p->pc.steps, *p->chains);
         for (Chain &ch : *p->chains) {
@@ -178,7 +189,7 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
         return nullptr;
     }
     std::string d;
-    static const char *bn[] = {"in", "out", "scratch"};
+    static const char *bn[] = {"in", "out", "scratch", "work"};
     for (size_t i = 0; i < p->pc.steps.size(); ++i) {
         const StepPlan &s = p->pc.steps[i];
         d += "  pass " + std::to_string(i) + ": " + s.desc + " [" + bn[s.src] + "->" + bn[s.dst] + "]";
@@ -205,6 +216,7 @@ extern "C" void b2fft_plan_destroy(b2fft_plan *p) {
         delete p->chains;
     }
     dev_free(p->scr);
+    dev_free(p->wrk);
     dev_free(p->dev_in);
     dev_free(p->dev_out);
 #if B2_CUDA
@@ -354,12 +366,12 @@ extern "C" int b2fft_execute(b2fft_plan *p, void *in, void *out) {
 extern "C" int b2fft_plan_num_passes(const b2fft_plan *p) { return p ? (int)p->pc.steps.size() : 0; }
 extern "C" int b2fft_plan_num_hbm_sweeps(const b2fft_plan *p) { return p ? (int)p->pc.steps.size() : 0; }
 extern "C" size_t b2fft_plan_scratch_bytes(const b2fft_plan *p) {
-    return p ? (size_t)p->pc.scr_reals * sizeof(real_t) : 0;
+    return p ? (size_t)(p->pc.scr_reals + p->pc.wrk_reals) * sizeof(real_t) : 0;
 }
 extern "C" int b2fft_plan_describe(const b2fft_plan *p, char *buf, size_t n) {
     if (!p) return 0;
     return snprintf(buf, n, "b200fft %s plan, %zu kernel pass(es), scratch %zu bytes\n%s", B2_PREC_NAME,
-                    p->pc.steps.size(), (size_t)p->pc.scr_reals * sizeof(real_t), p->pc.desc.c_str());
+                    p->pc.steps.size(), (size_t)(p->pc.scr_reals + p->pc.wrk_reals) * sizeof(real_t), p->pc.desc.c_str());
 }
 extern "C" double b2fft_plan_flops(const b2fft_plan *p) { return p ? p->pc.flops : 0.0; }
 extern "C" unsigned long long b2fft_launch_count(void) { return launch_counter(); }
@@ -393,5 +405,8 @@ extern "C" int b2fft_set_device(int d) {
 #endif
 }
 extern "C" const char *b2fft_last_error(void) { return last_error().c_str(); }
-extern "C" void b2fft_cleanup(void) { twiddles().clear(); }
+extern "C" void b2fft_cleanup(void) {
+    twiddles().clear();
+    blue_tables().clear();
+}
 extern "C" const char *b2fft_precision(void) { return B2_PREC_NAME; }

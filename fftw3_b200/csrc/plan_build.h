@@ -7,6 +7,7 @@
 #include <math.h>
 
 #include "b200fft.h"
+#include "blue_tables.h"
 #include "selector.h"
 
 struct b2fft_comm_s;
@@ -27,6 +28,7 @@ struct PlanCore {
     long long out_reals = 0;
     long long in_dense = 0, out_dense = 0;  // reals actually touched
     long long scr_reals = 0;
+    long long wrk_reals = 0;    // second plan-owned work array (Bluestein rows)
     double flops = 0;
     std::string desc;
 };
@@ -60,6 +62,16 @@ inline bool split_four_step(long long n, long long *n1o, long long *n2o) {
 }
 
 inline long long dst_extent(const StepPlan &s) {
+    if (s.kind == SK_BLUE) {
+        const BlueParams &b = s.bp;
+        long long lines = 1, e = 0;
+        for (int d = 0; d < b.nld; ++d) {
+            lines *= b.ln[d];
+            e += (b.ln[d] - 1) * b.ld[d];
+        }
+        if (b.mode != 2) return lines * b.M * 2;
+        return e + (long long)(b.nout - 1) * b.d_axis + (b.dst_real ? 1 : 2);
+    }
     if (s.kind != SK_PASS) {
         long long e = (long long)s.rp.m * s.rp.d_axis + 2;
         for (int d = 0; d < s.rp.nld; ++d) e += (s.rp.ln[d] - 1) * s.rp.ld[d];
@@ -78,6 +90,102 @@ inline bool lines_same(const std::vector<LDim> &L) {
     return true;
 }
 
+inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long d_axis,
+                         const std::vector<LDim> &lines, bool swap_in, bool swap_out,
+                         const std::vector<int> &dst_allowed);
+
+inline bool axis_direct_ok(long long n, bool row) {
+    const Caps c = caps();
+    if (n <= (row ? c.row : c.col)) return factorable(n);
+    long long a, b;
+    return split_four_step(n, &a, &b);
+}
+
+struct BlueSpec {
+    long long n = 0;
+    long long s_axis = 2, d_axis = 2;  // reals
+    bool src_real = false, dst_real = false, herm_in = false;
+    long long nout = 0;                // 0: n
+    bool swap_in = false, swap_out = false;
+    std::vector<LDim> lines;           // (src, dst) strides in reals
+};
+
+// One axis by Bluestein's algorithm: chirp-in to dense rows of M = 2^k >= 2n-1 in a plan-owned
+// work array, FFT_M, multiply by bhat, inverse FFT_M, chirp-out to the destination layout.
+inline bool add_bluestein_axis(PlanCore &pc, const BlueSpec &b, const std::vector<int> &dst_allowed) {
+    const long long n = b.n;
+    long long M = 1;
+    while (M < 2 * n - 1) M *= 2;
+    if (!axis_direct_ok(M, true)) {
+        set_error("length %lld: the Bluestein convolution length %lld is beyond the engine's limit", n, M);
+        return false;
+    }
+    BlueParams bp;
+    memset(&bp, 0, sizeof bp);
+    bp.n = (int)n;
+    bp.M = (int)M;
+    bp.nin = b.herm_in ? (int)(n / 2 + 1) : (int)n;
+    bp.nout = (int)(b.nout ? b.nout : n);
+    bp.src_real = b.src_real;
+    bp.dst_real = b.dst_real;
+    bp.herm_in = b.herm_in;
+    bp.swap_in = b.swap_in;
+    bp.swap_out = b.swap_out;
+    bp.s_axis = b.s_axis;
+    bp.d_axis = b.d_axis;
+    long long L = 1;
+    for (const LDim &l : b.lines) {
+        if (l.n <= 1) continue;
+        if (bp.nld >= B2_BLUE_MAXLD) {
+            set_error("Bluestein axis with more than %d batch dimensions", B2_BLUE_MAXLD);
+            return false;
+        }
+        bp.ln[bp.nld] = l.n;
+        bp.ls[bp.nld] = l.s;
+        bp.ld[bp.nld] = l.d;
+        ++bp.nld;
+        L *= l.n;
+    }
+    bp.chirp = blue_tables().chirp((unsigned long long)n);
+    bp.bhat = blue_tables().bhat((unsigned long long)n, (unsigned long long)M);
+    if (!bp.chirp || !bp.bhat) return false;
+    auto mk = [&](int mode, const char *what) {
+        StepPlan st;
+        st.kind = SK_BLUE;
+        st.bp = bp;
+        st.bp.mode = mode;
+        const long long len = mode == 2 ? bp.nout : M;
+        st.nblocks = L * ((len + 1023) / 1024);
+        st.nthreads = 256;
+        st.smem = 0;
+        char buf[160];
+        snprintf(buf, sizeof buf, "bluestein %s n=%lld M=%lld lines=%lld ctas=%lld", what, n, M, L, st.nblocks);
+        st.desc = buf;
+        return st;
+    };
+    const std::vector<int> work = {B_WRK, B_SCR};
+    {
+        StepPlan st = mk(0, "chirp-in");
+        st.dst_allowed = work;
+        pc.steps.push_back(st);
+    }
+    const std::vector<LDim> rows = {LDim{L, 2 * M, 2 * M, false}};
+    if (!add_c2c_axis(pc, M, 2, 2, rows, false, false, work)) return false;
+    {
+        StepPlan st = mk(1, "multiply");
+        st.inplace_ok = true;
+        st.dst_allowed = work;
+        pc.steps.push_back(st);
+    }
+    if (!add_c2c_axis(pc, M, 2, 2, rows, true, true, work)) return false;
+    {
+        StepPlan st = mk(2, "chirp-out");
+        st.dst_allowed = dst_allowed;
+        pc.steps.push_back(st);
+    }
+    return true;
+}
+
 // Append the step(s) for one complex axis.  `lines` carry (src, dst) strides in reals.
 // first/last: whether the backward swap is applied on the way in / out.
 inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long d_axis,
@@ -86,6 +194,16 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
     const Caps c = caps();
     const bool row = (s_axis <= 2 && d_axis <= 2);
     const long long cap = row ? c.row : c.col;
+    if (!axis_direct_ok(n, row)) {
+        BlueSpec b;
+        b.n = n;
+        b.s_axis = s_axis;
+        b.d_axis = d_axis;
+        b.swap_in = swap_in;
+        b.swap_out = swap_out;
+        b.lines = lines;
+        return add_bluestein_axis(pc, b, dst_allowed);
+    }
     if (n <= cap) {
         AxisSpec a;
         a.n = (int)n;
@@ -189,11 +307,13 @@ inline bool assign_buffers(PlanCore &pc) {
     }
     int state = norm(B_IN);
     pc.scr_reals = 0;
+    pc.wrk_reals = 0;
     for (int i = 0; i < ns; ++i) {
         pc.steps[i].src = state;
         pc.steps[i].dst = best[i];
         state = best[i];
         if (best[i] == B_SCR) pc.scr_reals = std::max(pc.scr_reals, dst_extent(pc.steps[i]));
+        if (best[i] == B_WRK) pc.wrk_reals = std::max(pc.wrk_reals, dst_extent(pc.steps[i]));
     }
     return true;
 }

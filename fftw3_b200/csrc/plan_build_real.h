@@ -187,7 +187,27 @@ inline bool build_real(PlanCore &pc) {
     if (!r2c && !leading_axes(true)) return false;
     const size_t first_real_step = pc.steps.size();
 
-    if (even && m <= cap) {
+    // lengths the radix kernels cannot do (a prime factor > 13, or odd and longer than one CTA's
+    // line): Bluestein on the full length, reading the real / Hermitian-half line directly
+    const bool direct_ok = even ? axis_direct_ok(m, unit_rows) : (nl <= cap && factorable(nl));
+    if (!direct_ok) {
+        BlueSpec b;
+        b.n = nl;
+        b.lines = rl;
+        if (r2c) {
+            b.src_real = true;
+            b.s_axis = T[L].is;
+            b.d_axis = 2 * T[L].os;
+            b.nout = hc;
+        } else {
+            b.herm_in = true;
+            b.dst_real = true;
+            b.s_axis = 2 * T[L].is;
+            b.d_axis = T[L].os;
+            b.swap_in = b.swap_out = true;
+        }
+        if (!add_bluestein_axis(pc, b, {B_OUT})) return false;
+    } else if (even && m <= cap) {
         AxisSpec a;
         a.n = (int)nl;
         a.rmode = r2c ? RM_R2C_HALF : RM_C2R_HALF;

@@ -24,6 +24,7 @@ struct HostPipe {
 struct b2fft_plan_s {
     b2::PlanCore pc;
     real_t *scr = nullptr;
+    real_t *wrk = nullptr;  // second work array (Bluestein rows), pc.wrk_reals
     // device staging for host-pointer executes (allocated on first use)
     real_t *dev_in = nullptr, *dev_out = nullptr;
     b2::stream_t stream = nullptr;

@@ -14,8 +14,8 @@
 
 namespace b2 {
 
-enum Buf { B_IN = 0, B_OUT = 1, B_SCR = 2 };
-enum StepKind { SK_PASS = 0, SK_RPOST = 1, SK_RPRE = 2 };
+enum Buf { B_IN = 0, B_OUT = 1, B_SCR = 2, B_WRK = 3, B_NBUF = 4 };  // SCR, WRK: plan-owned work arrays
+enum StepKind { SK_PASS = 0, SK_RPOST = 1, SK_RPRE = 2, SK_BLUE = 3 };
 
 // one line (batch) dimension of an axis pass; strides in reals
 struct LDim {
@@ -33,10 +33,27 @@ struct RealPPParams {
     int pts_per_block;     // pairs (k, m-k) handled by one CTA
 };
 
+// element-wise steps of Bluestein's algorithm (blue_kernel.cuh)
+#define B2_BLUE_MAXLD 8
+struct BlueParams {
+    int mode;          // 0 chirp-in, 1 multiply by bhat, 2 chirp-out
+    int n, M;          // transform length, convolution length
+    int nin;           // points stored in the source line: n, or n/2+1 for a Hermitian half
+    int nout;          // points written per line by chirp-out: n, or n/2+1 (r2c)
+    int src_real, dst_real, herm_in;
+    int swap_in, swap_out;     // backward transform = swap re/im going in and coming out
+    long long s_axis, d_axis;  // stride between consecutive points, in reals, of the user arrays
+    int nld;
+    long long ln[B2_BLUE_MAXLD], ls[B2_BLUE_MAXLD], ld[B2_BLUE_MAXLD];  // line dims, strides in reals
+    const cpx_t *chirp;  // c[j] = exp(-i pi j^2 / n), j < n
+    const cpx_t *bhat;   // FFT_M(conj(c) wrapped) / M
+};
+
 struct Step {
     int kind = SK_PASS;
     PassParams pp;
     RealPPParams rp;
+    BlueParams bp;
     int src = B_IN, dst = B_OUT;
     bool inplace_ok = false;  // same locations read and written per CTA
     bool reads_input_layout = false;

@@ -46,6 +46,9 @@ C2C_BIG = [(8192,), (16384,), (3 * 2 ** 13,), (2 ** 17,), (64, 64, 64), (4, 2 **
 R2C_SHAPES = [(2,), (4,), (6,), (7,), (9,), (16,), (30,), (64,), (1024,), (6, 8), (5, 9), (4, 4, 6),
               (3, 5, 7)]
 R2C_BIG = [(4096,), (2 ** 15,), (2 ** 17,), (3, 2 ** 14), (32, 32, 32)]
+# lengths with a prime factor > 13 (Bluestein path), alone and inside multi-dimensional transforms
+C2C_PRIME = [(17,), (19,), (97,), (34,), (1009,), (4099,), (2 * 8191,), (3, 23), (29, 8), (5, 31, 6), (127, 127)]
+R2C_PRIME = [(17,), (34,), (97,), (1009,), (2018,), (4, 46), (3, 5, 38), (37, 6), (10007,)]
 
 
 def check_c2c(lib, shape, seed=0):
@@ -219,11 +222,14 @@ def check_edge_cases(lib):
     lib.execute_dft(p, u2, v2)
     lib.destroy_plan(p)
     assert rel_l2(v2, np.fft.fft(u2.astype(np.complex128))) < tol(lib, 64)
-    # a length with a prime factor the radix set does not cover yet -> NULL plan, not garbage
-    w = np.zeros(17, dtype=lib.cplx)
-    p = lib.plan_dft_1d(17, w, w.copy(), -1)
-    if p:
-        lib.destroy_plan(p)
+    # a length with a prime factor > 13 goes through the Bluestein path (reference: dft-bluestein,
+    # fftw_api.c:1643-1688) -- a plan, and the same answer
+    w, wo = rand_c(rng, 17, lib), np.zeros(17, dtype=lib.cplx)
+    p = lib.plan_dft_1d(17, w, wo, -1)
+    assert p and "bluestein" in lib.sprint_plan(p)
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(wo, np.fft.fft(w.astype(np.complex128))) < 4 * tol(lib, 17)
 
 
 def check_properties(lib, shape, seed=7):

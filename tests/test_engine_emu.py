@@ -18,12 +18,12 @@ def lib(request):
     return capi.FFTW3Lib(path, request.param == "fp32")
 
 
-@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG, ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG + cases.C2C_PRIME, ids=lambda s: "x".join(map(str, s)))
 def test_c2c(lib, shape):
     cases.check_c2c(lib, shape)
 
 
-@pytest.mark.parametrize("shape", cases.R2C_SHAPES + cases.R2C_BIG, ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("shape", cases.R2C_SHAPES + cases.R2C_BIG + cases.R2C_PRIME, ids=lambda s: "x".join(map(str, s)))
 def test_r2c_c2r(lib, shape):
     cases.check_r2c_c2r(lib, shape)
 

@@ -26,14 +26,14 @@ def lib(request):
     return L
 
 
-@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG, ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG + cases.C2C_PRIME, ids=lambda s: "x".join(map(str, s)))
 def test_c2c(lib, shape):
     n0 = lib.lib.b2fft_launch_count()
     cases.check_c2c(lib, shape)
     assert lib.lib.b2fft_launch_count() > n0, "no CUDA kernel was launched"
 
 
-@pytest.mark.parametrize("shape", cases.R2C_SHAPES + cases.R2C_BIG, ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("shape", cases.R2C_SHAPES + cases.R2C_BIG + cases.R2C_PRIME, ids=lambda s: "x".join(map(str, s)))
 def test_r2c_c2r(lib, shape):
     cases.check_r2c_c2r(lib, shape)
 

@@ -19,7 +19,9 @@ REF = os.path.join(ROOT, "oracle", "_ref")
 PROBLEMS = ["icf1024", "ocf4096", "ocb4096", "orf1024", "orb1024", "irf1024", "icf16x16x16", "ocf64*8",
             "ib256", "orf30", "ocb100x12", "irf16x10", "obr12x6x4", "ocf13*3", "if7x5x3", "ocf8192",
             "ocf16384", "orf32768", "ocf64x64x64", "icf256*16", "obr128x64", "ocf3x5x7x2", "ocf1",
-            "orf2", "icb2x2", "ocf1000", "ocf512*12", "ocf2048*3", "irb64x66"]
+            "orf2", "icb2x2", "ocf1000", "ocf512*12", "ocf2048*3", "irb64x66",
+            # prime factors > 13: Bluestein path
+            "ocf17", "icb97", "orf34", "obr46", "ocf1009", "ocf23x29", "irf37x6", "ocf127*5"]
 
 
 def run(binary, args):
