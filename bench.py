@@ -102,7 +102,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.02)
+            self._stop.wait(0.002)  # the timed region of the default workload is ~15 ms
 
     def __enter__(self):
         if self.nv:
@@ -344,6 +344,14 @@ def run_gpu(args):
         if cpu:
             cpu.pop("ms_per_step", None)
     if rank == 0:
+        traffic = traffic_note = None
+        try:  # measured DRAM bytes per launch of the dominant kernel (one ncu --set full capture, profiles/)
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                t = json.load(f).get(args.workload)
+            if t:
+                traffic, traffic_note = t["dram_bytes_per_launch"], "%s, %s" % (t["kernel"], t["source"])
+        except (OSError, ValueError, KeyError):
+            pass
         line = {
             "metric": "FFTW-convention GFLOP/s (5 N log2 N / t), fftw_execute",
             "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
@@ -356,8 +364,8 @@ def run_gpu(args):
                        if nbytes > 512e6 else "working set fits L2 (latency-bound config)",
                        "global_passes": int(npasses), "sharding": "batch split across ranks, no collective"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes_per_step": nbytes, "kernels_per_step": launches / args.steps,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_note,
+                         "peak_source": peak_src, "algorithmic_bytes_per_step": nbytes, "kernels_per_step": launches / args.steps,
                          "median_step_ms": per[len(per) // 2], "min_step_ms": per[0]},
             "clocks": clk.summary(),
             "gpu_launches": launches,
