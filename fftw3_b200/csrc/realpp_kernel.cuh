@@ -25,31 +25,47 @@ B2_D void b2_realpp_body(const b2::RealPPParams &p, int post, const real_t *src,
     B2_FOR_THREADS {
         const int m = p.m;
         const int kend = (chunk + 1) * p.pts_per_block < hk ? (chunk + 1) * p.pts_per_block : hk;
-        for (int k = chunk * p.pts_per_block + tid; k < kend; k += B2_NTHREADS) {
-            const cpx_t *S = reinterpret_cast<const cpx_t *>(src + so);
-            // strides are in reals and even for complex arrays
-            const long long ss = p.s_axis / 2, ds = p.d_axis / 2;
-            cpx_t *D = reinterpret_cast<cpx_t *>(dst + dof);
-            if (post) {
-                if (k == 0) {
-                    const cpx_t z0 = b2_ldcg(S);
-                    D[0] = cpx_t{z0.x + z0.y, (real_t)0};
-                    D[(long long)m * ds] = cpx_t{z0.x - z0.y, (real_t)0};
-                } else {
-                    const cpx_t zk = b2_ldcg(S + (long long)k * ss), zc = cconj(b2_ldcg(S + (long long)(m - k) * ss));
-                    const cpx_t E = cscale(cadd(zk, zc), (real_t)0.5);
-                    const cpx_t O = cmul_mi(cscale(csub(zk, zc), (real_t)0.5));
-                    const cpx_t wO = cmul(p.twr[k], O);
-                    D[(long long)k * ds] = cadd(E, wO);
-                    if (k != m - k) D[(long long)(m - k) * ds] = cconj(csub(E, wO));
+        const cpx_t *S = reinterpret_cast<const cpx_t *>(src + so);
+        cpx_t *D = reinterpret_cast<cpx_t *>(dst + dof);
+        // strides are in reals and even for complex arrays
+        const long long ss = p.s_axis / 2, ds = p.d_axis / 2;
+        constexpr int U = 4;  // pairs in flight per thread: all loads are issued before the first use
+        for (int k0 = chunk * p.pts_per_block + tid; k0 < kend; k0 += U * B2_NTHREADS) {
+            cpx_t zk[U], zc[U], w[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int k = k0 + u * B2_NTHREADS;
+                if (k < kend) {
+                    zk[u] = b2_ldcg(S + (long long)k * ss);
+                    zc[u] = b2_ldcg(S + (long long)(m - k) * ss);
+                    w[u] = p.twr[k];
                 }
-            } else {
-                const cpx_t A = b2_ldcg(S + (long long)k * ss), B = cconj(b2_ldcg(S + (long long)(m - k) * ss));
-                const cpx_t sum = cadd(A, B), dif = csub(A, B);
-                const cpx_t Dd = cmul_pi(cmul(cconj(p.twr[k]), dif));
-                const cpx_t zk = cadd(sum, Dd), zmk = cconj(csub(sum, Dd));
-                D[(long long)k * ds] = cswap(zk);
-                if (k != 0 && k != m - k) D[(long long)(m - k) * ds] = cswap(zmk);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int k = k0 + u * B2_NTHREADS;
+                if (k >= kend) continue;
+                if (post) {
+                    if (k == 0) {
+                        const cpx_t z0 = zk[u];
+                        D[0] = cpx_t{z0.x + z0.y, (real_t)0};
+                        D[(long long)m * ds] = cpx_t{z0.x - z0.y, (real_t)0};
+                    } else {
+                        const cpx_t a = zk[u], b = cconj(zc[u]);
+                        const cpx_t E = cscale(cadd(a, b), (real_t)0.5);
+                        const cpx_t O = cmul_mi(cscale(csub(a, b), (real_t)0.5));
+                        const cpx_t wO = cmul(w[u], O);
+                        D[(long long)k * ds] = cadd(E, wO);
+                        if (k != m - k) D[(long long)(m - k) * ds] = cconj(csub(E, wO));
+                    }
+                } else {
+                    const cpx_t A = zk[u], B = cconj(zc[u]);
+                    const cpx_t sum = cadd(A, B), dif = csub(A, B);
+                    const cpx_t Dd = cmul_pi(cmul(cconj(w[u]), dif));
+                    const cpx_t z1 = cadd(sum, Dd), z2 = cconj(csub(sum, Dd));
+                    D[(long long)k * ds] = cswap(z1);
+                    if (k != 0 && k != m - k) D[(long long)(m - k) * ds] = cswap(z2);
+                }
             }
         }
     }
