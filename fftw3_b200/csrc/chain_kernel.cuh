@@ -49,7 +49,7 @@ B2_D void b2_chain_run_step(const ChainStep &s, long long bid, char *smem, int b
     if (s.kind == b2::SK_PASS) {
         const PassParams &pp = s.pp;
 #define B2_X_RUN(N, E, MODE, EPI, C)                                                        \
-    if (pp.m == N && s.mode == MODE && s.epi == (EPI ? 1 : 0)) {                            \
+    if (pp.m == N && s.mode == MODE && s.epi == (int)(EPI)) {                            \
         TileFFT<N, E, MODE, EPI>::run(pp, s.src, s.dst, bid, smem, b2_nthreads);            \
         return;                                                                             \
     }

@@ -112,6 +112,17 @@ static int run_chain(b2fft_plan *p, const Chain &ch, real_t *const *buf, stream_
 static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
     real_t *buf[B_NBUF] = {in, out, p->scr, p->wrk};
     const bool aligned = ((uintptr_t)in % sizeof(cpx_t)) == 0 && ((uintptr_t)out % sizeof(cpx_t)) == 0;
+    if (!aligned && p->needs_aligned) {
+        // arrays that are not aligned to a complex element: the same problem planned without the
+        // steps that need vector access (built on first use)
+        if (!p->alt) {
+            no_two_pass_real() = true;
+            p->alt = b2fft_plan_create(&p->pc.g);
+            no_two_pass_real() = false;
+            if (!p->alt) return -4;
+        }
+        return run_steps(p->alt, in, out, stream);
+    }
     const size_t ns = p->pc.steps.size();
     for (size_t i = 0; i < ns; ++i) {
         const StepPlan &s = p->pc.steps[i];
@@ -157,14 +168,34 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
     b2fft_plan *p = new b2fft_plan_s();
     p->pc.g = *g;
     p->pc.in_place = g->in_place != 0;
-    bool ok = (g->kind == B2FFT_C2C) ? build_c2c(p->pc) : build_real(p->pc);
-    if (ok) {
+    auto build = [&]() {
+        p->pc.steps.clear();
+        bool ok = (g->kind == B2FFT_C2C) ? build_c2c(p->pc) : build_real(p->pc);
+        if (!ok) return false;
         for (StepPlan &s : p->pc.steps) {
             s.gen_threads = s.nthreads;
             s.gen_pp = s.pp;
             s.gen_nblocks = s.nblocks;
             if (s.kind == SK_PASS) b2_select_tile_kernel(s);
         }
+        return true;
+    };
+    bool ok = build();
+    if (ok) {
+        // steps of the two-pass real path exist only as tile kernels: if the selector turned one down
+        // after all, take the three-pass path
+        bool missing = false;
+        for (const StepPlan &s : p->pc.steps)
+            if (s.needs_tile_kernel && s.fast_id < 0) missing = true;
+        if (missing) {
+            no_two_pass_real() = true;
+            ok = build();
+            no_two_pass_real() = false;
+        }
+        for (const StepPlan &s : p->pc.steps)
+            if (s.needs_tile_kernel) p->needs_aligned = true;
+    }
+    if (ok) {
         if (p->pc.scr_reals > 0) {
             p->scr = (real_t *)dev_malloc((size_t)p->pc.scr_reals * sizeof(real_t));
             if (!p->scr) ok = false;
@@ -217,6 +248,7 @@ extern "C" void b2fft_plan_destroy(b2fft_plan *p) {
     }
     dev_free(p->scr);
     dev_free(p->wrk);
+    if (p->alt) b2fft_plan_destroy(p->alt);
     dev_free(p->dev_in);
     dev_free(p->dev_out);
 #if B2_CUDA

@@ -38,6 +38,11 @@ struct PassParams {
     int epi_shift;         // exponent e = (hi << epi_shift) | lo
     const cpx_t *epi_lo;   // w_N^lo
     const cpx_t *epi_hi;   // w_N^(hi << shift)
+    // ---- two-pass real transform (plan_build_real.h): column pass that splits a pair of real
+    // columns (rsplit), row pass that folds the Hermitian half on the way out (fold_n > 0)
+    int rsplit;
+    long long fold_n;      // real length n = n1 * n2; outputs k > n/2 are stored as conj at n - k
+    int fold_n1;
     // ---- tile-kernel decode helpers, filled by b2_pp_prepare() just before a launch ----
     unsigned dv_m[B2_MAXLD], dv_s[B2_MAXLD];  // exact division by tiles0 (slot 0) and ln[1..] for indices < 2^31
     int lgC;                                  // log2(C), or -1 when C is not a power of two

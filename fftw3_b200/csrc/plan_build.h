@@ -56,6 +56,13 @@ inline bool split_four_step(long long n, long long *n1o, long long *n2o) {
     if (best < 0) return false;
     long long a = best, b = n / best;
     if (a < b) std::swap(a, b);  // larger factor to the column pass, shorter rows for pass B tiles
+    if (const char *e = getenv("FFTW_B200_SPLIT_N1")) {  // experiments: force the column-pass length
+        const long long f = atoll(e);
+        if (f > 1 && n % f == 0 && f <= c.col && n / f <= c.col && factorable(f) && factorable(n / f)) {
+            a = f;
+            b = n / f;
+        }
+    }
     *n1o = a;
     *n2o = b;
     return true;
@@ -79,6 +86,7 @@ inline long long dst_extent(const StepPlan &s) {
     }
     const PassParams &p = s.pp;
     long long e = (long long)(p.nstore - 1) * p.d_axis + p.d_pair + 1;
+    if (p.rsplit) e = (long long)(p.m / 2) * p.d_axis + 4;  // rows 0..m/2, two complex per column pair
     for (int d = 0; d < p.nld; ++d) e += (p.ln[d] - 1) * p.ld[d];
     for (const LDim &o : s.outer) e += (o.n - 1) * o.d;
     return e;

@@ -7,7 +7,42 @@
 #pragma once
 #include "plan_build.h"
 
+inline bool b2_have_tile_kernel(int n, int mode, int epi);  // tile_dispatch.cuh
+
 namespace b2 {
+
+// set while a plan is rebuilt without the two-pass real path (engine.cu: unaligned arrays, or a
+// tile kernel that was not selected after all)
+inline bool &no_two_pass_real() {
+    static thread_local bool v = false;
+    return v;
+}
+
+// n = n1 * n2 for the two-pass real transform: column pass of n1 over n2/2 column pairs, row pass of
+// n2 over n1/2+1 rows.  Both need their tile kernel; prefer balanced factors, then the shorter column.
+inline bool split_two_pass_real(long long n, long long *n1o, long long *n2o) {
+    long long best = -1, bestmax = 1ll << 62;
+    for (long long a = 4; a < n; a *= 2) {
+        if (n % a) break;
+        const long long b = n / a;
+        if (b < 4 || (b & (b - 1))) continue;
+        if (a > (1 << 20) || b > (1 << 20)) continue;
+        if (!b2_have_tile_kernel((int)a, 1, 2) || !b2_have_tile_kernel((int)b, 2, 0)) continue;
+        const long long mx = std::max(a, b);
+        if (mx < bestmax) {
+            bestmax = mx;
+            best = a;
+        }
+    }
+    if (const char *e = getenv("FFTW_B200_SPLIT_N1")) {
+        const long long f = atoll(e);
+        if (f >= 4 && n % f == 0 && b2_have_tile_kernel((int)f, 1, 2) && b2_have_tile_kernel((int)(n / f), 2, 0)) best = f;
+    }
+    if (best < 0) return false;
+    *n1o = best;
+    *n2o = n / best;
+    return true;
+}
 
 inline void fill_realpp(StepPlan &st, int post, int m, long long n_real, long long s_axis,
                         long long d_axis, const std::vector<LDim> &lines, bool use_src_for_both) {
@@ -278,6 +313,47 @@ inline bool build_real(PlanCore &pc) {
         std::vector<LDim> nz;
         for (const LDim &l : rl)
             if (l.n > 1) nz.push_back(l);
+        long long q1 = 0, q2 = 0;
+        if (r2c && !no_two_pass_real() && !getenv("FFTW_B200_NO_TWO_PASS_REAL") && (nl & (nl - 1)) == 0 &&
+            T[L].is == 1 && T[L].os == 1 && evens_src && evens_dst && split_two_pass_real(nl, &q1, &q2)) {
+            // ---- two passes: real column pairs (FFT + split + twiddle), then rows with a Hermitian fold
+            const long long rows = q1 / 2 + 1;
+            const std::vector<long long> cs2 = compact_strides(nz, rows * q2);
+            {   // pass 1: IN viewed as complex [q1][q2/2] -> SCR [q1/2+1][q2] complex
+                AxisSpec a;
+                a.n = (int)q1;
+                a.s_axis = q2;      // reals between consecutive j1 at fixed j2
+                a.d_axis = 2 * q2;  // reals between consecutive k1 rows of the intermediate
+                a.lines.push_back(LDim{q2 / 2, 2, 4, true});
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, nz[i].s, cs2[i], false});
+                a.epi_N = nl;
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.pp.rsplit = 1;
+                st.needs_tile_kernel = true;
+                st.dst_allowed = {B_SCR};
+                pc.steps.push_back(st);
+            }
+            {   // pass 2: rows of q2 for k1 = 0..q1/2, stored transposed at k1 + q1*k2 or folded to n - that
+                AxisSpec a;
+                a.n = (int)q2;
+                a.s_axis = 2;
+                a.d_axis = 2 * T[L].os * q1;
+                a.lines.push_back(LDim{rows, 2 * q2, 2 * T[L].os, false});
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, cs2[i], nz[i].d, false});
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.pp.fold_n = nl;
+                st.pp.fold_n1 = (int)q1;
+                st.needs_tile_kernel = true;
+                st.src_fixed = B_SCR;
+                st.dst_allowed = {B_OUT};
+                pc.steps.push_back(st);
+            }
+            (void)first_real_step;
+            if (!leading_axes(false)) return false;
+            return assign_buffers(pc);
+        }
         const std::vector<long long> cs = compact_strides(nz, m);
         if (r2c) {
             {   // A: IN (pairs of reals) -> SCR compact, column pass + twiddle

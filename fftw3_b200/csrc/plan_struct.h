@@ -32,6 +32,8 @@ struct b2fft_plan_s {
     SlabPlan *slab = nullptr;
     HostPipe *pipe = nullptr;
     std::vector<b2::Chain> *chains = nullptr;
+    bool needs_aligned = false;     // has steps without a generic-kernel form
+    b2fft_plan_s *alt = nullptr;    // the same problem without them, for unaligned arrays
 };
 void b2_slab_destroy(b2fft_plan_s *p);
 int b2_slab_execute(b2fft_plan_s *p, void *in, void *out);

@@ -57,6 +57,7 @@ struct Step {
     int src = B_IN, dst = B_OUT;
     bool inplace_ok = false;  // same locations read and written per CTA
     bool reads_input_layout = false;
+    bool needs_tile_kernel = false;  // no generic-kernel form (two-pass real transform)
     long long nblocks = 0;
     int nthreads = 0;
     int gen_threads = 0;        // launch shape of the generic kernel for this step (fallback when

@@ -14,7 +14,7 @@ struct TileEntry {
     void (*init)();
 };
 
-template <int N, int E, int MODE, bool EPI, int C>
+template <int N, int E, int MODE, int EPI, int C>
 struct TileInst {
     static constexpr int THREADS = C * (N / E);
     static constexpr int MINB = E >= 32 ? (THREADS <= 256 ? 2 : 1)
@@ -58,14 +58,14 @@ struct TileInst {
 #endif
     }
     static TileEntry entry() {
-        return TileEntry{N, E, MODE, EPI ? 1 : 0, C, THREADS, TileFFT<N, E, MODE, EPI>::smem_bytes(C), &smem_for, &launch, &init};
+        return TileEntry{N, E, MODE, EPI, C, THREADS, TileFFT<N, E, MODE, EPI>::smem_bytes(C), &smem_for, &launch, &init};
     }
 };
 
 // X(N, E, MODE, EPI, C): every instantiated tile kernel, in table order
 #define B2_TILE_ALLMODES(X, N, E, CROW, CCOL) \
-    X(N, E, MODE_ROW, false, CROW) X(N, E, MODE_COL, false, CCOL) X(N, E, MODE_COL, true, CCOL) \
-    X(N, E, MODE_ROW2COL, false, CCOL)
+    X(N, E, MODE_ROW, 0, CROW) X(N, E, MODE_COL, 0, CCOL) X(N, E, MODE_COL, 1, CCOL) \
+    X(N, E, MODE_COL, 2, CCOL) X(N, E, MODE_ROW2COL, 0, CCOL)
 // column-tile widths of the long column kernels (lines per CTA); overridable for experiments
 #ifndef B2_CC512
 #define B2_CC512 16
@@ -90,7 +90,7 @@ struct TileInst {
     B2_TILE_ALLMODES(X, 512, B2_E512, 8, B2_CC512)   \
     B2_TILE_ALLMODES(X, 1024, B2_E1024, 4, B2_CC1024)  \
     B2_TILE_ALLMODES(X, 2048, 16, 2, B2_CC2048)   \
-    X(4096, 16, MODE_ROW, false, 1) X(8192, 16, MODE_ROW, false, 1)
+    X(4096, 16, MODE_ROW, 0, 1) X(8192, 16, MODE_ROW, 0, 1)
 #else
 #define B2_TILE_LIST(X)                 \
     B2_TILE_ALLMODES(X, 64, 8, 32, 8)   \
@@ -98,7 +98,7 @@ struct TileInst {
     B2_TILE_ALLMODES(X, 256, 8, 8, 8)   \
     B2_TILE_ALLMODES(X, 512, 8, 4, 8)   \
     B2_TILE_ALLMODES(X, 1024, 8, 2, 8)  \
-    X(2048, 8, MODE_ROW, false, 1) X(4096, 8, MODE_ROW, false, 1)
+    X(2048, 8, MODE_ROW, 0, 1) X(4096, 8, MODE_ROW, 0, 1)
 #endif
 
 inline const std::vector<TileEntry> &b2_tile_table() {
@@ -106,6 +106,15 @@ inline const std::vector<TileEntry> &b2_tile_table() {
     static const std::vector<TileEntry> tab = {B2_TILE_LIST(B2_X_ENTRY)};
 #undef B2_X_ENTRY
     return tab;
+}
+
+// does a tile kernel exist for (length, mode, epilogue)?  (plan_build_real.h asks before it commits
+// to the two-pass real path, which has no generic-kernel form)
+inline bool b2_have_tile_kernel(int n, int mode, int epi) {
+    if (getenv("FFTW_B200_GENERIC_ONLY")) return false;
+    for (const TileEntry &e : b2_tile_table())
+        if (e.n == n && e.mode == mode && e.epi == epi) return true;
+    return false;
 }
 
 inline void b2_init_tile_kernels() {
@@ -125,14 +134,16 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
     int mode;
     if (p.s_axis == 2 && p.d_axis == 2)
         mode = MODE_ROW;
-    else if (p.s_axis != 2 && p.d_axis != 2 && p.ls[0] == 2 && p.ld[0] == 2 && p.ln[0] > 1)
+    else if (p.s_axis != 2 && p.d_axis != 2 && p.ls[0] == 2 && p.ld[0] == (p.rsplit ? 4 : 2) && p.ln[0] > 1)
         mode = MODE_COL;
     else if (p.s_axis == 2 && p.d_axis != 2 && p.ld[0] == 2 && p.ln[0] > 1)
         mode = MODE_ROW2COL;
     else
         return;
-    const int epi = p.epi_dim >= 0 ? 1 : 0;
+    const int epi = p.rsplit ? 2 : (p.epi_dim >= 0 ? 1 : 0);
     if (epi && mode != MODE_COL) return;
+    if (p.rsplit && p.epi_dim != 0) return;
+    if (p.fold_n > 0 && mode != MODE_ROW2COL) return;
     const std::vector<TileEntry> &tab = b2_tile_table();
     for (size_t i = 0; i < tab.size(); ++i) {
         const TileEntry &e = tab[i];
@@ -147,11 +158,12 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         s.nthreads = e.threads;
         s.smem = e.smem;
         static const char *mn[] = {"row", "col", "row->col"};
+        static const char *en[] = {"", "+twiddle", "+real-pair split+twiddle"};
         char buf[256];
         std::string rs;
         for (int i2 = 0; i2 < p.npass; ++i2) rs += (i2 ? "x" : "") + std::to_string(p.radix[i2]);
         snprintf(buf, sizeof buf, "c2c n=%d tile-kernel[%s%s] E=%d regs-resident, tile=%dx%d ctas=%lld threads=%d smem=%zuB",
-                 p.m, mn[mode], epi ? "+twiddle" : "", e.e, p.C, p.m, nb, e.threads, e.smem);
+                 p.m, mn[mode], p.fold_n > 0 ? "+hermitian fold" : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
         s.desc = buf;
         return;
     }

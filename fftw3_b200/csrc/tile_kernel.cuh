@@ -93,7 +93,8 @@ template <int R> B2_D void b2_twiddle_powers(cpx_t w1, cpx_t *w) {
     }
 }
 
-template <int N, int E, int MODE, bool EPI> struct TileFFT {
+// EPI: 0 none, 1 four-step twiddle on the way out, 2 split of a pair of real columns + twiddle
+template <int N, int E, int MODE, int EPI> struct TileFFT {
     typedef TileSched<N, E> S;
     static constexpr int T = N / E;  // threads per line
     static constexpr int PADSHIFT = sizeof(real_t) == 4 ? 4 : 3;
@@ -211,6 +212,98 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
         if constexpr (P + 1 < S::NP) passes_from<P + 1>(x);
     }
 
+    // w_N^e from the two-level table of the four-step epilogue
+    static B2_D cpx_t epi_root(const PassParams &p, unsigned long long e) {
+        return cmul(p.epi_hi[e >> p.epi_shift], p.epi_lo[e & ((1ull << p.epi_shift) - 1)]);
+    }
+
+    // EPI == 2, first pass of the two-pass real transform.  The line is the complex FFT Z of a pair
+    // of real columns (x_a + i x_b); per k1 <= N/2 form the two real spectra
+    //   Xa = (Z[k1] + conj Z[N-k1]) / 2,   Xb = -i (Z[k1] - conj Z[N-k1]) / 2,
+    // multiply by the four-step twiddles w_n^(k1*j2) of their columns j2 = 2*pair, 2*pair+1 and store
+    // both as one vector at row k1 of the [N/2+1][n2] intermediate.  The pairing stays inside the
+    // line, so it goes through this CTA's shared memory only.
+    // Reference: the same split is the hc2c step of rdft2-ct (ct_hc2c_direct_apply
+    // fftw/fftw_api.c:5831-5845) applied to column pairs instead of the whole half-length transform.
+    static B2_D void rsplit_exit(TileCtx &x, const PassParams &p, cpx_t *cdst, long long bid) {
+        (void)bid;
+        const int b2_nthreads = x.nthreads;
+        (void)b2_nthreads;
+        const int C = p.C;
+        B2_SYNC();  // the last exchange has been read
+        B2_FOR_THREADS {
+            cpx_t *v = B2_TREGS(x);
+            int c, t;
+            if (map(tid, C, p.lgC, c, t)) {
+                cpx_t *line = x.sm + (size_t)c * LS;
+                const int pt = phys(t);
+#pragma unroll
+                for (int q = 0; q < E; ++q) line[phys_k<T, 0>(t, pt, q)] = v[q];
+            }
+        }
+        B2_SYNC();
+        B2_FOR_THREADS {
+            int c, t;
+            map(tid, C, p.lgC, c, t);
+            if (c < x.nlines) {
+                const cpx_t *line = x.sm + (size_t)c * LS;
+                const unsigned long long j2 = 2ull * (unsigned long long)(x.l0 + c);  // even column of the pair
+                const long long ds = p.d_axis / 2;
+                cpx_t *row0 = cdst + (x.dbase + (x.l0 + c) * p.ld[0]) / 2;
+                struct alignas(16) Pair {  // one 16-byte vector store in single precision, two in double
+                    cpx_t a, b;
+                };
+                constexpr int HQ = E / 2;  // k1 = t + q*T, q < E/2 covers 0 .. N/2-1
+                const cpx_t wa0 = epi_root(p, j2 * (unsigned long long)t), was = epi_root(p, j2 * (unsigned long long)T);
+                const cpx_t w10 = epi_root(p, (unsigned long long)t), w1s = epi_root(p, (unsigned long long)T);
+                cpx_t pa[HQ], p1[HQ];
+                pa[0] = cpx_t{1, 0};
+                p1[0] = cpx_t{1, 0};
+                if (HQ > 1) {
+                    b2_twiddle_powers<HQ>(was, pa);
+                    b2_twiddle_powers<HQ>(w1s, p1);
+                }
+#pragma unroll
+                for (int q = 0; q < HQ; ++q) {
+                    const int k1 = t + q * T;
+                    const cpx_t za = line[phys(k1)], zb = cconj(line[phys((N - k1) & (N - 1))]);
+                    const cpx_t xa = cscale(cadd(za, zb), (real_t)0.5);
+                    const cpx_t xb = cmul_mi(cscale(csub(za, zb), (real_t)0.5));
+                    const cpx_t wa = q ? cmul(wa0, pa[q]) : wa0;
+                    const cpx_t w1 = q ? cmul(w10, p1[q]) : w10;
+                    Pair o;
+                    o.a = cmul(xa, wa);
+                    o.b = cmul(xb, cmul(wa, w1));
+                    *reinterpret_cast<Pair *>(row0 + (long long)k1 * ds) = o;
+                }
+                if (t == 0) {  // k1 = N/2 pairs with itself
+                    const int k1 = N / 2;
+                    const cpx_t za = line[phys(k1)];
+                    const cpx_t wa = epi_root(p, j2 * (unsigned long long)k1);
+                    Pair o;
+                    o.a = cmul(cpx_t{za.x, 0}, wa);
+                    o.b = cmul(cpx_t{za.y, 0}, cmul(wa, epi_root(p, (unsigned long long)k1)));
+                    *reinterpret_cast<Pair *>(row0 + (long long)k1 * ds) = o;
+                }
+            }
+        }
+    }
+
+    // second pass of the two-pass real transform: output index kk of the length-n spectrum goes to
+    // kk when kk <= n/2, else its conjugate goes to n - kk; rows k1 = 0 and n1/2 only keep the former
+    static B2_D bool fold_target(const PassParams &p, long long k1, long long k2, long long &idx, bool &conj) {
+        const long long kk = k1 + (long long)p.fold_n1 * k2;
+        if (2 * kk <= p.fold_n) {
+            idx = kk;
+            conj = false;
+            return true;
+        }
+        if (k1 == 0 || 2 * k1 == p.fold_n1) return false;
+        idx = p.fold_n - kk;
+        conj = true;
+        return true;
+    }
+
     static B2_D void run(const PassParams &p, const real_t *B2_RESTRICT src, real_t *B2_RESTRICT dst,
                          long long bid, char *smem, int b2_nthreads) {
         (void)b2_nthreads;
@@ -290,7 +383,9 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
         if constexpr (S::NP > 1) passes_from<1>(x);
 
         // ---- store (registers -> global), v[q] holds output index t + q*T ----
-        if (MODE != MODE_ROW2COL) {
+        if (EPI == 2) {
+            rsplit_exit(x, p, cdst, bid);
+        } else if (MODE != MODE_ROW2COL) {
             B2_FOR_THREADS {
                 cpx_t *v = B2_TREGS(x);
                 int c, t;
@@ -298,7 +393,7 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
                 if (live && c < x.nlines) {
                     const long long base = (x.dbase + (x.l0 + c) * p.ld[0]) / 2;
                     const long long ds = p.d_axis / 2;
-                    if (EPI) {
+                    if (EPI == 1) {
                         // w_Nbig^(i2*k), k = t + q*T: base * step^q, both from the two-level table
                         const unsigned long long i2 = (p.epi_dim == 0) ? (unsigned long long)(x.l0 + c)
                                                                        : (unsigned long long)x.i2base;
@@ -366,10 +461,21 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
 #pragma unroll
                             for (int q = 0; q < H; ++q) a[q] = cswap(a[q]);
                         }
+                        if (p.fold_n > 0) {
+                            cpx_t *fb = cdst + x.dbase / 2;
 #pragma unroll
-                        for (int q = 0; q < H; ++q) {
-                            *ps = a[q];
-                            ps += step;
+                            for (int q = 0; q < H; ++q) {
+                                long long idx;
+                                bool cj;
+                                if (fold_target(p, x.l0 + c, k0 + (h * H + q) * T, idx, cj))
+                                    fb[idx * lstep] = cj ? cconj(a[q]) : a[q];
+                            }
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < H; ++q) {
+                                *ps = a[q];
+                                ps += step;
+                            }
                         }
                     }
                 } else {
@@ -377,7 +483,12 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
                         const int k = idx / nl, c = idx - k * nl;
                         cpx_t a = x.sm[(size_t)c * LS + phys(k)];
                         if (p.swap_out) a = cswap(a);
-                        cdst[base + (long long)c * lstep + (long long)k * ds] = a;
+                        if (p.fold_n > 0) {
+                            long long fi;
+                            bool cj;
+                            if (fold_target(p, x.l0 + c, k, fi, cj)) cdst[x.dbase / 2 + fi * lstep] = cj ? cconj(a) : a;
+                        } else
+                            cdst[base + (long long)c * lstep + (long long)k * ds] = a;
                     }
                 }
             }
@@ -386,7 +497,7 @@ template <int N, int E, int MODE, bool EPI> struct TileFFT {
 };
 
 #if B2_CUDA
-template <int N, int E, int MODE, bool EPI, int MAXT, int MINB>
+template <int N, int E, int MODE, int EPI, int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB)
     b2_tile_kernel(const __grid_constant__ PassParams p, const real_t *B2_RESTRICT src,
                    real_t *B2_RESTRICT dst, long long bid0) {
