@@ -62,10 +62,13 @@ struct TileInst {
     }
 };
 
-// X(N, E, MODE, EPI, C): every instantiated tile kernel, in table order
+// X(N, E, MODE, EPI, C): every instantiated tile kernel, in table order.
+// B2_TILE_LIST: the complex kernels (also the ones a chained launch can run);
+// B2_TILE_LIST_REAL: the variants with a real-transform prologue / epilogue (EPI 2, 3, 4).
 #define B2_TILE_ALLMODES(X, N, E, CROW, CCOL) \
-    X(N, E, MODE_ROW, 0, CROW) X(N, E, MODE_COL, 0, CCOL) X(N, E, MODE_COL, 1, CCOL) \
-    X(N, E, MODE_COL, 2, CCOL) X(N, E, MODE_ROW2COL, 0, CCOL)
+    X(N, E, MODE_ROW, 0, CROW) X(N, E, MODE_COL, 0, CCOL) X(N, E, MODE_COL, 1, CCOL) X(N, E, MODE_ROW2COL, 0, CCOL)
+#define B2_TILE_REALMODES(X, N, E, CROW, CCOL) \
+    X(N, E, MODE_COL, 2, CCOL) X(N, E, MODE_ROW, 3, CROW) X(N, E, MODE_ROW, 4, CROW)
 // column-tile widths of the long column kernels (lines per CTA); overridable for experiments
 #ifndef B2_CC512
 #define B2_CC512 16
@@ -83,27 +86,33 @@ struct TileInst {
 #define B2_E1024 16
 #endif
 #if defined(FFTW_SINGLE)
-#define B2_TILE_LIST(X)                   \
-    B2_TILE_ALLMODES(X, 64, 8, 32, 16)    \
-    B2_TILE_ALLMODES(X, 128, 8, 16, 16)   \
-    B2_TILE_ALLMODES(X, 256, 16, 16, 16)  \
-    B2_TILE_ALLMODES(X, 512, B2_E512, 8, B2_CC512)   \
-    B2_TILE_ALLMODES(X, 1024, B2_E1024, 4, B2_CC1024)  \
-    B2_TILE_ALLMODES(X, 2048, 16, 2, B2_CC2048)   \
-    X(4096, 16, MODE_ROW, 0, 1) X(8192, 16, MODE_ROW, 0, 1)
+#define B2_TILE_SIZES(A, X)              \
+    A(X, 64, 8, 32, 16)                  \
+    A(X, 128, 8, 16, 16)                 \
+    A(X, 256, 16, 16, 16)                \
+    A(X, 512, B2_E512, 8, B2_CC512)      \
+    A(X, 1024, B2_E1024, 4, B2_CC1024)   \
+    A(X, 2048, 16, 2, B2_CC2048)
+#define B2_TILE_LIST(X) B2_TILE_SIZES(B2_TILE_ALLMODES, X) X(4096, 16, MODE_ROW, 0, 1) X(8192, 16, MODE_ROW, 0, 1)
+#define B2_TILE_LIST_REAL(X)               \
+    B2_TILE_SIZES(B2_TILE_REALMODES, X)    \
+    X(4096, 16, MODE_ROW, 3, 1) X(4096, 16, MODE_ROW, 4, 1) X(8192, 16, MODE_ROW, 3, 1) X(8192, 16, MODE_ROW, 4, 1)
 #else
-#define B2_TILE_LIST(X)                 \
-    B2_TILE_ALLMODES(X, 64, 8, 32, 8)   \
-    B2_TILE_ALLMODES(X, 128, 8, 16, 8)  \
-    B2_TILE_ALLMODES(X, 256, 8, 8, 8)   \
-    B2_TILE_ALLMODES(X, 512, 8, 4, 8)   \
-    B2_TILE_ALLMODES(X, 1024, 8, 2, 8)  \
-    X(2048, 8, MODE_ROW, 0, 1) X(4096, 8, MODE_ROW, 0, 1)
+#define B2_TILE_SIZES(A, X) \
+    A(X, 64, 8, 32, 8)      \
+    A(X, 128, 8, 16, 8)     \
+    A(X, 256, 8, 8, 8)      \
+    A(X, 512, 8, 4, 8)      \
+    A(X, 1024, 8, 2, 8)
+#define B2_TILE_LIST(X) B2_TILE_SIZES(B2_TILE_ALLMODES, X) X(2048, 8, MODE_ROW, 0, 1) X(4096, 8, MODE_ROW, 0, 1)
+#define B2_TILE_LIST_REAL(X)               \
+    B2_TILE_SIZES(B2_TILE_REALMODES, X)    \
+    X(2048, 8, MODE_ROW, 3, 1) X(2048, 8, MODE_ROW, 4, 1) X(4096, 8, MODE_ROW, 3, 1) X(4096, 8, MODE_ROW, 4, 1)
 #endif
 
 inline const std::vector<TileEntry> &b2_tile_table() {
 #define B2_X_ENTRY(N, E, MODE, EPI, C) TileInst<N, E, MODE, EPI, C>::entry(),
-    static const std::vector<TileEntry> tab = {B2_TILE_LIST(B2_X_ENTRY)};
+    static const std::vector<TileEntry> tab = {B2_TILE_LIST(B2_X_ENTRY) B2_TILE_LIST_REAL(B2_X_ENTRY)};
 #undef B2_X_ENTRY
     return tab;
 }
@@ -125,7 +134,10 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
     s.fast_id = -1;
     if (getenv("FFTW_B200_GENERIC_ONLY")) return;
     PassParams &p = s.pp;
-    if (s.kind != b2::SK_PASS || p.rmode != RM_C2C || !p.vec_ld || !p.vec_st) return;
+    if (s.kind != b2::SK_PASS || !p.vec_ld || !p.vec_st) return;
+    const bool real_half = (p.rmode == RM_R2C_HALF || p.rmode == RM_C2R_HALF);
+    if (p.rmode != RM_C2C && !real_half) return;
+    if (real_half && (p.s_axis != 2 || p.d_axis != 2 || p.s_pair != 1 || p.d_pair != 1)) return;
     if ((p.s_axis | p.d_axis) & 1) return;
     for (int d = 0; d < p.nld; ++d)
         if ((p.ls[d] | p.ld[d]) & 1) return;
@@ -140,8 +152,9 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         mode = MODE_ROW2COL;
     else
         return;
-    const int epi = p.rsplit ? 2 : (p.epi_dim >= 0 ? 1 : 0);
-    if (epi && mode != MODE_COL) return;
+    const int epi = p.rmode == RM_R2C_HALF ? 3 : p.rmode == RM_C2R_HALF ? 4 : p.rsplit ? 2 : (p.epi_dim >= 0 ? 1 : 0);
+    if (real_half && mode != MODE_ROW) return;
+    if ((epi == 1 || epi == 2) && mode != MODE_COL) return;
     if (p.rsplit && p.epi_dim != 0) return;
     if (p.fold_n > 0 && mode != MODE_ROW2COL) return;
     const std::vector<TileEntry> &tab = b2_tile_table();
@@ -158,12 +171,12 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         s.nthreads = e.threads;
         s.smem = e.smem;
         static const char *mn[] = {"row", "col", "row->col"};
-        static const char *en[] = {"", "+twiddle", "+real-pair split+twiddle"};
+        static const char *en[] = {"", "+twiddle", "+real-pair split+twiddle", "+hermitian split (r2c)", "+hermitian merge (c2r)"};
         char buf[256];
         std::string rs;
         for (int i2 = 0; i2 < p.npass; ++i2) rs += (i2 ? "x" : "") + std::to_string(p.radix[i2]);
-        snprintf(buf, sizeof buf, "c2c n=%d tile-kernel[%s%s] E=%d regs-resident, tile=%dx%d ctas=%lld threads=%d smem=%zuB",
-                 p.m, mn[mode], p.fold_n > 0 ? "+hermitian fold" : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
+        snprintf(buf, sizeof buf, "%s n=%d tile-kernel[%s%s] E=%d regs-resident, tile=%dx%d ctas=%lld threads=%d smem=%zuB",
+                 real_half ? (epi == 3 ? "r2c" : "c2r") : "c2c", real_half ? p.n : p.m, mn[mode], p.fold_n > 0 ? "+hermitian fold" : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
         s.desc = buf;
         return;
     }

@@ -289,6 +289,102 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
         }
     }
 
+    // EPI == 3: r2c of n = 2N reals per contiguous line.  The line holds Z = FFT_N(x[2j] + i x[2j+1]);
+    //   X[k] = E + w_n^k O,  X[N-k] = conj(E - w_n^k O),  E = (Z[k] + conj Z[N-k]) / 2,
+    //   O = -i (Z[k] - conj Z[N-k]) / 2,  and X[0] = Re Z0 + Im Z0, X[N] = Re Z0 - Im Z0.
+    // Same arithmetic as the generic kernel's r2c post-processing and as the reference's hc2c step
+    // (ct_hc2c_direct_apply fftw/fftw_api.c:5831-5845, codelets hc2cfdftv_*).
+    static B2_D void r2c_row_exit(TileCtx &x, const PassParams &p, cpx_t *cdst) {
+        const int b2_nthreads = x.nthreads;
+        (void)b2_nthreads;
+        const int C = p.C;
+        B2_SYNC();
+        B2_FOR_THREADS {
+            cpx_t *v = B2_TREGS(x);
+            int c, t;
+            if (map(tid, C, p.lgC, c, t)) {
+                cpx_t *line = x.sm + (size_t)c * LS;
+                const int pt = phys(t);
+#pragma unroll
+                for (int q = 0; q < E; ++q) line[phys_k<T, 0>(t, pt, q)] = v[q];
+            }
+        }
+        B2_SYNC();
+        B2_FOR_THREADS {
+            int c, t;
+            map(tid, C, p.lgC, c, t);
+            if (c < x.nlines) {
+                const cpx_t *line = x.sm + (size_t)c * LS;
+                cpx_t *D = cdst + (x.dbase + (x.l0 + c) * p.ld[0]) / 2;
+                constexpr int HQ = E / 2;  // k = t + q*T, q < E/2 covers 0 .. N/2-1
+                cpx_t zk[HQ], zc[HQ], w[HQ];
+#pragma unroll
+                for (int q = 0; q < HQ; ++q) {
+                    const int k = t + q * T;
+                    zk[q] = line[phys(k)];
+                    zc[q] = cconj(line[phys((N - k) & (N - 1))]);
+                    w[q] = p.twr[k];
+                }
+#pragma unroll
+                for (int q = 0; q < HQ; ++q) {
+                    const int k = t + q * T;
+                    if (k == 0) {
+                        D[0] = cpx_t{zk[q].x + zk[q].y, (real_t)0};
+                        D[N] = cpx_t{zk[q].x - zk[q].y, (real_t)0};
+                    } else {
+                        const cpx_t Ev = cscale(cadd(zk[q], zc[q]), (real_t)0.5);
+                        const cpx_t Ov = cmul_mi(cscale(csub(zk[q], zc[q]), (real_t)0.5));
+                        const cpx_t wO = cmul(w[q], Ov);
+                        D[k] = cadd(Ev, wO);
+                        D[N - k] = cconj(csub(Ev, wO));
+                    }
+                }
+                if (t == 0) D[N / 2] = cconj(line[phys(N / 2)]);  // k = N/2: w = -i, X = conj(Z)
+            }
+        }
+    }
+
+    // EPI == 4: c2r producing n = 2N reals per contiguous line from N+1 complex.  Merge
+    //   Z[k] = (A + B) + D,  Z[N-k] = conj((A + B) - D),  A = X[k], B = conj X[N-k],
+    //   D = i conj(w_n^k) (A - B),
+    // written re/im-swapped into the line (the backward transform = swap, forward FFT, swap).
+    // Reference: hc2cb* codelets driven by ct_hc2c_apply_dif_dft fftw/fftw_api.c:5591-5603.
+    static B2_D void c2r_row_enter(TileCtx &x, const PassParams &p, const cpx_t *csrc) {
+        const int b2_nthreads = x.nthreads;
+        (void)b2_nthreads;
+        const int C = p.C;
+        B2_FOR_THREADS {
+            int c, t;
+            map(tid, C, p.lgC, c, t);
+            if (c < x.nlines) {
+                cpx_t *line = x.sm + (size_t)c * LS;
+                const cpx_t *X = csrc + (x.sbase + (x.l0 + c) * p.ls[0]) / 2;
+                constexpr int HQ = E / 2;
+                cpx_t A[HQ], B[HQ], w[HQ];
+#pragma unroll
+                for (int q = 0; q < HQ; ++q) {
+                    const int k = t + q * T;
+                    A[q] = b2_ldcg(X + k);
+                    B[q] = cconj(b2_ldcg(X + (N - k)));
+                    w[q] = p.twr[k];
+                }
+#pragma unroll
+                for (int q = 0; q < HQ; ++q) {
+                    const int k = t + q * T;
+                    const cpx_t sum = cadd(A[q], B[q]), dif = csub(A[q], B[q]);
+                    const cpx_t Dd = cmul_pi(cmul(cconj(w[q]), dif));
+                    line[phys(k)] = cswap(cadd(sum, Dd));
+                    if (k != 0) line[phys(N - k)] = cswap(cconj(csub(sum, Dd)));
+                }
+                if (t == 0) {  // k = N/2 pairs with itself: w = -i, D = -(A - conj A)
+                    const cpx_t a = b2_ldcg(X + N / 2);
+                    line[phys(N / 2)] = cswap(cpx_t{2 * a.x, -2 * a.y});
+                }
+            }
+        }
+        B2_SYNC();
+    }
+
     // second pass of the two-pass real transform: output index kk of the length-n spectrum goes to
     // kk when kk <= n/2, else its conjugate goes to n - kk; rows k1 = 0 and n1/2 only keep the former
     static B2_D bool fold_target(const PassParams &p, long long k1, long long k2, long long &idx, bool &conj) {
@@ -325,6 +421,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
         cpx_t *cdst = reinterpret_cast<cpx_t *>(dst);
 
         // ---- load (global -> registers) + first radix pass ----
+        if (EPI == 4) c2r_row_enter(x, p, csrc);
         B2_FOR_THREADS {
             cpx_t *v = B2_TREGS(x);
             int c, t;
@@ -355,7 +452,18 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                     }
                 }
             }
-            if (active) {
+            if (EPI == 4) {
+                // c2r: the merged half-length input comes from shared memory (c2r_row_enter below)
+                if (active) {
+                    const cpx_t *line = x.sm + (size_t)c * LS;
+                    const int pt = phys(t);
+#pragma unroll
+                    for (int q = 0; q < E; ++q) v[q] = line[phys_k<T, 0>(t, pt, q)];
+                } else {
+#pragma unroll
+                    for (int q = 0; q < E; ++q) v[q] = cpx_t{0, 0};
+                }
+            } else if (active) {
                 // all strides are in reals and even here (vector access was checked by the selector)
                 const long long as = p.s_axis / 2;
                 const cpx_t *pl = csrc + ((x.sbase + (x.l0 + c) * p.ls[0]) / 2 + (long long)t * as);
@@ -378,13 +486,24 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
 #pragma unroll
                 for (int q = 0; q < E; ++q) v[q] = cpx_t{0, 0};
             }
-            butterflies<0>(x, v, c, t, live);
+            if (EPI != 4) butterflies<0>(x, v, c, t, live);
+        }
+        if (EPI == 4) {
+            B2_SYNC();  // every thread holds its inputs before pass 0 overwrites the line
+            B2_FOR_THREADS {
+                cpx_t *v = B2_TREGS(x);
+                int c, t;
+                const bool live = map(tid, C, p.lgC, c, t);
+                butterflies<0>(x, v, c, t, live);
+            }
         }
         if constexpr (S::NP > 1) passes_from<1>(x);
 
         // ---- store (registers -> global), v[q] holds output index t + q*T ----
         if (EPI == 2) {
             rsplit_exit(x, p, cdst, bid);
+        } else if (EPI == 3) {
+            r2c_row_exit(x, p, cdst);
         } else if (MODE != MODE_ROW2COL) {
             B2_FOR_THREADS {
                 cpx_t *v = B2_TREGS(x);
