@@ -41,6 +41,7 @@ struct PassParams {
     // ---- two-pass real transform (plan_build_real.h): column pass that splits a pair of real
     // columns (rsplit), row pass that folds the Hermitian half on the way out (fold_n > 0)
     int rsplit;
+    int pmerge;            // row pass whose line is built from two adjacent Hermitian half rows (two-pass c2r)
     long long fold_n;      // real length n = n1 * n2; outputs k > n/2 are stored as conj at n - k
     int fold_n1;
     // ---- tile-kernel decode helpers, filled by b2_pp_prepare() just before a launch ----

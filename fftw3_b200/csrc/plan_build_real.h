@@ -20,14 +20,18 @@ inline bool &no_two_pass_real() {
 
 // n = n1 * n2 for the two-pass real transform: column pass of n1 over n2/2 column pairs, row pass of
 // n2 over n1/2+1 rows.  Both need their tile kernel; prefer balanced factors, then the shorter column.
-inline bool split_two_pass_real(long long n, long long *n1o, long long *n2o) {
+inline bool split_two_pass_real(long long n, long long *n1o, long long *n2o, bool r2c = true) {
     long long best = -1, bestmax = 1ll << 62;
     for (long long a = 4; a < n; a *= 2) {
         if (n % a) break;
         const long long b = n / a;
         if (b < 4 || (b & (b - 1))) continue;
         if (a > (1 << 20) || b > (1 << 20)) continue;
-        if (!b2_have_tile_kernel((int)a, 1, 2) || !b2_have_tile_kernel((int)b, 2, 0)) continue;
+        // r2c: column pass n1 with pair split, row->col pass n2; c2r: column pass n2 with twiddle,
+        // row->col pass n1 with pair merge
+        if (r2c ? (!b2_have_tile_kernel((int)a, 1, 2) || !b2_have_tile_kernel((int)b, 2, 0))
+                : (!b2_have_tile_kernel((int)b, 1, 1) || !b2_have_tile_kernel((int)a, 2, 5)))
+            continue;
         const long long mx = std::max(a, b);
         if (mx < bestmax) {
             bestmax = mx;
@@ -36,7 +40,10 @@ inline bool split_two_pass_real(long long n, long long *n1o, long long *n2o) {
     }
     if (const char *e = getenv("FFTW_B200_SPLIT_N1")) {
         const long long f = atoll(e);
-        if (f >= 4 && n % f == 0 && b2_have_tile_kernel((int)f, 1, 2) && b2_have_tile_kernel((int)(n / f), 2, 0)) best = f;
+        if (f >= 4 && n % f == 0 &&
+            (r2c ? (b2_have_tile_kernel((int)f, 1, 2) && b2_have_tile_kernel((int)(n / f), 2, 0))
+                 : (b2_have_tile_kernel((int)(n / f), 1, 1) && b2_have_tile_kernel((int)f, 2, 5))))
+            best = f;
     }
     if (best < 0) return false;
     *n1o = best;
@@ -352,6 +359,51 @@ inline bool build_real(PlanCore &pc) {
             }
             (void)first_real_step;
             if (!leading_axes(false)) return false;
+            return assign_buffers(pc);
+        }
+        // (c2r: opt-in.  Measured on B200, 2^20 x 256: 1.56 ms against 1.33 ms for merge + two passes --
+        // the unfold + twiddle column pass runs 1744 instructions per thread at one 1024-thread CTA
+        // per SM; 2^16 x 4096: 1.01 against 1.07 ms.)
+        if (!r2c && getenv("FFTW_B200_TWO_PASS_C2R") && !no_two_pass_real() && (nl & (nl - 1)) == 0 &&
+            T[L].is == 1 && T[L].os == 1 && evens_src && evens_dst && split_two_pass_real(nl, &q1, &q2, false)) {
+            // ---- two passes, the mirror image of the r2c pair: columns k1 <= q1/2 of the Hermitian-
+            // unfolded spectrum (backward FFT over k2 + twiddle), then per pair of output columns a
+            // backward FFT over k1 whose input is merged from two Hermitian half rows
+            const long long rows = q1 / 2 + 1;
+            const std::vector<long long> cs2 = compact_strides(nz, rows * q2);
+            {   // pass 1: IN (n/2+1 complex) -> SCR [q2][q1/2+1]
+                AxisSpec a;
+                a.n = (int)q2;
+                a.s_axis = 2 * q1;
+                a.d_axis = 2 * rows;
+                a.lines.push_back(LDim{rows, 2, 2, true});
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, nz[i].s, cs2[i], false});
+                a.swap_in = a.swap_out = true;
+                a.epi_N = nl;
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.pp.fold_n = nl;
+                st.pp.fold_n1 = (int)q1;
+                st.needs_tile_kernel = true;
+                st.dst_allowed = {B_SCR};
+                pc.steps.push_back(st);
+            }
+            {   // pass 2: rows 2c, 2c+1 of SCR -> OUT viewed as complex [q1][q2/2], transposed store
+                AxisSpec a;
+                a.n = (int)q1;
+                a.s_axis = 2;
+                a.d_axis = q2;
+                a.lines.push_back(LDim{q2 / 2, 4 * rows, 2, false});
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, cs2[i], nz[i].d, false});
+                a.swap_out = true;
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.pp.pmerge = 1;
+                st.needs_tile_kernel = true;
+                st.src_fixed = B_SCR;
+                st.dst_allowed = {B_OUT};
+                pc.steps.push_back(st);
+            }
             return assign_buffers(pc);
         }
         const std::vector<long long> cs = compact_strides(nz, m);

@@ -68,7 +68,7 @@ struct TileInst {
 #define B2_TILE_ALLMODES(X, N, E, CROW, CCOL) \
     X(N, E, MODE_ROW, 0, CROW) X(N, E, MODE_COL, 0, CCOL) X(N, E, MODE_COL, 1, CCOL) X(N, E, MODE_ROW2COL, 0, CCOL)
 #define B2_TILE_REALMODES(X, N, E, CROW, CCOL) \
-    X(N, E, MODE_COL, 2, CCOL) X(N, E, MODE_ROW, 3, CROW) X(N, E, MODE_ROW, 4, CROW)
+    X(N, E, MODE_COL, 2, CCOL) X(N, E, MODE_ROW, 3, CROW) X(N, E, MODE_ROW, 4, CROW) X(N, E, MODE_ROW2COL, 5, CCOL)
 // column-tile widths of the long column kernels (lines per CTA); overridable for experiments
 #ifndef B2_CC512
 #define B2_CC512 16
@@ -152,11 +152,13 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         mode = MODE_ROW2COL;
     else
         return;
-    const int epi = p.rmode == RM_R2C_HALF ? 3 : p.rmode == RM_C2R_HALF ? 4 : p.rsplit ? 2 : (p.epi_dim >= 0 ? 1 : 0);
+    const int epi = p.rmode == RM_R2C_HALF ? 3 : p.rmode == RM_C2R_HALF ? 4 : p.pmerge ? 5 : p.rsplit ? 2 : (p.epi_dim >= 0 ? 1 : 0);
     if (real_half && mode != MODE_ROW) return;
     if ((epi == 1 || epi == 2) && mode != MODE_COL) return;
     if (p.rsplit && p.epi_dim != 0) return;
-    if (p.fold_n > 0 && mode != MODE_ROW2COL) return;
+    if (p.fold_n > 0 && mode != (p.swap_in ? MODE_COL : MODE_ROW2COL)) return;  // fold on the way out / unfold on the way in
+    if (p.pmerge && mode != MODE_ROW2COL) return;
+    if (p.fold_n > 0 && p.swap_in && (p.ls[0] != 2 || p.fold_n >= (1ll << 30))) return;  // unfold load: unit stride, 32-bit indices
     const std::vector<TileEntry> &tab = b2_tile_table();
     for (size_t i = 0; i < tab.size(); ++i) {
         const TileEntry &e = tab[i];
@@ -171,12 +173,12 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         s.nthreads = e.threads;
         s.smem = e.smem;
         static const char *mn[] = {"row", "col", "row->col"};
-        static const char *en[] = {"", "+twiddle", "+real-pair split+twiddle", "+hermitian split (r2c)", "+hermitian merge (c2r)"};
+        static const char *en[] = {"", "+twiddle", "+real-pair split+twiddle", "+hermitian split (r2c)", "+hermitian merge (c2r)", "+real-pair merge"};
         char buf[256];
         std::string rs;
         for (int i2 = 0; i2 < p.npass; ++i2) rs += (i2 ? "x" : "") + std::to_string(p.radix[i2]);
         snprintf(buf, sizeof buf, "%s n=%d tile-kernel[%s%s] E=%d regs-resident, tile=%dx%d ctas=%lld threads=%d smem=%zuB",
-                 real_half ? (epi == 3 ? "r2c" : "c2r") : "c2c", real_half ? p.n : p.m, mn[mode], p.fold_n > 0 ? "+hermitian fold" : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
+                 real_half ? (epi == 3 ? "r2c" : "c2r") : "c2c", real_half ? p.n : p.m, mn[mode], p.fold_n > 0 ? (p.swap_in ? "+hermitian unfold+twiddle" : "+hermitian fold") : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
         s.desc = buf;
         return;
     }

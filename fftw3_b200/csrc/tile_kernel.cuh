@@ -385,6 +385,46 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
         B2_SYNC();
     }
 
+    // EPI == 5, second pass of the two-pass c2r.  The line's input is two adjacent rows of N/2+1
+    // complex, Ua = U[.][2c] and Ub = U[.][2c+1] (Hermitian in k1); the length-N complex input whose
+    // backward transform is the real pair (x[..2c], x[..2c+1]) is
+    //   V[k1] = Ua[k1] + i Ub[k1],   V[N-k1] = conj Ua[k1] + i conj Ub[k1],
+    // written re/im-swapped into the line (backward = swap, forward FFT, swap).
+    static B2_D void pair_merge_enter(TileCtx &x, const PassParams &p, const cpx_t *csrc) {
+        const int b2_nthreads = x.nthreads;
+        (void)b2_nthreads;
+        const int C = p.C;
+        B2_FOR_THREADS {
+            int c, t;
+            map(tid, C, p.lgC, c, t);
+            if (c < x.nlines) {
+                cpx_t *line = x.sm + (size_t)c * LS;
+                const cpx_t *Ua = csrc + (x.sbase + (x.l0 + c) * p.ls[0]) / 2;
+                const cpx_t *Ub = Ua + (N / 2 + 1);
+                constexpr int HQ = E / 2;
+                cpx_t a[HQ], b[HQ];
+#pragma unroll
+                for (int q = 0; q < HQ; ++q) {
+                    a[q] = b2_ldcg(Ua + t + q * T);
+                    b[q] = b2_ldcg(Ub + t + q * T);
+                }
+#pragma unroll
+                for (int q = 0; q < HQ; ++q) {
+                    const int k = t + q * T;
+                    const cpx_t ib = cmul_pi(b[q]);                 // i Ub
+                    const cpx_t icb = cmul_pi(cconj(b[q]));         // i conj Ub
+                    line[phys(k)] = cswap(cadd(a[q], ib));
+                    if (k != 0) line[phys(N - k)] = cswap(cadd(cconj(a[q]), icb));
+                }
+                if (t == 0) {
+                    const cpx_t an = b2_ldcg(Ua + N / 2), bn = b2_ldcg(Ub + N / 2);
+                    line[phys(N / 2)] = cswap(cadd(an, cmul_pi(bn)));
+                }
+            }
+        }
+        B2_SYNC();
+    }
+
     // second pass of the two-pass real transform: output index kk of the length-n spectrum goes to
     // kk when kk <= n/2, else its conjugate goes to n - kk; rows k1 = 0 and n1/2 only keep the former
     static B2_D bool fold_target(const PassParams &p, long long k1, long long k2, long long &idx, bool &conj) {
@@ -422,6 +462,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
 
         // ---- load (global -> registers) + first radix pass ----
         if (EPI == 4) c2r_row_enter(x, p, csrc);
+        if (EPI == 5) pair_merge_enter(x, p, csrc);
         B2_FOR_THREADS {
             cpx_t *v = B2_TREGS(x);
             int c, t;
@@ -452,8 +493,8 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                     }
                 }
             }
-            if (EPI == 4) {
-                // c2r: the merged half-length input comes from shared memory (c2r_row_enter below)
+            if (EPI == 4 || EPI == 5) {
+                // c2r: the merged input comes from shared memory (c2r_row_enter / pair_merge_enter)
                 if (active) {
                     const cpx_t *line = x.sm + (size_t)c * LS;
                     const int pt = phys(t);
@@ -467,7 +508,22 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                 // all strides are in reals and even here (vector access was checked by the selector)
                 const long long as = p.s_axis / 2;
                 const cpx_t *pl = csrc + ((x.sbase + (x.l0 + c) * p.ls[0]) / 2 + (long long)t * as);
-                if (as == 1) {  // contiguous lines: the offsets fold into the load instructions
+                if (MODE == MODE_COL && p.fold_n > 0) {
+                    // two-pass c2r, first pass: element (k2, k1) of the full spectrum is X[kk] when
+                    // kk = k1 + n1*k2 <= n/2, else conj X[n - kk] (Hermitian unfold of the stored half)
+                    // (32-bit index arithmetic: the selector only takes this path for n < 2^30, unit stride)
+                    const cpx_t *fb = csrc + x.sbase / 2;
+                    const int fn = (int)p.fold_n, dk = p.fold_n1 * T;
+                    int kk = (int)(x.l0 + c) + p.fold_n1 * t;
+#pragma unroll
+                    for (int q = 0; q < E; ++q) {
+                        const bool far = 2 * kk > fn;
+                        cpx_t a = b2_ldcg(fb + (far ? fn - kk : kk));
+                        if (far) a.y = -a.y;
+                        v[q] = a;
+                        kk += dk;
+                    }
+                } else if (as == 1) {  // contiguous lines: the offsets fold into the load instructions
 #pragma unroll
                     for (int q = 0; q < E; ++q) v[q] = b2_ldcg(pl + q * T);
                 } else {
@@ -486,9 +542,9 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
 #pragma unroll
                 for (int q = 0; q < E; ++q) v[q] = cpx_t{0, 0};
             }
-            if (EPI != 4) butterflies<0>(x, v, c, t, live);
+            if (EPI != 4 && EPI != 5) butterflies<0>(x, v, c, t, live);
         }
-        if (EPI == 4) {
+        if (EPI == 4 || EPI == 5) {
             B2_SYNC();  // every thread holds its inputs before pass 0 overwrites the line
             B2_FOR_THREADS {
                 cpx_t *v = B2_TREGS(x);

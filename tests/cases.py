@@ -264,6 +264,7 @@ def check_chained_launch(lib, device=False):
     import os
     old = os.environ.get("FFTW_B200_CHAIN")
     os.environ["FFTW_B200_CHAIN"] = "1"
+    os.environ["FFTW_B200_NO_TWO_PASS_REAL"] = "1"  # the three-pass real plans are the ones with something to chain
     try:
         rng = np.random.default_rng(11)
         # 3-D: z and y passes of each plane group
@@ -288,7 +289,7 @@ def check_chained_launch(lib, device=False):
         xr = rand_r(rng, (hm, n), lib)
         yc = np.zeros((hm, n // 2 + 1), dtype=lib.cplx)
         p = lib.plan_many_dft_r2c([n], hm, xr, None, 1, n, yc, None, 1, n // 2 + 1)
-        assert p  # (the two-pass real path has nothing left to chain)
+        assert p and "chained launch" in lib.sprint_plan(p)
         lib.execute(p)
         lib.destroy_plan(p)
         assert rel_l2(yc, np.fft.rfft(xr.astype(np.float64), axis=1)) < tol(lib, n)
@@ -299,7 +300,28 @@ def check_chained_launch(lib, device=False):
         lib.destroy_plan(p)
         assert rel_l2(z, n * xr.astype(np.float64)) < 2 * tol(lib, n)
     finally:
+        os.environ.pop("FFTW_B200_NO_TWO_PASS_REAL", None)
         if old is None:
             os.environ.pop("FFTW_B200_CHAIN", None)
         else:
             os.environ["FFTW_B200_CHAIN"] = old
+
+
+def check_two_pass_c2r(lib):
+    """FFTW_B200_TWO_PASS_C2R=1: the mirror image of the two-pass r2c (unfold + column pass, pair merge
+    + row pass); off by default because the three-pass plan is faster at 2^20, kept parity-tested."""
+    import os
+    os.environ["FFTW_B200_TWO_PASS_C2R"] = "1"
+    try:
+        rng = np.random.default_rng(5)
+        for n, hm in ((2 ** 15, 3), (2 ** 17, 1)):
+            x = rand_r(rng, (hm, n), lib)
+            X = np.fft.rfft(x.astype(np.float64), axis=1).astype(lib.cplx)
+            z = np.zeros_like(x)
+            p = lib.plan_many_dft_c2r([n], hm, X, None, 1, n // 2 + 1, z, None, 1, n)
+            assert p and "real-pair merge" in lib.sprint_plan(p)
+            lib.execute(p)
+            lib.destroy_plan(p)
+            assert rel_l2(z, n * x.astype(np.float64)) < 2 * tol(lib, n)
+    finally:
+        os.environ.pop("FFTW_B200_TWO_PASS_C2R", None)

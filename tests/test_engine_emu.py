@@ -78,3 +78,7 @@ def test_plan_description_and_flops(lib):
 
 def test_chained_launch_opt_in(lib):
     cases.check_chained_launch(lib)
+
+
+def test_two_pass_c2r_opt_in(lib):
+    cases.check_two_pass_c2r(lib)

@@ -228,3 +228,7 @@ def test_host_arrays_go_through_the_chunked_pipeline(lib, howmany):
 def test_chained_launch_opt_in(lib):
     """the single-launch chain (acquire/release between CTAs of one grid) gives the same answers"""
     cases.check_chained_launch(lib)
+
+
+def test_two_pass_c2r_opt_in(lib):
+    cases.check_two_pass_c2r(lib)
