@@ -325,3 +325,123 @@ def check_two_pass_c2r(lib):
             assert rel_l2(z, n * x.astype(np.float64)) < 2 * tol(lib, n)
     finally:
         os.environ.pop("FFTW_B200_TWO_PASS_C2R", None)
+
+
+FUZZ_SIZES = [1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 12, 13, 15, 16, 17, 20, 23, 24, 25, 27, 30, 32, 36, 48, 49, 60, 64, 77,
+              96, 100, 121, 127, 128, 130, 169, 200, 243, 256, 289, 384, 500, 512, 1000, 1024, 1536, 2048, 2187, 4096]
+
+
+def check_fuzz(lib, ncases, seed, max_points=1 << 17):
+    """Random geometries through the advanced interface (fftw_plan_many_dft / _r2c / _c2r, reference
+    fftw_api.c:642-736): rank 1-3, sizes with and without large prime factors, random howmany, element
+    strides, embeddings and dists, in place and out of place, both signs -- against numpy's pocketfft in
+    double precision on the gathered data, and the gaps of strided outputs must stay untouched."""
+    rng = np.random.default_rng(seed)
+    done = 0
+    while done < ncases:
+        rank = int(rng.integers(1, 4))
+        n = [int(rng.choice(FUZZ_SIZES)) for _ in range(rank)]
+        hm = int(rng.integers(1, 6))
+        if int(np.prod(n)) * hm > max_points:
+            continue
+        kind = rng.choice(["c2c", "r2c", "c2r"])
+        inplace = bool(rng.integers(0, 2))
+        N = int(np.prod(n))
+        nc = n[:-1] + [n[-1] // 2 + 1]          # complex-side logical dims of a real transform
+        if kind == "c2c":
+            li, lo = n, n
+        elif kind == "r2c":
+            li, lo = n, nc
+        else:
+            li, lo = nc, n
+        def embed(logical):
+            e = list(logical)
+            for d in range(1, rank):
+                e[d] += int(rng.integers(0, 3))
+            return e
+        if inplace:
+            if kind == "c2c":
+                ie = oe = embed(n)
+                istride = ostride = int(rng.integers(1, 3))
+            else:  # padded rows: the real side has 2*(n/2+1) reals per row
+                ce = embed(nc)
+                re = ce[:-1] + [2 * ce[-1]]
+                ie, oe = (re, ce) if kind == "r2c" else (ce, re)
+                istride = ostride = 1
+        else:
+            ie, oe = embed(li), embed(lo)
+            istride, ostride = int(rng.integers(1, 3)), int(rng.integers(1, 3))
+        isz, osz = int(np.prod(ie)) * istride, int(np.prod(oe)) * ostride
+        if inplace and kind != "c2c":
+            idist = isz + (2 if kind == "r2c" else 1) * int(rng.integers(0, 2))
+            odist = idist // 2 if kind == "r2c" else idist * 2
+            if kind == "r2c" and idist % 2:
+                continue
+        elif inplace:
+            idist = odist = isz + int(rng.integers(0, 4))
+        else:
+            idist, odist = isz + int(rng.integers(0, 4)), osz + int(rng.integers(0, 4))
+        it = lib.real if kind == "r2c" else lib.cplx
+        ot = lib.real if kind == "c2r" else lib.cplx
+        ilen, olen = hm * idist + isz, hm * odist + osz
+
+        def gather(buf, emb, logical, stride, dist):
+            out = np.empty([hm] + list(logical), dtype=buf.dtype)
+            idx = np.indices(logical).reshape(rank, -1)
+            flat = np.zeros(idx.shape[1], dtype=np.int64)
+            for d in range(rank):
+                flat = flat * emb[d] + idx[d]
+            for k in range(hm):
+                out[k] = buf[k * dist + flat * stride].reshape(logical)
+            return out, flat
+
+        # input data
+        if kind == "c2r":
+            xr = rng.random([hm] + n) - 0.5
+            spec = np.fft.rfftn(xr, axes=tuple(range(1, rank + 1)))
+            src = np.zeros(ilen, dtype=np.complex128)
+            _, flat = gather(src, ie, li, istride, idist)
+            for k in range(hm):
+                src[k * idist + flat * istride] = spec[k].reshape(-1)
+            inbuf = src.astype(it)
+        else:
+            inbuf = (rand_r(rng, ilen, lib) if kind == "r2c" else rand_c(rng, ilen, lib))
+        sign = int(rng.choice([-1, 1])) if kind == "c2c" else (-1 if kind == "r2c" else 1)
+        if inplace:
+            nbytes = max(inbuf.nbytes, olen * np.dtype(ot).itemsize)
+            raw = np.zeros(nbytes + 16, dtype=np.uint8)
+            off = (-raw.ctypes.data) % 16
+            raw = raw[off:off + nbytes]
+            raw[:inbuf.nbytes] = inbuf.view(np.uint8)
+            a_in = raw[:inbuf.nbytes].view(it)
+            a_out = raw[:olen * np.dtype(ot).itemsize].view(ot)
+        else:
+            a_in, a_out = inbuf.copy(), np.zeros(olen, dtype=ot)
+        x_log, _ = gather(a_in.copy(), ie, li, istride, idist)
+        args = (n, hm, a_in, ie, istride, idist, a_out, oe, ostride, odist)
+        if kind == "c2c":
+            p = lib.plan_many_dft(*args, sign)
+        elif kind == "r2c":
+            p = lib.plan_many_dft_r2c(*args)
+        else:
+            p = lib.plan_many_dft_c2r(*args)
+        assert p, (kind, n, hm, ie, oe, istride, ostride, idist, odist, inplace)
+        lib.execute(p)
+        lib.destroy_plan(p)
+        y_log, flat_o = gather(a_out, oe, lo, ostride, odist)
+        axes = tuple(range(1, rank + 1))
+        if kind == "c2c":
+            ref = np.fft.fftn(x_log.astype(np.complex128), axes=axes) if sign < 0 else \
+                N * np.fft.ifftn(x_log.astype(np.complex128), axes=axes)
+        elif kind == "r2c":
+            ref = np.fft.rfftn(x_log.astype(np.float64), axes=axes)
+        else:
+            ref = N * xr
+        err = rel_l2(y_log, ref)
+        assert err < 4 * tol(lib, max(N, 2)), (kind, n, hm, ie, oe, istride, ostride, idist, odist, inplace, err)
+        if not inplace:
+            mask = np.ones(olen, dtype=bool)
+            for k in range(hm):
+                mask[k * odist + flat_o * ostride] = False
+            assert not a_out[mask].any(), "gaps of a strided output must stay untouched"
+        done += 1
