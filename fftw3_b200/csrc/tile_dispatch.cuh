@@ -87,6 +87,7 @@ struct TileInst {
 #endif
 #if defined(FFTW_SINGLE)
 #define B2_TILE_SIZES(A, X)              \
+    A(X, 32, 8, 64, 16)                  \
     A(X, 64, 8, 32, 16)                  \
     A(X, 128, 8, 16, 16)                 \
     A(X, 256, 16, 16, 16)                \
@@ -99,6 +100,7 @@ struct TileInst {
     X(4096, 16, MODE_ROW, 3, 1) X(4096, 16, MODE_ROW, 4, 1) X(8192, 16, MODE_ROW, 3, 1) X(8192, 16, MODE_ROW, 4, 1)
 #else
 #define B2_TILE_SIZES(A, X) \
+    A(X, 32, 8, 64, 8)      \
     A(X, 64, 8, 32, 8)      \
     A(X, 128, 8, 16, 8)     \
     A(X, 256, 8, 8, 8)      \
