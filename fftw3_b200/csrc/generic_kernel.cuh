@@ -30,13 +30,15 @@ B2_D void b2_store_pt(real_t *B2_RESTRICT dst, long long off, long long pair, in
 // one Stockham radix-R step over a tile: in/out are smem buffers of C lines, stride ls
 template <int R>
 B2_D void b2_radix_step(const cpx_t *in, cpx_t *out, const cpx_t *B2_RESTRICT tw, int m, int Ns,
-                        int nlines, int ls, int tid, int nthreads) {
+                        int nlines, int ls, int tid, int nthreads, unsigned nbm, unsigned nbs, unsigned nsm,
+                        unsigned nss) {
     const int nb = m / R;
     const int step = m / (Ns * R);
     const int total = nb * nlines;
     for (int b = tid; b < total; b += nthreads) {
-        const int c = b / nb, j = b - c * nb;
-        const int jd = j / Ns, jm = j - jd * Ns;
+        // exact multiply-shift divisions by nb and Ns (b2_pp_prepare_generic)
+        const int c = (int)b2_fastdiv((unsigned)b, nbm, nbs), j = b - c * nb;
+        const int jd = (int)b2_fastdiv((unsigned)j, nsm, nss), jm = j - jd * Ns;
         const cpx_t *x = in + (size_t)c * ls + j;
         cpx_t v[R];
 #pragma unroll
@@ -103,10 +105,10 @@ B2_D void b2_generic_pass_body(const PassParams &p, const real_t *B2_RESTRICT sr
         for (int idx = tid; idx < total; idx += B2_NTHREADS) {
             int c, j;
             if (p.ld_col) {
-                j = idx / nlines;
+                j = (nlines == p.C) ? (int)b2_fastdiv((unsigned)idx, p.gd_m[2], p.gd_s[2]) : idx / nlines;
                 c = idx - j * nlines;
             } else {
-                c = idx / p.nload;
+                c = (int)b2_fastdiv((unsigned)idx, p.gd_m[0], p.gd_s[0]);
                 j = idx - c * p.nload;
             }
             const long long off = S.soff[c] + (long long)j * p.s_axis;
@@ -127,7 +129,7 @@ B2_D void b2_generic_pass_body(const PassParams &p, const real_t *B2_RESTRICT sr
             const int m = p.m, hk = m / 2 + 1;
             const int total = nlines * hk;
             for (int idx = tid; idx < total; idx += B2_NTHREADS) {
-                const int c = idx / hk, k = idx - c * hk;
+                const int c = (int)b2_fastdiv((unsigned)idx, p.gd_m[3], p.gd_s[3]), k = idx - c * hk;
                 cpx_t *X = S.a + (size_t)c * ls;
                 const cpx_t A = X[k], B = cconj(X[m - k]);
                 const cpx_t sum = cadd(A, B), dif = csub(A, B);
@@ -164,15 +166,15 @@ B2_D void b2_generic_pass_body(const PassParams &p, const real_t *B2_RESTRICT sr
             const int R = p.radix[ps];
             B2_FOR_THREADS {
                 switch (R) {
-                case 2: b2_radix_step<2>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS); break;
-                case 3: b2_radix_step<3>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS); break;
-                case 4: b2_radix_step<4>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS); break;
-                case 5: b2_radix_step<5>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS); break;
-                case 7: b2_radix_step<7>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS); break;
-                case 8: b2_radix_step<8>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS); break;
-                case 11: b2_radix_step<11>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS); break;
-                case 13: b2_radix_step<13>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS); break;
-                case 16: b2_radix_step<16>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS); break;
+                case 2: b2_radix_step<2>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS, p.gnb_m[ps], p.gnb_s[ps], p.gns_m[ps], p.gns_s[ps]); break;
+                case 3: b2_radix_step<3>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS, p.gnb_m[ps], p.gnb_s[ps], p.gns_m[ps], p.gns_s[ps]); break;
+                case 4: b2_radix_step<4>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS, p.gnb_m[ps], p.gnb_s[ps], p.gns_m[ps], p.gns_s[ps]); break;
+                case 5: b2_radix_step<5>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS, p.gnb_m[ps], p.gnb_s[ps], p.gns_m[ps], p.gns_s[ps]); break;
+                case 7: b2_radix_step<7>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS, p.gnb_m[ps], p.gnb_s[ps], p.gns_m[ps], p.gns_s[ps]); break;
+                case 8: b2_radix_step<8>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS, p.gnb_m[ps], p.gnb_s[ps], p.gns_m[ps], p.gns_s[ps]); break;
+                case 11: b2_radix_step<11>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS, p.gnb_m[ps], p.gnb_s[ps], p.gns_m[ps], p.gns_s[ps]); break;
+                case 13: b2_radix_step<13>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS, p.gnb_m[ps], p.gnb_s[ps], p.gns_m[ps], p.gns_s[ps]); break;
+                case 16: b2_radix_step<16>(S.a, S.b, p.tw, p.m, Ns, nlines, ls, tid, B2_NTHREADS, p.gnb_m[ps], p.gnb_s[ps], p.gns_m[ps], p.gns_s[ps]); break;
                 default: break;
                 }
             }
@@ -190,7 +192,7 @@ B2_D void b2_generic_pass_body(const PassParams &p, const real_t *B2_RESTRICT sr
             const int m = p.m, hk = m / 2 + 1;
             const int total = nlines * hk;
             for (int idx = tid; idx < total; idx += B2_NTHREADS) {
-                const int c = idx / hk, k = idx - c * hk;
+                const int c = (int)b2_fastdiv((unsigned)idx, p.gd_m[3], p.gd_s[3]), k = idx - c * hk;
                 cpx_t *Z = S.a + (size_t)c * ls;
                 if (k == 0) {
                     const cpx_t z0 = Z[0];
@@ -215,10 +217,10 @@ B2_D void b2_generic_pass_body(const PassParams &p, const real_t *B2_RESTRICT sr
         for (int idx = tid; idx < total; idx += B2_NTHREADS) {
             int c, k;
             if (p.st_col) {
-                k = idx / nlines;
+                k = (nlines == p.C) ? (int)b2_fastdiv((unsigned)idx, p.gd_m[2], p.gd_s[2]) : idx / nlines;
                 c = idx - k * nlines;
             } else {
-                c = idx / p.nstore;
+                c = (int)b2_fastdiv((unsigned)idx, p.gd_m[1], p.gd_s[1]);
                 k = idx - c * p.nstore;
             }
             cpx_t v = S.a[(size_t)c * ls + k];
@@ -239,7 +241,13 @@ B2_D void b2_generic_pass_body(const PassParams &p, const real_t *B2_RESTRICT sr
 }
 
 #if B2_CUDA
-__global__ void b2_generic_pass_kernel(const __grid_constant__ PassParams p,
+#if defined(FFTW_SINGLE)
+#define B2_GENERIC_BOUNDS __maxnreg__(56)  // 384-thread CTAs (lengths 3*2^k) fit three to an SM, 512-thread CTAs two
+#else
+#define B2_GENERIC_BOUNDS __launch_bounds__(512, 1)  // a radix-16 butterfly in double is 64 registers of data alone
+#endif
+__global__ void B2_GENERIC_BOUNDS
+    b2_generic_pass_kernel(const __grid_constant__ PassParams p,
                                        const real_t *B2_RESTRICT src, real_t *B2_RESTRICT dst,
                                        long long bid0) {
     extern __shared__ __align__(16) char b2_smem[];

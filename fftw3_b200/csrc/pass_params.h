@@ -48,6 +48,10 @@ struct PassParams {
     unsigned dv_m[B2_MAXLD], dv_s[B2_MAXLD];  // exact division by tiles0 (slot 0) and ln[1..] for indices < 2^31
     int lgC;                                  // log2(C), or -1 when C is not a power of two
     unsigned pf_ahead;                        // L2 prefetch distance in tiles (0: off)
+    // ---- generic-kernel index helpers (b2_pp_prepare_generic): multiply-shift divisors ----
+    unsigned gd_m[4], gd_s[4];                // by nload, nstore, C, m/2+1
+    unsigned gnb_m[B2_MAXPASS], gnb_s[B2_MAXPASS];  // by m / radix[pass]
+    unsigned gns_m[B2_MAXPASS], gns_s[B2_MAXPASS];  // by Ns(pass) = prod of earlier radices
     long long nblocks;                        // tiles in the whole pass
 };
 
@@ -61,6 +65,18 @@ inline void b2_fastdiv_make(unsigned long long d, unsigned &m, unsigned &s) {
 }
 B2_HD unsigned b2_fastdiv(unsigned n, unsigned m, unsigned s) {
     return (unsigned)(((unsigned long long)n * m) >> s);
+}
+inline void b2_pp_prepare_generic(PassParams &p) {
+    const unsigned long long d[4] = {(unsigned long long)(p.nload > 0 ? p.nload : 1), (unsigned long long)(p.nstore > 0 ? p.nstore : 1),
+                                     (unsigned long long)(p.C > 0 ? p.C : 1), (unsigned long long)(p.m / 2 + 1)};
+    for (int i = 0; i < 4; ++i) b2_fastdiv_make(d[i], p.gd_m[i], p.gd_s[i]);
+    unsigned long long Ns = 1;
+    for (int ps = 0; ps < p.npass && ps < B2_MAXPASS; ++ps) {
+        const unsigned long long R = (unsigned long long)(p.radix[ps] > 0 ? p.radix[ps] : 1);
+        b2_fastdiv_make((unsigned long long)p.m / R > 0 ? (unsigned long long)p.m / R : 1, p.gnb_m[ps], p.gnb_s[ps]);
+        b2_fastdiv_make(Ns, p.gns_m[ps], p.gns_s[ps]);
+        Ns *= R;
+    }
 }
 inline void b2_pp_prepare(PassParams &p) {
     b2_fastdiv_make((unsigned long long)(p.tiles0 > 0 ? p.tiles0 : 1), p.dv_m[0], p.dv_s[0]);

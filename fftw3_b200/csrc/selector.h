@@ -282,6 +282,7 @@ inline bool make_pass_step(Step &st, const AxisSpec &a) {
              rmn[p.rmode], p.n, rs.c_str(), p.C, p.m, p.ld_col ? "col" : "row", p.st_col ? "col" : "row",
              st.nblocks, st.nthreads, st.smem, p.epi_dim >= 0 ? " +twiddle" : "");
     st.desc = buf;
+    b2_pp_prepare_generic(p);
     return true;
 }
 
