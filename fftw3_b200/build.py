@@ -103,7 +103,9 @@ def build_emu(prec: str, force: bool = False) -> str:
 
 
 def build_all(force: bool = False, verbose: bool = False):
-    return [build_product(p, force, verbose) for p in ("fp32", "fp64")]
+    # the two precisions are independent nvcc runs dominated by one translation unit each
+    with ThreadPoolExecutor(max_workers=2) as ex:
+        return list(ex.map(lambda p: build_product(p, force, verbose), ("fp32", "fp64")))
 
 
 if __name__ == "__main__":
