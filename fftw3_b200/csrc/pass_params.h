@@ -41,6 +41,11 @@ struct PassParams {
     // ---- two-pass real transform (plan_build_real.h): column pass that splits a pair of real
     // columns (rsplit), row pass that folds the Hermitian half on the way out (fold_n > 0)
     int rsplit;
+    // ---- fused Bluestein row passes (EPI 6: x*chirp in, *bhat out; EPI 7: *chirp out, first blue_n points)
+    int blue_mode;         // 0 none, 6, 7
+    int blue_n;            // transform length n (the line holds M = m points)
+    int blue_swap;         // user-level backward transform: swap re/im of x on the way in / of X on the way out
+    const cpx_t *blue_chirp, *blue_bhat;
     int pmerge;            // row pass whose line is built from two adjacent Hermitian half rows (two-pass c2r)
     long long fold_n;      // real length n = n1 * n2; outputs k > n/2 are stored as conj at n - k
     int fold_n1;

@@ -12,7 +12,17 @@
 
 struct b2fft_comm_s;
 
+inline bool b2_have_tile_kernel(int n, int mode, int epi);  // tile_dispatch.cuh
+
 namespace b2 {
+
+// set while a plan is rebuilt without the steps that exist only as tile kernels (two-pass real
+// transform, fused Bluestein passes) -- engine.cu: unaligned arrays, or a tile kernel that the
+// selector turned down after all
+inline bool &no_two_pass_real() {
+    static thread_local bool v = false;
+    return v;
+}
 
 struct StepPlan : Step {
     int src_fixed = -1;            // -1: wherever the data currently is
@@ -172,6 +182,39 @@ inline bool add_bluestein_axis(PlanCore &pc, const BlueSpec &b, const std::vecto
         return st;
     };
     const std::vector<int> work = {B_WRK, B_SCR};
+    // Contiguous complex lines and M within one CTA's reach: two fused row passes
+    //   [x * chirp, zero-pad, FFT_M, * bhat] -> work,  [FFT_M^-1, * chirp, first n points] -> destination
+    // instead of five sweeps over the padded rows.
+    bool line_even = true;
+    for (int d = 0; d < bp.nld; ++d)
+        if ((bp.ls[d] | bp.ld[d]) & 1) line_even = false;
+    if (!b.src_real && !b.dst_real && !b.herm_in && bp.nout == bp.n && b.s_axis == 2 && b.d_axis == 2 && line_even &&
+        !no_two_pass_real() && !getenv("FFTW_B200_NO_FUSED_BLUESTEIN") && b2_have_tile_kernel((int)M, 0, 6) &&
+        b2_have_tile_kernel((int)M, 0, 7)) {
+        for (int pass = 0; pass < 2; ++pass) {
+            AxisSpec a;
+            a.n = (int)M;
+            a.s_axis = a.d_axis = 2;
+            long long wstride = 2 * M;
+            for (int d = 0; d < bp.nld; ++d) {
+                a.lines.push_back(LDim{bp.ln[d], pass == 0 ? bp.ls[d] : wstride, pass == 0 ? wstride : bp.ld[d], false});
+                wstride *= bp.ln[d];
+            }
+            a.swap_in = a.swap_out = (pass == 1);
+            StepPlan st;
+            if (!make_pass_step(st, a)) return false;
+            st.pp.blue_mode = pass == 0 ? 6 : 7;
+            st.pp.blue_n = (int)n;
+            st.pp.blue_swap = pass == 0 ? b.swap_in : b.swap_out;
+            st.pp.blue_chirp = bp.chirp;
+            st.pp.blue_bhat = bp.bhat;
+            st.needs_tile_kernel = true;
+            st.inplace_ok = false;
+            st.dst_allowed = pass == 0 ? work : dst_allowed;
+            pc.steps.push_back(st);
+        }
+        return true;
+    }
     {
         StepPlan st = mk(0, "chirp-in");
         st.dst_allowed = work;

@@ -7,16 +7,7 @@
 #pragma once
 #include "plan_build.h"
 
-inline bool b2_have_tile_kernel(int n, int mode, int epi);  // tile_dispatch.cuh
-
 namespace b2 {
-
-// set while a plan is rebuilt without the two-pass real path (engine.cu: unaligned arrays, or a
-// tile kernel that was not selected after all)
-inline bool &no_two_pass_real() {
-    static thread_local bool v = false;
-    return v;
-}
 
 // n = n1 * n2 for the two-pass real transform: column pass of n1 over n2/2 column pairs, row pass of
 // n2 over n1/2+1 rows.  Both need their tile kernel; prefer balanced factors, then the shorter column.

@@ -68,7 +68,8 @@ struct TileInst {
 #define B2_TILE_ALLMODES(X, N, E, CROW, CCOL) \
     X(N, E, MODE_ROW, 0, CROW) X(N, E, MODE_COL, 0, CCOL) X(N, E, MODE_COL, 1, CCOL) X(N, E, MODE_ROW2COL, 0, CCOL)
 #define B2_TILE_REALMODES(X, N, E, CROW, CCOL) \
-    X(N, E, MODE_COL, 2, CCOL) X(N, E, MODE_ROW, 3, CROW) X(N, E, MODE_ROW, 4, CROW) X(N, E, MODE_ROW2COL, 5, CCOL)
+    X(N, E, MODE_COL, 2, CCOL) X(N, E, MODE_ROW, 3, CROW) X(N, E, MODE_ROW, 4, CROW) X(N, E, MODE_ROW2COL, 5, CCOL) \
+    X(N, E, MODE_ROW, 6, CROW) X(N, E, MODE_ROW, 7, CROW)
 // column-tile widths of the long column kernels (lines per CTA); overridable for experiments
 #ifndef B2_CC512
 #define B2_CC512 16
@@ -97,7 +98,8 @@ struct TileInst {
 #define B2_TILE_LIST(X) B2_TILE_SIZES(B2_TILE_ALLMODES, X) X(4096, 16, MODE_ROW, 0, 1) X(8192, 16, MODE_ROW, 0, 1)
 #define B2_TILE_LIST_REAL(X)               \
     B2_TILE_SIZES(B2_TILE_REALMODES, X)    \
-    X(4096, 16, MODE_ROW, 3, 1) X(4096, 16, MODE_ROW, 4, 1) X(8192, 16, MODE_ROW, 3, 1) X(8192, 16, MODE_ROW, 4, 1)
+    X(4096, 16, MODE_ROW, 3, 1) X(4096, 16, MODE_ROW, 4, 1) X(8192, 16, MODE_ROW, 3, 1) X(8192, 16, MODE_ROW, 4, 1) \
+    X(4096, 16, MODE_ROW, 6, 1) X(4096, 16, MODE_ROW, 7, 1) X(8192, 16, MODE_ROW, 6, 1) X(8192, 16, MODE_ROW, 7, 1)
 #else
 #define B2_TILE_SIZES(A, X) \
     A(X, 32, 8, 64, 8)      \
@@ -109,7 +111,8 @@ struct TileInst {
 #define B2_TILE_LIST(X) B2_TILE_SIZES(B2_TILE_ALLMODES, X) X(2048, 8, MODE_ROW, 0, 1) X(4096, 8, MODE_ROW, 0, 1)
 #define B2_TILE_LIST_REAL(X)               \
     B2_TILE_SIZES(B2_TILE_REALMODES, X)    \
-    X(2048, 8, MODE_ROW, 3, 1) X(2048, 8, MODE_ROW, 4, 1) X(4096, 8, MODE_ROW, 3, 1) X(4096, 8, MODE_ROW, 4, 1)
+    X(2048, 8, MODE_ROW, 3, 1) X(2048, 8, MODE_ROW, 4, 1) X(4096, 8, MODE_ROW, 3, 1) X(4096, 8, MODE_ROW, 4, 1) \
+    X(2048, 8, MODE_ROW, 6, 1) X(2048, 8, MODE_ROW, 7, 1) X(4096, 8, MODE_ROW, 6, 1) X(4096, 8, MODE_ROW, 7, 1)
 #endif
 
 inline const std::vector<TileEntry> &b2_tile_table() {
@@ -154,7 +157,8 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         mode = MODE_ROW2COL;
     else
         return;
-    const int epi = p.rmode == RM_R2C_HALF ? 3 : p.rmode == RM_C2R_HALF ? 4 : p.pmerge ? 5 : p.rsplit ? 2 : (p.epi_dim >= 0 ? 1 : 0);
+    const int epi = p.rmode == RM_R2C_HALF ? 3 : p.rmode == RM_C2R_HALF ? 4 : p.blue_mode ? p.blue_mode : p.pmerge ? 5 : p.rsplit ? 2 : (p.epi_dim >= 0 ? 1 : 0);
+    if (p.blue_mode && mode != MODE_ROW) return;
     if (real_half && mode != MODE_ROW) return;
     if ((epi == 1 || epi == 2) && mode != MODE_COL) return;
     if (p.rsplit && p.epi_dim != 0) return;
@@ -175,7 +179,7 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         s.nthreads = e.threads;
         s.smem = e.smem;
         static const char *mn[] = {"row", "col", "row->col"};
-        static const char *en[] = {"", "+twiddle", "+real-pair split+twiddle", "+hermitian split (r2c)", "+hermitian merge (c2r)", "+real-pair merge"};
+        static const char *en[] = {"", "+twiddle", "+real-pair split+twiddle", "+hermitian split (r2c)", "+hermitian merge (c2r)", "+real-pair merge", "+chirp in, x bhat out (bluestein)", "+chirp out (bluestein)"};
         char buf[256];
         std::string rs;
         for (int i2 = 0; i2 < p.npass; ++i2) rs += (i2 ? "x" : "") + std::to_string(p.radix[i2]);

@@ -523,6 +523,19 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                         v[q] = a;
                         kk += dk;
                     }
+                } else if (EPI == 6) {
+                    // Bluestein, first FFT: x[j] * chirp[j] for j < n, zero padding up to M = N
+#pragma unroll
+                    for (int q = 0; q < E; ++q) {
+                        const int j = t + q * T;
+                        cpx_t a = cpx_t{0, 0};
+                        if (j < p.blue_n) {
+                            a = b2_ldcg(pl + q * T);
+                            if (p.blue_swap) a = cswap(a);
+                            a = cmul(a, p.blue_chirp[j]);
+                        }
+                        v[q] = a;
+                    }
                 } else if (as == 1) {  // contiguous lines: the offsets fold into the load instructions
 #pragma unroll
                     for (int q = 0; q < E; ++q) v[q] = b2_ldcg(pl + q * T);
@@ -582,12 +595,26 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
 #pragma unroll
                         for (int q = 0; q < E; ++q) v[q] = cmul(v[q], q ? cmul(wb, wq[q]) : wb);
                     }
+                    if (EPI == 6) {  // Bluestein: spectrum of the padded line times bhat = FFT_M(conj chirp) / M
+#pragma unroll
+                        for (int q = 0; q < E; ++q) v[q] = cmul(v[q], p.blue_bhat[t + q * T]);
+                    }
                     if (p.swap_out) {
 #pragma unroll
                         for (int q = 0; q < E; ++q) v[q] = cswap(v[q]);
                     }
                     cpx_t *ps = cdst + (base + (long long)t * ds);
-                    if (ds == 1) {
+                    if (EPI == 7) {  // Bluestein, inverse FFT done: X[k] = conv[k] * chirp[k], k < n only
+#pragma unroll
+                        for (int q = 0; q < E; ++q) {
+                            const int k = t + q * T;
+                            if (k < p.blue_n) {
+                                cpx_t a = cmul(v[q], p.blue_chirp[k]);
+                                if (p.blue_swap) a = cswap(a);
+                                ps[q * T] = a;
+                            }
+                        }
+                    } else if (ds == 1) {
 #pragma unroll
                         for (int q = 0; q < E; ++q) ps[q * T] = v[q];
                     } else {
