@@ -139,6 +139,56 @@ static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
     return 0;
 }
 
+// ------------------------------------------------------------------------- scattered last step
+int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long long plane_stride, const long long *pstride) {
+    if (!p || p->pc.steps.empty() || nowners < 1 || nowners > B2_MAXSCAT || blk < 1) return -1;
+    if (p->chains && !p->chains->empty()) return -1;
+    const StepPlan &last = p->pc.steps.back();
+    if (last.kind != SK_PASS || last.fast_id < 0 || !last.outer.empty() || last.dst != B_OUT) return -1;
+    const TileEntry &e = b2_tile_table()[last.fast_id];
+    if (e.mode != MODE_COL || e.epi != 0) return -1;
+    StepPlan *st = new StepPlan(last);
+    PassParams &q = st->pp;
+    q = last.gen_pp;  // as built by make_pass_step, before the tile selection
+    q.scat_dim = -1;
+    for (int d = 1; d < q.nld; ++d)
+        if (q.ld[d] == plane_stride && q.scat_dim < 0) q.scat_dim = d;
+    if (q.nld == 1 && q.ln[0] > 0) q.scat_dim = -1;  // a single plane: coordinate 0
+    else if (q.scat_dim < 0) {
+        delete st;
+        return -1;
+    }
+    if (q.scat_dim >= 0) q.ld[q.scat_dim] = 0;  // the plane offset is per owner
+    q.scat_n = nowners;
+    q.scat_blk = (int)blk;
+    b2_fastdiv_make((unsigned long long)blk, q.scat_m, q.scat_s);
+    for (int o = 0; o < nowners; ++o) q.scat_pstride[o] = pstride[o];
+    b2_select_tile_kernel(*st);
+    if (st->fast_id < 0 || b2_tile_table()[st->fast_id].epi != 8) {
+        delete st;
+        return -1;
+    }
+    delete p->scat;
+    p->scat = st;
+    return 0;
+}
+
+int b2_plan_execute_scatter(b2fft_plan_s *p, void *in, void *out, real_t *const *bases, long long coord0,
+                            stream_t stream) {
+    if (!p || !p->scat) return -1;
+    real_t *buf[B_NBUF] = {(real_t *)in, (real_t *)out, p->scr, p->wrk};
+    const size_t ns = p->pc.steps.size();
+    for (size_t i = 0; i + 1 < ns; ++i) {
+        const StepPlan &s = p->pc.steps[i];
+        int rc = launch_step(s, buf[s.src], buf[s.dst], stream);
+        if (rc) return rc;
+    }
+    StepPlan s = *p->scat;
+    for (int o = 0; o < s.pp.scat_n; ++o) s.pp.scat_base[o] = bases[o];
+    s.pp.scat_coord0 = coord0;
+    return launch_step(s, buf[s.src], buf[s.dst], stream);
+}
+
 #if B2_CUDA
 static void pipe_destroy(b2fft_plan *p);
 #endif
@@ -249,6 +299,7 @@ extern "C" void b2fft_plan_destroy(b2fft_plan *p) {
     dev_free(p->scr);
     dev_free(p->wrk);
     if (p->alt) b2fft_plan_destroy(p->alt);
+    delete p->scat;
     dev_free(p->dev_in);
     dev_free(p->dev_out);
 #if B2_CUDA

@@ -8,6 +8,7 @@
 
 #define B2_MAXPASS 14
 #define B2_MAXLD 4
+#define B2_MAXSCAT 16
 
 enum { RM_C2C = 0, RM_R2C_HALF = 1, RM_C2R_HALF = 2, RM_R2C_FULL = 3, RM_C2R_FULL = 4 };
 
@@ -58,6 +59,16 @@ struct PassParams {
     unsigned gnb_m[B2_MAXPASS], gnb_s[B2_MAXPASS];  // by m / radix[pass]
     unsigned gns_m[B2_MAXPASS], gns_s[B2_MAXPASS];  // by Ns(pass) = prod of earlier radices
     long long nblocks;                        // tiles in the whole pass
+    // ---- scattered store of a column pass (slab exchange fused into the FFT, slab.cu): output row k
+    // of the plane with coordinate cc along line dim scat_dim belongs to owner o = k / scat_blk and is
+    // stored at scat_base[o] + (scat_coord0 + cc) * scat_pstride[o] + (k - o*scat_blk) * d_axis + line
+    // offset (reals).  The bases are the owners' receive buffers (peer memory over NVLink, or this
+    // rank's own).  scat_n == 0: off.
+    int scat_n, scat_blk, scat_dim;
+    unsigned scat_m, scat_s;                  // exact division by scat_blk
+    long long scat_coord0;
+    real_t *scat_base[B2_MAXSCAT];
+    long long scat_pstride[B2_MAXSCAT];
 };
 
 // Division by an invariant d for 0 <= n < 2^31 (Granlund-Montgomery): with l = ceil(log2 d) and

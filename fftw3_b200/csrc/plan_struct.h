@@ -34,6 +34,14 @@ struct b2fft_plan_s {
     std::vector<b2::Chain> *chains = nullptr;
     bool needs_aligned = false;     // has steps without a generic-kernel form
     b2fft_plan_s *alt = nullptr;    // the same problem without them, for unaligned arrays
+    b2::StepPlan *scat = nullptr;   // the last step re-selected with a scattered store (slab.cu)
 };
+// Fused slab exchange: turn the plan's last step (a column pass writing rows of the transformed
+// axis) into one that stores row k into the receive buffer of its owner k / blk.  plane_stride =
+// dst stride (reals) of the line dim that numbers the planes; pstride[o] = owner o's plane stride.
+// Returns 0 when the step qualifies (tile kernel, column mode, no other epilogue).
+int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long long plane_stride, const long long *pstride);
+int b2_plan_execute_scatter(b2fft_plan_s *p, void *in, void *out, real_t *const *bases, long long coord0,
+                            b2::stream_t stream);
 void b2_slab_destroy(b2fft_plan_s *p);
 int b2_slab_execute(b2fft_plan_s *p, void *in, void *out);

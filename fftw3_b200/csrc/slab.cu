@@ -207,7 +207,28 @@ struct SlabPlan {
     bool p2p = false;
     std::vector<cpx_t *> peerS, peerR;
     float *flag = nullptr;  // tiny device buffer for the cross-rank barrier
+    // fused exchange: the n1-axis pass of stage 1 stores every output row straight into its owner's
+    // receive buffer (tile kernel EPI 8) -- no send-side DMA, no second trip through HBM
+    bool fused = false;
+#if B2_CUDA
+    // DMA exchange: one stream per peer so that the copies to different peers run on different copy engines
+    std::vector<cudaStream_t> sx;
+    std::vector<cudaEvent_t> evx;
+    cudaEvent_t evb = nullptr;
+#endif
 };
+
+// switch the stage-1 plans to the scattered store; all-or-nothing
+static void slab_enable_fused(SlabPlan &s) {
+    s.fused = false;
+    if (getenv("B2FFT_SLAB_NO_FUSED") || (int)s.peerR.size() != s.P || s.P > B2_MAXSCAT) return;
+    std::vector<long long> ps(s.P);
+    for (int o = 0; o < s.P; ++o) ps[o] = (long long)blk_len(s.n1, s.b1, o) * s.n2 * 2;
+    bool ok = true;
+    for (b2fft_plan *p : {s.p1, s.p1_tail})
+        if (p) ok = ok && b2_plan_enable_scatter(p, s.P, (long long)s.b1, (long long)s.n1 * s.n2 * 2, ps.data()) == 0;
+    s.fused = ok && (s.p1 || s.p1_tail || s.ln0 == 0);
+}
 
 #if B2_CUDA
 static int slab_setup_p2p(SlabPlan &s);
@@ -283,6 +304,11 @@ void b2_slab_destroy(b2fft_plan_s *p) {
             if (s->peerR[q]) cudaIpcCloseMemHandle(s->peerR[q]);
         }
     if (s->flag) cudaFree(s->flag);
+    for (cudaStream_t x : s->sx)
+        if (x) cudaStreamDestroy(x);
+    for (cudaEvent_t e : s->evx)
+        if (e) cudaEventDestroy(e);
+    if (s->evb) cudaEventDestroy(s->evb);
 #endif
     dev_free(s->S);
     dev_free(s->R);
@@ -297,6 +323,23 @@ void b2_slab_destroy(b2fft_plan_s *p) {
 #endif
     delete s;
     p->slab = nullptr;
+}
+
+static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
+    SlabPlan *s = &sr;
+    const ptrdiff_t n0 = s->n0, n1 = s->n1, n2 = s->n2;
+    char buf[512];
+    snprintf(buf, sizeof buf,
+             "  slab 3-D c2c %td x %td x %td over %d ranks (rank %d: planes %td+%td, out rows %td+%td), %s output\n"
+             "  stage 1: %d chunk(s) of %td plane(s), (n1 x n2) FFTs in->send; exchange: %s\n"
+             "  stage 2: length-%td FFTs recv->out\n",
+             n0, n1, n2, s->P, s->pe, s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
+             s->nchunks, s->chunk,
+             s->fused ? "fused into the n1 pass: rows stored straight into their owner's receive buffer (peer memory over NVLink)"
+             : s->P == 1 ? "local copy" : s->p2p ? "strided DMA into peer memory (CUDA IPC over NVLink), one stream per peer, NCCL barrier"
+                                                : "ncclSend/ncclRecv per plane and peer",
+             n0);
+    bp->pc.desc = buf;
 }
 
 extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
@@ -366,8 +409,13 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
         for (cudaEvent_t &e : s->ev) ok = ok && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
         for (cudaEvent_t *e : {&s->t0, &s->t1, &s->t2, &s->t3}) ok = ok && cudaEventCreate(e) == cudaSuccess;
         if (ok) ok = slab_setup_p2p(*s) == 0;
+        if (ok && s->p2p) slab_enable_fused(*s);
     }
 #endif
+    if (ok && s->P == 1) {  // one rank: the "exchange" is the scatter into this rank's own receive buffer
+        s->peerR.assign(1, s->R);
+        slab_enable_fused(*s);
+    }
     if (!ok) {
         b2_slab_destroy(bp);
         delete bp;
@@ -375,17 +423,7 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
     }
     double N = (double)n0 * n1 * n2;
     bp->pc.flops = 5.0 * N * log2(N) / s->P;
-    char buf[512];
-    snprintf(buf, sizeof buf,
-             "  slab 3-D c2c %td x %td x %td over %d ranks (rank %d: planes %td+%td, out rows %td+%td), %s output\n"
-             "  stage 1: %d chunk(s) of %td plane(s), (n1 x n2) FFTs in->send; exchange: %s\n"
-             "  stage 2: length-%td FFTs recv->out\n",
-             n0, n1, n2, s->P, s->pe, s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
-             s->nchunks, s->chunk,
-             s->P == 1 ? "local copy" : s->p2p ? "strided DMA into peer memory (CUDA IPC over NVLink), NCCL barrier"
-                                                : "ncclSend/ncclRecv per plane and peer",
-             n0);
-    bp->pc.desc = buf;
+    slab_describe(*s, bp);
     return bp;
 }
 
@@ -495,12 +533,25 @@ static int slab_setup_p2p(SlabPlan &s) {
     B2_CK(cudaMemcpy(&bad, s.flag, sizeof(float), cudaMemcpyDeviceToHost));
     B2_CK(cudaMemset(s.flag, 0, 256));
     s.p2p = (bad == 0.0f);
+    if (s.p2p && !getenv("B2FFT_SLAB_ONE_STREAM")) {
+        s.sx.assign(s.P, nullptr);
+        s.evx.assign(s.P, nullptr);
+        for (int d = 0; d < s.P; ++d) {
+            B2_CK(cudaStreamCreateWithFlags(&s.sx[d], cudaStreamNonBlocking));
+            B2_CK(cudaEventCreateWithFlags(&s.evx[d], cudaEventDisableTiming));
+        }
+        B2_CK(cudaEventCreateWithFlags(&s.evb, cudaEventDisableTiming));
+    }
     return 0;
 }
-static int slab_exchange_p2p(SlabPlan &s, int chunk, bool reverse, cudaStream_t st) {
+// `after`: event the copies must wait for (the chunk's FFTs); with per-peer streams every copy runs on
+// its peer's stream and `st` later joins them (slab_join_peers)
+static int slab_exchange_p2p(SlabPlan &s, int chunk, bool reverse, cudaStream_t st0, cudaEvent_t after = nullptr) {
     const size_t esz = sizeof(cpx_t);
     for (int d = 0; d < s.P; ++d) {
         const int p = (s.pe + d) % s.P;
+        cudaStream_t st = (after && !s.sx.empty()) ? s.sx[d] : st0;
+        if (after) B2_CK(cudaStreamWaitEvent(st, after, 0));
         if (!reverse) {
             // my planes [a,b) of this chunk -> peer p's receive buffer R_p[s0 + i0][*][*]
             const ptrdiff_t ln1p = blk_len(s.n1, s.b1, p);
@@ -521,6 +572,13 @@ static int slab_exchange_p2p(SlabPlan &s, int chunk, bool reverse, cudaStream_t 
     }
     return 0;
 }
+static int slab_join_peers(SlabPlan &s, cudaStream_t st) {
+    for (size_t d = 0; d < s.sx.size(); ++d) {
+        B2_CK(cudaEventRecord(s.evx[d], s.sx[d]));
+        B2_CK(cudaStreamWaitEvent(st, s.evx[d], 0));
+    }
+    return 0;
+}
 #endif
 
 // stage 0: local (n1 x n2) FFTs of chunk k, in -> S
@@ -531,7 +589,24 @@ static int slab_stage1_chunk(SlabPlan &s, int k, cpx_t *in, stream_t st) {
     b2fft_plan *p = (s.p1 && cnt == std::min(s.chunk, s.ln0)) ? s.p1 : s.p1_tail;
     if (!p) return -6;
     const size_t off = (size_t)a * s.n1 * s.n2;
+    if (s.fused) {
+        std::vector<real_t *> bases(s.P);
+        for (int o = 0; o < s.P; ++o) bases[o] = (real_t *)s.peerR[o];
+        return b2_plan_execute_scatter(p, in + off, s.S + off, bases.data(), (long long)(s.s0 + a), st);
+    }
     return b2fft_execute_async(p, in + off, s.S + off, st);
+}
+
+// test hook (also usable by a caller with its own peer mapping): the receive buffers of all ranks as
+// seen from this process; switches stage 0 to the fused scatter.  Returns 1 when fused.
+extern "C" int b2fft_slab_set_peer_recv(b2fft_plan *p, void *const *recv, int n) {
+    if (!p || !p->slab || n != p->slab->P) return -1;
+    SlabPlan &s = *p->slab;
+    s.peerR.assign(n, nullptr);
+    for (int o = 0; o < n; ++o) s.peerR[o] = (cpx_t *)recv[o];
+    slab_enable_fused(s);
+    slab_describe(s, p);
+    return s.fused ? 1 : 0;
 }
 
 // ---- staged API: lets a test (or a caller with its own transport) drive the phases ----
@@ -550,7 +625,7 @@ extern "C" int b2fft_slab_stage(b2fft_plan *p, int stage, void *in, void *out) {
     if (stage == 0) {
         for (int k = 0; k < s.nchunks && !rc; ++k) rc = slab_stage1_chunk(s, k, (cpx_t *)in, st);
     } else if (stage == 1) {
-        for (int k = 0; k < s.nchunks && !rc; ++k) rc = slab_exchange(s, k, s.S, s.R, false, st);
+        for (int k = 0; k < s.nchunks && !rc && !s.fused; ++k) rc = slab_exchange(s, k, s.S, s.R, false, st);
     } else if (stage == 2) {
         if (s.p2) rc = b2fft_execute_async(s.p2, s.R, s.transposed_out ? out : (void *)s.R, st);
     } else if (stage == 3) {
@@ -590,28 +665,52 @@ int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
         dout = s.dev_out;
     }
     B2_CK(cudaEventRecord(s.t0, s.sc));
+    if (s.fused) {
+        // one stream: [barrier: nobody still reads the receive buffers] row pass, n1 pass + scatter, per
+        // chunk; [barrier: every rank's rows have landed]
+        int rc = slab_barrier(s, s.sc);
+        if (rc) return rc;
+        for (int k = 0; k < s.nchunks; ++k) {
+            rc = slab_stage1_chunk(s, k, din, s.sc);
+            if (rc) return rc;
+        }
+        rc = slab_barrier(s, s.sc);
+        if (rc) return rc;
+        B2_CK(cudaEventRecord(s.t1, s.sc));
+        B2_CK(cudaEventRecord(s.t2, s.sc));
+    } else {
     if (s.p2p) {
         // nobody may still be reading the receive buffer this exchange is about to overwrite
         int rc = slab_barrier(s, s.sn);
         if (rc) return rc;
+        if (!s.sx.empty()) {
+            B2_CK(cudaEventRecord(s.evb, s.sn));
+            for (cudaStream_t x : s.sx) B2_CK(cudaStreamWaitEvent(x, s.evb, 0));
+        }
     }
     for (int k = 0; k < s.nchunks; ++k) {
         int rc = slab_stage1_chunk(s, k, din, s.sc);
         if (rc) return rc;
         B2_CK(cudaEventRecord(s.ev[k], s.sc));
-        B2_CK(cudaStreamWaitEvent(s.sn, s.ev[k], 0));
-        rc = s.p2p ? slab_exchange_p2p(s, k, false, s.sn) : slab_exchange(s, k, s.S, s.R, false, s.sn);
+        if (s.p2p && !s.sx.empty())
+            rc = slab_exchange_p2p(s, k, false, s.sn, s.ev[k]);
+        else {
+            B2_CK(cudaStreamWaitEvent(s.sn, s.ev[k], 0));
+            rc = s.p2p ? slab_exchange_p2p(s, k, false, s.sn) : slab_exchange(s, k, s.S, s.R, false, s.sn);
+        }
         if (rc) return rc;
     }
     if (s.p2p) {
         // all pushes into my receive buffer have landed once every rank has passed this point
-        int rc = slab_barrier(s, s.sn);
+        int rc = slab_join_peers(s, s.sn);
+        if (!rc) rc = slab_barrier(s, s.sn);
         if (rc) return rc;
     }
     B2_CK(cudaEventRecord(s.t1, s.sc));
     B2_CK(cudaEventRecord(s.ev[s.nchunks], s.sn));
     B2_CK(cudaStreamWaitEvent(s.sc, s.ev[s.nchunks], 0));
     B2_CK(cudaEventRecord(s.t2, s.sc));
+    }
     if (s.p2) {
         int rc = b2fft_execute_async(s.p2, s.R, s.transposed_out ? (void *)dout : (void *)s.R, s.sc);
         if (rc) return rc;

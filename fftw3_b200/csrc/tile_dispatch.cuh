@@ -1,7 +1,7 @@
 // csrc/tile_dispatch.cuh -- table of instantiated tile kernels and the rule that picks one
 // for a step (the "selector over kernel configurations" for the hot geometries).
 #pragma once
-#include "tile_kernel.cuh"
+#include "colpipe_kernel.cuh"
 
 #ifndef B2_MINB256
 #define B2_MINB256 4
@@ -12,6 +12,7 @@ struct TileEntry {
     size_t (*smem_for)(int C);
     int (*launch)(const PassParams &, const real_t *, real_t *, long long, long long, int, size_t, b2::stream_t);
     void (*init)();
+    int pipe;  // 1: persistent, software-pipelined column kernel (colpipe_kernel.cuh)
 };
 
 template <int N, int E, int MODE, int EPI, int C>
@@ -58,7 +59,53 @@ struct TileInst {
 #endif
     }
     static TileEntry entry() {
-        return TileEntry{N, E, MODE, EPI, C, THREADS, TileFFT<N, E, MODE, EPI>::smem_bytes(C), &smem_for, &launch, &init};
+        return TileEntry{N, E, MODE, EPI, C, THREADS, TileFFT<N, E, MODE, EPI>::smem_bytes(C), &smem_for, &launch, &init, 0};
+    }
+};
+
+// persistent pipelined column kernel: grid = resident CTAs, each walks a stripe of tiles
+template <int N, int E, int EPI, int C>
+struct TilePipeInst {
+    static constexpr int THREADS = C * (N / E);
+    static constexpr int MINB = THREADS <= 256 ? 4 : THREADS <= 512 ? 2 : 1;
+    static int launch(const PassParams &p, const real_t *src, real_t *dst, long long b0, long long nb,
+                      int threads, size_t smem, b2::stream_t st) {
+#if B2_CUDA
+        if (((uintptr_t)src & 15) != 0)  // 16-byte async copies need a 16-byte aligned array
+            return TileInst<N, E, MODE_COL, EPI, C>::launch(p, src, dst, b0, nb, threads,
+                                                             TileFFT<N, E, MODE_COL, EPI>::smem_bytes(C), st);
+        static int wave = -1;
+        if (wave < 0) {
+            int occ = 1;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b2_colpipe_kernel<N, E, EPI, THREADS, MINB>, threads,
+                                                              smem) != cudaSuccess || occ < 1) {
+                cudaGetLastError();
+                occ = 1;
+            }
+            wave = occ * b2::sm_count();
+        }
+        PassParams q = p;
+        q.pf_ahead = 0;
+        const long long grid = nb < wave ? nb : wave;
+        b2_colpipe_kernel<N, E, EPI, THREADS, MINB><<<(unsigned)grid, threads, smem, st>>>(q, src, dst, b0, b0 + nb);
+        return 0;
+#else
+        (void)st;
+        std::vector<char> sm(smem + 64);
+        const long long grid = nb < 3 ? nb : 3;  // few "CTAs": every one walks a stripe of several tiles
+        for (long long b = 0; b < grid; ++b) TilePipe<N, E, EPI>::run(p, src, dst, b0 + b, b0 + nb, grid, sm.data(), threads);
+        return 0;
+#endif
+    }
+    static size_t smem_for(int c) { return TilePipe<N, E, EPI>::smem_bytes(c); }
+    static void init() {
+#if B2_CUDA
+        cudaFuncSetAttribute(b2_colpipe_kernel<N, E, EPI, THREADS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)TilePipe<N, E, EPI>::smem_bytes(C));
+#endif
+    }
+    static TileEntry entry() {
+        return TileEntry{N, E, MODE_COL, EPI, C, THREADS, TilePipe<N, E, EPI>::smem_bytes(C), &smem_for, &launch, &init, 1};
     }
 };
 
@@ -69,7 +116,7 @@ struct TileInst {
     X(N, E, MODE_ROW, 0, CROW) X(N, E, MODE_COL, 0, CCOL) X(N, E, MODE_COL, 1, CCOL) X(N, E, MODE_ROW2COL, 0, CCOL)
 #define B2_TILE_REALMODES(X, N, E, CROW, CCOL) \
     X(N, E, MODE_COL, 2, CCOL) X(N, E, MODE_ROW, 3, CROW) X(N, E, MODE_ROW, 4, CROW) X(N, E, MODE_ROW2COL, 5, CCOL) \
-    X(N, E, MODE_ROW, 6, CROW) X(N, E, MODE_ROW, 7, CROW)
+    X(N, E, MODE_ROW, 6, CROW) X(N, E, MODE_ROW, 7, CROW) X(N, E, MODE_COL, 8, CCOL)
 // column-tile widths of the long column kernels (lines per CTA); overridable for experiments
 #ifndef B2_CC512
 #define B2_CC512 16
@@ -115,10 +162,20 @@ struct TileInst {
     X(2048, 8, MODE_ROW, 6, 1) X(2048, 8, MODE_ROW, 7, 1) X(4096, 8, MODE_ROW, 6, 1) X(4096, 8, MODE_ROW, 7, 1)
 #endif
 
+// P(N, E, EPI, C): the pipelined column kernels; listed after the plain ones, preferred by the selector
+#define B2_PIPE_EPIS(P, N, E, C) P(N, E, 0, C) P(N, E, 1, C) P(N, E, 8, C)
+#if defined(FFTW_SINGLE)
+#define B2_PIPE_LIST(P) B2_PIPE_EPIS(P, 512, B2_E512, B2_CC512) B2_PIPE_EPIS(P, 1024, B2_E1024, B2_CC1024) B2_PIPE_EPIS(P, 2048, 16, B2_CC2048)
+#else
+#define B2_PIPE_LIST(P) B2_PIPE_EPIS(P, 512, 8, 8) B2_PIPE_EPIS(P, 1024, 8, 8)
+#endif
+
 inline const std::vector<TileEntry> &b2_tile_table() {
 #define B2_X_ENTRY(N, E, MODE, EPI, C) TileInst<N, E, MODE, EPI, C>::entry(),
-    static const std::vector<TileEntry> tab = {B2_TILE_LIST(B2_X_ENTRY) B2_TILE_LIST_REAL(B2_X_ENTRY)};
+#define B2_P_ENTRY(N, E, EPI, C) TilePipeInst<N, E, EPI, C>::entry(),
+    static const std::vector<TileEntry> tab = {B2_TILE_LIST(B2_X_ENTRY) B2_TILE_LIST_REAL(B2_X_ENTRY) B2_PIPE_LIST(B2_P_ENTRY)};
 #undef B2_X_ENTRY
+#undef B2_P_ENTRY
     return tab;
 }
 
@@ -157,34 +214,51 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         mode = MODE_ROW2COL;
     else
         return;
-    const int epi = p.rmode == RM_R2C_HALF ? 3 : p.rmode == RM_C2R_HALF ? 4 : p.blue_mode ? p.blue_mode : p.pmerge ? 5 : p.rsplit ? 2 : (p.epi_dim >= 0 ? 1 : 0);
+    const int epi = p.rmode == RM_R2C_HALF ? 3 : p.rmode == RM_C2R_HALF ? 4 : p.blue_mode ? p.blue_mode : p.pmerge ? 5 : p.rsplit ? 2 : p.scat_n > 0 ? 8 : (p.epi_dim >= 0 ? 1 : 0);
     if (p.blue_mode && mode != MODE_ROW) return;
     if (real_half && mode != MODE_ROW) return;
-    if ((epi == 1 || epi == 2) && mode != MODE_COL) return;
+    if ((epi == 1 || epi == 2 || epi == 8) && mode != MODE_COL) return;
+    if (epi == 8 && p.epi_dim >= 0) return;
     if (p.rsplit && p.epi_dim != 0) return;
     if (p.fold_n > 0 && mode != (p.swap_in ? MODE_COL : MODE_ROW2COL)) return;  // fold on the way out / unfold on the way in
     if (p.pmerge && mode != MODE_ROW2COL) return;
     if (p.fold_n > 0 && p.swap_in && (p.ls[0] != 2 || p.fold_n >= (1ll << 30))) return;  // unfold load: unit stride, 32-bit indices
     const std::vector<TileEntry> &tab = b2_tile_table();
+    // pipelined column kernels: 16-byte async copies -> every stride a multiple of 16 bytes
+    bool pipe_ok = !getenv("FFTW_B200_NO_PIPE");
+    if (sizeof(real_t) == 4) {
+        if (p.s_axis & 3) pipe_ok = false;
+        for (int d = 1; d < p.nld; ++d)
+            if (p.ls[d] & 3) pipe_ok = false;
+        for (const b2::LDim &o : s.outer)
+            if (o.s & 3) pipe_ok = false;
+    }
+    if (p.fold_n > 0) pipe_ok = false;  // the Hermitian unfold load is not a plain tile copy
+    if (const char *e = getenv("FFTW_B200_PIPE_MIN_N"))
+        if (p.m < atoi(e)) pipe_ok = false;
+    for (int pass = pipe_ok ? 1 : 0; pass >= 0 && s.fast_id < 0; --pass)
     for (size_t i = 0; i < tab.size(); ++i) {
         const TileEntry &e = tab[i];
-        if (e.n != p.m || e.mode != mode || e.epi != epi) continue;
+        if (e.n != p.m || e.mode != mode || e.epi != epi || e.pipe != pass) continue;
         s.fast_id = (int)i;
         p.C = e.c;
         p.tiles0 = (p.ln[0] + p.C - 1) / p.C;
         long long nb = p.tiles0;
         for (int d = 1; d < p.nld; ++d) nb *= p.ln[d];
-        if (nb >= (1ll << 31)) continue;  // the tile kernels decode a 31-bit tile index
+        if (nb >= (1ll << 31)) {  // the tile kernels decode a 31-bit tile index
+            s.fast_id = -1;
+            continue;
+        }
         s.nblocks = nb;
         s.nthreads = e.threads;
         s.smem = e.smem;
         static const char *mn[] = {"row", "col", "row->col"};
-        static const char *en[] = {"", "+twiddle", "+real-pair split+twiddle", "+hermitian split (r2c)", "+hermitian merge (c2r)", "+real-pair merge", "+chirp in, x bhat out (bluestein)", "+chirp out (bluestein)"};
+        static const char *en[] = {"", "+twiddle", "+real-pair split+twiddle", "+hermitian split (r2c)", "+hermitian merge (c2r)", "+real-pair merge", "+chirp in, x bhat out (bluestein)", "+chirp out (bluestein)", "+scatter to the owners' receive buffers (slab exchange)"};
         char buf[256];
         std::string rs;
         for (int i2 = 0; i2 < p.npass; ++i2) rs += (i2 ? "x" : "") + std::to_string(p.radix[i2]);
-        snprintf(buf, sizeof buf, "%s n=%d tile-kernel[%s%s] E=%d regs-resident, tile=%dx%d ctas=%lld threads=%d smem=%zuB",
-                 real_half ? (epi == 3 ? "r2c" : "c2r") : "c2c", real_half ? p.n : p.m, mn[mode], p.fold_n > 0 ? (p.swap_in ? "+hermitian unfold+twiddle" : "+hermitian fold") : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
+        snprintf(buf, sizeof buf, "%s n=%d tile-kernel[%s%s%s] E=%d regs-resident, tile=%dx%d ctas=%lld threads=%d smem=%zuB",
+                 real_half ? (epi == 3 ? "r2c" : "c2r") : "c2c", real_half ? p.n : p.m, mn[mode], e.pipe ? ", persistent, async-copy pipelined" : "", p.fold_n > 0 ? (p.swap_in ? "+hermitian unfold+twiddle" : "+hermitian fold") : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
         s.desc = buf;
         return;
     }

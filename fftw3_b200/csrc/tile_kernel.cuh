@@ -50,6 +50,7 @@ struct TileCtx {
     long long sbase, dbase;
     int nlines;
     int i2base;
+    int scoord;           // coordinate along the scatter dim (EPI 8)
     int nthreads;
 };
 
@@ -137,7 +138,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
 
     // tile index -> coordinates: exact multiply-shift divisions (b2_pp_prepare), 31-bit index
     static B2_D void decode(const PassParams &p, unsigned bid, long long &l0, int &nlines, long long &sbase,
-                            long long &dbase, int &i2base) {
+                            long long &dbase, int &i2base, int *scoord = nullptr) {
         const int C = p.C;
         unsigned rest = b2_fastdiv(bid, p.dv_m[0], p.dv_s[0]);
         const unsigned t0 = bid - rest * (unsigned)p.tiles0;
@@ -153,6 +154,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
             sbase += (long long)cc * p.ls[d];
             dbase += (long long)cc * p.ld[d];
             if (d == p.epi_dim) i2base = (int)cc;
+            if (EPI == 8 && scoord && d == p.scat_dim) *scoord = (int)cc;
         }
     }
 
@@ -440,6 +442,71 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
         return true;
     }
 
+    // registers -> global memory, v[q] holds output index t + q*T of line c (EPI 0, 1, 6, 7, 8)
+    static B2_D void store_regs(const TileCtx &x, const PassParams &p, cpx_t *cdst, cpx_t *v, int c, int t) {
+        const long long base = (x.dbase + (x.l0 + c) * p.ld[0]) / 2;
+        const long long ds = p.d_axis / 2;
+        if (EPI == 1) {
+            // w_Nbig^(i2*k), k = t + q*T: base * step^q, both from the two-level table
+            const unsigned long long i2 = (p.epi_dim == 0) ? (unsigned long long)(x.l0 + c)
+                                                           : (unsigned long long)x.i2base;
+            const unsigned long long mask = (1ull << p.epi_shift) - 1;
+            const unsigned long long e0 = i2 * (unsigned long long)t, e1 = i2 * (unsigned long long)T;
+            const cpx_t wb = cmul(p.epi_hi[e0 >> p.epi_shift], p.epi_lo[e0 & mask]);
+            const cpx_t ws = cmul(p.epi_hi[e1 >> p.epi_shift], p.epi_lo[e1 & mask]);
+            cpx_t wq[E];
+            wq[0] = cpx_t{1, 0};
+            b2_twiddle_powers<E>(ws, wq);
+#pragma unroll
+            for (int q = 0; q < E; ++q) v[q] = cmul(v[q], q ? cmul(wb, wq[q]) : wb);
+        }
+        if (EPI == 6) {  // Bluestein: spectrum of the padded line times bhat = FFT_M(conj chirp) / M
+#pragma unroll
+            for (int q = 0; q < E; ++q) v[q] = cmul(v[q], p.blue_bhat[t + q * T]);
+        }
+        if (p.swap_out) {
+#pragma unroll
+            for (int q = 0; q < E; ++q) v[q] = cswap(v[q]);
+        }
+        cpx_t *ps = cdst + (base + (long long)t * ds);
+        if (EPI == 8) {
+            // slab exchange fused into the store: row k goes to its owner's receive buffer
+            // (peer memory over NVLink, 128-byte segments per warp row), dbase excludes the
+            // scatter dim (its stride is per owner)
+            const long long plane = p.scat_coord0 + x.scoord;
+            const long long loff = x.dbase + (x.l0 + c) * p.ld[0];
+#pragma unroll
+            for (int q = 0; q < E; ++q) {
+                const unsigned k = (unsigned)(t + q * T);
+                const unsigned o = b2_fastdiv(k, p.scat_m, p.scat_s);
+                const long long r = (long long)(k - o * (unsigned)p.scat_blk);
+                cpx_t *po = reinterpret_cast<cpx_t *>(p.scat_base[o]) +
+                            (plane * p.scat_pstride[o] + r * p.d_axis + loff) / 2;
+                *po = v[q];
+            }
+        } else if (EPI == 7) {  // Bluestein, inverse FFT done: X[k] = conv[k] * chirp[k], k < n only
+#pragma unroll
+            for (int q = 0; q < E; ++q) {
+                const int k = t + q * T;
+                if (k < p.blue_n) {
+                    cpx_t a = cmul(v[q], p.blue_chirp[k]);
+                    if (p.blue_swap) a = cswap(a);
+                    ps[q * T] = a;
+                }
+            }
+        } else if (ds == 1) {
+#pragma unroll
+            for (int q = 0; q < E; ++q) ps[q * T] = v[q];
+        } else {
+            const long long step = (long long)T * ds;
+#pragma unroll
+            for (int q = 0; q < E; ++q) {
+                *ps = v[q];
+                ps += step;
+            }
+        }
+    }
+
     static B2_D void run(const PassParams &p, const real_t *B2_RESTRICT src, real_t *B2_RESTRICT dst,
                          long long bid, char *smem, int b2_nthreads) {
         (void)b2_nthreads;
@@ -456,7 +523,8 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
         x.vbase = vreg_store.data();
 #endif
         const int C = p.C;
-        decode(p, (unsigned)bid, x.l0, x.nlines, x.sbase, x.dbase, x.i2base);
+        x.scoord = 0;
+        decode(p, (unsigned)bid, x.l0, x.nlines, x.sbase, x.dbase, x.i2base, &x.scoord);
         const cpx_t *csrc = reinterpret_cast<const cpx_t *>(src);
         cpx_t *cdst = reinterpret_cast<cpx_t *>(dst);
 
@@ -578,54 +646,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                 cpx_t *v = B2_TREGS(x);
                 int c, t;
                 const bool live = map(tid, C, p.lgC, c, t);
-                if (live && c < x.nlines) {
-                    const long long base = (x.dbase + (x.l0 + c) * p.ld[0]) / 2;
-                    const long long ds = p.d_axis / 2;
-                    if (EPI == 1) {
-                        // w_Nbig^(i2*k), k = t + q*T: base * step^q, both from the two-level table
-                        const unsigned long long i2 = (p.epi_dim == 0) ? (unsigned long long)(x.l0 + c)
-                                                                       : (unsigned long long)x.i2base;
-                        const unsigned long long mask = (1ull << p.epi_shift) - 1;
-                        const unsigned long long e0 = i2 * (unsigned long long)t, e1 = i2 * (unsigned long long)T;
-                        const cpx_t wb = cmul(p.epi_hi[e0 >> p.epi_shift], p.epi_lo[e0 & mask]);
-                        const cpx_t ws = cmul(p.epi_hi[e1 >> p.epi_shift], p.epi_lo[e1 & mask]);
-                        cpx_t wq[E];
-                        wq[0] = cpx_t{1, 0};
-                        b2_twiddle_powers<E>(ws, wq);
-#pragma unroll
-                        for (int q = 0; q < E; ++q) v[q] = cmul(v[q], q ? cmul(wb, wq[q]) : wb);
-                    }
-                    if (EPI == 6) {  // Bluestein: spectrum of the padded line times bhat = FFT_M(conj chirp) / M
-#pragma unroll
-                        for (int q = 0; q < E; ++q) v[q] = cmul(v[q], p.blue_bhat[t + q * T]);
-                    }
-                    if (p.swap_out) {
-#pragma unroll
-                        for (int q = 0; q < E; ++q) v[q] = cswap(v[q]);
-                    }
-                    cpx_t *ps = cdst + (base + (long long)t * ds);
-                    if (EPI == 7) {  // Bluestein, inverse FFT done: X[k] = conv[k] * chirp[k], k < n only
-#pragma unroll
-                        for (int q = 0; q < E; ++q) {
-                            const int k = t + q * T;
-                            if (k < p.blue_n) {
-                                cpx_t a = cmul(v[q], p.blue_chirp[k]);
-                                if (p.blue_swap) a = cswap(a);
-                                ps[q * T] = a;
-                            }
-                        }
-                    } else if (ds == 1) {
-#pragma unroll
-                        for (int q = 0; q < E; ++q) ps[q * T] = v[q];
-                    } else {
-                        const long long step = (long long)T * ds;
-#pragma unroll
-                        for (int q = 0; q < E; ++q) {
-                            *ps = v[q];
-                            ps += step;
-                        }
-                    }
-                }
+                if (live && c < x.nlines) store_regs(x, p, cdst, v, c, t);
             }
         } else {
             // transposed exit: through shared memory, then neighbouring lanes walk the lines

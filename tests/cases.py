@@ -43,6 +43,9 @@ C2C_SHAPES = [(1,), (2,), (3,), (4,), (5,), (7,), (8,), (11,), (13,), (16,), (30
 C2C_BIG = [(8192,), (16384,), (3 * 2 ** 13,), (2 ** 17,), (64, 64, 64), (4, 2 ** 14),
            # tile-kernel modes with ragged tiles (line counts that are not multiples of the tile)
            (3, 128, 72), (20, 64), (64, 20), (7, 1024), (5, 2048), (2048, 5), (2 ** 18,), (3, 2 ** 16), (256, 256)]
+# long strided axes: the persistent async-copy pipelined column kernels (several tiles per CTA stripe,
+# ragged last tiles, plane dims, four-step twiddle epilogue)
+C2C_PIPE = [(512, 80), (1024, 36), (3, 512, 24), (2048, 20), (2, 1024, 8), (2 ** 19,)]
 R2C_SHAPES = [(2,), (4,), (6,), (7,), (9,), (16,), (30,), (64,), (1024,), (6, 8), (5, 9), (4, 4, 6),
               (3, 5, 7)]
 R2C_BIG = [(4096,), (2 ** 15,), (2 ** 17,), (3, 2 ** 14), (32, 32, 32)]

@@ -18,7 +18,7 @@ def lib(request):
     return capi.FFTW3Lib(path, request.param == "fp32")
 
 
-@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG + cases.C2C_PRIME, ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG + cases.C2C_PRIME + cases.C2C_PIPE, ids=lambda s: "x".join(map(str, s)))
 def test_c2c(lib, shape):
     cases.check_c2c(lib, shape)
 
@@ -73,6 +73,14 @@ def test_plan_description_and_flops(lib):
     assert "n=4096" in s and "pass 0" in s
     add, mul, fma = lib.flops(p)
     assert abs((add + mul + fma) - 5 * 4096 * 12 * 4) < 1e-6
+    lib.destroy_plan(p)
+
+
+def test_long_column_axes_take_the_pipelined_kernel(lib):
+    x = np.zeros((1024, 64), dtype=lib.cplx)
+    p = lib.plan_dft([1024, 64], x, x.copy(), -1)
+    assert p
+    assert "async-copy pipelined" in lib.sprint_plan(p), lib.sprint_plan(p)
     lib.destroy_plan(p)
 
 

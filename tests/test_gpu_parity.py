@@ -26,7 +26,7 @@ def lib(request):
     return L
 
 
-@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG + cases.C2C_PRIME, ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("shape", cases.C2C_SHAPES + cases.C2C_BIG + cases.C2C_PRIME + cases.C2C_PIPE, ids=lambda s: "x".join(map(str, s)))
 def test_c2c(lib, shape):
     n0 = lib.lib.b2fft_launch_count()
     cases.check_c2c(lib, shape)

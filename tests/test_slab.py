@@ -112,6 +112,49 @@ def test_ranks_simulated_in_one_process(shape, P, transposed):
         lib.lib.b2fft_comm_destroy(r["comm"])
 
 
+@pytest.mark.parametrize("prec", ["fp64", "fp32"])
+@pytest.mark.parametrize("P", [1, 2, 3, 8])
+@pytest.mark.parametrize("shape", [(12, 32, 6), (9, 64, 16), (20, 128, 3)], ids=lambda s: "x".join(map(str, s)))
+def test_fused_exchange_scatters_into_the_owners_receive_buffers(shape, P, prec):
+    """Stage 0 with the exchange fused into the n1 pass (tile kernel EPI 8): every rank stores row k1 of
+    its planes straight into the receive buffer of rank k1 / block -- here the 'peer memory' is the
+    other simulated ranks' buffers in this process.  No message is moved by the test."""
+    lib = load(prec)
+    lib.lib.b2fft_slab_set_peer_recv.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_int]
+    n0, n1, n2 = shape
+    rng = np.random.default_rng(P + n1)
+    x = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
+    ranks = []
+    for pe in range(P):
+        comm = lib.lib.b2fft_comm_detached(P, pe)
+        N, ln0, s0, ln1, s1 = local_sizes(lib, shape, comm)
+        xin = np.zeros(max(N, 1), dtype=lib.cplx)
+        xin[:ln0 * n1 * n2] = x[s0:s0 + ln0].ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = lib.lib.fftw_mpi_plan_dft_3d(n0, n1, n2, xin.ctypes.data, out.ctypes.data, comm, -1,
+                                            capi.FFTW_ESTIMATE | TRANSPOSED_OUT)
+        assert plan
+        R, bp = buffer_view(lib, plan, 1, lib.cplx)
+        ranks.append(dict(comm=comm, xin=xin, out=out, plan=plan, bp=bp, R=R))
+    recv = (C.c_void_p * P)(*[r["R"].ctypes.data for r in ranks])
+    for r in ranks:
+        assert lib.lib.b2fft_slab_set_peer_recv(r["bp"], recv, P) == 1, "fused path not taken"
+        assert "fused into the n1 pass" in lib.sprint_plan(r["plan"])
+    for r in ranks:
+        assert lib.lib.b2fft_slab_stage(r["bp"], 0, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+        assert lib.lib.b2fft_slab_stage(r["bp"], 1, r["xin"].ctypes.data, r["out"].ctypes.data) == 0  # no-op
+    tol = (1e-6 if lib.single else 1e-14) * np.log2(n0 * n1 * n2)
+    for pe, r in enumerate(ranks):
+        assert lib.lib.b2fft_slab_stage(r["bp"], 2, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+        ref = orc.mpi_dft_3d_local(x, P, pe, transposed_out=True)
+        got = r["out"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < tol, (pe, P)
+    for r in ranks:
+        lib.destroy_plan(r["plan"])
+        lib.lib.b2fft_comm_destroy(r["comm"])
+
+
 def _gloo_worker(rank, world, port, shape, q):
     try:
         import torch
