@@ -59,6 +59,25 @@ template <typename T> B2_HD cpx<T> csub(cpx<T> a, cpx<T> b) { return cpx<T>{a.x 
 template <typename T> B2_HD cpx<T> cmul(cpx<T> a, cpx<T> b) {
     return cpx<T>{a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x};
 }
+// Packed fp32 arithmetic (Blackwell FADD2 / FFMA2: two fp32 operations per issue slot), opt-in with
+// -DB2_F32X2=1.  Tried in round 1 because the tile kernels are issue-bound wherever only one or two
+// CTAs fit an SM and half of their FP instructions are complex additions.  Result (static SASS of
+// b2_tile_kernel<4096,16,row>): 348 FADD -> 96 FADD2 + 96 FFMA2, but +67 MOV and +18 FMUL to build
+// aligned register pairs, i.e. 1744 -> 1664 instructions (-4.6 %), and 48..116 bytes of spills in every
+// 64-register kernel.  Not worth it; left off.
+#ifndef B2_F32X2
+#define B2_F32X2 0
+#endif
+#if B2_CUDA && defined(FFTW_SINGLE) && B2_F32X2 && defined(__CUDA_ARCH__)
+template <> B2_HD cpx<float> cadd<float>(cpx<float> a, cpx<float> b) {
+    const float2 r = __fadd2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y));
+    return cpx<float>{r.x, r.y};
+}
+template <> B2_HD cpx<float> csub<float>(cpx<float> a, cpx<float> b) {
+    const float2 r = __ffma2_rn(make_float2(b.x, b.y), make_float2(-1.0f, -1.0f), make_float2(a.x, a.y));
+    return cpx<float>{r.x, r.y};
+}
+#endif
 template <typename T> B2_HD cpx<T> cconj(cpx<T> a) { return cpx<T>{a.x, -a.y}; }
 template <typename T> B2_HD cpx<T> cswap(cpx<T> a) { return cpx<T>{a.y, a.x}; }
 // a * (-i)

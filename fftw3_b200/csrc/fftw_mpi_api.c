@@ -24,6 +24,27 @@ ptrdiff_t fftw_mpi_local_size_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, MPI_C
     return fftw_mpi_local_size_3d_transposed(n0, n1, n2, comm, local_n0, local_0_start, &a, &b);
 }
 
+/* reference fftw/mpi/api.c:348-372 (local_size_many_transposed): rank 3, default blocks, sizes in
+ * units of complex elements including the howmany interleaved transforms */
+ptrdiff_t fftw_mpi_local_size_many_transposed(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block0,
+                                              ptrdiff_t block1, MPI_Comm comm, ptrdiff_t *local_n0,
+                                              ptrdiff_t *local_0_start, ptrdiff_t *local_n1,
+                                              ptrdiff_t *local_1_start) {
+    int P;
+    if (rnk != 3 || !n || !comm || howmany < 1) return 0;
+    P = b2fft_comm_size(comm);
+    if (block0 != FFTW_MPI_DEFAULT_BLOCK && block0 != (n[0] + P - 1) / P) return 0;
+    if (block1 != FFTW_MPI_DEFAULT_BLOCK && block1 != (n[1] + P - 1) / P) return 0;
+    return howmany * fftw_mpi_local_size_3d_transposed(n[0], n[1], n[2], comm, local_n0, local_0_start, local_n1,
+                                                       local_1_start);
+}
+ptrdiff_t fftw_mpi_local_size_many(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block0, MPI_Comm comm,
+                                   ptrdiff_t *local_n0, ptrdiff_t *local_0_start) {
+    ptrdiff_t a, b;
+    return fftw_mpi_local_size_many_transposed(rnk, n, howmany, block0, FFTW_MPI_DEFAULT_BLOCK, comm, local_n0,
+                                               local_0_start, &a, &b);
+}
+
 fftw_plan fftw_mpi_plan_many_dft(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block, ptrdiff_t tblock,
                                  FFTW_COMPLEX *in, FFTW_COMPLEX *out, MPI_Comm comm, int sign, unsigned flags) {
     fftw_plan p;

@@ -78,6 +78,34 @@ inline bool split_four_step(long long n, long long *n1o, long long *n2o) {
     return true;
 }
 
+// six-step split n = n1 * n2 * n3 for lengths beyond the square of the column limit (2^22 fp32,
+// 2^20 fp64): all three factors within the column limit, as balanced as possible, n1 >= n2 >= n3
+inline bool split_three(long long n, long long *n1o, long long *n2o, long long *n3o) {
+    const Caps c = caps();
+    double bestd = 1e300;
+    long long ba = -1, bb = -1;
+    for (long long a = 2; a <= c.col; ++a) {
+        if (n % a || !factorable(a)) continue;
+        const long long r = n / a;
+        for (long long b = 2; b <= a; ++b) {
+            if (r % b) continue;
+            const long long d = r / b;
+            if (d > b || d < 2 || !factorable(b) || !factorable(d)) continue;
+            const double spread = log((double)a) - log((double)d);
+            if (spread < bestd) {
+                bestd = spread;
+                ba = a;
+                bb = b;
+            }
+        }
+    }
+    if (ba < 0) return false;
+    *n1o = ba;
+    *n2o = bb;
+    *n3o = n / (ba * bb);
+    return true;
+}
+
 inline long long dst_extent(const StepPlan &s) {
     if (s.kind == SK_BLUE) {
         const BlueParams &b = s.bp;
@@ -115,8 +143,8 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
 inline bool axis_direct_ok(long long n, bool row) {
     const Caps c = caps();
     if (n <= (row ? c.row : c.col)) return factorable(n);
-    long long a, b;
-    return split_four_step(n, &a, &b);
+    long long a, b, d;
+    return split_four_step(n, &a, &b) || split_three(n, &a, &b, &d);
 }
 
 struct BlueSpec {
@@ -272,8 +300,65 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
     }
     long long n1, n2;
     if (!split_four_step(n, &n1, &n2)) {
-        set_error("length %lld: no four-step split with factors <= %d", n, c.col);
-        return false;
+        // ---- three passes, n = n1 * n2 * n3 (j = j1*n2*n3 + j2*n3 + j3, k = k1 + n1*k2 + n1*n2*k3):
+        //   1. n1-point FFTs over j1 for every (j2, j3), times w_n^(k1*(j2*n3 + j3))      [k1][j2][j3]
+        //   2. inside every row k1: n2-point FFTs over j2, times w_(n2*n3)^(k2*j3)        [k1][k2][j3]
+        //   3. n3-point FFTs over the contiguous j3, stored transposed at k1 + n1*k2 + n1*n2*k3
+        // i.e. the four-step split applied to n and again to each of its rows; passes 1 and 2 are
+        // column passes with a twiddle epilogue, pass 3 is the row -> column kernel with two line dims.
+        // (The reference recurses the same way: ct_mkplan fftw/fftw_api.c:2158-2270 plans the child
+        // of size m = n/r with another Cooley-Tukey step.)
+        long long n3;
+        if (!split_three(n, &n1, &n2, &n3)) {
+            set_error("length %lld: no split into two or three factors <= %d", n, c.col);
+            return false;
+        }
+        const long long np = n2 * n3;
+        {
+            AxisSpec a;
+            a.n = (int)n1;
+            a.s_axis = s_axis * np;
+            a.d_axis = d_axis * np;
+            a.lines = lines;
+            a.lines.push_back(LDim{np, s_axis, d_axis, true});
+            a.swap_in = swap_in;
+            a.epi_N = n;
+            StepPlan st;
+            if (!make_pass_step(st, a)) return false;
+            st.inplace_ok = (s_axis == d_axis) && lines_same(lines);
+            st.dst_allowed = dst_allowed;
+            pc.steps.push_back(st);
+        }
+        {
+            AxisSpec a;
+            a.n = (int)n2;
+            a.s_axis = a.d_axis = d_axis * n3;
+            for (const LDim &l : lines) a.lines.push_back(LDim{l.n, l.d, l.d, false});
+            a.lines.push_back(LDim{n1, d_axis * np, d_axis * np, false});
+            a.lines.push_back(LDim{n3, d_axis, d_axis, true});
+            a.epi_N = np;
+            StepPlan st;
+            if (!make_pass_step(st, a)) return false;
+            st.inplace_ok = true;
+            st.dst_allowed = dst_allowed;
+            pc.steps.push_back(st);
+        }
+        {
+            AxisSpec a;
+            a.n = (int)n3;
+            a.s_axis = d_axis;
+            a.d_axis = d_axis * n1 * n2;
+            for (const LDim &l : lines) a.lines.push_back(LDim{l.n, l.d, l.d, false});
+            a.lines.push_back(LDim{n1, d_axis * np, d_axis, false});
+            a.lines.push_back(LDim{n2, d_axis * n3, d_axis * n1, false});
+            a.swap_out = swap_out;
+            StepPlan st;
+            if (!make_pass_step(st, a)) return false;
+            st.inplace_ok = false;
+            st.dst_allowed = dst_allowed;
+            pc.steps.push_back(st);
+        }
+        return true;
     }
     {  // pass A: n2 interleaved sub-sequences of length n1, twiddle w_n^(i2*k1) on the way out
         AxisSpec a;

@@ -304,13 +304,48 @@ inline bool build_real(PlanCore &pc) {
     } else {
         // ---- four-step half-length complex transform through a compact scratch ----
         long long n1, n2;
-        if (!split_four_step(m, &n1, &n2)) {
-            set_error("real length %lld: no four-step split", nl);
-            return false;
-        }
         std::vector<LDim> nz;
         for (const LDim &l : rl)
             if (l.n > 1) nz.push_back(l);
+        if (!split_four_step(m, &n1, &n2)) {
+            // ---- half-length transform beyond the four-step limit (n > 2^23 fp32 / 2^21 fp64): the
+            // three-pass complex split of plan_build.h on the packed pairs, Hermitian split / merge
+            // as a separate in-place sweep.  Unit-stride lines only.
+            if (T[L].is != 1 || T[L].os != 1 || !evens_src || !evens_dst) {
+                set_error("real length %lld with a strided last dimension is beyond the four-step limit", nl);
+                return false;
+            }
+            if (r2c) {
+                std::vector<LDim> cl;
+                for (const LDim &l : nz) cl.push_back(LDim{l.n, l.s, l.d, false});
+                if (!add_c2c_axis(pc, m, 2, 2, cl, false, false, {B_OUT, B_SCR})) return false;
+                StepPlan st;
+                std::vector<LDim> ol;
+                for (const LDim &l : nz) ol.push_back(LDim{l.n, l.d, l.d, false});
+                fill_realpp(st, 1, (int)m, nl, 2, 2, ol, false);
+                if (!st.rp.twr) return false;
+                st.inplace_ok = true;
+                st.src_fixed = B_OUT;
+                st.dst_allowed = {B_OUT};
+                pc.steps.push_back(st);
+                if (!leading_axes(false)) return false;
+                return assign_buffers(pc);
+            }
+            const std::vector<long long> cs3 = compact_strides(nz, m);
+            {
+                StepPlan st;
+                std::vector<LDim> ol;
+                for (size_t i = 0; i < nz.size(); ++i) ol.push_back(LDim{nz[i].n, nz[i].s, cs3[i], false});
+                fill_realpp(st, 0, (int)m, nl, 2, 2, ol, false);
+                if (!st.rp.twr) return false;
+                st.dst_allowed = {B_SCR};
+                pc.steps.push_back(st);
+            }
+            std::vector<LDim> cl;
+            for (size_t i = 0; i < nz.size(); ++i) cl.push_back(LDim{nz[i].n, cs3[i], nz[i].d, false});
+            if (!add_c2c_axis(pc, m, 2, 2, cl, false, true, {B_OUT, B_SCR})) return false;
+            return assign_buffers(pc);
+        }
         long long q1 = 0, q2 = 0;
         if (r2c && !no_two_pass_real() && !getenv("FFTW_B200_NO_TWO_PASS_REAL") && (nl & (nl - 1)) == 0 &&
             T[L].is == 1 && T[L].os == 1 && evens_src && evens_dst && split_two_pass_real(nl, &q1, &q2)) {

@@ -111,6 +111,9 @@ inline Caps caps() {
     Caps c;
     c.row = sizeof(real_t) == 4 ? 8192 : 4096;
     c.col = sizeof(real_t) == 4 ? 2048 : 1024;
+    // experiments / tests: lower limits make the multi-pass splits reachable at small sizes
+    if (const char *e = getenv("FFTW_B200_COL_CAP")) c.col = std::max(4, std::min(c.col, atoi(e)));
+    if (const char *e = getenv("FFTW_B200_ROW_CAP")) c.row = std::max(4, std::min(c.row, atoi(e)));
     return c;
 }
 

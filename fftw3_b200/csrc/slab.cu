@@ -184,7 +184,11 @@ struct SlabMsg {
 };
 
 struct SlabPlan {
-    ptrdiff_t n0, n1, n2;
+    // n2 is the length of a contiguous row in complex elements = (last transform dim n2f) x (howmany
+    // interleaved transforms hm, fftw_mpi_plan_many_dft's tuple layout): everything but the FFT along
+    // that dim treats the row as opaque
+    ptrdiff_t n0, n1, n2, n2f = 0, hm = 1;
+    bool transposed_in = false;
     int P, pe, sign;
     bool transposed_out;
     ptrdiff_t b0, b1, ln0, ln1, s0, s1;
@@ -222,6 +226,12 @@ struct SlabPlan {
 static void slab_enable_fused(SlabPlan &s) {
     s.fused = false;
     if (getenv("B2FFT_SLAB_NO_FUSED") || (int)s.peerR.size() != s.P || s.P > B2_MAXSCAT) return;
+    // Measured on 2 B200 (profiles/r1_slab_fused_2gpu.md): the scattered store wins when a tile row is a
+    // full 128-byte segment (n1 <= 1024: 1024^3 7.09 ms against 8.12 ms with the DMA exchange) and loses
+    // when the 2048-point kernel's 8-line tiles turn the NVLink writes into 64-byte packets (2048^3:
+    // 72.6 against 63.8 ms).  B2FFT_SLAB_FUSED=1 forces it.
+    const long long col_limit = (long long)(sizeof(real_t) == 4 ? 1024 : 1024);
+    if (s.P > 1 && s.n1 > col_limit && !getenv("B2FFT_SLAB_FUSED")) return;
     std::vector<long long> ps(s.P);
     for (int o = 0; o < s.P; ++o) ps[o] = (long long)blk_len(s.n1, s.b1, o) * s.n2 * 2;
     bool ok = true;
@@ -242,9 +252,10 @@ static b2fft_plan *make_stage1(const SlabPlan &s, ptrdiff_t planes) {
     g.sign = s.sign;
     g.rank = 2;
     g.dims[0] = b2fft_dim{s.n1, s.n2, s.n2};
-    g.dims[1] = b2fft_dim{s.n2, 1, 1};
-    g.vrank = 1;
+    g.dims[1] = b2fft_dim{s.n2f, s.hm, s.hm};
+    g.vrank = s.hm > 1 ? 2 : 1;
     g.vdims[0] = b2fft_dim{planes, s.n1 * s.n2, s.n1 * s.n2};
+    g.vdims[1] = b2fft_dim{s.hm, 1, 1};
     g.in_place = 0;
     return b2fft_plan_create(&g);
 }
@@ -327,13 +338,14 @@ void b2_slab_destroy(b2fft_plan_s *p) {
 
 static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
     SlabPlan *s = &sr;
-    const ptrdiff_t n0 = s->n0, n1 = s->n1, n2 = s->n2;
-    char buf[512];
+    const ptrdiff_t n0 = s->n0, n1 = s->n1, n2 = s->n2f;
+    char buf[640];
     snprintf(buf, sizeof buf,
-             "  slab 3-D c2c %td x %td x %td over %d ranks (rank %d: planes %td+%td, out rows %td+%td), %s output\n"
+             "  slab 3-D c2c %td x %td x %td%s, %td interleaved transform(s), over %d ranks (rank %d: planes %td+%td, out rows %td+%td), %s output\n"
              "  stage 1: %d chunk(s) of %td plane(s), (n1 x n2) FFTs in->send; exchange: %s\n"
              "  stage 2: length-%td FFTs recv->out\n",
-             n0, n1, n2, s->P, s->pe, s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
+             n0, n1, n2, s->transposed_in ? " (first two dims exchanged: FFTW_MPI_TRANSPOSED_IN)" : "", s->hm, s->P, s->pe,
+             s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
              s->nchunks, s->chunk,
              s->fused ? "fused into the n1 pass: rows stored straight into their owner's receive buffer (peer memory over NVLink)"
              : s->P == 1 ? "local copy" : s->p2p ? "strided DMA into peer memory (CUDA IPC over NVLink), one stream per peer, NCCL barrier"
@@ -350,18 +362,27 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
         set_error("slab plan: bad arguments");
         return nullptr;
     }
-    if (howmany != 1) {
-        set_error("slab plan: howmany > 1 is not supported yet");
-        return nullptr;
-    }
-    if (transposed_in) {
-        set_error("slab plan: FFTW_MPI_TRANSPOSED_IN is not supported yet");
+    if (howmany < 1) {
+        set_error("slab plan: howmany must be positive");
         return nullptr;
     }
     if (ensure_device() != 0) return nullptr;
     SlabPlan *s = new SlabPlan();
+    // FFTW_MPI_TRANSPOSED_IN: the input is [local_n1][n0][n2], block-distributed over n1 -- that is the
+    // ordinary slab input of the problem with its first two dimensions exchanged, and (the DFT being
+    // separable) that problem's transposed output is this problem's natural output and vice versa
+    // (fftw/mpi/dft-rank-geq2-transposed.c:113-198 plans the same way: XM(dft_rank_geq2_transposed)
+    // serves both flags by swapping which half of the algorithm runs first).
+    s->transposed_in = transposed_in != 0;
+    if (transposed_in) {
+        std::swap(n0, n1);
+        transposed_out = !transposed_out;
+    }
     s->n0 = n0;
     s->n1 = n1;
+    s->n2f = n2;
+    s->hm = howmany;
+    n2 *= howmany;
     s->n2 = n2;
     s->P = c->size;
     s->pe = c->rank;
@@ -421,8 +442,8 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
         delete bp;
         return nullptr;
     }
-    double N = (double)n0 * n1 * n2;
-    bp->pc.flops = 5.0 * N * log2(N) / s->P;
+    double N = (double)n0 * n1 * s->n2f;
+    bp->pc.flops = 5.0 * N * log2(N) * (double)howmany / s->P;
     slab_describe(*s, bp);
     return bp;
 }

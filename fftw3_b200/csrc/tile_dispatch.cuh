@@ -234,6 +234,10 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
             if (o.s & 3) pipe_ok = false;
     }
     if (p.fold_n > 0) pipe_ok = false;  // the Hermitian unfold load is not a plain tile copy
+    // Measured on B200 (profiles/r1_colpipe_probe.md): the pipelined kernels win where one CTA fills the
+    // SM (1024 / 2048 points: 0.519 -> 0.476 ms, 0.683 -> 0.645 ms per GiB pass) and lose a few per cent
+    // at 512 points (two CTAs per SM already overlap) and for axis strides of hundreds of KiB
+    if (!getenv("FFTW_B200_PIPE_ALL") && (p.m < 1024 || p.s_axis * (long long)sizeof(real_t) >= (256ll << 10))) pipe_ok = false;
     if (const char *e = getenv("FFTW_B200_PIPE_MIN_N"))
         if (p.m < atoi(e)) pipe_ok = false;
     for (int pass = pipe_ok ? 1 : 0; pass >= 0 && s.fast_id < 0; --pass)

@@ -42,6 +42,13 @@ FFTW_EXTERN ptrdiff_t fftw_mpi_local_size_3d_transposed(ptrdiff_t n0, ptrdiff_t 
                                                         ptrdiff_t *local_n0, ptrdiff_t *local_0_start,
                                                         ptrdiff_t *local_n1, ptrdiff_t *local_1_start);
 
+/* reference fftw/mpi/fftw3-mpi.h:129-144 (rank 3, default blocks) */
+FFTW_EXTERN ptrdiff_t fftw_mpi_local_size_many_transposed(int rnk, const ptrdiff_t *n, ptrdiff_t howmany,
+                                                          ptrdiff_t block0, ptrdiff_t block1, MPI_Comm comm,
+                                                          ptrdiff_t *local_n0, ptrdiff_t *local_0_start,
+                                                          ptrdiff_t *local_n1, ptrdiff_t *local_1_start);
+FFTW_EXTERN ptrdiff_t fftw_mpi_local_size_many(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block0,
+                                               MPI_Comm comm, ptrdiff_t *local_n0, ptrdiff_t *local_0_start);
 FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_COMPLEX *in,
                                            FFTW_COMPLEX *out, MPI_Comm comm, int sign, unsigned flags);
 FFTW_EXTERN fftw_plan fftw_mpi_plan_many_dft(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block,

@@ -84,6 +84,20 @@ def test_long_column_axes_take_the_pipelined_kernel(lib):
     lib.destroy_plan(p)
 
 
+@pytest.mark.parametrize("shape", [(2 ** 15,), (3 * 2 ** 13,), (2, 2 ** 14), (2 ** 13, 3), (5 * 7 * 2 ** 9,)],
+                         ids=lambda s: "x".join(map(str, s)))
+def test_three_pass_split_beyond_the_four_step_limit(lib, shape, monkeypatch):
+    """n = n1*n2*n3 (six-step): with the per-kernel limits lowered to 32 / 64 points the split that
+    serves n > 2^22 (fp32) / 2^20 (fp64) on the GPU is reached at 2^15 points"""
+    monkeypatch.setenv("FFTW_B200_COL_CAP", "32")
+    monkeypatch.setenv("FFTW_B200_ROW_CAP", "64")
+    cases.check_c2c(lib, shape)
+    x = np.zeros(shape, dtype=lib.cplx)
+    p = lib.plan_dft(list(shape), x, x.copy(), -1)
+    assert lib.sprint_plan(p).count("pass ") >= 3
+    lib.destroy_plan(p)
+
+
 def test_chained_launch_opt_in(lib):
     cases.check_chained_launch(lib)
 

@@ -33,6 +33,16 @@ def test_c2c(lib, shape):
     assert lib.lib.b2fft_launch_count() > n0, "no CUDA kernel was launched"
 
 
+@pytest.mark.parametrize("shape", [(2 ** 23,), (3 * 2 ** 22,), (2, 2 ** 22)], ids=lambda s: "x".join(map(str, s)))
+def test_c2c_three_pass_lengths(lib, shape):
+    """beyond the four-step limit (2^22 fp32 / 2^20 fp64): n = n1*n2*n3, three HBM passes"""
+    cases.check_c2c(lib, shape)
+    x = np.zeros(shape, dtype=lib.cplx)
+    p = lib.plan_dft(list(shape), x, x.copy(), -1)
+    assert lib.sprint_plan(p).count("pass ") >= 3
+    lib.destroy_plan(p)
+
+
 @pytest.mark.parametrize("shape", cases.R2C_SHAPES + cases.R2C_BIG + cases.R2C_PRIME, ids=lambda s: "x".join(map(str, s)))
 def test_r2c_c2r(lib, shape):
     cases.check_r2c_c2r(lib, shape)

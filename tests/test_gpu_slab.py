@@ -15,6 +15,21 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+SHAPE1 = {}
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp64"])
+@pytest.mark.parametrize("shape", [(64, 48, 32), (20, 64, 24), (6, 1024, 40)], ids=lambda s: "x".join(map(str, s)))
+def test_single_rank_fused_and_unfused(prec, shape):
+    """n1 = 64 / 1024 take the scattered store into this rank's own receive buffer; 48 the copy"""
+    SHAPE1[True] = SHAPE1[False] = shape
+    try:
+        for tr in (True, False):
+            test_single_rank_device_arrays(prec, tr)
+    finally:
+        SHAPE1.clear()
+
+
 @pytest.mark.parametrize("prec", ["fp32", "fp64"])
 @pytest.mark.parametrize("transposed", [True, False])
 def test_single_rank_device_arrays(prec, transposed):
@@ -25,7 +40,7 @@ def test_single_rank_device_arrays(prec, transposed):
     L.fftw_mpi_plan_dft_3d.restype = C.c_void_p
     L.fftw_mpi_plan_dft_3d.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] * 3 + [C.c_int, C.c_uint]
     comm = L.fftw_mpi_comm_self()
-    shape = (64, 48, 32)
+    shape = SHAPE1.get(transposed, (64, 48, 32))
     rng = np.random.default_rng(3)
     xh = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
     x = torch.from_numpy(xh).cuda()
@@ -42,8 +57,10 @@ def test_single_rank_device_arrays(prec, transposed):
     lib.destroy_plan(plan)
 
 
-@pytest.mark.parametrize("shape", [(48, 40, 32), (50, 30, 16)], ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("shape", [(48, 40, 32), (50, 30, 16), (24, 64, 32), (21, 512, 48)],
+                         ids=lambda s: "x".join(map(str, s)))
 def test_two_ranks_over_nccl(shape):
+    """n1 = 64, 512: the exchange is fused into the n1 pass (stores into peer memory); 40, 30: DMA path"""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")

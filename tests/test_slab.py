@@ -155,6 +155,125 @@ def test_fused_exchange_scatters_into_the_owners_receive_buffers(shape, P, prec)
         lib.lib.b2fft_comm_destroy(r["comm"])
 
 
+TRANSPOSED_IN = 1 << 29
+
+
+def _exchange(ranks, n_a, n_b, rl):
+    """S = [la][n_b][rl] on the sender, R = [n_a][lb][rl] on the receiver (blocks over a, b)"""
+    for src in ranks:
+        if src["la"] == 0:
+            continue
+        Sv = src["S"][:src["la"] * n_b * rl].reshape(src["la"], n_b, rl)
+        for dst in ranks:
+            if dst["lb"] == 0:
+                continue
+            Rv = dst["R"][:n_a * dst["lb"] * rl].reshape(n_a, dst["lb"], rl)
+            Rv[src["sa"]:src["sa"] + src["la"]] = Sv[:, dst["sb"]:dst["sb"] + dst["lb"], :]
+
+
+@pytest.mark.parametrize("flags", [TRANSPOSED_IN, TRANSPOSED_IN | TRANSPOSED_OUT], ids=["tin", "tin_tout"])
+@pytest.mark.parametrize("P", [1, 2, 3])
+@pytest.mark.parametrize("shape", [(8, 6, 4), (10, 7, 5), (12, 32, 6)], ids=lambda s: "x".join(map(str, s)))
+def test_transposed_input(shape, P, flags):
+    """FFTW_MPI_TRANSPOSED_IN (fftw/doc/mpi.texi:470-509): the input is [local_n1][n0][n2], distributed
+    over n1; the output is natural ([local_n0][n1][n2]) or, with TRANSPOSED_OUT too, stays transposed."""
+    lib = load()
+    n0, n1, n2 = shape
+    rng = np.random.default_rng(17 + P)
+    x = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
+    xT = np.ascontiguousarray(x.transpose(1, 0, 2))
+    Y = orc.dft(x, -1)
+    tout = bool(flags & TRANSPOSED_OUT)
+    ranks = []
+    for pe in range(P):
+        comm = lib.lib.b2fft_comm_detached(P, pe)
+        N, ln0, s0, ln1, s1 = local_sizes(lib, shape, comm)
+        xin = np.zeros(max(N, 1), dtype=lib.cplx)
+        xin[:ln1 * n0 * n2] = xT[s1:s1 + ln1].ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = lib.lib.fftw_mpi_plan_dft_3d(n0, n1, n2, xin.ctypes.data, out.ctypes.data, comm, -1,
+                                            capi.FFTW_ESTIMATE | flags)
+        assert plan, "slab plan is NULL"
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        # inside the plan the first two dims are exchanged: its "a" axis is n1, its "b" axis n0
+        ranks.append(dict(comm=comm, la=ln1, sa=s1, lb=ln0, sb=s0, xin=xin, out=out, plan=plan, bp=bp, S=S, R=R))
+    for r in ranks:
+        assert lib.lib.b2fft_slab_stage(r["bp"], 0, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    if "fused into" not in lib.sprint_plan(ranks[0]["plan"]):
+        _exchange(ranks, n1, n0, n2)
+    for r in ranks:
+        assert lib.lib.b2fft_slab_stage(r["bp"], 2, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    if tout:  # the plan's natural output = this problem's transposed output: second exchange, back
+        for src in ranks:
+            if src["lb"] == 0:
+                continue
+            Rv = src["R"][:n1 * src["lb"] * n2].reshape(n1, src["lb"], n2)
+            for dst in ranks:
+                if dst["la"] == 0:
+                    continue
+                Ov = dst["out"][:dst["la"] * n0 * n2].reshape(dst["la"], n0, n2)
+                Ov[:, src["sb"]:src["sb"] + src["lb"], :] = Rv[dst["sa"]:dst["sa"] + dst["la"]]
+    for r in ranks:
+        ref = Y.transpose(1, 0, 2)[r["sa"]:r["sa"] + r["la"]] if tout else Y[r["sb"]:r["sb"] + r["lb"]]
+        got = r["out"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+        lib.destroy_plan(r["plan"])
+        lib.lib.b2fft_comm_destroy(r["comm"])
+
+
+@pytest.mark.parametrize("P", [1, 2, 3])
+@pytest.mark.parametrize("howmany", [2, 3])
+@pytest.mark.parametrize("shape", [(8, 6, 4), (9, 32, 5)], ids=lambda s: "x".join(map(str, s)))
+def test_many_interleaved_transforms(shape, howmany, P):
+    """fftw_mpi_plan_many_dft with howmany > 1: every element is a tuple of `howmany` complex numbers
+    (array n0 x n1 x n2 x howmany, last index contiguous; fftw/doc/mpi.texi 'Advanced distributed-transpose
+    interface' / mpi/api.c:592-636)."""
+    lib = load()
+    L = lib.lib
+    L.fftw_mpi_plan_many_dft.restype = C.c_void_p
+    L.fftw_mpi_plan_many_dft.argtypes = [C.c_int, C.POINTER(C.c_ssize_t), C.c_ssize_t, C.c_ssize_t, C.c_ssize_t,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint]
+    L.fftw_mpi_local_size_many_transposed.restype = C.c_ssize_t
+    L.fftw_mpi_local_size_many_transposed.argtypes = [C.c_int, C.POINTER(C.c_ssize_t), C.c_ssize_t, C.c_ssize_t,
+                                                      C.c_ssize_t, C.c_void_p] + [C.POINTER(C.c_ssize_t)] * 4
+    n0, n1, n2 = shape
+    rng = np.random.default_rng(howmany)
+    x = ((rng.random(shape + (howmany,)) - 0.5) + 1j * (rng.random(shape + (howmany,)) - 0.5)).astype(lib.cplx)
+    Y = np.stack([orc.dft(np.ascontiguousarray(x[..., h]), -1) for h in range(howmany)], axis=-1)
+    nn = (C.c_ssize_t * 3)(*shape)
+    rl = n2 * howmany
+    ranks = []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        v = [C.c_ssize_t() for _ in range(4)]
+        N = L.fftw_mpi_local_size_many_transposed(3, nn, howmany, 0, 0, comm, *[C.byref(t) for t in v])
+        ln0, s0, ln1, s1 = (t.value for t in v)
+        assert N == howmany * local_sizes(lib, shape, comm)[0]
+        xin = np.zeros(max(N, 1), dtype=lib.cplx)
+        xin[:ln0 * n1 * rl] = x[s0:s0 + ln0].ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = L.fftw_mpi_plan_many_dft(3, nn, howmany, 0, 0, xin.ctypes.data, out.ctypes.data, comm, -1,
+                                        capi.FFTW_ESTIMATE | TRANSPOSED_OUT)
+        assert plan, "slab plan is NULL"
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        ranks.append(dict(comm=comm, la=ln0, sa=s0, lb=ln1, sb=s1, xin=xin, out=out, plan=plan, bp=bp, S=S, R=R))
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 0, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    if "fused into" not in lib.sprint_plan(ranks[0]["plan"]):
+        _exchange(ranks, n0, n1, rl)
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 2, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+        ref = Y.transpose(1, 0, 2, 3)[r["sb"]:r["sb"] + r["lb"]]
+        got = r["out"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+        lib.destroy_plan(r["plan"])
+        L.b2fft_comm_destroy(r["comm"])
+
+
 def _gloo_worker(rank, world, port, shape, q):
     try:
         import torch
