@@ -146,6 +146,37 @@ class FFTW3Lib:
         d, h = arr(dims), arr(howmany_dims)
         return f(len(dims), C.cast(d, _vp), len(howmany_dims), C.cast(h, _vp), _ptr(inp), _ptr(out), sign, flags)
 
+    def _iodims(self, ds):
+        class IoDim(C.Structure):
+            _fields_ = [("n", C.c_int), ("is_", C.c_int), ("os", C.c_int)]
+        a = (IoDim * max(1, len(ds)))()
+        for i, (n, is_, os_) in enumerate(ds):
+            a[i].n, a[i].is_, a[i].os = n, is_, os_
+        return a
+
+    def plan_guru_split(self, kind, dims, howmany_dims, a, b, c, d=None, flags=FFTW_ESTIMATE):
+        """split-array guru plans (fftw3.h: fftw_plan_guru_split_dft / _split_dft_r2c / _split_dft_c2r);
+        strides in reals.  kind 'c2c': (ri, ii, ro, io); 'r2c': (in, ro, io); 'c2r': (ri, ii, out)."""
+        dd, hh = self._iodims(dims), self._iodims(howmany_dims)
+        head = [len(dims), C.cast(dd, _vp), len(howmany_dims), C.cast(hh, _vp)]
+        if kind == "c2c":
+            f = self.lib.fftw_plan_guru_split_dft
+            f.restype, f.argtypes = _vp, [C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_uint]
+            return f(*head, _ptr(a), _ptr(b), _ptr(c), _ptr(d), flags)
+        f = self.lib.fftw_plan_guru_split_dft_r2c if kind == "r2c" else self.lib.fftw_plan_guru_split_dft_c2r
+        f.restype, f.argtypes = _vp, [C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_uint]
+        return f(*head, _ptr(a), _ptr(b), _ptr(c), flags)
+
+    def execute_split(self, kind, plan, a, b, c, d=None):
+        if kind == "c2c":
+            f = self.lib.fftw_execute_split_dft
+            f.restype, f.argtypes = None, [_vp] * 5
+            f(plan, _ptr(a), _ptr(b), _ptr(c), _ptr(d))
+        else:
+            f = self.lib.fftw_execute_split_dft_r2c if kind == "r2c" else self.lib.fftw_execute_split_dft_c2r
+            f.restype, f.argtypes = None, [_vp] * 4
+            f(plan, _ptr(a), _ptr(b), _ptr(c))
+
     def plan_dft(self, n, inp, out, sign, flags=FFTW_ESTIMATE):
         return self.lib.fftw_plan_dft(len(n), _ints(n), _ptr(inp), _ptr(out), sign, flags)
 

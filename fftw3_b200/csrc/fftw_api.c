@@ -42,9 +42,33 @@ static fftw_plan finish(b2fft_geom *g, void *in, void *out, unsigned flags) {
         b2fft_plan_destroy(bp);
         return 0;
     }
+    memset(p, 0, sizeof *p);
     p->bp = bp;
     p->in = in;
     p->out = out;
+    p->kind = g->kind;
+    p->g = *g;
+    return p;
+}
+
+static fftw_plan finish_split(b2fft_geom *g, void *ri, void *ii, void *ro, void *io, unsigned flags) {
+    fftw_plan p;
+    b2fft_split *sp;
+    if (flags & FFTW_WISDOM_ONLY) return 0;
+    g->flags = flags;
+    sp = b2fft_split_plan_create(g);
+    if (!sp) return 0;
+    p = (fftw_plan)malloc(sizeof *p);
+    if (!p) {
+        b2fft_split_plan_destroy(sp);
+        return 0;
+    }
+    memset(p, 0, sizeof *p);
+    p->sp = sp;
+    p->ri = ri;
+    p->ii = ii;
+    p->ro = ro;
+    p->io = io;
     p->kind = g->kind;
     p->g = *g;
     return p;
@@ -270,44 +294,50 @@ fftw_plan fftw_plan_guru64_dft_c2r(int rank, const fftw_iodim64 *dims, int howma
     return finish(&g, in, out, flags);
 }
 
-#define UNUSED_GURU (void)rank, (void)dims, (void)howmany_rank, (void)howmany_dims, (void)flags
+/* split arrays: gather / transform / scatter on the device (csrc/split.cu); always the forward
+ * transform, like the reference (fftw_api.c:1420-1450: "sign" is fixed, callers swap ri/ii) */
 fftw_plan fftw_plan_guru_split_dft(int rank, const fftw_iodim *dims, int howmany_rank,
                                    const fftw_iodim *howmany_dims, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii,
                                    FFTW_REAL_TYPE *ro, FFTW_REAL_TYPE *io, unsigned flags) {
-    UNUSED_GURU, (void)ri, (void)ii, (void)ro, (void)io;
-    return 0;
+    GURU_BODY(B2FFT_C2C, -1)
+    return finish_split(&g, ri, ii, ro, io, flags);
 }
 fftw_plan fftw_plan_guru64_split_dft(int rank, const fftw_iodim64 *dims, int howmany_rank,
                                      const fftw_iodim64 *howmany_dims, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii,
                                      FFTW_REAL_TYPE *ro, FFTW_REAL_TYPE *io, unsigned flags) {
-    UNUSED_GURU, (void)ri, (void)ii, (void)ro, (void)io;
-    return 0;
+    GURU_BODY(B2FFT_C2C, -1)
+    return finish_split(&g, ri, ii, ro, io, flags);
 }
 fftw_plan fftw_plan_guru_split_dft_r2c(int rank, const fftw_iodim *dims, int howmany_rank,
                                        const fftw_iodim *howmany_dims, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *ro,
                                        FFTW_REAL_TYPE *io, unsigned flags) {
-    UNUSED_GURU, (void)in, (void)ro, (void)io;
-    return 0;
+    GURU_BODY(B2FFT_R2C, -1)
+    if (rank < 1) return 0;
+    return finish_split(&g, in, 0, ro, io, flags);
 }
 fftw_plan fftw_plan_guru_split_dft_c2r(int rank, const fftw_iodim *dims, int howmany_rank,
                                        const fftw_iodim *howmany_dims, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii,
                                        FFTW_REAL_TYPE *out, unsigned flags) {
-    UNUSED_GURU, (void)ri, (void)ii, (void)out;
-    return 0;
+    GURU_BODY(B2FFT_C2R, +1)
+    if (rank < 1) return 0;
+    return finish_split(&g, ri, ii, out, 0, flags);
 }
 fftw_plan fftw_plan_guru64_split_dft_r2c(int rank, const fftw_iodim64 *dims, int howmany_rank,
                                          const fftw_iodim64 *howmany_dims, FFTW_REAL_TYPE *in,
                                          FFTW_REAL_TYPE *ro, FFTW_REAL_TYPE *io, unsigned flags) {
-    UNUSED_GURU, (void)in, (void)ro, (void)io;
-    return 0;
+    GURU_BODY(B2FFT_R2C, -1)
+    if (rank < 1) return 0;
+    return finish_split(&g, in, 0, ro, io, flags);
 }
 fftw_plan fftw_plan_guru64_split_dft_c2r(int rank, const fftw_iodim64 *dims, int howmany_rank,
                                          const fftw_iodim64 *howmany_dims, FFTW_REAL_TYPE *ri,
                                          FFTW_REAL_TYPE *ii, FFTW_REAL_TYPE *out, unsigned flags) {
-    UNUSED_GURU, (void)ri, (void)ii, (void)out;
-    return 0;
+    GURU_BODY(B2FFT_C2R, +1)
+    if (rank < 1) return 0;
+    return finish_split(&g, ri, ii, out, 0, flags);
 }
 
+#define UNUSED_GURU (void)rank, (void)dims, (void)howmany_rank, (void)howmany_dims, (void)flags
 /* ------------------------------------------------------------------ r2r: not on the hot path */
 fftw_plan fftw_plan_many_r2r(int rank, const int *n, int howmany, FFTW_REAL_TYPE *in, const int *inembed,
                              int istride, int idist, FFTW_REAL_TYPE *out, const int *onembed, int ostride,
@@ -359,21 +389,30 @@ static void run(const fftw_plan p, void *in, void *out) {
         fprintf(stderr, "b200fft: fftw_execute failed (%d): %s\n", rc, b2fft_last_error());
     }
 }
+static void run_split(const fftw_plan p, void *ri, void *ii, void *ro, void *io) {
+    int rc;
+    if (!p || !p->sp) return;
+    rc = b2fft_split_execute(p->sp, ri, ii, ro, io);
+    if (rc != 0) fprintf(stderr, "b200fft: fftw_execute (split arrays) failed (%d): %s\n", rc, b2fft_last_error());
+}
 void fftw_execute(const fftw_plan p) {
-    if (p) run(p, p->in, p->out);
+    if (p && p->sp)
+        run_split(p, p->ri, p->ii, p->ro, p->io);
+    else if (p)
+        run(p, p->in, p->out);
 }
 void fftw_execute_dft(const fftw_plan p, FFTW_COMPLEX *in, FFTW_COMPLEX *out) { run(p, in, out); }
 void fftw_execute_dft_r2c(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out) { run(p, in, out); }
 void fftw_execute_dft_c2r(const fftw_plan p, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out) { run(p, in, out); }
 void fftw_execute_split_dft(const fftw_plan p, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii, FFTW_REAL_TYPE *ro,
                             FFTW_REAL_TYPE *io) {
-    (void)p, (void)ri, (void)ii, (void)ro, (void)io; /* split plans are never created */
+    if (p && p->sp && p->kind == B2FFT_C2C) run_split(p, ri, ii, ro, io);
 }
 void fftw_execute_split_dft_r2c(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *ro, FFTW_REAL_TYPE *io) {
-    (void)p, (void)in, (void)ro, (void)io;
+    if (p && p->sp && p->kind == B2FFT_R2C) run_split(p, in, 0, ro, io);
 }
 void fftw_execute_split_dft_c2r(const fftw_plan p, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii, FFTW_REAL_TYPE *out) {
-    (void)p, (void)ri, (void)ii, (void)out;
+    if (p && p->sp && p->kind == B2FFT_C2R) run_split(p, ri, ii, out, 0);
 }
 void fftw_execute_r2r(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out) {
     (void)p, (void)in, (void)out;
@@ -383,6 +422,7 @@ void fftw_execute_r2r(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out
 void fftw_destroy_plan(fftw_plan p) {
     if (!p) return; /* NULL is legal (reference fftw_api.c:410) */
     b2fft_plan_destroy(p->bp);
+    b2fft_split_plan_destroy(p->sp);
     free(p);
 }
 void fftw_cleanup(void) { b2fft_cleanup(); }
@@ -438,6 +478,12 @@ char *fftw_sprint_plan(const fftw_plan p) {
     int n;
     char *s;
     if (!p) return 0;
+    if (p->sp) {
+        n = b2fft_split_describe(p->sp, 0, 0);
+        s = (char *)malloc((size_t)n + 1);
+        if (s) b2fft_split_describe(p->sp, s, (size_t)n + 1);
+        return s;
+    }
     n = b2fft_plan_describe(p->bp, 0, 0);
     s = (char *)malloc((size_t)n + 1);
     if (s) b2fft_plan_describe(p->bp, s, (size_t)n + 1);
@@ -458,7 +504,7 @@ void fftw_free(void *p) { b2fft_free(p); }
 
 /* 5 N log2 N convention (fftw/libbench2/mflops.c:6-31), split evenly between adds and muls */
 void fftw_flops(const fftw_plan p, double *add, double *mul, double *fmas) {
-    double f = p ? b2fft_plan_flops(p->bp) : 0.0;
+    double f = !p ? 0.0 : p->sp ? b2fft_split_flops(p->sp) : b2fft_plan_flops(p->bp);
     if (add) *add = 0.6 * f;
     if (mul) *mul = 0.4 * f;
     if (fmas) *fmas = 0.0;

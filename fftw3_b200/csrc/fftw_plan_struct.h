@@ -8,5 +8,7 @@ struct fftw_plan_s {
     void *in, *out; /* the arrays given at plan time (reference: problem_dft.ri.., api.h:1874) */
     int kind;
     b2fft_geom g;
+    b2fft_split *sp;            /* split-array plan (bp is NULL then) */
+    void *ri, *ii, *ro, *io;    /* its arrays at plan time */
 };
 #endif

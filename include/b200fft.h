@@ -80,6 +80,20 @@ const char *b2fft_last_error(void);
 void        b2fft_cleanup(void);            /* drops cached twiddle tables / workspaces */
 const char *b2fft_precision(void);          /* "fp32" or "fp64" */
 
+/* ---- split-array transforms (separate real / imaginary arrays) ------------------------------
+ * Replaces fftw_plan_guru_split_dft / _split_dft_r2c / _split_dft_c2r and fftw_execute_split_dft*
+ * (reference fftw/fftw_api.c:1420-1517, 444-454).  The geometry uses the guru convention: strides
+ * of every split or real array are in REALS; dims[].n are logical sizes; kind selects c2c (always
+ * forward: swap the arrays for backward), r2c (real in, split out) or c2r (split in, real out).
+ * Arrays may be host or device pointers.  execute: c2c (ri, ii, ro, io); r2c (in, NULL, ro, io);
+ * c2r (ri, ii, out, NULL). */
+typedef struct b2fft_split_s b2fft_split;
+b2fft_split *b2fft_split_plan_create(const b2fft_geom *g);
+void         b2fft_split_plan_destroy(b2fft_split *p);
+int          b2fft_split_execute(b2fft_split *p, void *ri, void *ii, void *ro, void *io);
+int          b2fft_split_describe(const b2fft_split *p, char *buf, size_t buflen);
+double       b2fft_split_flops(const b2fft_split *p);
+
 /* ---- slab-distributed 3-D c2c (fftw_mpi_plan_dft_3d form), one process per GPU --------- */
 typedef struct b2fft_comm_s b2fft_comm;
 

@@ -448,3 +448,68 @@ def check_fuzz(lib, ncases, seed, max_points=1 << 17):
                 mask[k * odist + flat_o * ostride] = False
             assert not a_out[mask].any(), "gaps of a strided output must stay untouched"
         done += 1
+
+
+def check_split_arrays(lib, device=False):
+    """guru split-array interfaces (reference fftw_api.c:1420-1517): c2c on separate re / im arrays
+    (forward; backward by swapping the arrays), r2c with a split output, c2r with a split input;
+    strided and batched loop nests; new-array execute."""
+    rng = np.random.default_rng(11)
+    if device:
+        import torch
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        down = lambda t: t.cpu().numpy()
+    else:
+        up = lambda a: np.ascontiguousarray(a)
+        down = lambda a: a
+    # --- c2c, 2-D 12 x 16 with a batch of 3, arrays [batch][12][16], then backward by swapping
+    shape = (3, 12, 16)
+    x = rand_c(rng, shape, lib)
+    ri, ii = up(x.real.astype(lib.real)), up(x.imag.astype(lib.real))
+    ro, io = up(np.zeros(shape, lib.real)), up(np.zeros(shape, lib.real))
+    dims = [(12, 16, 16), (16, 1, 1)]
+    hd = [(3, 192, 192)]
+    p = lib.plan_guru_split("c2c", dims, hd, ri, ii, ro, io)
+    assert p, "split c2c plan is NULL"
+    assert "split-array" in lib.sprint_plan(p)
+    lib.execute(p)
+    ref = np.stack([orc.dft(x[b], -1) for b in range(3)])
+    got = down(ro) + 1j * down(io)
+    assert rel_l2(got, ref) < tol(lib, 192)
+    # backward through the same plan: swap real and imaginary arrays on both sides
+    br, bi = up(np.zeros(shape, lib.real)), up(np.zeros(shape, lib.real))
+    lib.execute_split("c2c", p, io, ro, bi, br)
+    back = down(br) + 1j * down(bi)
+    assert rel_l2(back / 192, x) < tol(lib, 192)
+    lib.destroy_plan(p)
+    # --- c2c 1-D, strided (every 3rd real), batch with distance, output transposed ([k][batch])
+    n, hm = 64, 5
+    rbuf, ibuf = rand_r(rng, (hm, 3 * n), lib), rand_r(rng, (hm, 3 * n), lib)
+    robuf, iobuf = np.full((n, hm), 7, lib.real), np.full((n, hm), 7, lib.real)
+    dri, dii, dro, dio = up(rbuf), up(ibuf), up(robuf), up(iobuf)
+    p = lib.plan_guru_split("c2c", [(n, 3, hm)], [(hm, 3 * n, 1)], dri, dii, dro, dio)
+    assert p
+    lib.execute(p)
+    xs = rbuf[:, ::3] + 1j * ibuf[:, ::3]
+    ref = np.stack([orc.dft(xs[b].astype(lib.cplx), -1) for b in range(hm)], axis=1)
+    assert rel_l2(down(dro) + 1j * down(dio), ref) < tol(lib, n)
+    lib.destroy_plan(p)
+    # --- r2c with a split output and c2r back, 2-D 10 x 18, batch 2
+    shape = (2, 10, 18)
+    hc = 18 // 2 + 1
+    xr = rand_r(rng, shape, lib)
+    din = up(xr)
+    ro, io = up(np.zeros((2, 10, hc), lib.real)), up(np.zeros((2, 10, hc), lib.real))
+    p = lib.plan_guru_split("r2c", [(10, 18, hc), (18, 1, 1)], [(2, 180, 10 * hc)], din, ro, io)
+    assert p, "split r2c plan is NULL"
+    lib.execute(p)
+    ref = np.stack([orc.r2c(xr[b]) for b in range(2)])
+    got = down(ro) + 1j * down(io)
+    assert rel_l2(got, ref) < tol(lib, 180)
+    lib.destroy_plan(p)
+    dout = up(np.zeros(shape, lib.real))
+    p = lib.plan_guru_split("c2r", [(10, hc, 18), (18, 1, 1)], [(2, 10 * hc, 180)], ro, io, dout)
+    assert p, "split c2r plan is NULL"
+    lib.execute(p)
+    assert rel_l2(down(dout) / 180, xr) < tol(lib, 180)
+    lib.destroy_plan(p)

@@ -98,6 +98,19 @@ def test_three_pass_split_beyond_the_four_step_limit(lib, shape, monkeypatch):
     lib.destroy_plan(p)
 
 
+@pytest.mark.parametrize("shape", [(2 ** 16,), (3, 2 ** 16), (2, 3 * 2 ** 14)], ids=lambda s: "x".join(map(str, s)))
+def test_real_transforms_beyond_the_four_step_limit(lib, shape, monkeypatch):
+    monkeypatch.setenv("FFTW_B200_COL_CAP", "32")
+    monkeypatch.setenv("FFTW_B200_ROW_CAP", "64")
+    cases.check_r2c_c2r(lib, shape)
+    if len(shape) == 1:
+        cases.check_r2c_inplace(lib, shape)
+
+
+def test_split_array_guru_interfaces(lib):
+    cases.check_split_arrays(lib)
+
+
 def test_chained_launch_opt_in(lib):
     cases.check_chained_launch(lib)
 

@@ -43,6 +43,11 @@ def test_c2c_three_pass_lengths(lib, shape):
     lib.destroy_plan(p)
 
 
+def test_r2c_c2r_three_pass_length(lib):
+    """n/2 beyond the four-step limit: 2^24 reals (fp32) / 2^22 (fp64)"""
+    cases.check_r2c_c2r(lib, (2 ** 24,) if lib.single else (2 ** 22,))
+
+
 @pytest.mark.parametrize("shape", cases.R2C_SHAPES + cases.R2C_BIG + cases.R2C_PRIME, ids=lambda s: "x".join(map(str, s)))
 def test_r2c_c2r(lib, shape):
     cases.check_r2c_c2r(lib, shape)
@@ -74,6 +79,11 @@ def test_many_r2c(lib):
 
 def test_golden_vectors_of_the_reference(lib, golden):
     cases.check_golden(lib, golden)
+
+
+def test_split_array_guru_interfaces(lib):
+    cases.check_split_arrays(lib)
+    cases.check_split_arrays(lib, device=True)
 
 
 def test_edge_cases(lib):
