@@ -348,7 +348,7 @@ static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
              s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
              s->nchunks, s->chunk,
              s->fused ? "fused into the n1 pass: rows stored straight into their owner's receive buffer (peer memory over NVLink)"
-             : s->P == 1 ? "local copy" : s->p2p ? "strided DMA into peer memory (CUDA IPC over NVLink), one stream per peer, NCCL barrier"
+             : s->P == 1 ? "local copy" : s->p2p ? "strided DMA into peer memory (CUDA IPC over NVLink), NCCL barrier"
                                                 : "ncclSend/ncclRecv per plane and peer",
              n0);
     bp->pc.desc = buf;
@@ -554,7 +554,12 @@ static int slab_setup_p2p(SlabPlan &s) {
     B2_CK(cudaMemcpy(&bad, s.flag, sizeof(float), cudaMemcpyDeviceToHost));
     B2_CK(cudaMemset(s.flag, 0, 256));
     s.p2p = (bad == 0.0f);
-    if (s.p2p && !getenv("B2FFT_SLAB_ONE_STREAM")) {
+    // One stream per peer (copies to different peers on different copy engines) is opt-in: on 8 B200
+    // (profiles/r1_slab_8gpu.md, 2048^3) the shifted schedule p = pe + d on ONE stream keeps every
+    // receiver paired with one sender at a time and exposes 6.0 ms of exchange, seven concurrent
+    // streams expose 9.0 ms (incast at the receivers); on 2 GPUs the difference is under 2 %.
+    const char *ps = getenv("B2FFT_SLAB_PEER_STREAMS");
+    if (s.p2p && ps && atoi(ps) > 0) {
         s.sx.assign(s.P, nullptr);
         s.evx.assign(s.P, nullptr);
         for (int d = 0; d < s.P; ++d) {

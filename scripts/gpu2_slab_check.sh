@@ -5,10 +5,10 @@ TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
 nvidia-smi -L | head -8
 timeout 900 python -m pytest tests/test_gpu_slab.py -m gpu -x -q 2>&1 | tail -3
 for wl in c2c_3d_1024_slab_fp32 c2c_3d_2048_slab_fp32; do
-  for v in fused dma dma1; do
-    unset B2FFT_SLAB_NO_FUSED B2FFT_SLAB_ONE_STREAM
+  for v in fused dma dmaN; do
+    unset B2FFT_SLAB_NO_FUSED B2FFT_SLAB_PEER_STREAMS
     [ $v = dma ] && export B2FFT_SLAB_NO_FUSED=1
-    [ $v = dma1 ] && export B2FFT_SLAB_NO_FUSED=1 B2FFT_SLAB_ONE_STREAM=1
+    [ $v = dmaN ] && export B2FFT_SLAB_NO_FUSED=1 B2FFT_SLAB_PEER_STREAMS=1
     echo "== $wl P=$N exchange=$v"
     timeout 600 $TR --nproc-per-node $N --master-port $((29800+RANDOM%100)) bench.py --gpus $N --workload $wl --steps 8 --warmup 3 --no-e2e --no-cpu 2>&1 \
       | grep -E '^\{|rror' | python -c "

@@ -1,5 +1,5 @@
 # 8-GPU box: the driver's scaling run for the default workload at N=8, then cfg5 (2048^3 slab) and 1024^3
-# with the exchange variants (default choice / forced fused / DMA with per-peer streams / DMA on one stream).
+# with the exchange variants (default choice / forced fused / DMA on one stream / DMA with per-peer streams).
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
 N=${1:-8}
 nvidia-smi -L | wc -l
@@ -13,11 +13,11 @@ for l in sys.stdin:
 '
 timeout 600 $TR --nproc-per-node $N --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 --no-e2e 2>&1 | grep -E '^\{' | python -c "$fmt"
 for wl in c2c_3d_2048_slab_fp32 c2c_3d_1024_slab_fp32; do
-  for v in default fused dma dma1; do
-    unset B2FFT_SLAB_NO_FUSED B2FFT_SLAB_ONE_STREAM B2FFT_SLAB_FUSED
+  for v in default fused dma dmaN; do
+    unset B2FFT_SLAB_NO_FUSED B2FFT_SLAB_PEER_STREAMS B2FFT_SLAB_FUSED
     [ $v = fused ] && export B2FFT_SLAB_FUSED=1
     [ $v = dma ] && export B2FFT_SLAB_NO_FUSED=1
-    [ $v = dma1 ] && export B2FFT_SLAB_NO_FUSED=1 B2FFT_SLAB_ONE_STREAM=1
+    [ $v = dmaN ] && export B2FFT_SLAB_NO_FUSED=1 B2FFT_SLAB_PEER_STREAMS=1
     echo "== $wl P=$N exchange=$v"
     timeout 600 $TR --nproc-per-node $N --master-port $((29600+RANDOM%300)) bench.py --gpus $N --workload $wl --steps 8 --warmup 3 --no-e2e --no-cpu 2>&1 \
       | grep -E '^\{|rror' | python -c "$fmt"
