@@ -81,7 +81,69 @@ fftw_plan fftw_mpi_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_CO
     return fftw_mpi_plan_many_dft(3, n, 1, FFTW_MPI_DEFAULT_BLOCK, FFTW_MPI_DEFAULT_BLOCK, in, out, comm, sign, flags);
 }
 
+/* real data (reference fftw/mpi/api.c:751-858): rank 3, howmany 1, default blocks */
+static fftw_plan mpi_rdft(int kind, int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t iblock,
+                          ptrdiff_t oblock, void *in, void *out, MPI_Comm comm, unsigned flags) {
+    fftw_plan p;
+    b2fft_plan *bp;
+    int P;
+    const int tin = (flags & FFTW_MPI_TRANSPOSED_IN) != 0, tout = (flags & FFTW_MPI_TRANSPOSED_OUT) != 0;
+    if (rnk != 3 || !n || !comm || howmany != 1) return 0;
+    P = b2fft_comm_size(comm);
+    if (iblock != FFTW_MPI_DEFAULT_BLOCK && iblock != (n[tin ? 1 : 0] + P - 1) / P) return 0;
+    if (oblock != FFTW_MPI_DEFAULT_BLOCK && oblock != (n[tout ? 1 : 0] + P - 1) / P) return 0;
+    bp = b2fft_slab_plan_rdft_3d(kind, n[0], n[1], n[2], comm, tin, tout, flags);
+    if (!bp) return 0;
+    p = (fftw_plan)malloc(sizeof *p);
+    if (!p) {
+        b2fft_plan_destroy(bp);
+        return 0;
+    }
+    memset(p, 0, sizeof *p);
+    p->bp = bp;
+    p->in = in;
+    p->out = out;
+    p->kind = kind;
+    return p;
+}
+fftw_plan fftw_mpi_plan_many_dft_r2c(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t iblock,
+                                     ptrdiff_t oblock, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out, MPI_Comm comm,
+                                     unsigned flags) {
+    return mpi_rdft(B2FFT_R2C, rnk, n, howmany, iblock, oblock, in, out, comm, flags);
+}
+fftw_plan fftw_mpi_plan_many_dft_c2r(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t iblock,
+                                     ptrdiff_t oblock, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out, MPI_Comm comm,
+                                     unsigned flags) {
+    return mpi_rdft(B2FFT_C2R, rnk, n, howmany, iblock, oblock, in, out, comm, flags);
+}
+fftw_plan fftw_mpi_plan_dft_r2c(int rnk, const ptrdiff_t *n, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out, MPI_Comm comm,
+                                unsigned flags) {
+    return fftw_mpi_plan_many_dft_r2c(rnk, n, 1, FFTW_MPI_DEFAULT_BLOCK, FFTW_MPI_DEFAULT_BLOCK, in, out, comm, flags);
+}
+fftw_plan fftw_mpi_plan_dft_c2r(int rnk, const ptrdiff_t *n, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out, MPI_Comm comm,
+                                unsigned flags) {
+    return fftw_mpi_plan_many_dft_c2r(rnk, n, 1, FFTW_MPI_DEFAULT_BLOCK, FFTW_MPI_DEFAULT_BLOCK, in, out, comm, flags);
+}
+fftw_plan fftw_mpi_plan_dft_r2c_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out,
+                                   MPI_Comm comm, unsigned flags) {
+    ptrdiff_t n[3];
+    n[0] = n0;
+    n[1] = n1;
+    n[2] = n2;
+    return fftw_mpi_plan_dft_r2c(3, n, in, out, comm, flags);
+}
+fftw_plan fftw_mpi_plan_dft_c2r_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out,
+                                   MPI_Comm comm, unsigned flags) {
+    ptrdiff_t n[3];
+    n[0] = n0;
+    n[1] = n1;
+    n[2] = n2;
+    return fftw_mpi_plan_dft_c2r(3, n, in, out, comm, flags);
+}
+
 void fftw_mpi_execute_dft(fftw_plan p, FFTW_COMPLEX *in, FFTW_COMPLEX *out) { fftw_execute_dft(p, in, out); }
+void fftw_mpi_execute_dft_r2c(fftw_plan p, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out) { fftw_execute_dft_r2c(p, in, out); }
+void fftw_mpi_execute_dft_c2r(fftw_plan p, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out) { fftw_execute_dft_c2r(p, in, out); }
 
 int fftw_mpi_nccl_unique_id(void *id128) { return b2fft_nccl_unique_id(id128); }
 MPI_Comm fftw_mpi_comm_from_nccl(const void *id128, int n_pes, int my_pe) {

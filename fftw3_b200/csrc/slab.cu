@@ -189,6 +189,13 @@ struct SlabPlan {
     // that dim treats the row as opaque
     ptrdiff_t n0, n1, n2, n2f = 0, hm = 1;
     bool transposed_in = false;
+    // kind: B2FFT_C2C, or the real forms (fftw_mpi_plan_dft_r2c_3d / _c2r_3d): the contiguous row then
+    // holds n2f/2+1 complex, the real side is padded to 2(n2f/2+1) reals per row
+    // (fftw/mpi/rdft2-rank-geq2-transposed.c:47-70, fftw/doc/mpi.texi "Multi-dimensional MPI DFTs of Real Data").
+    // c2r runs the pipeline backwards: n0 FFTs (pA), reverse exchange, local 2-D c2r (pB).
+    int kind = B2FFT_C2C;
+    bool c2r_tin = false;            // c2r with FFTW_MPI_TRANSPOSED_IN: the input is [local_n1][n0][n2c]
+    b2fft_plan *pA = nullptr, *pB = nullptr;
     int P, pe, sign;
     bool transposed_out;
     ptrdiff_t b0, b1, ln0, ln1, s0, s1;
@@ -248,6 +255,18 @@ static b2fft_plan *make_stage1(const SlabPlan &s, ptrdiff_t planes) {
     if (planes <= 0) return nullptr;
     b2fft_geom g;
     memset(&g, 0, sizeof g);
+    if (s.kind == B2FFT_R2C) {
+        // real [planes][n1][2*n2c] -> complex [planes][n1][n2c]
+        g.kind = B2FFT_R2C;
+        g.sign = -1;
+        g.rank = 2;
+        g.dims[0] = b2fft_dim{s.n1, 2 * s.n2, s.n2};
+        g.dims[1] = b2fft_dim{s.n2f, 1, 1};
+        g.vrank = 1;
+        g.vdims[0] = b2fft_dim{planes, s.n1 * 2 * s.n2, s.n1 * s.n2};
+        g.in_place = 0;
+        return b2fft_plan_create(&g);
+    }
     g.kind = B2FFT_C2C;
     g.sign = s.sign;
     g.rank = 2;
@@ -282,6 +301,44 @@ static b2fft_plan *make_stage2(const SlabPlan &s) {
     return b2fft_plan_create(&g);
 }
 
+// c2r, first step: backward length-n0 FFTs.  Transposed input [ln1][n0][rl] -> receive layout
+// [n0][ln1][rl]; natural input: in place on the receive layout (filled by the forward exchange).
+static b2fft_plan *make_c2r_a(const SlabPlan &s) {
+    if (s.ln1 <= 0) return nullptr;
+    b2fft_geom g;
+    memset(&g, 0, sizeof g);
+    g.kind = B2FFT_C2C;
+    g.sign = +1;
+    g.rank = 1;
+    g.vrank = 2;
+    if (s.c2r_tin) {
+        g.dims[0] = b2fft_dim{s.n0, s.n2, s.ln1 * s.n2};
+        g.vdims[0] = b2fft_dim{s.ln1, s.n0 * s.n2, s.n2};
+        g.in_place = 0;
+    } else {
+        g.dims[0] = b2fft_dim{s.n0, s.ln1 * s.n2, s.ln1 * s.n2};
+        g.vdims[0] = b2fft_dim{s.ln1, s.n2, s.n2};
+        g.in_place = 1;
+    }
+    g.vdims[1] = b2fft_dim{s.n2, 1, 1};
+    return b2fft_plan_create(&g);
+}
+// c2r, last step: local 2-D c2r, complex [ln0][n1][n2c] -> real [ln0][n1][2*n2c]
+static b2fft_plan *make_c2r_b(const SlabPlan &s) {
+    if (s.ln0 <= 0) return nullptr;
+    b2fft_geom g;
+    memset(&g, 0, sizeof g);
+    g.kind = B2FFT_C2R;
+    g.sign = +1;
+    g.rank = 2;
+    g.dims[0] = b2fft_dim{s.n1, s.n2, 2 * s.n2};
+    g.dims[1] = b2fft_dim{s.n2f, 1, 1};
+    g.vrank = 1;
+    g.vdims[0] = b2fft_dim{s.ln0, s.n1 * s.n2, s.n1 * 2 * s.n2};
+    g.in_place = 0;
+    return b2fft_plan_create(&g);
+}
+
 // messages of the n0 <-> n1 exchange for the planes [i0a, i0b) of every rank's local range
 // (same chunk index on every rank).  forward = S -> R; the reverse exchange swaps the roles.
 static void slab_messages(const SlabPlan &s, int chunk, std::vector<SlabMsg> &sends, std::vector<SlabMsg> &recvs) {
@@ -308,6 +365,8 @@ void b2_slab_destroy(b2fft_plan_s *p) {
     b2fft_plan_destroy(s->p1);
     b2fft_plan_destroy(s->p1_tail);
     b2fft_plan_destroy(s->p2);
+    b2fft_plan_destroy(s->pA);
+    b2fft_plan_destroy(s->pB);
 #if B2_CUDA
     for (int q = 0; q < (int)s->peerS.size(); ++q)
         if (q != s->pe) {
@@ -341,10 +400,11 @@ static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
     const ptrdiff_t n0 = s->n0, n1 = s->n1, n2 = s->n2f;
     char buf[640];
     snprintf(buf, sizeof buf,
-             "  slab 3-D c2c %td x %td x %td%s, %td interleaved transform(s), over %d ranks (rank %d: planes %td+%td, out rows %td+%td), %s output\n"
+             "  slab 3-D %s %td x %td x %td%s, %td interleaved transform(s), over %d ranks (rank %d: planes %td+%td, out rows %td+%td), %s output\n"
              "  stage 1: %d chunk(s) of %td plane(s), (n1 x n2) FFTs in->send; exchange: %s\n"
              "  stage 2: length-%td FFTs recv->out\n",
-             n0, n1, n2, s->transposed_in ? " (first two dims exchanged: FFTW_MPI_TRANSPOSED_IN)" : "", s->hm, s->P, s->pe,
+             s->kind == B2FFT_C2C ? "c2c" : s->kind == B2FFT_R2C ? "r2c" : "c2r (n0 FFTs, reverse exchange, local 2-D c2r)", n0, n1, n2,
+             s->transposed_in ? (s->kind == B2FFT_C2C ? " (first two dims exchanged: FFTW_MPI_TRANSPOSED_IN)" : " (transposed input)") : "", s->hm, s->P, s->pe,
              s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
              s->nchunks, s->chunk,
              s->fused ? "fused into the n1 pass: rows stored straight into their owner's receive buffer (peer memory over NVLink)"
@@ -354,10 +414,30 @@ static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
     bp->pc.desc = buf;
 }
 
+static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
+                                    b2fft_comm *c, int sign, int transposed_in, int transposed_out);
+
 extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
                                               b2fft_comm *c, int sign, int transposed_in, int transposed_out,
                                               unsigned flags) {
     (void)flags;
+    return slab_plan_create(B2FFT_C2C, n0, n1, n2, howmany, c, sign, transposed_in, transposed_out);
+}
+// kind = B2FFT_R2C (real [ln0][n1][2(n2/2+1)] -> complex, natural or transposed output) or B2FFT_C2R
+// (complex, natural or transposed input -> real [ln0][n1][2(n2/2+1)]); n2 is the logical real length
+extern "C" b2fft_plan *b2fft_slab_plan_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, b2fft_comm *c,
+                                               int transposed_in, int transposed_out, unsigned flags) {
+    (void)flags;
+    if (kind != B2FFT_R2C && kind != B2FFT_C2R) return nullptr;
+    if ((kind == B2FFT_R2C && transposed_in) || (kind == B2FFT_C2R && transposed_out)) {
+        set_error("slab real transform: a transposed REAL array is not supported");
+        return nullptr;
+    }
+    return slab_plan_create(kind, n0, n1, n2, 1, c, kind == B2FFT_R2C ? -1 : +1, transposed_in, transposed_out);
+}
+
+static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
+                                    b2fft_comm *c, int sign, int transposed_in, int transposed_out) {
     if (!c || n0 <= 0 || n1 <= 0 || n2 <= 0) {
         set_error("slab plan: bad arguments");
         return nullptr;
@@ -373,15 +453,18 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
     // separable) that problem's transposed output is this problem's natural output and vice versa
     // (fftw/mpi/dft-rank-geq2-transposed.c:113-198 plans the same way: XM(dft_rank_geq2_transposed)
     // serves both flags by swapping which half of the algorithm runs first).
+    s->kind = kind;
     s->transposed_in = transposed_in != 0;
-    if (transposed_in) {
+    if (kind == B2FFT_C2C && transposed_in) {
         std::swap(n0, n1);
         transposed_out = !transposed_out;
     }
+    s->c2r_tin = (kind == B2FFT_C2R && transposed_in);
     s->n0 = n0;
     s->n1 = n1;
     s->n2f = n2;
     s->hm = howmany;
+    if (kind != B2FFT_C2C) n2 = n2 / 2 + 1;  // complex elements per row
     n2 *= howmany;
     s->n2 = n2;
     s->P = c->size;
@@ -395,13 +478,23 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
     // chunks of planes: enough to overlap, few enough to keep the messages large
     const ptrdiff_t maxl0 = s->b0;
     s->nchunks = (int)std::max<ptrdiff_t>(1, std::min<ptrdiff_t>(8, maxl0 / 8));
+    if (const char *e = getenv("B2FFT_SLAB_CHUNKS")) s->nchunks = (int)std::max<ptrdiff_t>(1, std::min<ptrdiff_t>(atoi(e), maxl0));
     if (s->P == 1) s->nchunks = 1;
     s->chunk = (maxl0 + s->nchunks - 1) / s->nchunks;
     s->nchunks = (int)((maxl0 + s->chunk - 1) / s->chunk);
     b2fft_plan *bp = new b2fft_plan_s();
     bp->slab = s;
     bool ok = true;
-    if (s->ln0 > 0) {
+    if (kind == B2FFT_C2R) {
+        if (s->ln1 > 0) {
+            s->pA = make_c2r_a(*s);
+            ok = ok && s->pA;
+        }
+        if (ok && s->ln0 > 0) {
+            s->pB = make_c2r_b(*s);
+            ok = ok && s->pB;
+        }
+    } else if (s->ln0 > 0) {
         const ptrdiff_t full = std::min(s->chunk, s->ln0);
         s->p1 = make_stage1(*s, full);
         ok = ok && s->p1;
@@ -411,7 +504,7 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
             ok = ok && s->p1_tail;
         }
     }
-    if (ok && s->ln1 > 0) {
+    if (ok && s->ln1 > 0 && kind != B2FFT_C2R) {
         s->p2 = make_stage2(*s);
         ok = ok && s->p2;
     }
@@ -430,10 +523,10 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
         for (cudaEvent_t &e : s->ev) ok = ok && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
         for (cudaEvent_t *e : {&s->t0, &s->t1, &s->t2, &s->t3}) ok = ok && cudaEventCreate(e) == cudaSuccess;
         if (ok) ok = slab_setup_p2p(*s) == 0;
-        if (ok && s->p2p) slab_enable_fused(*s);
+        if (ok && s->p2p && kind != B2FFT_C2R) slab_enable_fused(*s);
     }
 #endif
-    if (ok && s->P == 1) {  // one rank: the "exchange" is the scatter into this rank's own receive buffer
+    if (ok && s->P == 1 && kind != B2FFT_C2R) {  // one rank: the "exchange" is the scatter into this rank's own receive buffer
         s->peerR.assign(1, s->R);
         slab_enable_fused(*s);
     }
@@ -443,7 +536,7 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
         return nullptr;
     }
     double N = (double)n0 * n1 * s->n2f;
-    bp->pc.flops = 5.0 * N * log2(N) * (double)howmany / s->P;
+    bp->pc.flops = (kind == B2FFT_C2C ? 5.0 : 2.5) * N * log2(N) * (double)howmany / s->P;
     slab_describe(*s, bp);
     return bp;
 }
@@ -559,10 +652,11 @@ static int slab_setup_p2p(SlabPlan &s) {
     // receiver paired with one sender at a time and exposes 6.0 ms of exchange, seven concurrent
     // streams expose 9.0 ms (incast at the receivers); on 2 GPUs the difference is under 2 %.
     const char *ps = getenv("B2FFT_SLAB_PEER_STREAMS");
-    if (s.p2p && ps && atoi(ps) > 0) {
-        s.sx.assign(s.P, nullptr);
-        s.evx.assign(s.P, nullptr);
-        for (int d = 0; d < s.P; ++d) {
+    if (s.p2p && ps && atoi(ps) > 1) {
+        const int ns = std::min(atoi(ps), s.P);  // peer offset d copies on stream d % ns
+        s.sx.assign(ns, nullptr);
+        s.evx.assign(ns, nullptr);
+        for (int d = 0; d < ns; ++d) {
             B2_CK(cudaStreamCreateWithFlags(&s.sx[d], cudaStreamNonBlocking));
             B2_CK(cudaEventCreateWithFlags(&s.evx[d], cudaEventDisableTiming));
         }
@@ -572,19 +666,21 @@ static int slab_setup_p2p(SlabPlan &s) {
 }
 // `after`: event the copies must wait for (the chunk's FFTs); with per-peer streams every copy runs on
 // its peer's stream and `st` later joins them (slab_join_peers)
-static int slab_exchange_p2p(SlabPlan &s, int chunk, bool reverse, cudaStream_t st0, cudaEvent_t after = nullptr) {
+static int slab_exchange_p2p(SlabPlan &s, int chunk, bool reverse, cudaStream_t st0, cudaEvent_t after = nullptr,
+                             const cpx_t *fwd_src = nullptr) {
     const size_t esz = sizeof(cpx_t);
+    if (!fwd_src) fwd_src = s.S;
     for (int d = 0; d < s.P; ++d) {
         const int p = (s.pe + d) % s.P;
-        cudaStream_t st = (after && !s.sx.empty()) ? s.sx[d] : st0;
-        if (after) B2_CK(cudaStreamWaitEvent(st, after, 0));
+        cudaStream_t st = (after && !s.sx.empty()) ? s.sx[d % (int)s.sx.size()] : st0;
+        if (after && d < std::max<int>(1, (int)s.sx.size())) B2_CK(cudaStreamWaitEvent(st, after, 0));
         if (!reverse) {
             // my planes [a,b) of this chunk -> peer p's receive buffer R_p[s0 + i0][*][*]
             const ptrdiff_t ln1p = blk_len(s.n1, s.b1, p);
             const ptrdiff_t a = std::min<ptrdiff_t>(s.ln0, chunk * s.chunk), b = std::min<ptrdiff_t>(s.ln0, a + s.chunk);
             if (ln1p <= 0 || b <= a) continue;
             B2_CK(cudaMemcpy2DAsync(s.peerR[p] + (size_t)((s.s0 + a) * ln1p) * s.n2, (size_t)ln1p * s.n2 * esz,
-                                    s.S + (size_t)(a * s.n1 + p * s.b1) * s.n2, (size_t)s.n1 * s.n2 * esz,
+                                    fwd_src + (size_t)(a * s.n1 + p * s.b1) * s.n2, (size_t)s.n1 * s.n2 * esz,
                                     (size_t)ln1p * s.n2 * esz, (size_t)(b - a), cudaMemcpyDeviceToDevice, st));
         } else {
             // my rows of peer p's planes [a,b) -> peer p's send buffer S_p[i0][s1 + j1][*]
@@ -648,7 +744,20 @@ extern "C" int b2fft_slab_stage(b2fft_plan *p, int stage, void *in, void *out) {
     st = s.sc;
 #endif
     int rc = 0;
-    if (stage == 0) {
+    if (s.kind == B2FFT_C2R) {
+        // c2r: 0 forward exchange in -> recv (natural input only), 1 backward n0 FFTs, 2 reverse
+        // exchange recv -> send, 3 local 2-D c2r send -> out
+        if (stage == 0) {
+            for (int k = 0; k < s.nchunks && !rc && !s.c2r_tin; ++k) rc = slab_exchange(s, k, (cpx_t *)in, s.R, false, st);
+        } else if (stage == 1) {
+            if (s.pA) rc = b2fft_execute_async(s.pA, s.c2r_tin ? in : (void *)s.R, s.R, st);
+        } else if (stage == 2) {
+            for (int k = 0; k < s.nchunks && !rc; ++k) rc = slab_exchange(s, k, s.S, s.R, true, st);
+        } else if (stage == 3) {
+            if (s.pB) rc = b2fft_execute_async(s.pB, s.S, out, st);
+        } else
+            rc = -1;
+    } else if (stage == 0) {
         for (int k = 0; k < s.nchunks && !rc; ++k) rc = slab_stage1_chunk(s, k, (cpx_t *)in, st);
     } else if (stage == 1) {
         for (int k = 0; k < s.nchunks && !rc && !s.fused; ++k) rc = slab_exchange(s, k, s.S, s.R, false, st);
@@ -677,8 +786,9 @@ int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
 #if B2_CUDA
     cpx_t *din = (cpx_t *)in, *dout = (cpx_t *)out;
     const bool hin = !is_device_ptr(in), hout = !is_device_ptr(out);
-    const size_t in_b = (size_t)s.ln0 * s.n1 * s.n2 * sizeof(cpx_t);
-    const size_t out_b = (size_t)(s.transposed_out ? s.ln1 * s.n0 : s.ln0 * s.n1) * s.n2 * sizeof(cpx_t);
+    // (the padded real side of r2c / c2r has 2*n2 reals per row: the same bytes as n2 complex)
+    const size_t in_b = (size_t)(s.c2r_tin ? s.ln1 * s.n0 : s.ln0 * s.n1) * s.n2 * sizeof(cpx_t);
+    const size_t out_b = (size_t)(s.transposed_out && s.kind != B2FFT_C2R ? s.ln1 * s.n0 : s.ln0 * s.n1) * s.n2 * sizeof(cpx_t);
     if (hin) {
         if (!s.dev_in) s.dev_in = (cpx_t *)dev_malloc(std::max<size_t>(in_b, 16));
         if (!s.dev_in) return -3;
@@ -691,6 +801,32 @@ int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
         dout = s.dev_out;
     }
     B2_CK(cudaEventRecord(s.t0, s.sc));
+    if (s.kind == B2FFT_C2R) {
+        int rc = 0;
+        if (s.p2p) rc = slab_barrier(s, s.sc);  // every rank has finished reading the buffers of its last execute
+        if (!s.c2r_tin) {
+            for (int k = 0; k < s.nchunks && !rc; ++k)
+                rc = s.p2p ? slab_exchange_p2p(s, k, false, s.sc, nullptr, din) : slab_exchange(s, k, din, s.R, false, s.sc);
+            if (!rc && s.p2p) rc = slab_barrier(s, s.sc);
+        }
+        if (!rc && s.pA) rc = b2fft_execute_async(s.pA, s.c2r_tin ? (void *)din : (void *)s.R, s.R, s.sc);
+        if (rc) return rc;
+        B2_CK(cudaEventRecord(s.t1, s.sc));
+        for (int k = 0; k < s.nchunks && !rc; ++k)
+            rc = s.p2p ? slab_exchange_p2p(s, k, true, s.sc) : slab_exchange(s, k, s.S, s.R, true, s.sc);
+        if (!rc && s.p2p) rc = slab_barrier(s, s.sc);
+        if (rc) return rc;
+        B2_CK(cudaEventRecord(s.t2, s.sc));
+        if (s.pB) rc = b2fft_execute_async(s.pB, s.S, dout, s.sc);
+        if (rc) return rc;
+        B2_CK(cudaEventRecord(s.t3, s.sc));
+        if (hout) B2_CK(cudaMemcpyAsync(out, dout, out_b, cudaMemcpyDeviceToHost, s.sc));
+        B2_CK(cudaStreamSynchronize(s.sc));
+        cudaEventElapsedTime(&s.ms[0], s.t0, s.t1);
+        cudaEventElapsedTime(&s.ms[1], s.t1, s.t2);
+        cudaEventElapsedTime(&s.ms[2], s.t2, s.t3);
+        return 0;
+    }
     if (s.fused) {
         // one stream: [barrier: nobody still reads the receive buffers] row pass, n1 pass + scatter, per
         // chunk; [barrier: every rank's rows have landed]

@@ -113,9 +113,18 @@ int         b2fft_comm_size(const b2fft_comm *c);
 b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
                                    b2fft_comm *c, int sign, int transposed_in,
                                    int transposed_out, unsigned flags);
+/* the receive buffers of all ranks as seen from this process (test hook / callers with their own
+ * peer mapping): switches the plan to the fused exchange; returns 1 when it did */
+int         b2fft_slab_set_peer_recv(b2fft_plan *p, void *const *recv, int n);
+/* Real-data forms (fftw_mpi_plan_dft_r2c_3d / _c2r_3d, reference fftw/mpi/api.c:751-858): kind =
+ * B2FFT_R2C (real [local_n0][n1][2(n2/2+1)] in, complex out, natural or FFTW_MPI_TRANSPOSED_OUT) or
+ * B2FFT_C2R (complex in, natural or FFTW_MPI_TRANSPOSED_IN, real out).  n2 = logical real length. */
+b2fft_plan *b2fft_slab_plan_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, b2fft_comm *c,
+                                    int transposed_in, int transposed_out, unsigned flags);
 /* Staged execution, for callers that bring their own transport and for the CPU tests of the
  * multi-rank path: stage 0 local (n1 x n2) FFTs in -> send buffer; 1 exchange (NCCL); 2 length-n0
- * FFTs recv buffer -> out; 3 (natural-order output only) exchange back.  b2fft_slab_buffer returns
+ * FFTs recv buffer -> out; 3 (natural-order output only) exchange back (c2r plans: 0 forward exchange
+ * of a natural input, 1 backward n0 FFTs, 2 reverse exchange, 3 local 2-D c2r).  b2fft_slab_buffer returns
  * the send (0) / receive (1) buffer.  b2fft_comm_detached carries (rank, size) without NCCL. */
 int         b2fft_slab_stage(b2fft_plan *p, int stage, void *in, void *out);
 void       *b2fft_slab_buffer(b2fft_plan *p, int which, size_t *bytes);

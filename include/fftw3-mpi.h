@@ -56,6 +56,27 @@ FFTW_EXTERN fftw_plan fftw_mpi_plan_many_dft(int rnk, const ptrdiff_t *n, ptrdif
                                              MPI_Comm comm, int sign, unsigned flags);
 FFTW_EXTERN void fftw_mpi_execute_dft(fftw_plan p, FFTW_COMPLEX *in, FFTW_COMPLEX *out);
 
+/* real data, rank 3 (reference fftw/mpi/fftw3-mpi.h:161-194): the real array is [local_n0][n1][2(n2/2+1)],
+ * the complex one [local_n0][n1][n2/2+1] or, transposed, [local_n1][n0][n2/2+1]; local sizes come from
+ * fftw_mpi_local_size_3d(_transposed)(n0, n1, n2/2+1, ...) in complex elements, as in the reference.
+ * r2c accepts FFTW_MPI_TRANSPOSED_OUT, c2r FFTW_MPI_TRANSPOSED_IN. */
+FFTW_EXTERN fftw_plan fftw_mpi_plan_many_dft_r2c(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t iblock,
+                                                 ptrdiff_t oblock, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out,
+                                                 MPI_Comm comm, unsigned flags);
+FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_r2c(int rnk, const ptrdiff_t *n, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out,
+                                            MPI_Comm comm, unsigned flags);
+FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_r2c_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_REAL_TYPE *in,
+                                               FFTW_COMPLEX *out, MPI_Comm comm, unsigned flags);
+FFTW_EXTERN fftw_plan fftw_mpi_plan_many_dft_c2r(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t iblock,
+                                                 ptrdiff_t oblock, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out,
+                                                 MPI_Comm comm, unsigned flags);
+FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_c2r(int rnk, const ptrdiff_t *n, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out,
+                                            MPI_Comm comm, unsigned flags);
+FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_c2r_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_COMPLEX *in,
+                                               FFTW_REAL_TYPE *out, MPI_Comm comm, unsigned flags);
+FFTW_EXTERN void fftw_mpi_execute_dft_r2c(fftw_plan p, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out);
+FFTW_EXTERN void fftw_mpi_execute_dft_c2r(fftw_plan p, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out);
+
 /* ---- extensions: communicator bootstrap without MPI ---- */
 FFTW_EXTERN int      fftw_mpi_nccl_unique_id(void *id128);            /* rank 0: fills 128 bytes */
 FFTW_EXTERN MPI_Comm fftw_mpi_comm_from_nccl(const void *id128, int n_pes, int my_pe);

@@ -274,6 +274,134 @@ def test_many_interleaved_transforms(shape, howmany, P):
         L.b2fft_comm_destroy(r["comm"])
 
 
+def _real_api(lib):
+    L = lib.lib
+    for nm in ("fftw_mpi_plan_dft_r2c_3d", "fftw_mpi_plan_dft_c2r_3d"):
+        f = getattr(L, nm)
+        f.restype = C.c_void_p
+        f.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] * 3 + [C.c_uint]
+    return L
+
+
+@pytest.mark.parametrize("transposed", [True, False], ids=["transposed_out", "natural_out"])
+@pytest.mark.parametrize("P", [1, 2, 3])
+@pytest.mark.parametrize("shape", [(8, 6, 10), (10, 7, 9), (6, 32, 12)], ids=lambda s: "x".join(map(str, s)))
+def test_real_to_complex_slab(shape, P, transposed):
+    """fftw_mpi_plan_dft_r2c_3d (fftw/mpi/api.c:853-858; layout fftw/doc/mpi.texi 'Multi-dimensional MPI
+    DFTs of Real Data'): real [local_n0][n1][2(n2/2+1)] -> complex [local_n1][n0][n2/2+1] (transposed)
+    or [local_n0][n1][n2/2+1]."""
+    lib = load()
+    L = _real_api(lib)
+    n0, n1, n2 = shape
+    n2c = n2 // 2 + 1
+    rng = np.random.default_rng(31 + P)
+    x = (rng.random(shape) - 0.5).astype(lib.real)
+    Y = orc.r2c(x)
+    ranks = []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        N, ln0, s0, ln1, s1 = local_sizes(lib, (n0, n1, n2c), comm)
+        xin = np.zeros(2 * max(N, 1), dtype=lib.real)
+        pad = np.zeros((ln0, n1, 2 * n2c), dtype=lib.real)
+        pad[:, :, :n2] = x[s0:s0 + ln0]
+        xin[:pad.size] = pad.ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = L.fftw_mpi_plan_dft_r2c_3d(n0, n1, n2, xin.ctypes.data, out.ctypes.data, comm,
+                                          capi.FFTW_ESTIMATE | (TRANSPOSED_OUT if transposed else 0))
+        assert plan, "slab r2c plan is NULL"
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        ranks.append(dict(comm=comm, la=ln0, sa=s0, lb=ln1, sb=s1, xin=xin, out=out, plan=plan, bp=bp, S=S, R=R))
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 0, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    if "fused into" not in lib.sprint_plan(ranks[0]["plan"]):
+        _exchange(ranks, n0, n1, n2c)
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 2, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    if not transposed:
+        for src in ranks:
+            if src["lb"] == 0:
+                continue
+            Rv = src["R"][:n0 * src["lb"] * n2c].reshape(n0, src["lb"], n2c)
+            for dst in ranks:
+                if dst["la"] == 0:
+                    continue
+                Ov = dst["out"][:dst["la"] * n1 * n2c].reshape(dst["la"], n1, n2c)
+                Ov[:, src["sb"]:src["sb"] + src["lb"], :] = Rv[dst["sa"]:dst["sa"] + dst["la"]]
+    for r in ranks:
+        ref = Y.transpose(1, 0, 2)[r["sb"]:r["sb"] + r["lb"]] if transposed else Y[r["sa"]:r["sa"] + r["la"]]
+        got = r["out"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+        lib.destroy_plan(r["plan"])
+        L.b2fft_comm_destroy(r["comm"])
+
+
+@pytest.mark.parametrize("tin", [True, False], ids=["transposed_in", "natural_in"])
+@pytest.mark.parametrize("P", [1, 2, 3])
+@pytest.mark.parametrize("shape", [(8, 6, 10), (10, 7, 9), (6, 32, 12)], ids=lambda s: "x".join(map(str, s)))
+def test_complex_to_real_slab(shape, P, tin):
+    """fftw_mpi_plan_dft_c2r_3d: the pipeline backwards -- n0 FFTs, reverse exchange, local 2-D c2r"""
+    lib = load()
+    L = _real_api(lib)
+    n0, n1, n2 = shape
+    n2c = n2 // 2 + 1
+    rng = np.random.default_rng(41 + P)
+    x = (rng.random(shape) - 0.5).astype(lib.real)
+    Y = orc.r2c(x)
+    YT = np.ascontiguousarray(Y.transpose(1, 0, 2))
+    ranks = []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        N, ln0, s0, ln1, s1 = local_sizes(lib, (n0, n1, n2c), comm)
+        cin = np.zeros(max(N, 1), dtype=lib.cplx)
+        if tin:
+            cin[:ln1 * n0 * n2c] = YT[s1:s1 + ln1].ravel()
+        else:
+            cin[:ln0 * n1 * n2c] = Y[s0:s0 + ln0].ravel()
+        out = np.zeros(2 * max(N, 1), dtype=lib.real)
+        plan = L.fftw_mpi_plan_dft_c2r_3d(n0, n1, n2, cin.ctypes.data, out.ctypes.data, comm,
+                                          capi.FFTW_ESTIMATE | (TRANSPOSED_IN if tin else 0))
+        assert plan, "slab c2r plan is NULL"
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        ranks.append(dict(comm=comm, la=ln0, sa=s0, lb=ln1, sb=s1, cin=cin, out=out, plan=plan, bp=bp, S=S, R=R))
+    if P == 1:  # one rank: the whole pipeline through fftw_execute
+        r = ranks[0]
+        lib.execute(r["plan"])
+    else:
+        if not tin:  # forward exchange of the natural input straight into the receive layout
+            for src in ranks:
+                if src["la"] == 0:
+                    continue
+                Iv = src["cin"][:src["la"] * n1 * n2c].reshape(src["la"], n1, n2c)
+                for dst in ranks:
+                    if dst["lb"] == 0:
+                        continue
+                    Rv = dst["R"][:n0 * dst["lb"] * n2c].reshape(n0, dst["lb"], n2c)
+                    Rv[src["sa"]:src["sa"] + src["la"]] = Iv[:, dst["sb"]:dst["sb"] + dst["lb"], :]
+        for r in ranks:
+            assert L.b2fft_slab_stage(r["bp"], 1, r["cin"].ctypes.data, r["out"].ctypes.data) == 0
+        for src in ranks:  # reverse exchange: receive layout -> [la][n1][n2c]
+            if src["lb"] == 0:
+                continue
+            Rv = src["R"][:n0 * src["lb"] * n2c].reshape(n0, src["lb"], n2c)
+            for dst in ranks:
+                if dst["la"] == 0:
+                    continue
+                Sv = dst["S"][:dst["la"] * n1 * n2c].reshape(dst["la"], n1, n2c)
+                Sv[:, src["sb"]:src["sb"] + src["lb"], :] = Rv[dst["sa"]:dst["sa"] + dst["la"]]
+        for r in ranks:
+            assert L.b2fft_slab_stage(r["bp"], 3, r["cin"].ctypes.data, r["out"].ctypes.data) == 0
+    for r in ranks:
+        ref = x[r["sa"]:r["sa"] + r["la"]] * (n0 * n1 * n2)
+        got = r["out"][:r["la"] * n1 * 2 * n2c].reshape(r["la"], n1, 2 * n2c)[:, :, :n2]
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+        lib.destroy_plan(r["plan"])
+        L.b2fft_comm_destroy(r["comm"])
+
+
 def _gloo_worker(rank, world, port, shape, q):
     try:
         import torch
