@@ -69,6 +69,49 @@ def main():
             assert err < tol, (rank, transposed, sign, err)
             assert np.array_equal(x.cpu().numpy(), xin), "out-of-place slab transform must preserve its input"
             lib.destroy_plan(plan)
+    # ---- real data: r2c (natural / transposed output) and c2r back (natural / transposed input)
+    for nm in ("fftw_mpi_plan_dft_r2c_3d", "fftw_mpi_plan_dft_c2r_3d"):
+        f = getattr(L, nm)
+        f.restype = C.c_void_p
+        f.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] * 3 + [C.c_uint]
+    n2c = n2 // 2 + 1
+    nalloc_r = L.fftw_mpi_local_size_3d_transposed(n0, n1, n2c, comm, *[C.byref(t) for t in v])
+    ln0, s0, ln1, s1 = (t.value for t in v)
+    xr = (rng.random(shape) - 0.5).astype(lib.real)
+    Y = orc.r2c(xr)
+    for transposed in (True, False):
+        pad = np.zeros((ln0, n1, 2 * n2c), dtype=lib.real)
+        pad[:, :, :n2] = xr[s0:s0 + ln0]
+        rin = np.zeros(2 * nalloc_r, dtype=lib.real)
+        rin[:pad.size] = pad.ravel()
+        x = torch.from_numpy(rin).cuda()
+        y = torch.zeros(nalloc_r, dtype=torch.complex64 if lib.single else torch.complex128, device="cuda")
+        plan = L.fftw_mpi_plan_dft_r2c_3d(n0, n1, n2, x.data_ptr(), y.data_ptr(), comm,
+                                          capi.FFTW_ESTIMATE | ((1 << 30) if transposed else 0))
+        assert plan, L.b2fft_last_error()
+        lib.execute(plan)
+        lib.execute(plan)
+        torch.cuda.synchronize()
+        ref = Y.transpose(1, 0, 2)[s1:s1 + ln1] if transposed else Y[s0:s0 + ln0]
+        got = y.cpu().numpy()[:ref.size].reshape(ref.shape)
+        err = float(np.linalg.norm(got - ref) / np.linalg.norm(ref)) if ref.size else 0.0
+        worst = max(worst, err)
+        assert err < tol, (rank, "r2c", transposed, err)
+        lib.destroy_plan(plan)
+        # and back: c2r from that layout
+        z = torch.zeros(2 * nalloc_r, dtype=x.dtype, device="cuda")
+        plan = L.fftw_mpi_plan_dft_c2r_3d(n0, n1, n2, y.data_ptr(), z.data_ptr(), comm,
+                                          capi.FFTW_ESTIMATE | ((1 << 29) if transposed else 0))
+        assert plan, L.b2fft_last_error()
+        lib.execute(plan)
+        lib.execute(plan)
+        torch.cuda.synchronize()
+        back = z.cpu().numpy()[:ln0 * n1 * 2 * n2c].reshape(ln0, n1, 2 * n2c)[:, :, :n2] / (n0 * n1 * n2)
+        want = xr[s0:s0 + ln0]
+        err = float(np.linalg.norm(back - want) / np.linalg.norm(want)) if want.size else 0.0
+        worst = max(worst, err)
+        assert err < tol, (rank, "c2r", transposed, err)
+        lib.destroy_plan(plan)
     t = torch.tensor([worst], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:

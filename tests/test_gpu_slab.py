@@ -57,6 +57,50 @@ def test_single_rank_device_arrays(prec, transposed):
     lib.destroy_plan(plan)
 
 
+@pytest.mark.parametrize("prec", ["fp32", "fp64"])
+@pytest.mark.parametrize("shape", [(16, 12, 20), (10, 64, 50), (5, 1024, 18)], ids=lambda s: "x".join(map(str, s)))
+def test_single_rank_real_data(prec, shape):
+    """fftw_mpi_plan_dft_r2c_3d / _c2r_3d on one rank, device arrays, all four layouts"""
+    import torch
+    lib = capi.FFTW3Lib(build.lib_path(prec), prec == "fp32")
+    L = lib.lib
+    L.fftw_mpi_comm_self.restype = C.c_void_p
+    for nm in ("fftw_mpi_plan_dft_r2c_3d", "fftw_mpi_plan_dft_c2r_3d"):
+        f = getattr(L, nm)
+        f.restype = C.c_void_p
+        f.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] * 3 + [C.c_uint]
+    comm = L.fftw_mpi_comm_self()
+    n0, n1, n2 = shape
+    n2c = n2 // 2 + 1
+    rng = np.random.default_rng(9)
+    xr = (rng.random(shape) - 0.5).astype(lib.real)
+    Y = orc.r2c(xr)
+    tol = (1e-6 if lib.single else 1e-14) * np.log2(np.prod(shape))
+    pad = np.zeros((n0, n1, 2 * n2c), dtype=lib.real)
+    pad[:, :, :n2] = xr
+    for transposed in (True, False):
+        x = torch.from_numpy(pad).cuda()
+        y = torch.zeros((n0 * n1 * n2c,), dtype=torch.complex64 if lib.single else torch.complex128, device="cuda")
+        plan = L.fftw_mpi_plan_dft_r2c_3d(n0, n1, n2, x.data_ptr(), y.data_ptr(), comm,
+                                          capi.FFTW_ESTIMATE | ((1 << 30) if transposed else 0))
+        assert plan
+        lib.execute(plan)
+        torch.cuda.synchronize()
+        ref = Y.transpose(1, 0, 2) if transposed else Y
+        got = y.cpu().numpy().reshape(ref.shape)
+        assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < tol
+        lib.destroy_plan(plan)
+        z = torch.zeros_like(x)
+        plan = L.fftw_mpi_plan_dft_c2r_3d(n0, n1, n2, y.data_ptr(), z.data_ptr(), comm,
+                                          capi.FFTW_ESTIMATE | ((1 << 29) if transposed else 0))
+        assert plan
+        lib.execute(plan)
+        torch.cuda.synchronize()
+        back = z.cpu().numpy()[:, :, :n2] / np.prod(shape)
+        assert np.linalg.norm(back - xr) / np.linalg.norm(xr) < tol
+        lib.destroy_plan(plan)
+
+
 @pytest.mark.parametrize("shape", [(48, 40, 32), (50, 30, 16), (24, 64, 32), (21, 512, 48)],
                          ids=lambda s: "x".join(map(str, s)))
 def test_two_ranks_over_nccl(shape):
