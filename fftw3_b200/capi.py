@@ -177,6 +177,24 @@ class FFTW3Lib:
             f.restype, f.argtypes = None, [_vp] * 4
             f(plan, _ptr(a), _ptr(b), _ptr(c))
 
+    def plan_r2r(self, n, inp, out, kinds, flags=FFTW_ESTIMATE):
+        f = self.lib.fftw_plan_r2r
+        f.restype, f.argtypes = _vp, [C.c_int, _ip, _vp, _vp, _ip, C.c_uint]
+        return f(len(n), _ints(n), _ptr(inp), _ptr(out), _ints(kinds), flags)
+
+    def plan_many_r2r(self, n, howmany, inp, inembed, istride, idist, out, onembed, ostride, odist, kinds,
+                      flags=FFTW_ESTIMATE):
+        f = self.lib.fftw_plan_many_r2r
+        f.restype = _vp
+        f.argtypes = [C.c_int, _ip, C.c_int, _vp, _ip, C.c_int, C.c_int, _vp, _ip, C.c_int, C.c_int, _ip, C.c_uint]
+        return f(len(n), _ints(n), howmany, _ptr(inp), _ints(inembed), istride, idist, _ptr(out), _ints(onembed),
+                 ostride, odist, _ints(kinds), flags)
+
+    def execute_r2r(self, plan, inp, out):
+        f = self.lib.fftw_execute_r2r
+        f.restype, f.argtypes = None, [_vp, _vp, _vp]
+        f(plan, _ptr(inp), _ptr(out))
+
     def plan_dft(self, n, inp, out, sign, flags=FFTW_ESTIMATE):
         return self.lib.fftw_plan_dft(len(n), _ints(n), _ptr(inp), _ptr(out), sign, flags)
 

@@ -27,12 +27,53 @@ static int kosher(int rank, const int *n, int howmany) {
     return 1;
 }
 
+/* ---- wisdom: the set of problems planned (or imported) so far.  The selector is deterministic, so a
+ * wisdom entry carries no plan, only the problem's signature; what it preserves of the reference's
+ * contract is FFTW_WISDOM_ONLY (NULL unless the problem is in the accumulated wisdom,
+ * fftw_api.c:332-337) and a round-trippable export / import / forget (fftw_api.c:895-1168). */
+#define WIS_MAX 4096
+static uint64_t wis_key[WIS_MAX];
+static int wis_n = 0;
+static uint64_t wis_hash(const b2fft_geom *g) {
+    uint64_t h = 1469598103934665603ull;
+    int i;
+#define WIS_MIX(v) h = (h ^ (uint64_t)(v)) * 1099511628211ull
+    WIS_MIX(g->kind);
+    WIS_MIX(g->sign + 2);
+    WIS_MIX(g->rank);
+    WIS_MIX(g->vrank);
+    WIS_MIX(g->in_place);
+    WIS_MIX(sizeof(FFTW_REAL_TYPE));
+    for (i = 0; i < g->rank; ++i) {
+        WIS_MIX(g->dims[i].n);
+        WIS_MIX(g->dims[i].is);
+        WIS_MIX(g->dims[i].os);
+    }
+    for (i = 0; i < g->vrank; ++i) {
+        WIS_MIX(g->vdims[i].n);
+        WIS_MIX(g->vdims[i].is);
+        WIS_MIX(g->vdims[i].os);
+    }
+#undef WIS_MIX
+    return h;
+}
+static int wis_has(uint64_t k) {
+    int i;
+    for (i = 0; i < wis_n; ++i)
+        if (wis_key[i] == k) return 1;
+    return 0;
+}
+static void wis_add(uint64_t k) {
+    if (!wis_has(k) && wis_n < WIS_MAX) wis_key[wis_n++] = k;
+}
+
 static fftw_plan finish(b2fft_geom *g, void *in, void *out, unsigned flags) {
     fftw_plan p;
     b2fft_plan *bp;
-    /* the reference answers WISDOM_ONLY with NULL when it has no wisdom (fftw_api.c:332-337);
-     * this engine keeps no wisdom, every plan is computed by the selector. */
-    if (flags & FFTW_WISDOM_ONLY) return 0;
+    g->in_place = (in == out);
+    /* the reference answers WISDOM_ONLY with NULL when it has no wisdom for the problem
+     * (fftw_api.c:332-337) */
+    if ((flags & FFTW_WISDOM_ONLY) && !wis_has(wis_hash(g))) return 0;
     g->flags = flags;
     g->in_place = (in == out);
     bp = b2fft_plan_create(g);
@@ -48,6 +89,7 @@ static fftw_plan finish(b2fft_geom *g, void *in, void *out, unsigned flags) {
     p->out = out;
     p->kind = g->kind;
     p->g = *g;
+    wis_add(wis_hash(g));
     return p;
 }
 
@@ -337,45 +379,82 @@ fftw_plan fftw_plan_guru64_split_dft_c2r(int rank, const fftw_iodim64 *dims, int
     return finish_split(&g, ri, ii, out, 0, flags);
 }
 
-#define UNUSED_GURU (void)rank, (void)dims, (void)howmany_rank, (void)howmany_dims, (void)flags
-/* ------------------------------------------------------------------ r2r: not on the hot path */
+/* ------------------------------------------------------------------ r2r (csrc/r2r.cu) */
+static fftw_plan finish_r2r(int rank, const b2fft_dim *dims, int vrank, const b2fft_dim *vdims,
+                            const fftw_r2r_kind *kind, void *in, void *out, unsigned flags) {
+    fftw_plan p;
+    b2fft_r2r *rr;
+    int k[B2FFT_MAXRANK], i;
+    if (flags & FFTW_WISDOM_ONLY) return 0;
+    if (rank < 0 || rank > B2FFT_MAXRANK || (rank > 0 && !kind)) return 0;
+    for (i = 0; i < rank; ++i) k[i] = (int)kind[i];
+    rr = b2fft_r2r_plan_create(rank, dims, vrank, vdims, k);
+    if (!rr) return 0;
+    p = (fftw_plan)malloc(sizeof *p);
+    if (!p) {
+        b2fft_r2r_plan_destroy(rr);
+        return 0;
+    }
+    memset(p, 0, sizeof *p);
+    p->rr = rr;
+    p->in = in;
+    p->out = out;
+    p->kind = -1;
+    return p;
+}
 fftw_plan fftw_plan_many_r2r(int rank, const int *n, int howmany, FFTW_REAL_TYPE *in, const int *inembed,
                              int istride, int idist, FFTW_REAL_TYPE *out, const int *onembed, int ostride,
                              int odist, const fftw_r2r_kind *kind, unsigned flags) {
-    (void)rank, (void)n, (void)howmany, (void)in, (void)inembed, (void)istride, (void)idist, (void)out;
-    (void)onembed, (void)ostride, (void)odist, (void)kind, (void)flags;
-    return 0;
+    b2fft_geom g;
+    b2fft_dim v;
+    if (!kosher(rank, n, howmany)) return 0;
+    memset(&g, 0, sizeof g);
+    rowmajor(&g, rank, n, inembed ? inembed : n, onembed ? onembed : n, istride, ostride);
+    v.n = howmany;
+    v.is = idist;
+    v.os = odist;
+    return finish_r2r(rank, g.dims, 1, &v, kind, in, out, flags);
 }
 fftw_plan fftw_plan_r2r(int rank, const int *n, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out,
                         const fftw_r2r_kind *kind, unsigned flags) {
-    (void)rank, (void)n, (void)in, (void)out, (void)kind, (void)flags;
-    return 0;
+    return fftw_plan_many_r2r(rank, n, 1, in, 0, 1, 1, out, 0, 1, 1, kind, flags);
 }
 fftw_plan fftw_plan_r2r_1d(int n, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out, fftw_r2r_kind kind, unsigned flags) {
-    (void)n, (void)in, (void)out, (void)kind, (void)flags;
-    return 0;
+    return fftw_plan_r2r(1, &n, in, out, &kind, flags);
 }
 fftw_plan fftw_plan_r2r_2d(int n0, int n1, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out, fftw_r2r_kind kind0,
                            fftw_r2r_kind kind1, unsigned flags) {
-    (void)n0, (void)n1, (void)in, (void)out, (void)kind0, (void)kind1, (void)flags;
-    return 0;
+    int n[2];
+    fftw_r2r_kind k[2];
+    n[0] = n0;
+    n[1] = n1;
+    k[0] = kind0;
+    k[1] = kind1;
+    return fftw_plan_r2r(2, n, in, out, k, flags);
 }
 fftw_plan fftw_plan_r2r_3d(int n0, int n1, int n2, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out,
                            fftw_r2r_kind kind0, fftw_r2r_kind kind1, fftw_r2r_kind kind2, unsigned flags) {
-    (void)n0, (void)n1, (void)n2, (void)in, (void)out, (void)kind0, (void)kind1, (void)kind2, (void)flags;
-    return 0;
+    int n[3];
+    fftw_r2r_kind k[3];
+    n[0] = n0;
+    n[1] = n1;
+    n[2] = n2;
+    k[0] = kind0;
+    k[1] = kind1;
+    k[2] = kind2;
+    return fftw_plan_r2r(3, n, in, out, k, flags);
 }
 fftw_plan fftw_plan_guru_r2r(int rank, const fftw_iodim *dims, int howmany_rank, const fftw_iodim *howmany_dims,
                              FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out, const fftw_r2r_kind *kind,
                              unsigned flags) {
-    UNUSED_GURU, (void)in, (void)out, (void)kind;
-    return 0;
+    GURU_BODY(B2FFT_C2C, -1)
+    return finish_r2r(rank, g.dims, howmany_rank, g.vdims, kind, in, out, flags);
 }
 fftw_plan fftw_plan_guru64_r2r(int rank, const fftw_iodim64 *dims, int howmany_rank,
                                const fftw_iodim64 *howmany_dims, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out,
                                const fftw_r2r_kind *kind, unsigned flags) {
-    UNUSED_GURU, (void)in, (void)out, (void)kind;
-    return 0;
+    GURU_BODY(B2FFT_C2C, -1)
+    return finish_r2r(rank, g.dims, howmany_rank, g.vdims, kind, in, out, flags);
 }
 
 /* ------------------------------------------------------------------ execution */
@@ -395,8 +474,16 @@ static void run_split(const fftw_plan p, void *ri, void *ii, void *ro, void *io)
     rc = b2fft_split_execute(p->sp, ri, ii, ro, io);
     if (rc != 0) fprintf(stderr, "b200fft: fftw_execute (split arrays) failed (%d): %s\n", rc, b2fft_last_error());
 }
+static void run_r2r(const fftw_plan p, void *in, void *out) {
+    int rc;
+    if (!p || !p->rr) return;
+    rc = b2fft_r2r_execute(p->rr, in, out);
+    if (rc != 0) fprintf(stderr, "b200fft: fftw_execute (r2r) failed (%d): %s\n", rc, b2fft_last_error());
+}
 void fftw_execute(const fftw_plan p) {
-    if (p && p->sp)
+    if (p && p->rr)
+        run_r2r(p, p->in, p->out);
+    else if (p && p->sp)
         run_split(p, p->ri, p->ii, p->ro, p->io);
     else if (p)
         run(p, p->in, p->out);
@@ -414,19 +501,18 @@ void fftw_execute_split_dft_r2c(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_REAL
 void fftw_execute_split_dft_c2r(const fftw_plan p, FFTW_REAL_TYPE *ri, FFTW_REAL_TYPE *ii, FFTW_REAL_TYPE *out) {
     if (p && p->sp && p->kind == B2FFT_C2R) run_split(p, ri, ii, out, 0);
 }
-void fftw_execute_r2r(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out) {
-    (void)p, (void)in, (void)out;
-}
+void fftw_execute_r2r(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out) { run_r2r(p, in, out); }
 
 /* ------------------------------------------------------------------ lifecycle */
 void fftw_destroy_plan(fftw_plan p) {
     if (!p) return; /* NULL is legal (reference fftw_api.c:410) */
     b2fft_plan_destroy(p->bp);
     b2fft_split_plan_destroy(p->sp);
+    b2fft_r2r_plan_destroy(p->rr);
     free(p);
 }
 void fftw_cleanup(void) { b2fft_cleanup(); }
-void fftw_forget_wisdom(void) {}
+void fftw_forget_wisdom(void) { wis_n = 0; }
 void fftw_set_timelimit(double t) { (void)t; }
 
 /* The reference keeps these four in its threads library (fftw/threads/api.c:39-86).  A GPU
@@ -436,40 +522,79 @@ void fftw_plan_with_nthreads(int nthreads) { (void)nthreads; }
 void fftw_cleanup_threads(void) { fftw_cleanup(); }
 void fftw_make_planner_thread_safe(void) {}
 
-/* wisdom: nothing to remember -- the selector is deterministic.  Export writes an empty but
- * well-formed wisdom list; import accepts anything and reports success. */
-static const char empty_wisdom[] = "(b200fft_wisdom)\n";
+/* wisdom I/O: "(b200fft_wisdom-1 <hex signature> ...)" */
+static const char wis_head[] = "(b200fft_wisdom-1";
 char *fftw_export_wisdom_to_string(void) {
-    char *s = (char *)malloc(sizeof empty_wisdom);
-    if (s) memcpy(s, empty_wisdom, sizeof empty_wisdom);
+    size_t cap = sizeof wis_head + (size_t)wis_n * 18 + 4, len;
+    char *s = (char *)malloc(cap);
+    int i;
+    if (!s) return 0;
+    len = (size_t)sprintf(s, "%s", wis_head);
+    for (i = 0; i < wis_n; ++i) len += (size_t)sprintf(s + len, " %016llx", (unsigned long long)wis_key[i]);
+    sprintf(s + len, ")\n");
     return s;
 }
 void fftw_export_wisdom_to_file(FILE *f) {
-    if (f) fputs(empty_wisdom, f);
+    char *s = fftw_export_wisdom_to_string();
+    if (f && s) fputs(s, f);
+    free(s);
 }
 int fftw_export_wisdom_to_filename(const char *filename) {
     FILE *f = fopen(filename, "w");
     if (!f) return 0;
-    fputs(empty_wisdom, f);
+    fftw_export_wisdom_to_file(f);
     return fclose(f) == 0;
 }
 void fftw_export_wisdom(fftw_write_char_func write_char, void *data) {
-    const char *c;
-    if (!write_char) return;
-    for (c = empty_wisdom; *c; ++c) write_char(*c, data);
+    char *s = fftw_export_wisdom_to_string(), *c;
+    if (write_char && s)
+        for (c = s; *c; ++c) write_char(*c, data);
+    free(s);
 }
 int fftw_import_system_wisdom(void) { return 0; }
+/* 1 on success, 0 on a malformed list (reference: fftw_import_wisdom_from_string, fftw_api.c:1139) */
+int fftw_import_wisdom_from_string(const char *s) {
+    const char *c;
+    if (!s) return 0;
+    while (*s == ' ' || *s == '\n' || *s == '\t') ++s;
+    if (strncmp(s, wis_head, sizeof wis_head - 1) != 0) return 0;
+    c = s + sizeof wis_head - 1;
+    for (;;) {
+        char *end;
+        unsigned long long k;
+        while (*c == ' ' || *c == '\n' || *c == '\t') ++c;
+        if (*c == ')') return 1;
+        if (!*c) return 0;
+        k = strtoull(c, &end, 16);
+        if (end == c) return 0;
+        wis_add((uint64_t)k);
+        c = end;
+    }
+}
+int fftw_import_wisdom_from_file(FILE *f) {
+    char buf[WIS_MAX * 18 + 64];
+    size_t n;
+    if (!f) return 0;
+    n = fread(buf, 1, sizeof buf - 1, f);
+    buf[n] = 0;
+    return fftw_import_wisdom_from_string(buf);
+}
 int fftw_import_wisdom_from_filename(const char *filename) {
     FILE *f = fopen(filename, "r");
+    int ok;
     if (!f) return 0;
+    ok = fftw_import_wisdom_from_file(f);
     fclose(f);
-    return 1;
+    return ok;
 }
-int fftw_import_wisdom_from_file(FILE *f) { return f != 0; }
-int fftw_import_wisdom_from_string(const char *s) { return s != 0; }
 int fftw_import_wisdom(fftw_read_char_func read_char, void *data) {
-    (void)data;
-    return read_char != 0;
+    char buf[WIS_MAX * 18 + 64];
+    size_t n = 0;
+    int c;
+    if (!read_char) return 0;
+    while (n + 1 < sizeof buf && (c = read_char(data)) != EOF) buf[n++] = (char)c;
+    buf[n] = 0;
+    return fftw_import_wisdom_from_string(buf);
 }
 
 /* plan printing: the selected kernel configurations (reference prints its solver tree,
@@ -478,6 +603,12 @@ char *fftw_sprint_plan(const fftw_plan p) {
     int n;
     char *s;
     if (!p) return 0;
+    if (p->rr) {
+        n = b2fft_r2r_describe(p->rr, 0, 0);
+        s = (char *)malloc((size_t)n + 1);
+        if (s) b2fft_r2r_describe(p->rr, s, (size_t)n + 1);
+        return s;
+    }
     if (p->sp) {
         n = b2fft_split_describe(p->sp, 0, 0);
         s = (char *)malloc((size_t)n + 1);
@@ -504,7 +635,7 @@ void fftw_free(void *p) { b2fft_free(p); }
 
 /* 5 N log2 N convention (fftw/libbench2/mflops.c:6-31), split evenly between adds and muls */
 void fftw_flops(const fftw_plan p, double *add, double *mul, double *fmas) {
-    double f = !p ? 0.0 : p->sp ? b2fft_split_flops(p->sp) : b2fft_plan_flops(p->bp);
+    double f = !p ? 0.0 : p->rr ? b2fft_r2r_flops(p->rr) : p->sp ? b2fft_split_flops(p->sp) : b2fft_plan_flops(p->bp);
     if (add) *add = 0.6 * f;
     if (mul) *mul = 0.4 * f;
     if (fmas) *fmas = 0.0;

@@ -10,5 +10,6 @@ struct fftw_plan_s {
     b2fft_geom g;
     b2fft_split *sp;            /* split-array plan (bp is NULL then) */
     void *ri, *ii, *ro, *io;    /* its arrays at plan time */
+    b2fft_r2r *rr;              /* real-to-real plan (bp is NULL then) */
 };
 #endif

@@ -94,6 +94,16 @@ int          b2fft_split_execute(b2fft_split *p, void *ri, void *ii, void *ro, v
 int          b2fft_split_describe(const b2fft_split *p, char *buf, size_t buflen);
 double       b2fft_split_flops(const b2fft_split *p);
 
+/* ---- real-to-real transforms (fftw_plan_r2r*, reference fftw/fftw_api.c:1085-1170, 11700-14160) -----
+ * kinds[i] is the fftw_r2r_kind of transform dim i (FFTW_R2HC ... FFTW_RODFT11, fftw3.h:117-121);
+ * strides in reals; host or device arrays. */
+typedef struct b2fft_r2r_s b2fft_r2r;
+b2fft_r2r *b2fft_r2r_plan_create(int rank, const b2fft_dim *dims, int vrank, const b2fft_dim *vdims, const int *kinds);
+void       b2fft_r2r_plan_destroy(b2fft_r2r *p);
+int        b2fft_r2r_execute(b2fft_r2r *p, void *in, void *out);
+int        b2fft_r2r_describe(const b2fft_r2r *p, char *buf, size_t buflen);
+double     b2fft_r2r_flops(const b2fft_r2r *p);
+
 /* ---- slab-distributed 3-D c2c (fftw_mpi_plan_dft_3d form), one process per GPU --------- */
 typedef struct b2fft_comm_s b2fft_comm;
 

@@ -174,3 +174,70 @@ def mpi_dft_3d_local(x_global, n_pes, my_pe, transposed_out=True, sign=-1):
     if rc:
         raise ValueError("oracle_mpi_dft_3d_local failed")
     return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# real-to-real kinds (TEST INFRASTRUCTURE like the rest of this module): direct O(n^2) restatement of
+# the definitions the reference implements (fftw/doc/reference.texi "1d Real-even DFTs (DCTs)" and
+# "1d Real-odd DFTs (DSTs)"; solvers fftw/fftw_api.c:11700-14160, kinds fftw/fftw3.h:117-121).  Pinned
+# against outputs of the reference itself: tests/golden/r2r_golden.npz (tests/golden/make_golden_r2r.py).
+R2R_KINDS = {"R2HC": 0, "HC2R": 1, "DHT": 2, "REDFT00": 3, "REDFT01": 4, "REDFT10": 5, "REDFT11": 6,
+             "RODFT00": 7, "RODFT01": 8, "RODFT10": 9, "RODFT11": 10}
+
+
+def r2r_1d(x, kind):
+    """one-dimensional r2r transform of the last axis, float64"""
+    x = np.asarray(x, dtype=np.float64)
+    n = x.shape[-1]
+    j = np.arange(n)[None, :]
+    k = np.arange(n)[:, None]
+    pi = np.pi
+    if kind == 0:  # R2HC: r0, r1, ..., r_{n/2}, i_{(n+1)/2-1}, ..., i_1
+        F = np.fft.fft(x, axis=-1)
+        out = np.empty_like(x)
+        out[..., :n // 2 + 1] = F.real[..., :n // 2 + 1]
+        for kk in range(1, (n + 1) // 2):
+            out[..., n - kk] = F.imag[..., kk]
+        return out
+    if kind == 1:  # HC2R: unnormalised inverse of R2HC
+        F = np.zeros(x.shape[:-1] + (n // 2 + 1,), dtype=np.complex128)
+        F[..., :n // 2 + 1] = x[..., :n // 2 + 1]
+        for kk in range(1, (n + 1) // 2):
+            F[..., kk] += 1j * x[..., n - kk]
+        return np.fft.irfft(F, n=n, axis=-1) * n
+    if kind == 2:  # DHT
+        F = np.fft.fft(x, axis=-1)
+        return F.real - F.imag
+    if kind == 3:  # REDFT00
+        M = 2 * np.cos(pi * j * k / (n - 1))
+        M[:, 0] = 1
+        M[:, n - 1] = (-1.0) ** np.arange(n)
+    elif kind == 5:  # REDFT10
+        M = 2 * np.cos(pi * (j + 0.5) * k / n)
+    elif kind == 4:  # REDFT01
+        M = 2 * np.cos(pi * j * (k + 0.5) / n)
+        M[:, 0] = 1
+    elif kind == 6:  # REDFT11
+        M = 2 * np.cos(pi * (j + 0.5) * (k + 0.5) / n)
+    elif kind == 7:  # RODFT00
+        M = 2 * np.sin(pi * (j + 1) * (k + 1) / (n + 1))
+    elif kind == 9:  # RODFT10
+        M = 2 * np.sin(pi * (j + 0.5) * (k + 1) / n)
+    elif kind == 8:  # RODFT01
+        M = 2 * np.sin(pi * (j + 1) * (k + 0.5) / n)
+        M[:, n - 1] = (-1.0) ** np.arange(n)
+    elif kind == 10:  # RODFT11
+        M = 2 * np.sin(pi * (j + 0.5) * (k + 0.5) / n)
+    else:
+        raise ValueError(kind)
+    return x @ M.T
+
+
+def r2r(x, kinds):
+    """multi-dimensional: kinds[i] along axis -(len(kinds)) + i (the transform dims are the last ones)"""
+    y = np.asarray(x, dtype=np.float64)
+    r = len(kinds)
+    for i, kd in enumerate(kinds):
+        ax = y.ndim - r + i
+        y = np.moveaxis(r2r_1d(np.moveaxis(y, ax, -1), kd), -1, ax)
+    return y

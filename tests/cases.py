@@ -12,6 +12,8 @@ from __future__ import annotations
 
 import math
 
+import ctypes as C
+
 import numpy as np
 
 from fftw3_b200 import capi
@@ -200,8 +202,32 @@ def check_edge_cases(lib):
     # invalid sizes -> NULL plan, like the reference (fftw_api.c:863-877)
     assert not lib.plan_many_dft([0], 1, x, None, 1, 1, x, None, 1, 1, -1)
     assert not lib.plan_many_dft([4], -1, x, None, 1, 4, x, None, 1, 4, -1)
-    # FFTW_WISDOM_ONLY without wisdom -> NULL (fftw_api.c:332-337)
-    assert not lib.plan_dft_1d(8, x, x, -1, capi.FFTW_ESTIMATE | capi.FFTW_WISDOM_ONLY)
+    # FFTW_WISDOM_ONLY without wisdom -> NULL (fftw_api.c:332-337); with it -> a plan; wisdom survives an
+    # export / forget / import round trip (fftw_api.c:895-1168)
+    L = lib.lib
+    L.fftw_export_wisdom_to_string.restype = C.c_void_p
+    L.fftw_import_wisdom_from_string.argtypes = [C.c_char_p]
+    L.fftw_forget_wisdom()
+    wo = capi.FFTW_ESTIMATE | capi.FFTW_WISDOM_ONLY
+    assert not lib.plan_dft_1d(8, x, x, -1, wo)
+    p = lib.plan_dft_1d(8, x, x, -1)
+    assert p
+    lib.destroy_plan(p)
+    p = lib.plan_dft_1d(8, x, x, -1, wo)
+    assert p, "the problem was planned before: it is in the accumulated wisdom"
+    lib.destroy_plan(p)
+    assert not lib.plan_dft_1d(16, np.zeros(16, lib.cplx), np.zeros(16, lib.cplx), -1, wo)
+    sp = L.fftw_export_wisdom_to_string()
+    text = C.string_at(sp)
+    C.CDLL(None).free(C.c_void_p(sp))
+    assert text.startswith(b"(b200fft_wisdom-1 ") and text.rstrip().endswith(b")")
+    L.fftw_forget_wisdom()
+    assert not lib.plan_dft_1d(8, x, x, -1, wo)
+    assert L.fftw_import_wisdom_from_string(text) == 1
+    p = lib.plan_dft_1d(8, x, x, -1, wo)
+    assert p
+    lib.destroy_plan(p)
+    assert L.fftw_import_wisdom_from_string(b"(fftw-3.3.8 fftw_wisdom #x0 #x0)") == 0  # not ours: rejected
     # howmany = 0 is a legal no-op
     p = lib.plan_many_dft([4], 0, x, None, 1, 4, x, None, 1, 4, -1)
     assert p
@@ -512,4 +538,76 @@ def check_split_arrays(lib, device=False):
     assert p, "split c2r plan is NULL"
     lib.execute(p)
     assert rel_l2(down(dout) / 180, xr) < tol(lib, 180)
+    lib.destroy_plan(p)
+
+
+R2R_SIZES = [2, 3, 4, 5, 8, 9, 16, 30, 64, 100, 255, 1024]
+
+
+def check_r2r(lib, r2r_golden, device=False):
+    """every fftw_r2r_kind (fftw3.h:117-121): against the reference's own outputs (golden, fp64 inputs),
+    against the oracle at sizes the golden file does not hold, multi-dimensional mixes, batched /
+    strided `many` form, in place, new-array execute."""
+    rng = np.random.default_rng(23)
+    if device:
+        import torch
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        down = lambda t: t.cpu().numpy()
+    else:
+        up = lambda a: np.ascontiguousarray(a)
+        down = lambda a: a
+
+    def run(x, kinds):
+        xi = up(np.ascontiguousarray(x, dtype=lib.real))
+        yo = up(np.zeros(x.shape, lib.real))
+        p = lib.plan_r2r(list(x.shape), xi, yo, kinds)
+        assert p, ("r2r plan is NULL", x.shape, kinds)
+        lib.execute(p)
+        lib.destroy_plan(p)
+        return down(yo)
+
+    scale = 40.0  # the zero-stuffed 8n extension adds 3 bits to log2 N; sums of 2n terms
+    for name, kd in orc.R2R_KINDS.items():
+        for n in R2R_SIZES:
+            if name == "REDFT00" and n < 2:
+                continue
+            key = f"{name}_{n}_in"
+            if key in r2r_golden.files:
+                x, ref = r2r_golden[key], r2r_golden[f"{name}_{n}_out"]
+            else:
+                x = rng.random(n) - 0.5
+                ref = orc.r2r_1d(x, kd)
+            got = run(x, [kd])
+            assert rel_l2(got, ref) < scale * tol(lib, 8 * n), (name, n, rel_l2(got, ref))
+    for key, kinds in (("2d_REDFT10xRODFT00", [5, 7]), ("3d_DHTxREDFT00xR2HC", [2, 3, 0])):
+        x, ref = r2r_golden[key + "_in"], r2r_golden[key + "_out"]
+        assert rel_l2(run(x, kinds), ref) < scale * tol(lib, x.size * 8)
+    # round trips: REDFT10 <-> REDFT01 and R2HC <-> HC2R are inverses up to 2n and n
+    x = rng.random((3, 48)) - 0.5
+    a = run(x[0], [orc.R2R_KINDS["REDFT10"]])
+    assert rel_l2(run(a, [orc.R2R_KINDS["REDFT01"]]) / (2 * 48), x[0]) < scale * tol(lib, 8 * 48)
+    h = run(x[1], [orc.R2R_KINDS["R2HC"]])
+    assert rel_l2(run(h, [orc.R2R_KINDS["HC2R"]]) / 48, x[1]) < scale * tol(lib, 48)
+    # many: 5 transforms of 12 x 10 (RODFT10 x REDFT11) embedded in 13 x 11 with distance, in place
+    n, emb, hm = [12, 10], [13, 11], 5
+    dist = 13 * 11 + 4
+    buf = (rng.random(hm * dist) - 0.5).astype(lib.real)
+    ref = buf.astype(np.float64).copy()
+    for b in range(hm):
+        blk = ref[b * dist:b * dist + 13 * 11].reshape(13, 11)
+        blk[:12, :10] = orc.r2r(blk[:12, :10].copy(), [9, 6])
+    d = up(buf)
+    p = lib.plan_many_r2r(n, hm, d, emb, 1, dist, d, emb, 1, dist, [9, 6])
+    assert p, "many_r2r plan is NULL"
+    lib.execute(p)
+    assert rel_l2(down(d), ref) < scale * tol(lib, 8 * 120)
+    # new-array execute on the same plan
+    buf2 = (rng.random(hm * dist) - 0.5).astype(lib.real)
+    ref2 = buf2.astype(np.float64).copy()
+    for b in range(hm):
+        blk = ref2[b * dist:b * dist + 13 * 11].reshape(13, 11)
+        blk[:12, :10] = orc.r2r(blk[:12, :10].copy(), [9, 6])
+    d2 = up(buf2)
+    lib.execute_r2r(p, d2, d2)
+    assert rel_l2(down(d2), ref2) < scale * tol(lib, 8 * 120)
     lib.destroy_plan(p)

@@ -16,3 +16,9 @@ def pytest_configure(config):
 def golden():
     import numpy as np
     return np.load(os.path.join(ROOT, "tests", "golden", "ref_golden.npz"))
+
+
+@pytest.fixture(scope="session")
+def r2r_golden():
+    import numpy as np
+    return np.load(os.path.join(ROOT, "tests", "golden", "r2r_golden.npz"))

@@ -111,6 +111,10 @@ def test_split_array_guru_interfaces(lib):
     cases.check_split_arrays(lib)
 
 
+def test_r2r_kinds(lib, r2r_golden):
+    cases.check_r2r(lib, r2r_golden)
+
+
 def test_chained_launch_opt_in(lib):
     cases.check_chained_launch(lib)
 

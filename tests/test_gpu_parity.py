@@ -86,6 +86,11 @@ def test_split_array_guru_interfaces(lib):
     cases.check_split_arrays(lib, device=True)
 
 
+def test_r2r_kinds(lib, r2r_golden):
+    cases.check_r2r(lib, r2r_golden)
+    cases.check_r2r(lib, r2r_golden, device=True)
+
+
 def test_edge_cases(lib):
     cases.check_edge_cases(lib)
 

@@ -134,3 +134,14 @@ def test_mpi_slab_layout(P):
         N2, a, b = orc.mpi_local_size_3d(n0, n1, n2, P, p)
         assert (a, b) == (ln0, ls0) and N2 >= ln0 * n1 * n2
     assert seen0 == n0 and seen1 == n1
+
+
+def test_r2r_restatement_matches_the_reference(r2r_golden):
+    """oracle.r2r_1d / r2r (direct sums from the manual's definitions) against outputs of the reference"""
+    g = r2r_golden
+    for name, kd in orc.R2R_KINDS.items():
+        for n in (2, 3, 4, 5, 8, 9, 16, 30, 64):
+            x, y = g[f"{name}_{n}_in"], g[f"{name}_{n}_out"]
+            assert np.linalg.norm(orc.r2r_1d(x, kd) - y) / np.linalg.norm(y) < 1e-13, (name, n)
+    assert np.linalg.norm(orc.r2r(g["2d_REDFT10xRODFT00_in"], [5, 7]) - g["2d_REDFT10xRODFT00_out"]) < 1e-12
+    assert np.linalg.norm(orc.r2r(g["3d_DHTxREDFT00xR2HC_in"], [2, 3, 0]) - g["3d_DHTxREDFT00xR2HC_out"]) < 1e-12
