@@ -299,7 +299,17 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
         return true;
     }
     long long n1, n2;
-    if (!split_four_step(n, &n1, &n2)) {
+    bool two_pass = split_four_step(n, &n1, &n2);
+    if (two_pass && !getenv("FFTW_B200_NO_PREFER3")) {
+        // Measured on B200 (profiles/r1_long1d_probe.md): three passes through the 128..256-point kernels
+        // (4 CTAs per SM, ~0.35 ms per GiB pass) beat two passes through the 2048-point (fp32) or
+        // 1024-point (fp64) kernels, which run one CTA per SM: fp32 2^22 1.31 ms in two passes against
+        // 2^23 / 2^24 at 1.17 / 1.14 ms in three; fp64 2^20 1.34 ms against 2^21 at 1.07 ms.
+        const long long big = sizeof(real_t) == 4 ? 2048 : 1024;
+        long long a3, b3, c3;
+        if (std::max(n1, n2) >= big && split_three(n, &a3, &b3, &c3) && a3 < big) two_pass = false;
+    }
+    if (!two_pass) {
         // ---- three passes, n = n1 * n2 * n3 (j = j1*n2*n3 + j2*n3 + j3, k = k1 + n1*k2 + n1*n2*k3):
         //   1. n1-point FFTs over j1 for every (j2, j3), times w_n^(k1*(j2*n3 + j3))      [k1][j2][j3]
         //   2. inside every row k1: n2-point FFTs over j2, times w_(n2*n3)^(k2*j3)        [k1][k2][j3]

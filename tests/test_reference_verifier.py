@@ -21,7 +21,12 @@ PROBLEMS = ["icf1024", "ocf4096", "ocb4096", "orf1024", "orb1024", "irf1024", "i
             "ocf16384", "orf32768", "ocf64x64x64", "icf256*16", "obr128x64", "ocf3x5x7x2", "ocf1",
             "orf2", "icb2x2", "ocf1000", "ocf512*12", "ocf2048*3", "irb64x66",
             # prime factors > 13: Bluestein path
-            "ocf17", "icb97", "orf34", "obr46", "ocf1009", "ocf23x29", "irf37x6", "ocf127*5"]
+            "ocf17", "icb97", "orf34", "obr46", "ocf1009", "ocf23x29", "irf37x6", "ocf127*5",
+            # r2r kinds (k = PROBLEM_R2R; f/b/h = R2HC/HC2R/DHT, eXY/oXY = REDFT/RODFT; libbench2/problem.c:150-190)
+            "ok16e10", "ok16e00", "ok15o11", "ik32h", "ok64f", "ok64b", "ok12e01x10o10", "ok8e11*5", "ok100o01",
+            "ik30o00", "ok256e10", "ok9o10x7e11",
+            # split arrays ('/': libbench2/problem.c:259): guru split interfaces
+            "o/cf64", "i/cf16x16", "o/rf64", "o/rb30", "o/cf1024*4", "o/cb12x10"]
 
 
 def run(binary, args):
