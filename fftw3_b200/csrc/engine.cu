@@ -401,6 +401,7 @@ extern "C" int b2fft_execute_async(b2fft_plan *p, void *in, void *out, void *str
 
 extern "C" int b2fft_execute(b2fft_plan *p, void *in, void *out) {
     if (!p) return -1;
+    std::lock_guard<std::mutex> guard(p->exec_mutex);
     if (p->slab) return b2_slab_execute(p, in, out);
     if (p->pc.empty) return 0;
     if (ensure_device() != 0) return -1;

@@ -5,6 +5,7 @@
  * (fftw_mkproblem_dft_d :4110, fftw_mkapiplan :317-407) it fills a flat geometry descriptor
  * and hands it to the CUDA engine through the C-ABI of include/b200fft.h.
  */
+#include <pthread.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -26,6 +27,15 @@ static int kosher(int rank, const int *n, int howmany) {
         if (n[i] <= 0) return 0;
     return 1;
 }
+
+/* ---- planner lock.  In the reference every planner / destroy / wisdom call shares one global planner
+ * and is NOT thread-safe unless fftw_make_planner_thread_safe() installed mutex hooks
+ * (fftw_api.c:258-263, threads/api.c:83-86).  Here the shared state is the twiddle / chirp table cache
+ * and the wisdom set; the lock is always taken (it costs nothing next to a plan), so the call that
+ * installs it in the reference is a no-op. */
+static pthread_mutex_t planner_lock = PTHREAD_MUTEX_INITIALIZER;
+#define PLANNER_LOCK() pthread_mutex_lock(&planner_lock)
+#define PLANNER_UNLOCK() pthread_mutex_unlock(&planner_lock)
 
 /* ---- wisdom: the set of problems planned (or imported) so far.  The selector is deterministic, so a
  * wisdom entry carries no plan, only the problem's signature; what it preserves of the reference's
@@ -67,7 +77,15 @@ static void wis_add(uint64_t k) {
     if (!wis_has(k) && wis_n < WIS_MAX) wis_key[wis_n++] = k;
 }
 
+static fftw_plan finish_locked(b2fft_geom *g, void *in, void *out, unsigned flags);
 static fftw_plan finish(b2fft_geom *g, void *in, void *out, unsigned flags) {
+    fftw_plan p;
+    PLANNER_LOCK();
+    p = finish_locked(g, in, out, flags);
+    PLANNER_UNLOCK();
+    return p;
+}
+static fftw_plan finish_locked(b2fft_geom *g, void *in, void *out, unsigned flags) {
     fftw_plan p;
     b2fft_plan *bp;
     g->in_place = (in == out);
@@ -98,7 +116,9 @@ static fftw_plan finish_split(b2fft_geom *g, void *ri, void *ii, void *ro, void 
     b2fft_split *sp;
     if (flags & FFTW_WISDOM_ONLY) return 0;
     g->flags = flags;
+    PLANNER_LOCK();
     sp = b2fft_split_plan_create(g);
+    PLANNER_UNLOCK();
     if (!sp) return 0;
     p = (fftw_plan)malloc(sizeof *p);
     if (!p) {
@@ -388,7 +408,9 @@ static fftw_plan finish_r2r(int rank, const b2fft_dim *dims, int vrank, const b2
     if (flags & FFTW_WISDOM_ONLY) return 0;
     if (rank < 0 || rank > B2FFT_MAXRANK || (rank > 0 && !kind)) return 0;
     for (i = 0; i < rank; ++i) k[i] = (int)kind[i];
+    PLANNER_LOCK();
     rr = b2fft_r2r_plan_create(rank, dims, vrank, vdims, k);
+    PLANNER_UNLOCK();
     if (!rr) return 0;
     p = (fftw_plan)malloc(sizeof *p);
     if (!p) {
@@ -506,12 +528,18 @@ void fftw_execute_r2r(const fftw_plan p, FFTW_REAL_TYPE *in, FFTW_REAL_TYPE *out
 /* ------------------------------------------------------------------ lifecycle */
 void fftw_destroy_plan(fftw_plan p) {
     if (!p) return; /* NULL is legal (reference fftw_api.c:410) */
+    PLANNER_LOCK();
     b2fft_plan_destroy(p->bp);
     b2fft_split_plan_destroy(p->sp);
     b2fft_r2r_plan_destroy(p->rr);
+    PLANNER_UNLOCK();
     free(p);
 }
-void fftw_cleanup(void) { b2fft_cleanup(); }
+void fftw_cleanup(void) {
+    PLANNER_LOCK();
+    b2fft_cleanup();
+    PLANNER_UNLOCK();
+}
 void fftw_forget_wisdom(void) { wis_n = 0; }
 void fftw_set_timelimit(double t) { (void)t; }
 

@@ -1,5 +1,7 @@
 // csrc/plan_struct.h -- the opaque b2fft_plan of include/b200fft.h
 #pragma once
+#include <mutex>
+
 #include "plan_build.h"
 
 namespace b2 {
@@ -35,6 +37,10 @@ struct b2fft_plan_s {
     bool needs_aligned = false;     // has steps without a generic-kernel form
     b2fft_plan_s *alt = nullptr;    // the same problem without them, for unaligned arrays
     b2::StepPlan *scat = nullptr;   // the last step re-selected with a scattered store (slab.cu)
+    // fftw_execute is re-entrant in the reference, also for one plan from several threads
+    // (fftw_api.c:428-454: plans are read-only after awake).  Here a plan owns work arrays and
+    // staging buffers, so synchronous executes of the SAME plan are serialised.
+    std::mutex exec_mutex;
 };
 // Fused slab exchange: turn the plan's last step (a column pass writing rows of the transformed
 // axis) into one that stores row k into the receive buffer of its owner k / blk.  plane_stride =

@@ -611,3 +611,45 @@ def check_r2r(lib, r2r_golden, device=False):
     lib.execute_r2r(p, d2, d2)
     assert rel_l2(down(d2), ref2) < scale * tol(lib, 8 * 120)
     lib.destroy_plan(p)
+
+
+def check_threads(lib):
+    """fftw_execute_dft from several threads on ONE plan with different arrays, and plan creation /
+    destruction from several threads at once (reference contract: execute is re-entrant,
+    fftw_api.c:428-454; the planner needs fftw_make_planner_thread_safe, threads/api.c:83-86)."""
+    import threading
+    lib.lib.fftw_make_planner_thread_safe()
+    rng = np.random.default_rng(5)
+    n, hm = 1 << 14, 3  # two kernel passes and a plan-owned scratch array
+    x0 = rand_c(rng, (hm, n), lib)
+    p = lib.plan_many_dft([n], hm, x0, None, 1, n, x0.copy(), None, 1, n, -1)
+    assert p
+    errs = []
+
+    def work(seed):
+        try:
+            r = np.random.default_rng(seed)
+            for it in range(4):
+                x = rand_c(r, (hm, n), lib)
+                y = np.empty_like(x)
+                lib.execute_dft(p, x, y)
+                ref = orc.dft_batched(x, -1)
+                e = rel_l2(y, ref)
+                if not e < tol(lib, n):
+                    errs.append(("execute", seed, it, e))
+                m = 64 << (seed % 3)
+                a = rand_c(r, (m,), lib)
+                q = lib.plan_dft_1d(m, a, a.copy(), -1)
+                if not q:
+                    errs.append(("plan", seed, it))
+                lib.destroy_plan(q)
+        except Exception as ex:  # pragma: no cover
+            errs.append(("exception", seed, repr(ex)))
+
+    th = [threading.Thread(target=work, args=(s,)) for s in range(6)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    lib.destroy_plan(p)
+    assert not errs, errs

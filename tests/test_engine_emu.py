@@ -115,6 +115,10 @@ def test_r2r_kinds(lib, r2r_golden):
     cases.check_r2r(lib, r2r_golden)
 
 
+def test_threads_share_a_plan_and_the_planner(lib):
+    cases.check_threads(lib)
+
+
 def test_chained_launch_opt_in(lib):
     cases.check_chained_launch(lib)
 

@@ -91,6 +91,10 @@ def test_r2r_kinds(lib, r2r_golden):
     cases.check_r2r(lib, r2r_golden, device=True)
 
 
+def test_threads_share_a_plan_and_the_planner(lib):
+    cases.check_threads(lib)
+
+
 def test_edge_cases(lib):
     cases.check_edge_cases(lib)
 
