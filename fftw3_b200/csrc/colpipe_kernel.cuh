@@ -132,6 +132,7 @@ template <int N, int E, int EPI> struct TilePipe {
         prefetch(p, csrc, (unsigned)first, x.sm, x.nthreads);
         for (long long tile = first; tile < end; tile += stride) {
             x.scoord = 0;
+            x.fcoord = 0;
             F::decode(p, (unsigned)tile, x.l0, x.nlines, x.sbase, x.dbase, x.i2base, &x.scoord);
             b2_cp_async_wait_all();
             B2_SYNC();  // the tile has landed (every thread waited for its own copies)

@@ -50,6 +50,11 @@ struct PassParams {
     int pmerge;            // row pass whose line is built from two adjacent Hermitian half rows (two-pass c2r)
     long long fold_n;      // real length n = n1 * n2; outputs k > n/2 are stored as conj at n - k
     int fold_n1;
+    // three-pass real transform (n = n1*n2*n3): the row pass's output index is
+    //   k1 + fold_cmul * (coordinate along line dim fold_dim) + fold_pmul * (point index);
+    // fold_dim == 0: none (two-pass form, index k1 + fold_n1 * point).  That dim's ld is 0.
+    int fold_dim, fold_cmul;
+    long long fold_pmul;
     // ---- tile-kernel decode helpers, filled by b2_pp_prepare() just before a launch ----
     unsigned dv_m[B2_MAXLD], dv_s[B2_MAXLD];  // exact division by tiles0 (slot 0) and ln[1..] for indices < 2^31
     int lgC;                                  // log2(C), or -1 when C is not a power of two

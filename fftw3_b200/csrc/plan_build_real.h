@@ -42,6 +42,29 @@ inline bool split_two_pass_real(long long n, long long *n1o, long long *n2o, boo
     return true;
 }
 
+// three-pass real split n = q1 * q2 * q3 through the short (<= 256-point) kernels: pair-split column
+// pass q1, twiddled column pass q2 inside every row, row -> column pass q3 with the Hermitian fold
+inline bool split_three_pass_real(long long n, long long *q1o, long long *q2o, long long *q3o) {
+    if (n & (n - 1)) return false;
+    long long cap = 256;
+    if (const char *e = getenv("FFTW_B200_REAL3_CAP")) cap = std::max(32ll, atoll(e));
+    for (long long a = cap; a >= 32; a /= 2) {
+        if (n % a || !b2_have_tile_kernel((int)a, 1, 2)) continue;
+        const long long Q = n / a;
+        // q2 >= q3, as balanced as possible
+        for (long long c = 32; c * c <= Q; c *= 2) {
+            const long long b = Q / c;
+            if (b * c != Q || b > cap || c > b) continue;
+            if (!b2_have_tile_kernel((int)b, 1, 1) || !b2_have_tile_kernel((int)c, 2, 0)) continue;
+            *q1o = a;
+            *q2o = b;
+            *q3o = c;  // keeps the last (largest c) found: the most balanced pair
+        }
+        if (*q1o == a) return true;
+    }
+    return false;
+}
+
 inline void fill_realpp(StepPlan &st, int post, int m, long long n_real, long long s_axis,
                         long long d_axis, const std::vector<LDim> &lines, bool use_src_for_both) {
     st.kind = post ? SK_RPOST : SK_RPRE;
@@ -347,6 +370,82 @@ inline bool build_real(PlanCore &pc) {
             return assign_buffers(pc);
         }
         long long q1 = 0, q2 = 0;
+        long long t1 = 0, t2 = 0, t3 = 0;
+        // ---- three passes through the short kernels (four CTAs per SM) instead of two through the
+        // 1024-point ones (one CTA per SM): see profiles/r1_real3_probe.md
+        // Measured on B200 (profiles/r1_real3_probe.md, 2^20 x 256 fp32): 1.27 ms against 1.21 ms for the two-pass
+        // plan -- at 2^20 the factors are 256 x 64 x 64 and the 64-point kernels' 8 KB tiles do not reach the
+        // 256-point kernels' bandwidth.  So: default only where no two-pass split exists (n > 2^22 fp32 /
+        // 2^20 fp64, where it replaces four passes), FFTW_B200_THREE_PASS_REAL=1 forces it from 2^19 on.
+        long long u1 = 0, u2 = 0;
+        const bool want3 = getenv("FFTW_B200_THREE_PASS_REAL") ? nl >= (1ll << 19) : !split_two_pass_real(nl, &u1, &u2);
+        if (r2c && !no_two_pass_real() && !getenv("FFTW_B200_NO_TWO_PASS_REAL") && !getenv("FFTW_B200_NO_THREE_PASS_REAL") &&
+            want3 && nl < (1ll << 31) && (nl & (nl - 1)) == 0 && T[L].is == 1 && T[L].os == 1 && evens_src && evens_dst &&
+            split_three_pass_real(nl, &t1, &t2, &t3)) {
+            const long long rows = t1 / 2 + 1, Q = t2 * t3;
+            const std::vector<long long> cs3 = compact_strides(nz, rows * Q);
+            {   // pass 1: IN viewed as complex [t1][Q/2] -> SCR [t1/2+1][Q], pair split + w_n^(k1*j)
+                AxisSpec a;
+                a.n = (int)t1;
+                a.s_axis = Q;
+                a.d_axis = 2 * Q;
+                a.lines.push_back(LDim{Q / 2, 2, 4, true});
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, nz[i].s, cs3[i], false});
+                a.epi_N = nl;
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.pp.rsplit = 1;
+                st.needs_tile_kernel = true;
+                st.dst_allowed = {B_SCR};
+                pc.steps.push_back(st);
+            }
+            {   // pass 2: inside every row k1, t2-point FFTs over j2 (stride t3), times w_Q^(k2*j3); in place
+                AxisSpec a;
+                a.n = (int)t2;
+                a.s_axis = a.d_axis = 2 * t3;
+                a.lines.push_back(LDim{t3, 2, 2, true});
+                a.lines.push_back(LDim{rows, 2 * Q, 2 * Q, false});
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, cs3[i], cs3[i], false});
+                a.epi_N = Q;
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                st.inplace_ok = true;
+                st.needs_tile_kernel = true;
+                st.src_fixed = B_SCR;
+                st.dst_allowed = {B_SCR};
+                pc.steps.push_back(st);
+            }
+            {   // pass 3: rows of t3 for every (k1, k2), output index k1 + t1*k2 + t1*t2*k3, folded
+                AxisSpec a;
+                a.n = (int)t3;
+                a.s_axis = 2;
+                a.d_axis = 2 * t1 * t2;
+                a.lines.push_back(LDim{rows, 2 * Q, 2, false});
+                a.lines.push_back(LDim{t2, 2 * t3, 2 * t1, false});
+                for (size_t i = 0; i < nz.size(); ++i) a.lines.push_back(LDim{nz[i].n, cs3[i], nz[i].d, false});
+                StepPlan st;
+                if (!make_pass_step(st, a)) return false;
+                PassParams &q = st.pp;
+                q.fold_n = nl;
+                q.fold_n1 = (int)t1;
+                q.fold_dim = 0;
+                for (int d = 1; d < q.nld; ++d)
+                    if (q.ln[d] == t2 && q.ls[d] == 2 * t3 && q.ld[d] == 2 * t1 && q.fold_dim == 0) q.fold_dim = d;
+                if (q.fold_dim == 0) {
+                    set_error("three-pass real transform: fold dimension lost in canonicalisation");
+                    return false;
+                }
+                q.ld[q.fold_dim] = 0;  // the k2 offset enters through the folded index
+                q.fold_cmul = (int)t1;
+                q.fold_pmul = t1 * t2;
+                st.needs_tile_kernel = true;
+                st.src_fixed = B_SCR;
+                st.dst_allowed = {B_OUT};
+                pc.steps.push_back(st);
+            }
+            if (!leading_axes(false)) return false;
+            return assign_buffers(pc);
+        }
         if (r2c && !no_two_pass_real() && !getenv("FFTW_B200_NO_TWO_PASS_REAL") && (nl & (nl - 1)) == 0 &&
             T[L].is == 1 && T[L].os == 1 && evens_src && evens_dst && split_two_pass_real(nl, &q1, &q2)) {
             // ---- two passes: real column pairs (FFT + split + twiddle), then rows with a Hermitian fold

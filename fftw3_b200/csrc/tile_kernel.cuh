@@ -51,6 +51,7 @@ struct TileCtx {
     int nlines;
     int i2base;
     int scoord;           // coordinate along the scatter dim (EPI 8)
+    int fcoord;           // coordinate along the fold dim (three-pass real transform)
     int nthreads;
 };
 
@@ -138,7 +139,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
 
     // tile index -> coordinates: exact multiply-shift divisions (b2_pp_prepare), 31-bit index
     static B2_D void decode(const PassParams &p, unsigned bid, long long &l0, int &nlines, long long &sbase,
-                            long long &dbase, int &i2base, int *scoord = nullptr) {
+                            long long &dbase, int &i2base, int *scoord = nullptr, int *fcoord = nullptr) {
         const int C = p.C;
         unsigned rest = b2_fastdiv(bid, p.dv_m[0], p.dv_s[0]);
         const unsigned t0 = bid - rest * (unsigned)p.tiles0;
@@ -155,6 +156,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
             dbase += (long long)cc * p.ld[d];
             if (d == p.epi_dim) i2base = (int)cc;
             if (EPI == 8 && scoord && d == p.scat_dim) *scoord = (int)cc;
+            if (MODE == MODE_ROW2COL && fcoord && d == p.fold_dim) *fcoord = (int)cc;
         }
     }
 
@@ -429,8 +431,9 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
 
     // second pass of the two-pass real transform: output index kk of the length-n spectrum goes to
     // kk when kk <= n/2, else its conjugate goes to n - kk; rows k1 = 0 and n1/2 only keep the former
-    static B2_D bool fold_target(const PassParams &p, long long k1, long long k2, long long &idx, bool &conj) {
-        const long long kk = k1 + (long long)p.fold_n1 * k2;
+    static B2_D bool fold_target(const PassParams &p, long long k1, long long k2, int fc, long long &idx, bool &conj) {
+        const long long kk = p.fold_dim > 0 ? k1 + (long long)p.fold_cmul * fc + p.fold_pmul * k2
+                                            : k1 + (long long)p.fold_n1 * k2;
         if (2 * kk <= p.fold_n) {
             idx = kk;
             conj = false;
@@ -524,7 +527,8 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
 #endif
         const int C = p.C;
         x.scoord = 0;
-        decode(p, (unsigned)bid, x.l0, x.nlines, x.sbase, x.dbase, x.i2base, &x.scoord);
+        x.fcoord = 0;
+        decode(p, (unsigned)bid, x.l0, x.nlines, x.sbase, x.dbase, x.i2base, &x.scoord, &x.fcoord);
         const cpx_t *csrc = reinterpret_cast<const cpx_t *>(src);
         cpx_t *cdst = reinterpret_cast<cpx_t *>(dst);
 
@@ -690,7 +694,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                             for (int q = 0; q < H; ++q) {
                                 long long idx;
                                 bool cj;
-                                if (fold_target(p, x.l0 + c, k0 + (h * H + q) * T, idx, cj))
+                                if (fold_target(p, x.l0 + c, k0 + (h * H + q) * T, x.fcoord, idx, cj))
                                     fb[idx * lstep] = cj ? cconj(a[q]) : a[q];
                             }
                         } else {
@@ -709,7 +713,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                         if (p.fold_n > 0) {
                             long long fi;
                             bool cj;
-                            if (fold_target(p, x.l0 + c, k, fi, cj)) cdst[x.dbase / 2 + fi * lstep] = cj ? cconj(a) : a;
+                            if (fold_target(p, x.l0 + c, k, x.fcoord, fi, cj)) cdst[x.dbase / 2 + fi * lstep] = cj ? cconj(a) : a;
                         } else
                             cdst[base + (long long)c * lstep + (long long)k * ds] = a;
                     }

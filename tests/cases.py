@@ -50,7 +50,8 @@ C2C_BIG = [(8192,), (16384,), (3 * 2 ** 13,), (2 ** 17,), (64, 64, 64), (4, 2 **
 C2C_PIPE = [(512, 80), (1024, 36), (3, 512, 24), (2048, 20), (2, 1024, 8), (2 ** 19,)]
 R2C_SHAPES = [(2,), (4,), (6,), (7,), (9,), (16,), (30,), (64,), (1024,), (6, 8), (5, 9), (4, 4, 6),
               (3, 5, 7)]
-R2C_BIG = [(4096,), (2 ** 15,), (2 ** 17,), (3, 2 ** 14), (32, 32, 32)]
+R2C_BIG = [(4096,), (2 ** 15,), (2 ** 17,), (3, 2 ** 14), (32, 32, 32),
+           (2 ** 19,), (2, 2 ** 20)]
 # lengths with a prime factor > 13 (Bluestein path), alone and inside multi-dimensional transforms
 C2C_PRIME = [(17,), (19,), (97,), (34,), (1009,), (4099,), (2 * 8191,), (3, 23), (29, 8), (5, 31, 6), (127, 127)]
 R2C_PRIME = [(17,), (34,), (97,), (1009,), (2018,), (4, 46), (3, 5, 38), (37, 6), (10007,)]

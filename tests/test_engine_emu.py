@@ -28,7 +28,7 @@ def test_r2c_c2r(lib, shape):
     cases.check_r2c_c2r(lib, shape)
 
 
-@pytest.mark.parametrize("shape", [(10,), (16,), (3, 10), (4, 6, 8), (7,), (2 ** 15,)],
+@pytest.mark.parametrize("shape", [(10,), (16,), (3, 10), (4, 6, 8), (7,), (2 ** 15,), (2 ** 19,)],
                          ids=lambda s: "x".join(map(str, s)))
 def test_r2c_inplace(lib, shape):
     cases.check_r2c_inplace(lib, shape)
@@ -117,6 +117,20 @@ def test_r2r_kinds(lib, r2r_golden):
 
 def test_threads_share_a_plan_and_the_planner(lib):
     cases.check_threads(lib)
+
+
+@pytest.mark.parametrize("shape", [(2 ** 19,), (2, 2 ** 20), (3, 2 ** 19)], ids=lambda s: "x".join(map(str, s)))
+def test_three_pass_real_transform(lib, shape, monkeypatch):
+    """pair-split column pass, twiddled column pass inside every row, folded row pass (default above the
+    two-pass limit, forced here at sizes the emulation can run)"""
+    monkeypatch.setenv("FFTW_B200_THREE_PASS_REAL", "1")
+    cases.check_r2c_c2r(lib, shape)
+    x = np.zeros(shape[-1], dtype=lib.real)
+    p = lib.plan_dft_r2c([shape[-1]], x, np.zeros(shape[-1] // 2 + 1, dtype=lib.cplx))
+    assert "hermitian fold" in lib.sprint_plan(p) and lib.sprint_plan(p).count("  pass ") == 3
+    lib.destroy_plan(p)
+    if len(shape) == 1:
+        cases.check_r2c_inplace(lib, shape)
 
 
 def test_chained_launch_opt_in(lib):

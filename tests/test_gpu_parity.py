@@ -53,7 +53,7 @@ def test_r2c_c2r(lib, shape):
     cases.check_r2c_c2r(lib, shape)
 
 
-@pytest.mark.parametrize("shape", [(10,), (16,), (3, 10), (4, 6, 8), (7,), (2 ** 15,)],
+@pytest.mark.parametrize("shape", [(10,), (16,), (3, 10), (4, 6, 8), (7,), (2 ** 15,), (2 ** 19,)],
                          ids=lambda s: "x".join(map(str, s)))
 def test_r2c_inplace(lib, shape):
     cases.check_r2c_inplace(lib, shape)
