@@ -137,6 +137,40 @@ def test_device_pointers_batched_4096(lib):
     lib.destroy_plan(p)
 
 
+def test_full_size_config2_4096x65536_fp32(lib):
+    """BASELINE.json configs[1] at its full size (2^28 points, 2 GiB in + 2 GiB out): 64 sampled transforms
+    against the oracle, Parseval over the whole batch, backward(forward(x)) = N x."""
+    import torch
+    if not lib.single:
+        pytest.skip("config 2 is single precision")
+    n, howmany = 4096, 65536
+    g = torch.Generator(device="cuda").manual_seed(2)
+    x = torch.view_as_complex(torch.rand((howmany, n, 2), device="cuda", dtype=torch.float32, generator=g) - 0.5)
+    y = torch.empty_like(x)
+    p = lib.plan_many_dft([n], howmany, x, None, 1, n, y, None, 1, n, capi.FFTW_FORWARD)
+    assert p
+    lib.execute(p)
+    torch.cuda.synchronize()
+    rows = np.random.default_rng(0).choice(howmany, 64, replace=False)
+    rows.sort()
+    idx = torch.from_numpy(rows).cuda()
+    from oracle import pyoracle as orc
+    ref = orc.dft_batched(x[idx].cpu().numpy(), -1)
+    assert cases.rel_l2(y[idx].cpu().numpy(), ref) < cases.tol(lib, n)
+    ex = float((x.real.double() ** 2 + x.imag.double() ** 2).sum())
+    ey = float((y.real.double() ** 2 + y.imag.double() ** 2).sum())
+    assert abs(ey / (n * ex) - 1) < 1e-5, "Parseval"
+    pb = lib.plan_many_dft([n], howmany, y, None, 1, n, y, None, 1, n, capi.FFTW_BACKWARD)
+    assert pb
+    lib.execute(pb)
+    torch.cuda.synchronize()
+    y /= n
+    num = float(((y - x).real.double() ** 2 + (y - x).imag.double() ** 2).sum())
+    assert (num / ex) ** 0.5 < cases.tol(lib, n), "round trip"
+    lib.destroy_plan(p)
+    lib.destroy_plan(pb)
+
+
 def test_device_3d_in_place_and_out_of_place(lib):
     import torch
     rng = np.random.default_rng(12)
