@@ -15,24 +15,12 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-SHAPE1 = {}
-
-
-@pytest.mark.parametrize("prec", ["fp32", "fp64"])
-@pytest.mark.parametrize("shape", [(64, 48, 32), (20, 64, 24), (6, 1024, 40)], ids=lambda s: "x".join(map(str, s)))
-def test_single_rank_fused_and_unfused(prec, shape):
-    """n1 = 64 / 1024 take the scattered store into this rank's own receive buffer; 48 the copy"""
-    SHAPE1[True] = SHAPE1[False] = shape
-    try:
-        for tr in (True, False):
-            test_single_rank_device_arrays(prec, tr)
-    finally:
-        SHAPE1.clear()
-
-
 @pytest.mark.parametrize("prec", ["fp32", "fp64"])
 @pytest.mark.parametrize("transposed", [True, False])
-def test_single_rank_device_arrays(prec, transposed):
+@pytest.mark.parametrize("shape", [(64, 48, 32), (20, 64, 24), (6, 1024, 40)], ids=lambda s: "x".join(map(str, s)))
+def test_single_rank_device_arrays(prec, transposed, shape):
+    """n1 = 64 / 1024: the n1 pass scatters straight into this rank's own receive buffer (fused exchange);
+    n1 = 48: staged copy"""
     import torch
     lib = capi.FFTW3Lib(build.lib_path(prec), prec == "fp32")
     L = lib.lib
@@ -40,7 +28,6 @@ def test_single_rank_device_arrays(prec, transposed):
     L.fftw_mpi_plan_dft_3d.restype = C.c_void_p
     L.fftw_mpi_plan_dft_3d.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] * 3 + [C.c_int, C.c_uint]
     comm = L.fftw_mpi_comm_self()
-    shape = SHAPE1.get(transposed, (64, 48, 32))
     rng = np.random.default_rng(3)
     xh = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
     x = torch.from_numpy(xh).cuda()
@@ -51,6 +38,38 @@ def test_single_rank_device_arrays(prec, transposed):
     lib.execute(plan)
     torch.cuda.synchronize()
     ref = orc.mpi_dft_3d_local(xh, 1, 0, transposed_out=transposed)
+    got = y.cpu().numpy().reshape(ref.shape)
+    tol = (1e-6 if lib.single else 1e-14) * np.log2(np.prod(shape))
+    assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < tol
+    lib.destroy_plan(plan)
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp64"])
+@pytest.mark.parametrize("flags", [1 << 29, (1 << 29) | (1 << 30)], ids=["tin", "tin_tout"])
+@pytest.mark.parametrize("shape,howmany", [((12, 10, 8), 1), ((16, 64, 6), 3), ((64, 20, 5), 2)],
+                         ids=lambda v: "x".join(map(str, v)) if isinstance(v, tuple) else str(v))
+def test_single_rank_transposed_in_and_howmany(prec, flags, shape, howmany):
+    """FFTW_MPI_TRANSPOSED_IN and interleaved howmany > 1 through fftw_mpi_plan_many_dft + fftw_execute"""
+    import torch
+    lib = capi.FFTW3Lib(build.lib_path(prec), prec == "fp32")
+    L = lib.lib
+    L.fftw_mpi_comm_self.restype = C.c_void_p
+    L.fftw_mpi_plan_many_dft.restype = C.c_void_p
+    L.fftw_mpi_plan_many_dft.argtypes = [C.c_int, C.POINTER(C.c_ssize_t), C.c_ssize_t, C.c_ssize_t, C.c_ssize_t,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint]
+    comm = L.fftw_mpi_comm_self()
+    n0, n1, n2 = shape
+    rng = np.random.default_rng(13)
+    xh = ((rng.random(shape + (howmany,)) - 0.5) + 1j * (rng.random(shape + (howmany,)) - 0.5)).astype(lib.cplx)
+    Y = np.stack([orc.dft(np.ascontiguousarray(xh[..., h]), -1) for h in range(howmany)], axis=-1)
+    x = torch.from_numpy(np.ascontiguousarray(xh.transpose(1, 0, 2, 3))).cuda()   # [n1][n0][n2][howmany]
+    y = torch.zeros(xh.size, dtype=x.dtype, device="cuda")
+    nn = (C.c_ssize_t * 3)(*shape)
+    plan = L.fftw_mpi_plan_many_dft(3, nn, howmany, 0, 0, x.data_ptr(), y.data_ptr(), comm, -1, capi.FFTW_ESTIMATE | flags)
+    assert plan
+    lib.execute(plan)
+    torch.cuda.synchronize()
+    ref = Y.transpose(1, 0, 2, 3) if flags & (1 << 30) else Y
     got = y.cpu().numpy().reshape(ref.shape)
     tol = (1e-6 if lib.single else 1e-14) * np.log2(np.prod(shape))
     assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < tol
