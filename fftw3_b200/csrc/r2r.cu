@@ -7,8 +7,9 @@
 // reference's manual defines the kinds with (fftw/doc/reference.texi "1d Real-even DFTs (DCTs)",
 // "1d Real-odd DFTs (DSTs)"), one dimension at a time on a dense work array:
 //
-//   embed   x (n reals) -> y (N reals): the even / odd extension of the kind, zero-stuffed where the
-//           kind samples at half-integers (N = n, 2(n-1), 2(n+1), 4n or 8n)
+//   embed   x (n reals) -> y (N reals): the even / odd extension of the kind (N = n, 2(n-1), 2(n+1));
+//           types II / III (x10, x01) use the length-2n extension and a quarter-sample twiddle
+//           exp(-+ i pi k / 2n) after the r2c (II) or before the c2r (III); type IV the 8n zero-stuffed one
 //   r2c_N   batched over all lines of the array                    [the hot kernels]
 //   extract X[k] = Re or -Im of F at the kind's index map
 //
@@ -16,6 +17,8 @@
 // the r2c path accepts; the 4n / 8n extensions cost bandwidth, which is acceptable for a family that
 // SURVEY.md section 8(f) ranks last -- a dedicated n-point pre/post-twiddle kernel is the obvious
 // follow-up where a kind matters.
+#include <math.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -33,7 +36,7 @@ static long long r2r_ext_len(int kind, long long n) {
     case K_R2HC: case K_HC2R: case K_DHT: return n;
     case K_REDFT00: return 2 * (n - 1);
     case K_RODFT00: return 2 * (n + 1);
-    case K_REDFT10: case K_REDFT01: case K_RODFT10: case K_RODFT01: return 4 * n;
+    case K_REDFT10: case K_REDFT01: case K_RODFT10: case K_RODFT01: return 2 * n;  // + a quarter-sample twiddle
     case K_REDFT11: case K_RODFT11: return 8 * n;
     }
     return -1;
@@ -70,13 +73,7 @@ B2_HD real_t b2_r2r_embed(const R2RLineParams &p, const real_t *x, long long q) 
     switch (p.kind) {
     case K_R2HC: case K_DHT: return x[q * sd];
     case K_REDFT00: return x[(q <= N / 2 ? q : N - q) * sd];
-    case K_REDFT10:
-        if (!(q & 1)) return 0;
-        return x[(q < 2 * n ? (q - 1) / 2 : (4 * n - q - 1) / 2) * sd];
-    case K_REDFT01:
-        if (q < n) return x[q * sd];
-        if (q > 3 * n) return x[(4 * n - q) * sd];
-        return 0;
+    case K_REDFT10: return q < n ? x[q * sd] : x[(2 * n - 1 - q) * sd];
     case K_REDFT11:
         if (!(q & 1)) return 0;
         if (q < 2 * n) return x[((q - 1) / 2) * sd];
@@ -85,13 +82,7 @@ B2_HD real_t b2_r2r_embed(const R2RLineParams &p, const real_t *x, long long q) 
     case K_RODFT00:
         if (q == 0 || q == n + 1) return 0;
         return q <= n ? x[(q - 1) * sd] : -x[(N - q - 1) * sd];
-    case K_RODFT10:
-        if (!(q & 1)) return 0;
-        return q < 2 * n ? x[((q - 1) / 2) * sd] : -x[((4 * n - q - 1) / 2) * sd];
-    case K_RODFT01:
-        if (q >= 1 && q <= n) return (q == n ? (real_t)0.5 : (real_t)1) * x[(q - 1) * sd];
-        if (q >= 3 * n) return -(q == 3 * n ? (real_t)0.5 : (real_t)1) * x[(4 * n - q - 1) * sd];
-        return 0;
+    case K_RODFT10: return q < n ? x[q * sd] : -x[(2 * n - 1 - q) * sd];
     case K_RODFT11:
         if (!(q & 1)) return 0;
         if (q < 2 * n) return x[((q - 1) / 2) * sd];
@@ -106,18 +97,42 @@ B2_HD real_t b2_r2r_extract(const R2RLineParams &p, const cpx_t *F, long long k)
     switch (p.kind) {
     case K_R2HC: return 2 * k <= n ? F[k].x : F[n - k].y;
     case K_DHT: return 2 * k <= n ? F[k].x - F[k].y : F[n - k].x + F[n - k].y;
-    case K_REDFT00: case K_REDFT10: return F[k].x;
-    case K_REDFT01: case K_REDFT11: return F[2 * k + 1].x;
-    case K_RODFT00: case K_RODFT10: return -F[k + 1].y;
-    case K_RODFT01: case K_RODFT11: return -F[2 * k + 1].y;
+    case K_REDFT00: return F[k].x;
+    case K_REDFT11: return F[2 * k + 1].x;
+    case K_RODFT00: return -F[k + 1].y;
+    case K_RODFT11: return -F[2 * k + 1].y;
+    case K_REDFT10: {  // F_k = exp(i pi k / 2n) X_k
+        const double a = 3.14159265358979323846 * (double)k / (double)(2 * n);
+        return (real_t)((double)F[k].x * cos(a) + (double)F[k].y * sin(a));
+    }
+    case K_RODFT10: {  // F_m = -i exp(i pi m / 2n) X_k, m = k + 1
+        const double a = 3.14159265358979323846 * (double)(k + 1) / (double)(2 * n);
+        return (real_t)((double)F[k + 1].x * sin(a) - (double)F[k + 1].y * cos(a));
+    }
     }
     return 0;
 }
-// HC2R: Hermitian half F[k], k <= n/2, from the halfcomplex line h
+B2_HD bool b2_r2r_is_c2r(int kind) { return kind == K_HC2R || kind == K_REDFT01 || kind == K_RODFT01; }
+// the kinds computed by a c2r: Hermitian half F[k], k <= N/2, built from the line h
+//   HC2R     the halfcomplex line itself
+//   REDFT01  F_j = x_j exp(i pi j / 2n), F_n = 0:          c2r_2n(F)[k] = x_0 + 2 sum x_j cos(pi j (k+1/2) / n)
+//   RODFT01  F_j = -i x_(j-1) exp(i pi j / 2n), F_0 = 0, F_n = x_(n-1)
 B2_HD cpx_t b2_r2r_hc(const R2RLineParams &p, const real_t *h, long long k) {
     const long long n = p.n, sd = p.sd;
-    if (k == 0 || 2 * k == n) return cpx_t{h[k * sd], 0};
-    return cpx_t{h[k * sd], h[(n - k) * sd]};
+    if (p.kind == K_HC2R) {
+        if (k == 0 || 2 * k == n) return cpx_t{h[k * sd], 0};
+        return cpx_t{h[k * sd], h[(n - k) * sd]};
+    }
+    const double a = 3.14159265358979323846 * (double)k / (double)(2 * n);
+    if (p.kind == K_REDFT01) {
+        if (k == n) return cpx_t{0, 0};
+        const double v = (double)h[k * sd];
+        return cpx_t{(real_t)(v * cos(a)), (real_t)(v * sin(a))};
+    }
+    if (k == 0) return cpx_t{0, 0};
+    const double v = (double)h[(k - 1) * sd];
+    if (k == n) return cpx_t{(real_t)v, 0};
+    return cpx_t{(real_t)(v * sin(a)), (real_t)(-v * cos(a))};  // -i v exp(i a)
 }
 
 #if B2_CUDA
@@ -135,8 +150,8 @@ __global__ void __launch_bounds__(256) b2_r2r_copy_kernel(const R2RCopyParams p,
 }
 __global__ void __launch_bounds__(256) b2_r2r_embed_kernel(const R2RLineParams p, const real_t *B2_RESTRICT D,
                                                            real_t *B2_RESTRICT W1, cpx_t *B2_RESTRICT W2) {
-    if (p.kind == K_HC2R) {
-        const long long hc = p.n / 2 + 1;
+    if (b2_r2r_is_c2r(p.kind)) {
+        const long long hc = p.N / 2 + 1;
         B2_GRID_LOOP(i, p.lines * hc) {
             const long long l = i / hc, k = i - l * hc;
             W2[i] = b2_r2r_hc(p, D + b2_r2r_line_base(p, l), k);
@@ -154,7 +169,7 @@ __global__ void __launch_bounds__(256) b2_r2r_extract_kernel(const R2RLineParams
         // consecutive threads walk the lines (the dense dim), not the points of one line
         const long long k = i / p.lines, l = i - k * p.lines;
         real_t *x = D + b2_r2r_line_base(p, l);
-        x[k * p.sd] = p.kind == K_HC2R ? W1[l * p.n + k] : b2_r2r_extract(p, W2 + l * (p.N / 2 + 1), k);
+        x[k * p.sd] = b2_r2r_is_c2r(p.kind) ? W1[l * p.N + k] : b2_r2r_extract(p, W2 + l * (p.N / 2 + 1), k);
     }
 }
 #endif
@@ -239,12 +254,12 @@ extern "C" b2fft_r2r *b2fft_r2r_plan_create(int rank, const b2fft_dim *dims, int
         if (dims[i].n == 1 && kinds[i] <= K_DHT) continue;  // length-1 R2HC / HC2R / DHT: the identity
         b2fft_geom g;
         memset(&g, 0, sizeof g);
-        g.kind = kinds[i] == K_HC2R ? B2FFT_C2R : B2FFT_R2C;
-        g.sign = kinds[i] == K_HC2R ? +1 : -1;
+        g.kind = b2_r2r_is_c2r(kinds[i]) ? B2FFT_C2R : B2FFT_R2C;
+        g.sign = b2_r2r_is_c2r(kinds[i]) ? +1 : -1;
         g.rank = 1;
         g.vrank = 1;
         const long long hc = d.lp.N / 2 + 1;
-        if (kinds[i] == K_HC2R) {
+        if (b2_r2r_is_c2r(kinds[i])) {
             g.dims[0] = b2fft_dim{(ptrdiff_t)d.lp.N, 1, 1};
             g.vdims[0] = b2fft_dim{(ptrdiff_t)d.lp.lines, (ptrdiff_t)hc, (ptrdiff_t)d.lp.N};
         } else {
@@ -309,17 +324,17 @@ extern "C" int b2fft_r2r_execute(b2fft_r2r *r, void *in_, void *out_) {
         const R2RLineParams &p = d.lp;
         const long long hc = p.N / 2 + 1;
 #if B2_CUDA
-        b2_r2r_embed_kernel<<<r2r_grid(p.lines * (p.kind == K_HC2R ? hc : p.N)), 256>>>(p, r->D, r->W1, r->W2);
+        b2_r2r_embed_kernel<<<r2r_grid(p.lines * (b2_r2r_is_c2r(p.kind) ? hc : p.N)), 256>>>(p, r->D, r->W1, r->W2);
         ++launch_counter();
         B2_CK(cudaGetLastError());
 #else
-        if (p.kind == K_HC2R) {
+        if (b2_r2r_is_c2r(p.kind)) {
             for (long long i = 0; i < p.lines * hc; ++i) r->W2[i] = b2_r2r_hc(p, r->D + b2_r2r_line_base(p, i / hc), i % hc);
         } else {
             for (long long i = 0; i < p.lines * p.N; ++i) r->W1[i] = b2_r2r_embed(p, r->D + b2_r2r_line_base(p, i / p.N), i % p.N);
         }
 #endif
-        int rc = p.kind == K_HC2R ? b2fft_execute_async(d.plan, r->W2, r->W1, nullptr)
+        int rc = b2_r2r_is_c2r(p.kind) ? b2fft_execute_async(d.plan, r->W2, r->W1, nullptr)
                                   : b2fft_execute_async(d.plan, r->W1, r->W2, nullptr);
         if (rc) return rc;
 #if B2_CUDA
@@ -330,7 +345,7 @@ extern "C" int b2fft_r2r_execute(b2fft_r2r *r, void *in_, void *out_) {
         for (long long i = 0; i < p.lines * p.n; ++i) {
             const long long k = i / p.lines, l = i % p.lines;
             real_t *x = r->D + b2_r2r_line_base(p, l);
-            x[k * p.sd] = p.kind == K_HC2R ? r->W1[l * p.n + k] : b2_r2r_extract(p, r->W2 + l * hc, k);
+            x[k * p.sd] = b2_r2r_is_c2r(p.kind) ? r->W1[l * p.N + k] : b2_r2r_extract(p, r->W2 + l * hc, k);
         }
 #endif
     }
