@@ -179,6 +179,7 @@ struct R2RDim {
     b2fft_plan *plan = nullptr;
 };
 struct b2fft_r2r_s {
+    std::mutex exec_mutex;  // executes of one plan share its work arrays: serialised
     R2RCopyParams in_cp, out_cp;
     long long in_extent = 0, out_extent = 0, total = 0;
     std::vector<R2RDim> dims;
@@ -295,6 +296,7 @@ extern "C" b2fft_r2r *b2fft_r2r_plan_create(int rank, const b2fft_dim *dims, int
 
 extern "C" int b2fft_r2r_execute(b2fft_r2r *r, void *in_, void *out_) {
     if (!r) return -1;
+    std::lock_guard<std::mutex> guard(r->exec_mutex);
     if (ensure_device() != 0) return -1;
     if (r->total <= 0) return 0;
     real_t *in = (real_t *)in_, *out = (real_t *)out_;

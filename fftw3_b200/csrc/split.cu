@@ -55,6 +55,7 @@ __global__ void __launch_bounds__(256) b2_split_scatter_kernel(const SplitCopyPa
 #endif
 
 struct b2fft_split_s {
+    std::mutex exec_mutex;  // executes of one plan share its work arrays: serialised
     int kind = B2FFT_C2C;
     SplitCopyParams in_cp, out_cp;  // complex-side loop nests (c2c: both; r2c: out; c2r: in)
     long long in_extent = 0, out_extent = 0;  // reals spanned by one split array
@@ -208,6 +209,7 @@ static int split_unstage(real_t *dev, real_t *user, long long extent) {
 // c2c: (ri, ii) -> (ro, io).  r2c: `ri` is the real input, ii unused.  c2r: `ro` is the real output, io unused.
 extern "C" int b2fft_split_execute(b2fft_split *s, void *ri_, void *ii_, void *ro_, void *io_) {
     if (!s) return -1;
+    std::lock_guard<std::mutex> guard(s->exec_mutex);
     if (ensure_device() != 0) return -1;
     real_t *ri = (real_t *)ri_, *ii = (real_t *)ii_, *ro = (real_t *)ro_, *io = (real_t *)io_;
     int rc = 0;
