@@ -17,8 +17,14 @@ using namespace b2;
 
 // ------------------------------------------------------------------------- launching
 static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream_t stream) {
-    // host loops over the line dims that did not fit in the kernel descriptor
-    std::vector<long long> idx(s.outer.size(), 0);
+    // host loops over the line dims that did not fit in the kernel descriptor (almost never any)
+    long long idx_store[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    std::vector<long long> idx_heap;
+    long long *idx = idx_store;
+    if (s.outer.size() > 8) {
+        idx_heap.assign(s.outer.size(), 0);
+        idx = idx_heap.data();
+    }
     for (;;) {
         long long so = 0, dof = 0;
         for (size_t i = 0; i < s.outer.size(); ++i) {
@@ -70,11 +76,11 @@ static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream
 #endif
         }
         size_t i = 0;
-        for (; i < idx.size(); ++i) {
+        for (; i < s.outer.size(); ++i) {
             if (++idx[i] < s.outer[i].n) break;
             idx[i] = 0;
         }
-        if (i == idx.size()) break;
+        if (i == s.outer.size()) break;
     }
     return 0;
 }
@@ -140,7 +146,8 @@ static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
 }
 
 // ------------------------------------------------------------------------- scattered last step
-int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long long plane_stride, const long long *pstride) {
+int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long long plane_stride, const long long *pstride,
+                           int self) {
     if (!p || p->pc.steps.empty() || nowners < 1 || nowners > B2_MAXSCAT || blk < 1) return -1;
     if (p->chains && !p->chains->empty()) return -1;
     const StepPlan &last = p->pc.steps.back();
@@ -160,6 +167,8 @@ int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long lon
     }
     if (q.scat_dim >= 0) q.ld[q.scat_dim] = 0;  // the plane offset is per owner
     q.scat_n = nowners;
+    q.scat_self1 = self >= 0 ? self + 1 : 0;
+    q.scat_lplane = plane_stride;
     q.scat_blk = (int)blk;
     b2_fastdiv_make((unsigned long long)blk, q.scat_m, q.scat_s);
     for (int o = 0; o < nowners; ++o) q.scat_pstride[o] = pstride[o];

@@ -72,6 +72,10 @@ struct PassParams {
     int scat_n, scat_blk, scat_dim;
     unsigned scat_m, scat_s;                  // exact division by scat_blk
     long long scat_coord0;
+    // hybrid form (scat_self1 = own rank + 1; 0: every owner is scattered): only the rows this rank owns
+    // go to scat_base[self]; the others stay in place at dst + cc * scat_lplane + k * d_axis for the DMA
+    int scat_self1;
+    long long scat_lplane;
     real_t *scat_base[B2_MAXSCAT];
     long long scat_pstride[B2_MAXSCAT];
 };

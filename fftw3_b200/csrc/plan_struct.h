@@ -46,7 +46,9 @@ struct b2fft_plan_s {
 // axis) into one that stores row k into the receive buffer of its owner k / blk.  plane_stride =
 // dst stride (reals) of the line dim that numbers the planes; pstride[o] = owner o's plane stride.
 // Returns 0 when the step qualifies (tile kernel, column mode, no other epilogue).
-int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long long plane_stride, const long long *pstride);
+// self >= 0: hybrid form, only owner `self` is scattered, the other rows stay in place.
+int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long long plane_stride, const long long *pstride,
+                           int self = -1);
 int b2_plan_execute_scatter(b2fft_plan_s *p, void *in, void *out, real_t *const *bases, long long coord0,
                             b2::stream_t stream);
 void b2_slab_destroy(b2fft_plan_s *p);

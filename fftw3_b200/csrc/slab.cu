@@ -221,6 +221,9 @@ struct SlabPlan {
     // fused exchange: the n1-axis pass of stage 1 stores every output row straight into its owner's
     // receive buffer (tile kernel EPI 8) -- no send-side DMA, no second trip through HBM
     bool fused = false;
+    // hybrid: the n1 pass stores the rows this rank owns straight into its own receive buffer and leaves
+    // the others in place for the DMA, which then skips the local 1/P of the exchange
+    bool hybrid = false;
 #if B2_CUDA
     // DMA exchange: one stream per peer so that the copies to different peers run on different copy engines
     std::vector<cudaStream_t> sx;
@@ -232,19 +235,26 @@ struct SlabPlan {
 // switch the stage-1 plans to the scattered store; all-or-nothing
 static void slab_enable_fused(SlabPlan &s) {
     s.fused = false;
+    s.hybrid = false;
     if (getenv("B2FFT_SLAB_NO_FUSED") || (int)s.peerR.size() != s.P || s.P > B2_MAXSCAT) return;
     // Measured on 2 B200 (profiles/r1_slab_fused_2gpu.md): the scattered store wins when a tile row is a
     // full 128-byte segment (n1 <= 1024: 1024^3 7.09 ms against 8.12 ms with the DMA exchange) and loses
     // when the 2048-point kernel's 8-line tiles turn the NVLink writes into 64-byte packets (2048^3:
     // 72.6 against 63.8 ms).  B2FFT_SLAB_FUSED=1 forces it.
     const long long col_limit = (long long)(sizeof(real_t) == 4 ? 1024 : 1024);
-    if (s.P > 1 && s.n1 > col_limit && !getenv("B2FFT_SLAB_FUSED")) return;
+    // Above that limit (and with B2FFT_SLAB_HYBRID=1 anywhere): hybrid -- only the rows this rank owns are
+    // scattered (local stores), the copy engines move the P-1 remote blocks and no longer the local one.
+    bool hybrid = s.P > 1 && ((s.n1 > col_limit && !getenv("B2FFT_SLAB_FUSED")) || getenv("B2FFT_SLAB_HYBRID"));
+    if (hybrid && getenv("B2FFT_SLAB_NO_HYBRID")) return;
     std::vector<long long> ps(s.P);
     for (int o = 0; o < s.P; ++o) ps[o] = (long long)blk_len(s.n1, s.b1, o) * s.n2 * 2;
     bool ok = true;
     for (b2fft_plan *p : {s.p1, s.p1_tail})
-        if (p) ok = ok && b2_plan_enable_scatter(p, s.P, (long long)s.b1, (long long)s.n1 * s.n2 * 2, ps.data()) == 0;
-    s.fused = ok && (s.p1 || s.p1_tail || s.ln0 == 0);
+        if (p) ok = ok && b2_plan_enable_scatter(p, s.P, (long long)s.b1, (long long)s.n1 * s.n2 * 2, ps.data(),
+                                                 hybrid ? s.pe : -1) == 0;
+    ok = ok && (s.p1 || s.p1_tail || s.ln0 == 0);
+    s.fused = ok && !hybrid;
+    s.hybrid = ok && hybrid;
 }
 
 #if B2_CUDA
@@ -408,6 +418,7 @@ static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
              s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
              s->nchunks, s->chunk,
              s->fused ? "fused into the n1 pass: rows stored straight into their owner's receive buffer (peer memory over NVLink)"
+             : s->hybrid ? "local block stored by the n1 pass, remote blocks by strided DMA into peer memory (CUDA IPC over NVLink), NCCL barrier"
              : s->P == 1 ? "local copy" : s->p2p ? "strided DMA into peer memory (CUDA IPC over NVLink), NCCL barrier"
                                                 : "ncclSend/ncclRecv per plane and peer",
              n0);
@@ -570,12 +581,17 @@ static int slab_exchange(SlabPlan &s, int chunk, cpx_t *sb, cpx_t *rb, bool reve
     NcclApi *a = nccl();
     const int dt = sizeof(real_t) == 4 ? 7 : 8;  // ncclFloat32 / ncclFloat64
     B2_NCCL(a->GroupStart());
-    for (const SlabMsg &m : (reverse ? recvs : sends))
+    const bool skip_self = s.hybrid && !reverse && sb == s.S;  // the n1 pass stored the local block itself
+    for (const SlabMsg &m : (reverse ? recvs : sends)) {
+        if (skip_self && m.peer == s.pe) continue;
         B2_NCCL(a->Send(reverse ? (const void *)(rb + m.roff) : (const void *)(sb + m.soff), (size_t)m.cnt * 2, dt,
                         m.peer, s.comm->nc, st));
-    for (const SlabMsg &m : (reverse ? sends : recvs))
+    }
+    for (const SlabMsg &m : (reverse ? sends : recvs)) {
+        if (skip_self && m.peer == s.pe) continue;
         B2_NCCL(a->Recv(reverse ? (void *)(sb + m.soff) : (void *)(rb + m.roff), (size_t)m.cnt * 2, dt, m.peer,
                         s.comm->nc, st));
+    }
     B2_NCCL(a->GroupEnd());
     return 0;
 #else
@@ -676,6 +692,7 @@ static int slab_exchange_p2p(SlabPlan &s, int chunk, bool reverse, cudaStream_t 
         if (after && d < std::max<int>(1, (int)s.sx.size())) B2_CK(cudaStreamWaitEvent(st, after, 0));
         if (!reverse) {
             // my planes [a,b) of this chunk -> peer p's receive buffer R_p[s0 + i0][*][*]
+            if (s.hybrid && p == s.pe && fwd_src == s.S) continue;  // the n1 pass stored the local block itself
             const ptrdiff_t ln1p = blk_len(s.n1, s.b1, p);
             const ptrdiff_t a = std::min<ptrdiff_t>(s.ln0, chunk * s.chunk), b = std::min<ptrdiff_t>(s.ln0, a + s.chunk);
             if (ln1p <= 0 || b <= a) continue;
@@ -711,7 +728,7 @@ static int slab_stage1_chunk(SlabPlan &s, int k, cpx_t *in, stream_t st) {
     b2fft_plan *p = (s.p1 && cnt == std::min(s.chunk, s.ln0)) ? s.p1 : s.p1_tail;
     if (!p) return -6;
     const size_t off = (size_t)a * s.n1 * s.n2;
-    if (s.fused) {
+    if (s.fused || s.hybrid) {
         std::vector<real_t *> bases(s.P);
         for (int o = 0; o < s.P; ++o) bases[o] = (real_t *)s.peerR[o];
         return b2_plan_execute_scatter(p, in + off, s.S + off, bases.data(), (long long)(s.s0 + a), st);

@@ -40,7 +40,8 @@ struct TileInst {
         // strides of MiBs (a TLB miss per hint) -- so it is only switched on where it pays.
         const bool pays = (MODE == MODE_COL) ? (p.s_axis * (long long)sizeof(real_t) < (1ll << 20)) : (N <= 128);
         PassParams q = p;
-        q.pf_ahead = (pays || getenv("FFTW_B200_PF")) ? (unsigned)wave : 0u;
+        static const bool pf_forced = getenv("FFTW_B200_PF") != nullptr;  // read once: getenv per launch shows at 10 us steps
+        q.pf_ahead = (pays || pf_forced) ? (unsigned)wave : 0u;
         b2_tile_kernel<N, E, MODE, EPI, THREADS, MINB><<<(unsigned)nb, threads, smem, st>>>(q, src, dst, b0);
         return 0;
 #else

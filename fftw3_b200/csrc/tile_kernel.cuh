@@ -485,6 +485,8 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                 const long long r = (long long)(k - o * (unsigned)p.scat_blk);
                 cpx_t *po = reinterpret_cast<cpx_t *>(p.scat_base[o]) +
                             (plane * p.scat_pstride[o] + r * p.d_axis + loff) / 2;
+                if (p.scat_self1 > 0 && (int)o != p.scat_self1 - 1)
+                    po = cdst + ((long long)x.scoord * p.scat_lplane + (long long)k * p.d_axis + loff) / 2;
                 *po = v[q];
             }
         } else if (EPI == 7) {  // Bluestein, inverse FFT done: X[k] = conv[k] * chirp[k], k < n only

@@ -132,3 +132,17 @@ def test_two_ranks_over_nccl(shape):
            os.path.join(ROOT, "tests", "slab_nccl_worker.py"), *map(str, shape)]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     assert r.returncode == 0 and "SLAB_OK" in r.stdout, r.stdout[-3000:]
+
+
+def test_two_ranks_hybrid_exchange():
+    """the exchange taken above n1 = 1024 (local block stored by the n1 pass, remote blocks by DMA), forced
+    at a size the oracle can check"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(29900 + os.getpid() % 90),
+           os.path.join(ROOT, "tests", "slab_nccl_worker.py"), "24", "64", "32"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600,
+                       env=dict(os.environ, B2FFT_SLAB_HYBRID="1"))
+    assert r.returncode == 0 and "SLAB_OK" in r.stdout, r.stdout[-3000:]

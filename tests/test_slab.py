@@ -274,6 +274,58 @@ def test_many_interleaved_transforms(shape, howmany, P):
         L.b2fft_comm_destroy(r["comm"])
 
 
+@pytest.mark.parametrize("P", [2, 3, 8])
+@pytest.mark.parametrize("shape", [(12, 32, 6), (9, 64, 16)], ids=lambda s: "x".join(map(str, s)))
+def test_hybrid_exchange_stores_the_local_block_itself(shape, P, monkeypatch):
+    """hybrid exchange (default for n1 > 1024, forced here): the n1 pass writes the rows this rank owns
+    straight into its own receive buffer and leaves the rest in the send buffer; the test moves only the
+    REMOTE blocks, so a local block that the kernel did not place would stay zero."""
+    monkeypatch.setenv("B2FFT_SLAB_HYBRID", "1")
+    lib = load()
+    lib.lib.b2fft_slab_set_peer_recv.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_int]
+    n0, n1, n2 = shape
+    rng = np.random.default_rng(3 * P + n1)
+    x = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
+    ranks = []
+    for pe in range(P):
+        comm = lib.lib.b2fft_comm_detached(P, pe)
+        N, ln0, s0, ln1, s1 = local_sizes(lib, shape, comm)
+        xin = np.zeros(max(N, 1), dtype=lib.cplx)
+        xin[:ln0 * n1 * n2] = x[s0:s0 + ln0].ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = lib.lib.fftw_mpi_plan_dft_3d(n0, n1, n2, xin.ctypes.data, out.ctypes.data, comm, -1,
+                                            capi.FFTW_ESTIMATE | TRANSPOSED_OUT)
+        assert plan
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        R[:] = 0
+        ranks.append(dict(comm=comm, pe=pe, la=ln0, sa=s0, lb=ln1, sb=s1, xin=xin, out=out, plan=plan, bp=bp, S=S, R=R))
+    recv = (C.c_void_p * P)(*[r["R"].ctypes.data for r in ranks])
+    for r in ranks:
+        assert lib.lib.b2fft_slab_set_peer_recv(r["bp"], recv, P) == 0  # not the fully fused form ...
+        assert "local block stored by the n1 pass" in lib.sprint_plan(r["plan"])  # ... but the hybrid one
+    for r in ranks:
+        assert lib.lib.b2fft_slab_stage(r["bp"], 0, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    for src in ranks:  # remote blocks only
+        if src["la"] == 0:
+            continue
+        Sv = src["S"][:src["la"] * n1 * n2].reshape(src["la"], n1, n2)
+        for dst in ranks:
+            if dst["lb"] == 0 or dst["pe"] == src["pe"]:
+                continue
+            Rv = dst["R"][:n0 * dst["lb"] * n2].reshape(n0, dst["lb"], n2)
+            Rv[src["sa"]:src["sa"] + src["la"]] = Sv[:, dst["sb"]:dst["sb"] + dst["lb"], :]
+    for pe, r in enumerate(ranks):
+        assert lib.lib.b2fft_slab_stage(r["bp"], 2, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+        ref = orc.mpi_dft_3d_local(x, P, pe, transposed_out=True)
+        got = r["out"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13, (pe, P)
+    for r in ranks:
+        lib.destroy_plan(r["plan"])
+        lib.lib.b2fft_comm_destroy(r["comm"])
+
+
 def _real_api(lib):
     L = lib.lib
     for nm in ("fftw_mpi_plan_dft_r2c_3d", "fftw_mpi_plan_dft_c2r_3d"):
