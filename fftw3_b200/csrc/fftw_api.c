@@ -540,7 +540,11 @@ void fftw_cleanup(void) {
     b2fft_cleanup();
     PLANNER_UNLOCK();
 }
-void fftw_forget_wisdom(void) { wis_n = 0; }
+void fftw_forget_wisdom(void) {
+    PLANNER_LOCK();
+    wis_n = 0;
+    PLANNER_UNLOCK();
+}
 void fftw_set_timelimit(double t) { (void)t; }
 
 /* The reference keeps these four in its threads library (fftw/threads/api.c:39-86).  A GPU
@@ -553,12 +557,14 @@ void fftw_make_planner_thread_safe(void) {}
 /* wisdom I/O: "(b200fft_wisdom-1 <hex signature> ...)" */
 static const char wis_head[] = "(b200fft_wisdom-1";
 char *fftw_export_wisdom_to_string(void) {
-    size_t cap = sizeof wis_head + (size_t)wis_n * 18 + 4, len;
+    size_t cap = sizeof wis_head + (size_t)wis_n * 18 + 32, len;
     char *s = (char *)malloc(cap);
     int i;
     if (!s) return 0;
+    PLANNER_LOCK();
     len = (size_t)sprintf(s, "%s", wis_head);
-    for (i = 0; i < wis_n; ++i) len += (size_t)sprintf(s + len, " %016llx", (unsigned long long)wis_key[i]);
+    for (i = 0; i < wis_n && len + 24 < cap; ++i) len += (size_t)sprintf(s + len, " %016llx", (unsigned long long)wis_key[i]);
+    PLANNER_UNLOCK();
     sprintf(s + len, ")\n");
     return s;
 }
@@ -595,7 +601,9 @@ int fftw_import_wisdom_from_string(const char *s) {
         if (!*c) return 0;
         k = strtoull(c, &end, 16);
         if (end == c) return 0;
+        PLANNER_LOCK();
         wis_add((uint64_t)k);
+        PLANNER_UNLOCK();
         c = end;
     }
 }
