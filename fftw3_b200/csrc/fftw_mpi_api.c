@@ -31,12 +31,13 @@ ptrdiff_t fftw_mpi_local_size_many_transposed(int rnk, const ptrdiff_t *n, ptrdi
                                               ptrdiff_t *local_0_start, ptrdiff_t *local_n1,
                                               ptrdiff_t *local_1_start) {
     int P;
-    if (rnk != 3 || !n || !comm || howmany < 1) return 0;
+    if ((rnk != 3 && rnk != 2) || !n || !comm || howmany < 1) return 0;
     P = b2fft_comm_size(comm);
     if (block0 != FFTW_MPI_DEFAULT_BLOCK && block0 != (n[0] + P - 1) / P) return 0;
     if (block1 != FFTW_MPI_DEFAULT_BLOCK && block1 != (n[1] + P - 1) / P) return 0;
-    return howmany * fftw_mpi_local_size_3d_transposed(n[0], n[1], n[2], comm, local_n0, local_0_start, local_n1,
-                                                       local_1_start);
+    /* rank 2 = rank 3 with a last dimension of one element (the slab algorithm never looks inside a row) */
+    return howmany * fftw_mpi_local_size_3d_transposed(n[0], n[1], rnk == 3 ? n[2] : 1, comm, local_n0, local_0_start,
+                                                       local_n1, local_1_start);
 }
 ptrdiff_t fftw_mpi_local_size_many(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block0, MPI_Comm comm,
                                    ptrdiff_t *local_n0, ptrdiff_t *local_0_start) {
@@ -50,7 +51,12 @@ fftw_plan fftw_mpi_plan_many_dft(int rnk, const ptrdiff_t *n, ptrdiff_t howmany,
     fftw_plan p;
     b2fft_plan *bp;
     int P;
-    if (rnk != 3 || !n || !comm) return 0; /* the slab path is 3-D */
+    ptrdiff_t n3[3];
+    if ((rnk != 3 && rnk != 2) || !n || !comm) return 0; /* the slab path: 3-D, and 2-D as n2 = 1 */
+    n3[0] = n[0];
+    n3[1] = n[1];
+    n3[2] = rnk == 3 ? n[2] : 1;
+    n = n3;
     P = b2fft_comm_size(comm);
     /* only the default ceil(n/P) blocks (FFTW_MPI_DEFAULT_BLOCK, or the same value spelled out) */
     if (block != FFTW_MPI_DEFAULT_BLOCK && block != (n[0] + P - 1) / P) return 0;
@@ -139,6 +145,24 @@ fftw_plan fftw_mpi_plan_dft_c2r_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFT
     n[1] = n1;
     n[2] = n2;
     return fftw_mpi_plan_dft_c2r(3, n, in, out, comm, flags);
+}
+
+/* 2-D forms (reference fftw/mpi/api.c:488-492, 631-636): [local_n0][n1] in, [local_n1][n0] transposed out */
+ptrdiff_t fftw_mpi_local_size_2d_transposed(ptrdiff_t n0, ptrdiff_t n1, MPI_Comm comm, ptrdiff_t *local_n0,
+                                            ptrdiff_t *local_0_start, ptrdiff_t *local_n1, ptrdiff_t *local_1_start) {
+    return fftw_mpi_local_size_3d_transposed(n0, n1, 1, comm, local_n0, local_0_start, local_n1, local_1_start);
+}
+ptrdiff_t fftw_mpi_local_size_2d(ptrdiff_t n0, ptrdiff_t n1, MPI_Comm comm, ptrdiff_t *local_n0,
+                                 ptrdiff_t *local_0_start) {
+    ptrdiff_t a, b;
+    return fftw_mpi_local_size_2d_transposed(n0, n1, comm, local_n0, local_0_start, &a, &b);
+}
+fftw_plan fftw_mpi_plan_dft_2d(ptrdiff_t n0, ptrdiff_t n1, FFTW_COMPLEX *in, FFTW_COMPLEX *out, MPI_Comm comm,
+                               int sign, unsigned flags) {
+    ptrdiff_t n[2];
+    n[0] = n0;
+    n[1] = n1;
+    return fftw_mpi_plan_many_dft(2, n, 1, FFTW_MPI_DEFAULT_BLOCK, FFTW_MPI_DEFAULT_BLOCK, in, out, comm, sign, flags);
 }
 
 void fftw_mpi_execute_dft(fftw_plan p, FFTW_COMPLEX *in, FFTW_COMPLEX *out) { fftw_execute_dft(p, in, out); }

@@ -49,6 +49,14 @@ FFTW_EXTERN ptrdiff_t fftw_mpi_local_size_many_transposed(int rnk, const ptrdiff
                                                           ptrdiff_t *local_n1, ptrdiff_t *local_1_start);
 FFTW_EXTERN ptrdiff_t fftw_mpi_local_size_many(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block0,
                                                MPI_Comm comm, ptrdiff_t *local_n0, ptrdiff_t *local_0_start);
+/* 2-D: [local_n0][n1] in, [local_n1][n0] with FFTW_MPI_TRANSPOSED_OUT (reference fftw/mpi/fftw3-mpi.h:113-128) */
+FFTW_EXTERN ptrdiff_t fftw_mpi_local_size_2d(ptrdiff_t n0, ptrdiff_t n1, MPI_Comm comm, ptrdiff_t *local_n0,
+                                             ptrdiff_t *local_0_start);
+FFTW_EXTERN ptrdiff_t fftw_mpi_local_size_2d_transposed(ptrdiff_t n0, ptrdiff_t n1, MPI_Comm comm,
+                                                        ptrdiff_t *local_n0, ptrdiff_t *local_0_start,
+                                                        ptrdiff_t *local_n1, ptrdiff_t *local_1_start);
+FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_2d(ptrdiff_t n0, ptrdiff_t n1, FFTW_COMPLEX *in, FFTW_COMPLEX *out,
+                                           MPI_Comm comm, int sign, unsigned flags);
 FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_COMPLEX *in,
                                            FFTW_COMPLEX *out, MPI_Comm comm, int sign, unsigned flags);
 FFTW_EXTERN fftw_plan fftw_mpi_plan_many_dft(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block,

@@ -326,6 +326,69 @@ def test_hybrid_exchange_stores_the_local_block_itself(shape, P, monkeypatch):
         lib.lib.b2fft_comm_destroy(r["comm"])
 
 
+@pytest.mark.parametrize("flags", [0, TRANSPOSED_OUT, TRANSPOSED_IN], ids=["natural", "tout", "tin"])
+@pytest.mark.parametrize("P", [1, 2, 3])
+@pytest.mark.parametrize("shape", [(8, 6), (10, 32), (64, 9)], ids=lambda s: "x".join(map(str, s)))
+def test_two_dimensional_slab(shape, P, flags):
+    """fftw_mpi_plan_dft_2d (fftw/mpi/api.c:631-636): the 3-D machinery with rows of one element"""
+    lib = load()
+    L = lib.lib
+    L.fftw_mpi_plan_dft_2d.restype = C.c_void_p
+    L.fftw_mpi_plan_dft_2d.argtypes = [C.c_ssize_t] * 2 + [C.c_void_p] * 3 + [C.c_int, C.c_uint]
+    L.fftw_mpi_local_size_2d_transposed.restype = C.c_ssize_t
+    L.fftw_mpi_local_size_2d_transposed.argtypes = [C.c_ssize_t] * 2 + [C.c_void_p] + [C.POINTER(C.c_ssize_t)] * 4
+    n0, n1 = shape
+    rng = np.random.default_rng(7 + P)
+    x = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
+    Y = orc.dft(x, -1)
+    tin, tout = bool(flags & TRANSPOSED_IN), bool(flags & TRANSPOSED_OUT)
+    ranks = []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        v = [C.c_ssize_t() for _ in range(4)]
+        N = L.fftw_mpi_local_size_2d_transposed(n0, n1, comm, *[C.byref(t) for t in v])
+        ln0, s0, ln1, s1 = (t.value for t in v)
+        assert (N, ln0, s0, ln1, s1) == orc.mpi_local_size_3d_transposed(n0, n1, 1, P, pe)
+        xin = np.zeros(max(N, 1), dtype=lib.cplx)
+        if tin:
+            xin[:ln1 * n0] = x.T[s1:s1 + ln1].ravel()
+        else:
+            xin[:ln0 * n1] = x[s0:s0 + ln0].ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = L.fftw_mpi_plan_dft_2d(n0, n1, xin.ctypes.data, out.ctypes.data, comm, -1, capi.FFTW_ESTIMATE | flags)
+        assert plan, "2-D slab plan is NULL"
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        # inside a TRANSPOSED_IN plan the two dims are exchanged
+        a = dict(la=ln1, sa=s1, lb=ln0, sb=s0) if tin else dict(la=ln0, sa=s0, lb=ln1, sb=s1)
+        ranks.append(dict(comm=comm, xin=xin, out=out, plan=plan, bp=bp, S=S, R=R, ln0=ln0, s0=s0, ln1=ln1, s1=s1, **a))
+    na, nb = (n1, n0) if tin else (n0, n1)
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 0, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    if "fused into" not in lib.sprint_plan(ranks[0]["plan"]):
+        _exchange(ranks, na, nb, 1)
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 2, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    plan_natural = (tin == tout)  # the plan's own output is natural: second exchange, back
+    if plan_natural:
+        for src in ranks:
+            if src["lb"] == 0:
+                continue
+            Rv = src["R"][:na * src["lb"]].reshape(na, src["lb"])
+            for dst in ranks:
+                if dst["la"] == 0:
+                    continue
+                Ov = dst["out"][:dst["la"] * nb].reshape(dst["la"], nb)
+                Ov[:, src["sb"]:src["sb"] + src["lb"]] = Rv[dst["sa"]:dst["sa"] + dst["la"]]
+    for r in ranks:
+        ref = Y.T[r["s1"]:r["s1"] + r["ln1"]] if tout else Y[r["s0"]:r["s0"] + r["ln0"]]
+        got = r["out"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+        lib.destroy_plan(r["plan"])
+        L.b2fft_comm_destroy(r["comm"])
+
+
 def _real_api(lib):
     L = lib.lib
     for nm in ("fftw_mpi_plan_dft_r2c_3d", "fftw_mpi_plan_dft_c2r_3d"):
