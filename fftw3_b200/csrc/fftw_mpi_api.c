@@ -33,11 +33,11 @@ ptrdiff_t fftw_mpi_local_size_many_transposed(int rnk, const ptrdiff_t *n, ptrdi
     int P;
     if ((rnk != 3 && rnk != 2) || !n || !comm || howmany < 1) return 0;
     P = b2fft_comm_size(comm);
-    if (block0 != FFTW_MPI_DEFAULT_BLOCK && block0 != (n[0] + P - 1) / P) return 0;
-    if (block1 != FFTW_MPI_DEFAULT_BLOCK && block1 != (n[1] + P - 1) / P) return 0;
+    if (block0 < 0 || block1 < 0) return 0;
     /* rank 2 = rank 3 with a last dimension of one element (the slab algorithm never looks inside a row) */
-    return howmany * fftw_mpi_local_size_3d_transposed(n[0], n[1], rnk == 3 ? n[2] : 1, comm, local_n0, local_0_start,
-                                                       local_n1, local_1_start);
+    return howmany * b2fft_slab_local_size_3d_blocks(n[0], n[1], rnk == 3 ? n[2] : 1, block0, block1, P,
+                                                     b2fft_comm_rank(comm), local_n0, local_0_start, local_n1,
+                                                     local_1_start);
 }
 ptrdiff_t fftw_mpi_local_size_many(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t block0, MPI_Comm comm,
                                    ptrdiff_t *local_n0, ptrdiff_t *local_0_start) {
@@ -58,12 +58,22 @@ fftw_plan fftw_mpi_plan_many_dft(int rnk, const ptrdiff_t *n, ptrdiff_t howmany,
     n3[2] = rnk == 3 ? n[2] : 1;
     n = n3;
     P = b2fft_comm_size(comm);
-    /* only the default ceil(n/P) blocks (FFTW_MPI_DEFAULT_BLOCK, or the same value spelled out) */
-    if (block != FFTW_MPI_DEFAULT_BLOCK && block != (n[0] + P - 1) / P) return 0;
-    if (tblock != FFTW_MPI_DEFAULT_BLOCK && tblock != (n[1] + P - 1) / P) return 0;
-    /* more blocks than ranks cannot be distributed (reference fftw/mpi/api.c:578-582) */
-    bp = b2fft_slab_plan_dft_3d(n[0], n[1], n[2], howmany, comm, sign, (flags & FFTW_MPI_TRANSPOSED_IN) != 0,
-                                (flags & FFTW_MPI_TRANSPOSED_OUT) != 0, flags);
+    (void)P;
+    /* block = block size of the distributed INPUT dimension, tblock = of the distributed OUTPUT dimension
+     * (reference fftw/mpi/api.c:604-611); a plan whose output is distributed like its input (no flag, or both)
+     * needs the same block on both sides.  More blocks than ranks -> NULL (fftw/mpi/api.c:578-582). */
+    if (block < 0 || tblock < 0) return 0;
+    {
+        const int tin = (flags & FFTW_MPI_TRANSPOSED_IN) != 0, tout = (flags & FFTW_MPI_TRANSPOSED_OUT) != 0;
+        const ptrdiff_t nin = n[tin ? 1 : 0];
+        ptrdiff_t b1 = tblock;
+        if (tin == tout) {
+            const ptrdiff_t bi = block ? block : (nin + P - 1) / P, bo = tblock ? tblock : (nin + P - 1) / P;
+            if (bi != bo) return 0;
+            b1 = 0;
+        }
+        bp = b2fft_slab_plan_dft_3d_blocks(n[0], n[1], n[2], howmany, block, b1, comm, sign, tin, tout, flags);
+    }
     if (!bp) return 0;
     p = (fftw_plan)malloc(sizeof *p);
     if (!p) {

@@ -32,10 +32,23 @@ static ptrdiff_t blk_len(ptrdiff_t n, ptrdiff_t block, int pe) {
     return left <= 0 ? 0 : std::min(left, block);
 }
 
+// block0 / block1: block sizes of the n0 (input) and n1 (transposed output) distributions, 0 = ceil(n/P);
+// a block size that needs more than P blocks cannot be distributed (fftw/mpi/api.c:578-582): returns 0
+extern "C" ptrdiff_t b2fft_slab_local_size_3d_blocks(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t block0,
+                                                    ptrdiff_t block1, int P, int pe, ptrdiff_t *local_n0,
+                                                    ptrdiff_t *local_0_start, ptrdiff_t *local_n1,
+                                                    ptrdiff_t *local_1_start);
 extern "C" ptrdiff_t b2fft_slab_local_size_3d_transposed(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, int P,
                                                          int pe, ptrdiff_t *local_n0, ptrdiff_t *local_0_start,
                                                          ptrdiff_t *local_n1, ptrdiff_t *local_1_start) {
-    const ptrdiff_t b0 = blk_default(n0, P), b1 = blk_default(n1, P);
+    return b2fft_slab_local_size_3d_blocks(n0, n1, n2, 0, 0, P, pe, local_n0, local_0_start, local_n1, local_1_start);
+}
+extern "C" ptrdiff_t b2fft_slab_local_size_3d_blocks(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t block0,
+                                                    ptrdiff_t block1, int P, int pe, ptrdiff_t *local_n0,
+                                                    ptrdiff_t *local_0_start, ptrdiff_t *local_n1,
+                                                    ptrdiff_t *local_1_start) {
+    const ptrdiff_t b0 = block0 > 0 ? block0 : blk_default(n0, P), b1 = block1 > 0 ? block1 : blk_default(n1, P);
+    if ((n0 + b0 - 1) / b0 > P || (n1 + b1 - 1) / b1 > P) return 0;
     const ptrdiff_t l0 = blk_len(n0, b0, pe), l1 = blk_len(n1, b1, pe);
     if (local_n0) *local_n0 = l0;
     if (local_0_start) *local_0_start = l0 ? pe * b0 : 0;
@@ -426,7 +439,16 @@ static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
 }
 
 static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
-                                    b2fft_comm *c, int sign, int transposed_in, int transposed_out);
+                                    b2fft_comm *c, int sign, int transposed_in, int transposed_out,
+                                    ptrdiff_t block0 = 0, ptrdiff_t block1 = 0);
+// block0: block size of the distributed INPUT dimension (n0, or n1 with transposed_in), block1: of the
+// distributed OUTPUT dimension; 0 = default (fftw_mpi_plan_many_dft's block / tblock, fftw/mpi/api.c:592-636)
+extern "C" b2fft_plan *b2fft_slab_plan_dft_3d_blocks(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
+                                                     ptrdiff_t block0, ptrdiff_t block1, b2fft_comm *c, int sign,
+                                                     int transposed_in, int transposed_out, unsigned flags) {
+    (void)flags;
+    return slab_plan_create(B2FFT_C2C, n0, n1, n2, howmany, c, sign, transposed_in, transposed_out, block0, block1);
+}
 
 extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
                                               b2fft_comm *c, int sign, int transposed_in, int transposed_out,
@@ -448,7 +470,8 @@ extern "C" b2fft_plan *b2fft_slab_plan_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t
 }
 
 static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
-                                    b2fft_comm *c, int sign, int transposed_in, int transposed_out) {
+                                    b2fft_comm *c, int sign, int transposed_in, int transposed_out,
+                                    ptrdiff_t block0, ptrdiff_t block1) {
     if (!c || n0 <= 0 || n1 <= 0 || n2 <= 0) {
         set_error("slab plan: bad arguments");
         return nullptr;
@@ -483,9 +506,16 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
     s->sign = sign < 0 ? -1 : +1;
     s->transposed_out = transposed_out != 0;
     s->comm = c;
-    s->b0 = blk_default(n0, s->P);
-    s->b1 = blk_default(n1, s->P);
-    s->alloc_elems = (size_t)b2fft_slab_local_size_3d_transposed(n0, n1, n2, s->P, s->pe, &s->ln0, &s->s0, &s->ln1, &s->s1);
+    // inside the plan dimension "0" is the one distributed on input, "1" the one distributed after the
+    // exchange: with the c2c TRANSPOSED_IN swap above the caller's input / output block sizes already line up
+    s->b0 = block0 > 0 ? block0 : blk_default(n0, s->P);
+    s->b1 = block1 > 0 ? block1 : blk_default(n1, s->P);
+    if ((n0 + s->b0 - 1) / s->b0 > s->P || (n1 + s->b1 - 1) / s->b1 > s->P) {
+        set_error("slab plan: more blocks than ranks");
+        delete s;
+        return nullptr;
+    }
+    s->alloc_elems = (size_t)b2fft_slab_local_size_3d_blocks(n0, n1, n2, s->b0, s->b1, s->P, s->pe, &s->ln0, &s->s0, &s->ln1, &s->s1);
     // chunks of planes: enough to overlap, few enough to keep the messages large
     const ptrdiff_t maxl0 = s->b0;
     s->nchunks = (int)std::max<ptrdiff_t>(1, std::min<ptrdiff_t>(8, maxl0 / 8));

@@ -113,6 +113,12 @@ ptrdiff_t b2fft_slab_local_size_3d_transposed(ptrdiff_t n0, ptrdiff_t n1, ptrdif
                                               ptrdiff_t *local_n0, ptrdiff_t *local_0_start,
                                               ptrdiff_t *local_n1, ptrdiff_t *local_1_start);
 
+/* the same with explicit block sizes (0 = ceil(n/P)): fftw_mpi_local_size_many_transposed / fftw_mpi_plan_many_dft.
+ * block0 distributes the plan's input dimension, block1 its post-exchange dimension. */
+ptrdiff_t b2fft_slab_local_size_3d_blocks(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t block0, ptrdiff_t block1,
+                                          int n_pes, int my_pe, ptrdiff_t *local_n0, ptrdiff_t *local_0_start,
+                                          ptrdiff_t *local_n1, ptrdiff_t *local_1_start);
+
 int         b2fft_nccl_unique_id(void *id128);                 /* fills 128 bytes */
 b2fft_comm *b2fft_comm_create(const void *id128, int n_pes, int my_pe);
 b2fft_comm *b2fft_comm_self(void);                             /* single-rank communicator */
@@ -123,6 +129,9 @@ int         b2fft_comm_size(const b2fft_comm *c);
 b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
                                    b2fft_comm *c, int sign, int transposed_in,
                                    int transposed_out, unsigned flags);
+b2fft_plan *b2fft_slab_plan_dft_3d_blocks(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
+                                          ptrdiff_t block0, ptrdiff_t block1, b2fft_comm *c, int sign,
+                                          int transposed_in, int transposed_out, unsigned flags);
 /* the receive buffers of all ranks as seen from this process (test hook / callers with their own
  * peer mapping): switches the plan to the fused exchange; returns 1 when it did */
 int         b2fft_slab_set_peer_recv(b2fft_plan *p, void *const *recv, int n);

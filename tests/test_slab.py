@@ -389,6 +389,66 @@ def test_two_dimensional_slab(shape, P, flags):
         L.b2fft_comm_destroy(r["comm"])
 
 
+@pytest.mark.parametrize("flags", [TRANSPOSED_OUT, TRANSPOSED_IN], ids=["tout", "tin"])
+@pytest.mark.parametrize("shape,P,b_n0,b_n1", [((10, 12, 4), 4, 4, 5), ((9, 32, 3), 3, 5, 16), ((8, 6, 5), 2, 6, 3)],
+                         ids=["10x12x4", "9x32x3", "8x6x5"])
+def test_explicit_block_sizes(shape, P, b_n0, b_n1, flags):
+    """fftw_mpi_plan_many_dft with block / tblock other than ceil(n/P) (fftw/mpi/api.c:592-636, block.c:46-50):
+    uneven and empty ranks; more blocks than ranks -> NULL"""
+    lib = load()
+    L = lib.lib
+    L.fftw_mpi_plan_many_dft.restype = C.c_void_p
+    L.fftw_mpi_plan_many_dft.argtypes = [C.c_int, C.POINTER(C.c_ssize_t), C.c_ssize_t, C.c_ssize_t, C.c_ssize_t,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint]
+    L.fftw_mpi_local_size_many_transposed.restype = C.c_ssize_t
+    L.fftw_mpi_local_size_many_transposed.argtypes = [C.c_int, C.POINTER(C.c_ssize_t), C.c_ssize_t, C.c_ssize_t,
+                                                      C.c_ssize_t, C.c_void_p] + [C.POINTER(C.c_ssize_t)] * 4
+    n0, n1, n2 = shape
+    tin = bool(flags & TRANSPOSED_IN)
+    blk, tblk = (b_n1, b_n0) if tin else (b_n0, b_n1)
+    rng = np.random.default_rng(P + blk)
+    x = ((rng.random(shape) - 0.5) + 1j * (rng.random(shape) - 0.5)).astype(lib.cplx)
+    Y = orc.dft(x, -1)
+    nn = (C.c_ssize_t * 3)(*shape)
+    # local_size_many_transposed: block0 over n0, block1 over n1; the plan: block over the INPUT dim, tblock over the OUTPUT dim
+    ranks = []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        v = [C.c_ssize_t() for _ in range(4)]
+        N = L.fftw_mpi_local_size_many_transposed(3, nn, 1, b_n0, b_n1, comm, *[C.byref(t) for t in v])
+        ln0, s0, ln1, s1 = (t.value for t in v)
+        assert ln0 == max(0, min(b_n0, n0 - pe * b_n0)) and ln1 == max(0, min(b_n1, n1 - pe * b_n1))
+        xin = np.zeros(max(N, 1), dtype=lib.cplx)
+        if tin:
+            xin[:ln1 * n0 * n2] = x.transpose(1, 0, 2)[s1:s1 + ln1].ravel()
+        else:
+            xin[:ln0 * n1 * n2] = x[s0:s0 + ln0].ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = L.fftw_mpi_plan_many_dft(3, nn, 1, blk, tblk, xin.ctypes.data, out.ctypes.data, comm, -1,
+                                        capi.FFTW_ESTIMATE | flags)
+        assert plan, "slab plan with explicit blocks is NULL"
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        a = dict(la=ln1, sa=s1, lb=ln0, sb=s0) if tin else dict(la=ln0, sa=s0, lb=ln1, sb=s1)
+        ranks.append(dict(comm=comm, xin=xin, out=out, plan=plan, bp=bp, S=S, R=R, ln0=ln0, s0=s0, ln1=ln1, s1=s1, **a))
+    na, nb = (n1, n0) if tin else (n0, n1)
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 0, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    _exchange(ranks, na, nb, n2)
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 2, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+        ref = Y[r["s0"]:r["s0"] + r["ln0"]] if tin else Y.transpose(1, 0, 2)[r["s1"]:r["s1"] + r["ln1"]]
+        got = r["out"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+        lib.destroy_plan(r["plan"])
+    # a block size that needs more blocks than ranks cannot be distributed
+    assert not L.fftw_mpi_plan_many_dft(3, nn, 1, 1, 0, ranks[0]["xin"].ctypes.data, ranks[0]["out"].ctypes.data,
+                                        ranks[0]["comm"], -1, capi.FFTW_ESTIMATE | flags) or max(n0, n1) <= P
+    for r in ranks:
+        L.b2fft_comm_destroy(r["comm"])
+
+
 def _real_api(lib):
     L = lib.lib
     for nm in ("fftw_mpi_plan_dft_r2c_3d", "fftw_mpi_plan_dft_c2r_3d"):
