@@ -71,3 +71,34 @@ def test_product_contains_only_sm100a_code(product):
     out = subprocess.run(["cuobjdump", "-lelf", path], stdout=subprocess.PIPE, text=True).stdout
     archs = set(re.findall(r"sm_\d+a?", out))
     assert archs == {"sm_100a"}, archs
+
+
+def _build_dropin(prec, lib_path, tmp_path):
+    """examples/dropin.c: a C99 program written against include/fftw3.h only (-pedantic -Werror)"""
+    import subprocess
+    exe = str(tmp_path / f"dropin_{prec}")
+    cmd = ["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", *(["-DFFTW_SINGLE"] if prec == "fp32" else []),
+           "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "examples", "dropin.c"), "-o", exe, lib_path, "-lm",
+           "-Wl,-rpath," + os.path.dirname(lib_path)]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0, r.stdout
+    return exe
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp64"])
+def test_c_program_against_the_public_header_runs_on_the_emulation_build(prec, tmp_path):
+    import subprocess
+    from fftw3_b200 import build
+    exe = _build_dropin(prec, build.build_emu(prec), tmp_path)
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert r.returncode == 0 and "dropin: ok" in r.stdout, r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prec", ["fp32", "fp64"])
+def test_c_program_against_the_public_header_runs_on_b200(prec, tmp_path):
+    import subprocess
+    from fftw3_b200 import build
+    exe = _build_dropin(prec, build.lib_path(prec), tmp_path)
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert r.returncode == 0 and "dropin: ok" in r.stdout, r.stdout
