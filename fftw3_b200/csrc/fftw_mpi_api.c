@@ -104,11 +104,15 @@ static fftw_plan mpi_rdft(int kind, int rnk, const ptrdiff_t *n, ptrdiff_t howma
     b2fft_plan *bp;
     int P;
     const int tin = (flags & FFTW_MPI_TRANSPOSED_IN) != 0, tout = (flags & FFTW_MPI_TRANSPOSED_OUT) != 0;
-    if (rnk != 3 || !n || !comm || howmany != 1) return 0;
+    if ((rnk != 3 && rnk != 2) || !n || !comm || howmany != 1) return 0;
     P = b2fft_comm_size(comm);
-    if (iblock != FFTW_MPI_DEFAULT_BLOCK && iblock != (n[tin ? 1 : 0] + P - 1) / P) return 0;
-    if (oblock != FFTW_MPI_DEFAULT_BLOCK && oblock != (n[tout ? 1 : 0] + P - 1) / P) return 0;
-    bp = b2fft_slab_plan_rdft_3d(kind, n[0], n[1], n[2], comm, tin, tout, flags);
+    {   /* default blocks only; in 2-D the distributed "dimension 1" is the n1/2+1 complex columns */
+        const ptrdiff_t d1 = rnk == 2 ? n[1] / 2 + 1 : n[1];
+        if (iblock != FFTW_MPI_DEFAULT_BLOCK && iblock != ((tin ? d1 : n[0]) + P - 1) / P) return 0;
+        if (oblock != FFTW_MPI_DEFAULT_BLOCK && oblock != ((tout ? d1 : n[0]) + P - 1) / P) return 0;
+    }
+    bp = rnk == 3 ? b2fft_slab_plan_rdft_3d(kind, n[0], n[1], n[2], comm, tin, tout, flags)
+                  : b2fft_slab_plan_rdft_2d(kind, n[0], n[1], comm, tin, tout, flags);
     if (!bp) return 0;
     p = (fftw_plan)malloc(sizeof *p);
     if (!p) {
@@ -139,6 +143,20 @@ fftw_plan fftw_mpi_plan_dft_r2c(int rnk, const ptrdiff_t *n, FFTW_REAL_TYPE *in,
 fftw_plan fftw_mpi_plan_dft_c2r(int rnk, const ptrdiff_t *n, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out, MPI_Comm comm,
                                 unsigned flags) {
     return fftw_mpi_plan_many_dft_c2r(rnk, n, 1, FFTW_MPI_DEFAULT_BLOCK, FFTW_MPI_DEFAULT_BLOCK, in, out, comm, flags);
+}
+fftw_plan fftw_mpi_plan_dft_r2c_2d(ptrdiff_t n0, ptrdiff_t n1, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out, MPI_Comm comm,
+                                   unsigned flags) {
+    ptrdiff_t n[2];
+    n[0] = n0;
+    n[1] = n1;
+    return fftw_mpi_plan_dft_r2c(2, n, in, out, comm, flags);
+}
+fftw_plan fftw_mpi_plan_dft_c2r_2d(ptrdiff_t n0, ptrdiff_t n1, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out, MPI_Comm comm,
+                                   unsigned flags) {
+    ptrdiff_t n[2];
+    n[0] = n0;
+    n[1] = n1;
+    return fftw_mpi_plan_dft_c2r(2, n, in, out, comm, flags);
 }
 fftw_plan fftw_mpi_plan_dft_r2c_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out,
                                    MPI_Comm comm, unsigned flags) {

@@ -208,6 +208,11 @@ struct SlabPlan {
     // c2r runs the pipeline backwards: n0 FFTs (pA), reverse exchange, local 2-D c2r (pB).
     int kind = B2FFT_C2C;
     bool c2r_tin = false;            // c2r with FFTW_MPI_TRANSPOSED_IN: the input is [local_n1][n0][n2c]
+    // 2-D real data (fftw_mpi_plan_dft_r2c_2d / _c2r_2d): the half-complex dimension itself is the one that
+    // gets distributed after the exchange -- n1 = n1f/2+1 complex columns, rows of one element (n2 = 1),
+    // and the local real step is a batched 1-D r2c / c2r over the n1f-long rows
+    bool real2d = false;
+    ptrdiff_t n1f = 0;
     b2fft_plan *pA = nullptr, *pB = nullptr;
     int P, pe, sign;
     bool transposed_out;
@@ -278,6 +283,17 @@ static b2fft_plan *make_stage1(const SlabPlan &s, ptrdiff_t planes) {
     if (planes <= 0) return nullptr;
     b2fft_geom g;
     memset(&g, 0, sizeof g);
+    if (s.kind == B2FFT_R2C && s.real2d) {
+        // real [rows][2*n1c] -> complex [rows][n1c]
+        g.kind = B2FFT_R2C;
+        g.sign = -1;
+        g.rank = 1;
+        g.dims[0] = b2fft_dim{s.n1f, 1, 1};
+        g.vrank = 1;
+        g.vdims[0] = b2fft_dim{planes, 2 * s.n1, s.n1};
+        g.in_place = 0;
+        return b2fft_plan_create(&g);
+    }
     if (s.kind == B2FFT_R2C) {
         // real [planes][n1][2*n2c] -> complex [planes][n1][n2c]
         g.kind = B2FFT_R2C;
@@ -353,6 +369,14 @@ static b2fft_plan *make_c2r_b(const SlabPlan &s) {
     memset(&g, 0, sizeof g);
     g.kind = B2FFT_C2R;
     g.sign = +1;
+    if (s.real2d) {
+        g.rank = 1;
+        g.dims[0] = b2fft_dim{s.n1f, 1, 1};
+        g.vrank = 1;
+        g.vdims[0] = b2fft_dim{s.ln0, s.n1, 2 * s.n1};
+        g.in_place = 0;
+        return b2fft_plan_create(&g);
+    }
     g.rank = 2;
     g.dims[0] = b2fft_dim{s.n1, s.n2, 2 * s.n2};
     g.dims[1] = b2fft_dim{s.n2f, 1, 1};
@@ -440,7 +464,7 @@ static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
 
 static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
                                     b2fft_comm *c, int sign, int transposed_in, int transposed_out,
-                                    ptrdiff_t block0 = 0, ptrdiff_t block1 = 0);
+                                    ptrdiff_t block0 = 0, ptrdiff_t block1 = 0, bool real2d = false);
 // block0: block size of the distributed INPUT dimension (n0, or n1 with transposed_in), block1: of the
 // distributed OUTPUT dimension; 0 = default (fftw_mpi_plan_many_dft's block / tblock, fftw/mpi/api.c:592-636)
 extern "C" b2fft_plan *b2fft_slab_plan_dft_3d_blocks(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
@@ -469,9 +493,21 @@ extern "C" b2fft_plan *b2fft_slab_plan_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t
     return slab_plan_create(kind, n0, n1, n2, 1, c, kind == B2FFT_R2C ? -1 : +1, transposed_in, transposed_out);
 }
 
+// 2-D real data: n1 is the logical real length of the rows
+extern "C" b2fft_plan *b2fft_slab_plan_rdft_2d(int kind, ptrdiff_t n0, ptrdiff_t n1, b2fft_comm *c, int transposed_in,
+                                               int transposed_out, unsigned flags) {
+    (void)flags;
+    if (kind != B2FFT_R2C && kind != B2FFT_C2R) return nullptr;
+    if ((kind == B2FFT_R2C && transposed_in) || (kind == B2FFT_C2R && transposed_out)) {
+        set_error("slab real transform: a transposed REAL array is not supported");
+        return nullptr;
+    }
+    return slab_plan_create(kind, n0, n1, 1, 1, c, kind == B2FFT_R2C ? -1 : +1, transposed_in, transposed_out, 0, 0, true);
+}
+
 static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
                                     b2fft_comm *c, int sign, int transposed_in, int transposed_out,
-                                    ptrdiff_t block0, ptrdiff_t block1) {
+                                    ptrdiff_t block0, ptrdiff_t block1, bool real2d) {
     if (!c || n0 <= 0 || n1 <= 0 || n2 <= 0) {
         set_error("slab plan: bad arguments");
         return nullptr;
@@ -494,11 +530,16 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
         transposed_out = !transposed_out;
     }
     s->c2r_tin = (kind == B2FFT_C2R && transposed_in);
+    s->real2d = real2d;
+    if (real2d) {
+        s->n1f = n1;
+        n1 = n1 / 2 + 1;  // complex columns: the dimension the exchange distributes
+    }
     s->n0 = n0;
     s->n1 = n1;
     s->n2f = n2;
     s->hm = howmany;
-    if (kind != B2FFT_C2C) n2 = n2 / 2 + 1;  // complex elements per row
+    if (kind != B2FFT_C2C && !real2d) n2 = n2 / 2 + 1;  // complex elements per row
     n2 *= howmany;
     s->n2 = n2;
     s->P = c->size;
@@ -576,7 +617,7 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
         delete bp;
         return nullptr;
     }
-    double N = (double)n0 * n1 * s->n2f;
+    double N = (double)n0 * (real2d ? s->n1f : n1) * s->n2f;
     bp->pc.flops = (kind == B2FFT_C2C ? 5.0 : 2.5) * N * log2(N) * (double)howmany / s->P;
     slab_describe(*s, bp);
     return bp;

@@ -73,6 +73,13 @@ FFTW_EXTERN fftw_plan fftw_mpi_plan_many_dft_r2c(int rnk, const ptrdiff_t *n, pt
                                                  MPI_Comm comm, unsigned flags);
 FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_r2c(int rnk, const ptrdiff_t *n, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out,
                                             MPI_Comm comm, unsigned flags);
+/* 2-D real data (reference fftw/mpi/fftw3-mpi.h:168-170, 182-184): real [local_n0][2(n1/2+1)]; complex
+ * [local_n0][n1/2+1] or [local_n1][n0] with local_n1 blocks of the n1/2+1 columns
+ * (sizes from fftw_mpi_local_size_2d[_transposed](n0, n1/2+1, ...)) */
+FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_r2c_2d(ptrdiff_t n0, ptrdiff_t n1, FFTW_REAL_TYPE *in, FFTW_COMPLEX *out,
+                                               MPI_Comm comm, unsigned flags);
+FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_c2r_2d(ptrdiff_t n0, ptrdiff_t n1, FFTW_COMPLEX *in, FFTW_REAL_TYPE *out,
+                                               MPI_Comm comm, unsigned flags);
 FFTW_EXTERN fftw_plan fftw_mpi_plan_dft_r2c_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_REAL_TYPE *in,
                                                FFTW_COMPLEX *out, MPI_Comm comm, unsigned flags);
 FFTW_EXTERN fftw_plan fftw_mpi_plan_many_dft_c2r(int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t iblock,

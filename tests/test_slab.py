@@ -577,6 +577,94 @@ def test_complex_to_real_slab(shape, P, tin):
         L.b2fft_comm_destroy(r["comm"])
 
 
+@pytest.mark.parametrize("transposed", [True, False], ids=["transposed", "natural"])
+@pytest.mark.parametrize("P", [1, 2, 3])
+@pytest.mark.parametrize("shape", [(8, 10), (12, 9), (6, 64)], ids=lambda s: "x".join(map(str, s)))
+def test_two_dimensional_real_slab(shape, P, transposed):
+    """fftw_mpi_plan_dft_r2c_2d and _c2r_2d back (fftw/mpi/api.c:845-851, 867-873): the n1/2+1 complex columns
+    are the dimension the exchange distributes"""
+    lib = load()
+    L = lib.lib
+    for nm in ("fftw_mpi_plan_dft_r2c_2d", "fftw_mpi_plan_dft_c2r_2d"):
+        f = getattr(L, nm)
+        f.restype = C.c_void_p
+        f.argtypes = [C.c_ssize_t] * 2 + [C.c_void_p] * 3 + [C.c_uint]
+    n0, n1 = shape
+    n1c = n1 // 2 + 1
+    rng = np.random.default_rng(51 + P)
+    x = (rng.random(shape) - 0.5).astype(lib.real)
+    Y = orc.r2c(x)
+    fwd, bwd = [], []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        N, ln0, s0, ln1, s1 = local_sizes(lib, (n0, n1c, 1), comm)
+        rin = np.zeros(2 * max(N, 1), dtype=lib.real)
+        pad = np.zeros((ln0, 2 * n1c), dtype=lib.real)
+        pad[:, :n1] = x[s0:s0 + ln0]
+        rin[:pad.size] = pad.ravel()
+        cbuf = np.zeros(max(N, 1), dtype=lib.cplx)
+        rout = np.zeros(2 * max(N, 1), dtype=lib.real)
+        pf = L.fftw_mpi_plan_dft_r2c_2d(n0, n1, rin.ctypes.data, cbuf.ctypes.data, comm,
+                                        capi.FFTW_ESTIMATE | (TRANSPOSED_OUT if transposed else 0))
+        pb = L.fftw_mpi_plan_dft_c2r_2d(n0, n1, cbuf.ctypes.data, rout.ctypes.data, comm,
+                                        capi.FFTW_ESTIMATE | (TRANSPOSED_IN if transposed else 0))
+        assert pf and pb, "2-D real slab plan is NULL"
+        geo = dict(comm=comm, la=ln0, sa=s0, lb=ln1, sb=s1, rin=rin, cbuf=cbuf, rout=rout)
+        for plan, lst in ((pf, fwd), (pb, bwd)):
+            S, bp = buffer_view(lib, plan, 0, lib.cplx)
+            R, _ = buffer_view(lib, plan, 1, lib.cplx)
+            lst.append(dict(plan=plan, bp=bp, S=S, R=R, **geo))
+
+    def reverse_exchange(ranks, dst_key):  # receive layout [n0][lb] -> [la][n1c] rows
+        for src in ranks:
+            if src["lb"] == 0:
+                continue
+            Rv = src["R"][:n0 * src["lb"]].reshape(n0, src["lb"])
+            for dst in ranks:
+                if dst["la"] == 0:
+                    continue
+                Dv = dst[dst_key][:dst["la"] * n1c].reshape(dst["la"], n1c)
+                Dv[:, src["sb"]:src["sb"] + src["lb"]] = Rv[dst["sa"]:dst["sa"] + dst["la"]]
+
+    # ---- r2c
+    for r in fwd:
+        assert L.b2fft_slab_stage(r["bp"], 0, r["rin"].ctypes.data, r["cbuf"].ctypes.data) == 0
+    _exchange(fwd, n0, n1c, 1)
+    for r in fwd:
+        assert L.b2fft_slab_stage(r["bp"], 2, r["rin"].ctypes.data, r["cbuf"].ctypes.data) == 0
+    if not transposed:
+        reverse_exchange(fwd, "cbuf")
+    for r in fwd:
+        ref = Y.T[r["sb"]:r["sb"] + r["lb"]] if transposed else Y[r["sa"]:r["sa"] + r["la"]]
+        got = r["cbuf"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+    # ---- c2r from that layout
+    if not transposed:  # forward exchange of the natural input straight into the receive layout
+        for src in bwd:
+            if src["la"] == 0:
+                continue
+            Iv = src["cbuf"][:src["la"] * n1c].reshape(src["la"], n1c)
+            for dst in bwd:
+                if dst["lb"] == 0:
+                    continue
+                Rv = dst["R"][:n0 * dst["lb"]].reshape(n0, dst["lb"])
+                Rv[src["sa"]:src["sa"] + src["la"]] = Iv[:, dst["sb"]:dst["sb"] + dst["lb"]]
+    for r in bwd:
+        assert L.b2fft_slab_stage(r["bp"], 1, r["cbuf"].ctypes.data, r["rout"].ctypes.data) == 0
+    reverse_exchange(bwd, "S")
+    for r in bwd:
+        assert L.b2fft_slab_stage(r["bp"], 3, r["cbuf"].ctypes.data, r["rout"].ctypes.data) == 0
+        want = x[r["sa"]:r["sa"] + r["la"]] * (n0 * n1)
+        got = r["rout"][:r["la"] * 2 * n1c].reshape(r["la"], 2 * n1c)[:, :n1]
+        if want.size:
+            assert np.linalg.norm(got - want) / np.linalg.norm(want) < 1e-13
+    for r in fwd + bwd:
+        lib.destroy_plan(r["plan"])
+    for r in fwd:
+        L.b2fft_comm_destroy(r["comm"])
+
+
 def _gloo_worker(rank, world, port, shape, q):
     try:
         import torch
