@@ -104,14 +104,14 @@ static fftw_plan mpi_rdft(int kind, int rnk, const ptrdiff_t *n, ptrdiff_t howma
     b2fft_plan *bp;
     int P;
     const int tin = (flags & FFTW_MPI_TRANSPOSED_IN) != 0, tout = (flags & FFTW_MPI_TRANSPOSED_OUT) != 0;
-    if ((rnk != 3 && rnk != 2) || !n || !comm || howmany != 1) return 0;
+    if ((rnk != 3 && rnk != 2) || !n || !comm || howmany < 1 || (rnk == 2 && howmany != 1)) return 0;
     P = b2fft_comm_size(comm);
     {   /* default blocks only; in 2-D the distributed "dimension 1" is the n1/2+1 complex columns */
         const ptrdiff_t d1 = rnk == 2 ? n[1] / 2 + 1 : n[1];
         if (iblock != FFTW_MPI_DEFAULT_BLOCK && iblock != ((tin ? d1 : n[0]) + P - 1) / P) return 0;
         if (oblock != FFTW_MPI_DEFAULT_BLOCK && oblock != ((tout ? d1 : n[0]) + P - 1) / P) return 0;
     }
-    bp = rnk == 3 ? b2fft_slab_plan_rdft_3d(kind, n[0], n[1], n[2], comm, tin, tout, flags)
+    bp = rnk == 3 ? b2fft_slab_plan_many_rdft_3d(kind, n[0], n[1], n[2], howmany, comm, tin, tout, flags)
                   : b2fft_slab_plan_rdft_2d(kind, n[0], n[1], comm, tin, tout, flags);
     if (!bp) return 0;
     p = (fftw_plan)malloc(sizeof *p);

@@ -299,10 +299,12 @@ static b2fft_plan *make_stage1(const SlabPlan &s, ptrdiff_t planes) {
         g.kind = B2FFT_R2C;
         g.sign = -1;
         g.rank = 2;
+        // (s.n2 = n2c * howmany: with interleaved tuples the n2 transform has stride howmany on both sides)
         g.dims[0] = b2fft_dim{s.n1, 2 * s.n2, s.n2};
-        g.dims[1] = b2fft_dim{s.n2f, 1, 1};
-        g.vrank = 1;
+        g.dims[1] = b2fft_dim{s.n2f, s.hm, s.hm};
+        g.vrank = s.hm > 1 ? 2 : 1;
         g.vdims[0] = b2fft_dim{planes, s.n1 * 2 * s.n2, s.n1 * s.n2};
+        g.vdims[1] = b2fft_dim{s.hm, 1, 1};
         g.in_place = 0;
         return b2fft_plan_create(&g);
     }
@@ -379,9 +381,10 @@ static b2fft_plan *make_c2r_b(const SlabPlan &s) {
     }
     g.rank = 2;
     g.dims[0] = b2fft_dim{s.n1, s.n2, 2 * s.n2};
-    g.dims[1] = b2fft_dim{s.n2f, 1, 1};
-    g.vrank = 1;
+    g.dims[1] = b2fft_dim{s.n2f, s.hm, s.hm};
+    g.vrank = s.hm > 1 ? 2 : 1;
     g.vdims[0] = b2fft_dim{s.ln0, s.n1 * s.n2, s.n1 * 2 * s.n2};
+    g.vdims[1] = b2fft_dim{s.hm, 1, 1};
     g.in_place = 0;
     return b2fft_plan_create(&g);
 }
@@ -482,6 +485,17 @@ extern "C" b2fft_plan *b2fft_slab_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdif
 }
 // kind = B2FFT_R2C (real [ln0][n1][2(n2/2+1)] -> complex, natural or transposed output) or B2FFT_C2R
 // (complex, natural or transposed input -> real [ln0][n1][2(n2/2+1)]); n2 is the logical real length
+extern "C" b2fft_plan *b2fft_slab_plan_many_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2,
+                                                    ptrdiff_t howmany, b2fft_comm *c, int transposed_in,
+                                                    int transposed_out, unsigned flags) {
+    (void)flags;
+    if (kind != B2FFT_R2C && kind != B2FFT_C2R) return nullptr;
+    if ((kind == B2FFT_R2C && transposed_in) || (kind == B2FFT_C2R && transposed_out)) {
+        set_error("slab real transform: a transposed REAL array is not supported");
+        return nullptr;
+    }
+    return slab_plan_create(kind, n0, n1, n2, howmany, c, kind == B2FFT_R2C ? -1 : +1, transposed_in, transposed_out);
+}
 extern "C" b2fft_plan *b2fft_slab_plan_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, b2fft_comm *c,
                                                int transposed_in, int transposed_out, unsigned flags) {
     (void)flags;

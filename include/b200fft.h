@@ -140,6 +140,9 @@ int         b2fft_slab_set_peer_recv(b2fft_plan *p, void *const *recv, int n);
  * B2FFT_C2R (complex in, natural or FFTW_MPI_TRANSPOSED_IN, real out).  n2 = logical real length. */
 b2fft_plan *b2fft_slab_plan_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, b2fft_comm *c,
                                     int transposed_in, int transposed_out, unsigned flags);
+/* the same with `howmany` interleaved transforms (tuples of howmany reals / complex per element) */
+b2fft_plan *b2fft_slab_plan_many_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
+                                         b2fft_comm *c, int transposed_in, int transposed_out, unsigned flags);
 /* 2-D real data (fftw_mpi_plan_dft_r2c_2d / _c2r_2d): real [local_n0][2(n1/2+1)], complex [local_n0][n1/2+1] or,
  * transposed, [local_n1c][n0] with the n1/2+1 complex columns block-distributed. */
 b2fft_plan *b2fft_slab_plan_rdft_2d(int kind, ptrdiff_t n0, ptrdiff_t n1, b2fft_comm *c, int transposed_in,

@@ -665,6 +665,78 @@ def test_two_dimensional_real_slab(shape, P, transposed):
         L.b2fft_comm_destroy(r["comm"])
 
 
+@pytest.mark.parametrize("P", [1, 2, 3])
+@pytest.mark.parametrize("howmany", [2, 3])
+def test_real_slab_with_interleaved_transforms(howmany, P):
+    """fftw_mpi_plan_many_dft_r2c / _c2r with howmany > 1: tuples of howmany reals (complex) per element"""
+    lib = load()
+    L = lib.lib
+    for nm in ("fftw_mpi_plan_many_dft_r2c", "fftw_mpi_plan_many_dft_c2r"):
+        f = getattr(L, nm)
+        f.restype = C.c_void_p
+        f.argtypes = [C.c_int, C.POINTER(C.c_ssize_t), C.c_ssize_t, C.c_ssize_t, C.c_ssize_t, C.c_void_p, C.c_void_p,
+                      C.c_void_p, C.c_uint]
+    n0, n1, n2 = 6, 8, 10
+    n2c, hm = n2 // 2 + 1, howmany
+    rl = n2c * hm
+    rng = np.random.default_rng(61 + P)
+    x = (rng.random((n0, n1, n2, hm)) - 0.5).astype(lib.real)
+    Y = np.stack([orc.r2c(np.ascontiguousarray(x[..., h])) for h in range(hm)], axis=-1)  # [n0][n1][n2c][hm]
+    nn = (C.c_ssize_t * 3)(n0, n1, n2)
+    fwd, bwd = [], []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        N, ln0, s0, ln1, s1 = local_sizes(lib, (n0, n1, n2c), comm)
+        N *= hm
+        pad = np.zeros((ln0, n1, 2 * n2c, hm), dtype=lib.real)
+        pad[:, :, :n2, :] = x[s0:s0 + ln0]
+        rin = np.zeros(2 * max(N, 1), dtype=lib.real)
+        rin[:pad.size] = pad.ravel()
+        cbuf = np.zeros(max(N, 1), dtype=lib.cplx)
+        rout = np.zeros(2 * max(N, 1), dtype=lib.real)
+        pf = L.fftw_mpi_plan_many_dft_r2c(3, nn, hm, 0, 0, rin.ctypes.data, cbuf.ctypes.data, comm,
+                                          capi.FFTW_ESTIMATE | TRANSPOSED_OUT)
+        pb = L.fftw_mpi_plan_many_dft_c2r(3, nn, hm, 0, 0, cbuf.ctypes.data, rout.ctypes.data, comm,
+                                          capi.FFTW_ESTIMATE | TRANSPOSED_IN)
+        assert pf and pb, "slab real plan with howmany is NULL"
+        geo = dict(comm=comm, la=ln0, sa=s0, lb=ln1, sb=s1, rin=rin, cbuf=cbuf, rout=rout)
+        for plan, lst in ((pf, fwd), (pb, bwd)):
+            S, bp = buffer_view(lib, plan, 0, lib.cplx)
+            R, _ = buffer_view(lib, plan, 1, lib.cplx)
+            lst.append(dict(plan=plan, bp=bp, S=S, R=R, **geo))
+    for r in fwd:
+        assert L.b2fft_slab_stage(r["bp"], 0, r["rin"].ctypes.data, r["cbuf"].ctypes.data) == 0
+    if "fused into" not in lib.sprint_plan(fwd[0]["plan"]):
+        _exchange(fwd, n0, n1, rl)
+    for r in fwd:
+        assert L.b2fft_slab_stage(r["bp"], 2, r["rin"].ctypes.data, r["cbuf"].ctypes.data) == 0
+        ref = Y.transpose(1, 0, 2, 3)[r["sb"]:r["sb"] + r["lb"]]
+        got = r["cbuf"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+    for r in bwd:  # transposed input -> n0 FFTs -> reverse exchange -> local 2-D c2r
+        assert L.b2fft_slab_stage(r["bp"], 1, r["cbuf"].ctypes.data, r["rout"].ctypes.data) == 0
+    for src in bwd:
+        if src["lb"] == 0:
+            continue
+        Rv = src["R"][:n0 * src["lb"] * rl].reshape(n0, src["lb"], rl)
+        for dst in bwd:
+            if dst["la"] == 0:
+                continue
+            Sv = dst["S"][:dst["la"] * n1 * rl].reshape(dst["la"], n1, rl)
+            Sv[:, src["sb"]:src["sb"] + src["lb"], :] = Rv[dst["sa"]:dst["sa"] + dst["la"]]
+    for r in bwd:
+        assert L.b2fft_slab_stage(r["bp"], 3, r["cbuf"].ctypes.data, r["rout"].ctypes.data) == 0
+        want = x[r["sa"]:r["sa"] + r["la"]] * (n0 * n1 * n2)
+        got = r["rout"][:r["la"] * n1 * 2 * rl].reshape(r["la"], n1, 2 * n2c, hm)[:, :, :n2, :]
+        if want.size:
+            assert np.linalg.norm(got - want) / np.linalg.norm(want) < 1e-13
+    for r in fwd + bwd:
+        lib.destroy_plan(r["plan"])
+    for r in fwd:
+        L.b2fft_comm_destroy(r["comm"])
+
+
 def _gloo_worker(rank, world, port, shape, q):
     try:
         import torch
