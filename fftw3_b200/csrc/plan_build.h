@@ -508,12 +508,39 @@ inline bool build_c2c(PlanCore &pc) {
             set_error("negative strides are not supported");
             return false;
         }
-    if (pc.in_place)
+    // In place with different input and output strides (e.g. a batched transform written back transposed):
+    // solvable when both stride sets address the same locations (reference: fftw_tensor_inplace_locations
+    // fftw_api.c:17298, checked in fftw_mkproblem_dft :4090-4094).  The transform then runs through the
+    // plan's work arrays in the OUTPUT layout and one last sweep copies it over the input.
+    bool relayout = false;
+    if (pc.in_place) {
+        std::vector<std::pair<long long, long long>> li, lo;
         for (const GDim &d : all)
-            if (d.n > 1 && d.is != d.os) {
-                set_error("in-place transform with different input and output strides");
-                return false;
+            if (d.n > 1) {
+                if (d.is != d.os) relayout = true;
+                li.push_back({d.is, d.n});
+                lo.push_back({d.os, d.n});
             }
+        // same location sets <=> equal after sorting by stride and merging contiguous dims
+        // (fftw_tensor_compress_contiguous on both sides, then fftw_tensor_equal)
+        auto compress = [](std::vector<std::pair<long long, long long>> &v) {
+            std::sort(v.begin(), v.end());
+            for (size_t i = 0; i + 1 < v.size();) {
+                if (v[i + 1].first == v[i].first * v[i].second) {
+                    v[i].second *= v[i + 1].second;
+                    v.erase(v.begin() + i + 1);
+                } else
+                    ++i;
+            }
+        };
+        compress(li);
+        compress(lo);
+        if (relayout && li != lo) {
+            set_error("in-place transform whose input and output strides address different locations");
+            return false;
+        }
+    }
+    const std::vector<int> fft_dst = relayout ? std::vector<int>{B_SCR, B_WRK} : std::vector<int>{B_OUT, B_SCR};
     // axes: smallest output stride first
     std::vector<int> order;
     for (int i = 0; i < (int)T.size(); ++i)
@@ -528,7 +555,7 @@ inline bool build_c2c(PlanCore &pc) {
         StepPlan st;
         if (!make_pass_step(st, a)) return false;
         st.inplace_ok = lines_same(a.lines);
-        st.dst_allowed = {B_OUT, B_SCR};
+        st.dst_allowed = fft_dst;
         pc.steps.push_back(st);
     }
     for (size_t oi = 0; oi < order.size(); ++oi) {
@@ -539,8 +566,18 @@ inline bool build_c2c(PlanCore &pc) {
             if (i != ax) lines.push_back(LDim{T[i].n, 2 * (first ? T[i].is : T[i].os), 2 * T[i].os, false});
         for (const GDim &d : V) lines.push_back(LDim{d.n, 2 * (first ? d.is : d.os), 2 * d.os, false});
         if (!add_c2c_axis(pc, T[ax].n, 2 * (first ? T[ax].is : T[ax].os), 2 * T[ax].os, lines,
-                          bwd && first, bwd && last, {B_OUT, B_SCR}))
+                          bwd && first, bwd && last, fft_dst))
             return false;
+    }
+    if (relayout) {  // work array (output layout) -> the user's array
+        AxisSpec a;
+        a.n = 1;
+        for (const GDim &d : all) a.lines.push_back(LDim{d.n, 2 * d.os, 2 * d.os, false});
+        StepPlan st;
+        if (!make_pass_step(st, a)) return false;
+        st.inplace_ok = false;
+        st.dst_allowed = {B_OUT};
+        pc.steps.push_back(st);
     }
     return assign_buffers(pc);
 }

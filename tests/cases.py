@@ -654,3 +654,34 @@ def check_threads(lib):
         t.join()
     lib.destroy_plan(p)
     assert not errs, errs
+
+
+def check_inplace_relayout(lib, device=False):
+    """in place with different input and output strides that address the same locations (reference:
+    fftw_tensor_inplace_locations fftw_api.c:17298; e.g. a batch written back transposed); different
+    locations -> NULL"""
+    rng = np.random.default_rng(3)
+    if device:
+        import torch
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        down = lambda t: t.cpu().numpy()
+    else:
+        up = lambda a: np.ascontiguousarray(a)
+        down = lambda a: a
+    for n, hm in [(16, 5), (64, 48), (100, 7), (4096, 3), (2 ** 14, 2), (17, 4)]:
+        x = rand_c(rng, (hm, n), lib)
+        buf = up(x.copy().ravel())
+        p = lib.plan_many_dft([n], hm, buf, None, 1, n, buf, None, hm, 1, capi.FFTW_FORWARD)
+        assert p, (n, hm)
+        lib.execute(p)
+        lib.destroy_plan(p)
+        assert rel_l2(down(buf).reshape(n, hm), orc.dft_batched(x, -1).T) < tol(lib, n), (n, hm)
+    x = rand_c(rng, (12, 20), lib)
+    buf = up(x.copy().ravel())
+    p = lib.plan_guru_dft([(12, 20, 1), (20, 1, 12)], [], buf, buf, capi.FFTW_BACKWARD)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(down(buf).reshape(20, 12), orc.dft(x, +1).T) < tol(lib, 240)
+    y = up(np.zeros(64, dtype=lib.cplx))
+    assert not lib.plan_many_dft([8], 2, y, None, 1, 8, y, None, 2, 20, capi.FFTW_FORWARD)

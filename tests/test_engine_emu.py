@@ -133,6 +133,10 @@ def test_three_pass_real_transform(lib, shape, monkeypatch):
         cases.check_r2c_inplace(lib, shape)
 
 
+def test_in_place_with_different_strides(lib):
+    cases.check_inplace_relayout(lib)
+
+
 def test_chained_launch_opt_in(lib):
     cases.check_chained_launch(lib)
 

@@ -95,6 +95,11 @@ def test_threads_share_a_plan_and_the_planner(lib):
     cases.check_threads(lib)
 
 
+def test_in_place_with_different_strides(lib):
+    cases.check_inplace_relayout(lib)
+    cases.check_inplace_relayout(lib, device=True)
+
+
 def test_edge_cases(lib):
     cases.check_edge_cases(lib)
 
