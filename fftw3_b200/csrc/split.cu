@@ -62,6 +62,7 @@ struct b2fft_split_s {
     b2fft_plan *inner = nullptr;
     cpx_t *dense = nullptr;
     real_t *stage[4] = {nullptr, nullptr, nullptr, nullptr};  // device copies of host ri, ii, ro, io
+    long long stage_reals[4] = {0, 0, 0, 0};
     std::string desc;
 };
 
@@ -185,7 +186,14 @@ extern "C" void b2fft_split_plan_destroy(b2fft_split *s) {
 static real_t *split_stage(b2fft_split *s, int slot, real_t *user, long long extent, bool upload) {
     if (!user || extent <= 0 || is_device_ptr(user)) return user;
 #if B2_CUDA
-    if (!s->stage[slot]) s->stage[slot] = (real_t *)dev_malloc((size_t)extent * sizeof(real_t));
+    if (s->stage[slot] && s->stage_reals[slot] < extent) {  // the union span of overlapping arrays depends on the pointers
+        dev_free(s->stage[slot]);
+        s->stage[slot] = nullptr;
+    }
+    if (!s->stage[slot]) {
+        s->stage[slot] = (real_t *)dev_malloc((size_t)extent * sizeof(real_t));
+        s->stage_reals[slot] = extent;
+    }
     if (!s->stage[slot]) return nullptr;
     if (upload && cudaMemcpy(s->stage[slot], user, (size_t)extent * sizeof(real_t), cudaMemcpyHostToDevice) != cudaSuccess) {
         set_error("split execute: host -> device copy failed");
@@ -229,13 +237,32 @@ extern "C" int b2fft_split_execute(b2fft_split *s, void *ri_, void *ii_, void *r
     if (s->kind != B2FFT_C2R) {
         // a strided host output keeps whatever lives in its gaps: stage its current content first
         const bool dense_out = s->out_extent == s->out_cp.total;
-        real_t *dr = split_stage(s, 2, ro, s->out_extent, !dense_out), *di = split_stage(s, 3, io, s->out_extent, !dense_out);
-        if ((s->out_extent > 0) && (!dr || !di)) return -3;
-        rc = split_copy(s->out_cp, false, dr, di, s->dense);
-        if (rc) return rc;
-        rc = split_unstage(dr, ro, s->out_extent);
-        if (!rc) rc = split_unstage(di, io, s->out_extent);
-        if (rc) return rc;
+        real_t *dr, *di;
+        real_t *lo = ro < io ? ro : io, *hi = ro < io ? io : ro;
+        const bool overlap = ro && io && s->out_extent > 0 && (hi - lo) < s->out_extent && !is_device_ptr(ro) && !is_device_ptr(io);
+        if (overlap) {
+            // host (ro, io) ranges that interleave or overlap -- the documented usage ro = out, io = out + 1
+            // with stride 2: ONE staged copy of the union span, both arrays addressed inside it, so that the
+            // write-back of one array cannot bring back stale values of the other
+            const long long span = (long long)(hi - lo) + s->out_extent;
+            real_t *base = split_stage(s, 2, lo, span, true);
+            if (!base) return -3;
+            dr = base + (ro - lo);
+            di = base + (io - lo);
+            rc = split_copy(s->out_cp, false, dr, di, s->dense);
+            if (rc) return rc;
+            rc = split_unstage(base, lo, span);
+            if (rc) return rc;
+        } else {
+            dr = split_stage(s, 2, ro, s->out_extent, !dense_out);
+            di = split_stage(s, 3, io, s->out_extent, !dense_out);
+            if ((s->out_extent > 0) && (!dr || !di)) return -3;
+            rc = split_copy(s->out_cp, false, dr, di, s->dense);
+            if (rc) return rc;
+            rc = split_unstage(dr, ro, s->out_extent);
+            if (!rc) rc = split_unstage(di, io, s->out_extent);
+            if (rc) return rc;
+        }
     }
 #if B2_CUDA
     B2_CK(cudaDeviceSynchronize());

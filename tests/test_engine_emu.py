@@ -109,6 +109,7 @@ def test_real_transforms_beyond_the_four_step_limit(lib, shape, monkeypatch):
 
 def test_split_array_guru_interfaces(lib):
     cases.check_split_arrays(lib)
+    cases.check_split_interleaved_host(lib)
 
 
 def test_r2r_kinds(lib, r2r_golden):

@@ -84,6 +84,7 @@ def test_golden_vectors_of_the_reference(lib, golden):
 def test_split_array_guru_interfaces(lib):
     cases.check_split_arrays(lib)
     cases.check_split_arrays(lib, device=True)
+    cases.check_split_interleaved_host(lib)
 
 
 def test_r2r_kinds(lib, r2r_golden):
