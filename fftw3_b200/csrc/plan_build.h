@@ -273,6 +273,7 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
     const Caps c = caps();
     const bool row = (s_axis <= 2 && d_axis <= 2);
     const long long cap = row ? c.row : c.col;
+    const bool both = swap_in && swap_out;
     if (!axis_direct_ok(n, row)) {
         BlueSpec b;
         b.n = n;
@@ -332,6 +333,9 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
             a.lines = lines;
             a.lines.push_back(LDim{np, s_axis, d_axis, true});
             a.swap_in = swap_in;
+            a.swap_out = both;  // swap . swap = identity between the passes of one axis: every pass of a
+                                // backward transform swaps on both sides, so that a kernel can take the
+                                // direction as ONE compile-time flag (coltma_kernel.cuh)
             a.epi_N = n;
             StepPlan st;
             if (!make_pass_step(st, a)) return false;
@@ -342,6 +346,7 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
         {
             AxisSpec a;
             a.n = (int)n2;
+            a.swap_in = a.swap_out = both;
             a.s_axis = a.d_axis = d_axis * n3;
             for (const LDim &l : lines) a.lines.push_back(LDim{l.n, l.d, l.d, false});
             a.lines.push_back(LDim{n1, d_axis * np, d_axis * np, false});
@@ -361,6 +366,7 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
             for (const LDim &l : lines) a.lines.push_back(LDim{l.n, l.d, l.d, false});
             a.lines.push_back(LDim{n1, d_axis * np, d_axis, false});
             a.lines.push_back(LDim{n2, d_axis * n3, d_axis * n1, false});
+            a.swap_in = both;
             a.swap_out = swap_out;
             StepPlan st;
             if (!make_pass_step(st, a)) return false;
@@ -378,6 +384,7 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
         a.lines = lines;
         a.lines.push_back(LDim{n2, s_axis, d_axis, true});
         a.swap_in = swap_in;
+        a.swap_out = both;
         a.epi_N = n;
         StepPlan st;
         if (!make_pass_step(st, a)) return false;
@@ -392,6 +399,7 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
         a.d_axis = d_axis * n1;
         for (const LDim &l : lines) a.lines.push_back(LDim{l.n, l.d, l.d, false});
         a.lines.push_back(LDim{n1, d_axis * n2, d_axis, false});
+        a.swap_in = both;
         a.swap_out = swap_out;
         StepPlan st;
         if (!make_pass_step(st, a)) return false;
@@ -565,8 +573,9 @@ inline bool build_c2c(PlanCore &pc) {
         for (int i = 0; i < (int)T.size(); ++i)
             if (i != ax) lines.push_back(LDim{T[i].n, 2 * (first ? T[i].is : T[i].os), 2 * T[i].os, false});
         for (const GDim &d : V) lines.push_back(LDim{d.n, 2 * (first ? d.is : d.os), 2 * d.os, false});
-        if (!add_c2c_axis(pc, T[ax].n, 2 * (first ? T[ax].is : T[ax].os), 2 * T[ax].os, lines,
-                          bwd && first, bwd && last, fft_dst))
+        // backward = swap re/im, forward transform, swap: applied per axis (two swaps between axes cancel)
+        (void)last;
+        if (!add_c2c_axis(pc, T[ax].n, 2 * (first ? T[ax].is : T[ax].os), 2 * T[ax].os, lines, bwd, bwd, fft_dst))
             return false;
     }
     if (relayout) {  // work array (output layout) -> the user's array

@@ -233,8 +233,7 @@ inline bool build_real(PlanCore &pc) {
             }
             const bool bwd = !r2c;
             std::vector<int> allowed = on_input ? std::vector<int>{B_IN, B_SCR} : std::vector<int>{B_OUT, B_SCR};
-            if (!add_c2c_axis(pc, T[ax].n, st_of(ax), st_of(ax), lines, bwd && oi == 0,
-                              bwd && oi + 1 == order.size(), allowed))
+            if (!add_c2c_axis(pc, T[ax].n, st_of(ax), st_of(ax), lines, bwd, bwd, allowed))
                 return false;
         }
         return true;

@@ -2,6 +2,7 @@
 // for a step (the "selector over kernel configurations" for the hot geometries).
 #pragma once
 #include "colpipe_kernel.cuh"
+#include "coltma_kernel.cuh"
 
 #ifndef B2_MINB256
 #define B2_MINB256 4
@@ -12,7 +13,7 @@ struct TileEntry {
     size_t (*smem_for)(int C);
     int (*launch)(const PassParams &, const real_t *, real_t *, long long, long long, int, size_t, b2::stream_t);
     void (*init)();
-    int pipe;  // 1: persistent, software-pipelined column kernel (colpipe_kernel.cuh)
+    int pipe;  // 1: persistent, software-pipelined column kernel (colpipe_kernel.cuh); 2: TMA column kernel (coltma_kernel.cuh)
 };
 
 template <int N, int E, int MODE, int EPI, int C>
@@ -110,6 +111,45 @@ struct TilePipeInst {
     }
 };
 
+#if defined(B2_HAVE_COLTMA)
+// persistent TMA column kernel (coltma_kernel.cuh): grid = resident CTAs, each walks a stripe of tiles
+template <int N, int EPI>
+struct ColTmaInst {
+    typedef ColTmaShape<N> H;
+    static int launch(const PassParams &p, const real_t *src, real_t *dst, long long b0, long long nb,
+                      int threads, size_t smem, b2::stream_t st) {
+        (void)threads, (void)smem;
+        CUtensorMap tm;
+        if (((uintptr_t)src & 15) != 0 || !b2_coltma_make_map(&tm, p, src, H::C, N))  // TMA needs 16-byte aligned arrays / strides
+            return TileInst<N, 16, MODE_COL, EPI, H::C>::launch(p, src, dst, b0, nb, H::THREADS,
+                                                                 TileFFT<N, 16, MODE_COL, EPI>::smem_bytes(H::C), st);
+        static int wave = -1;
+        if (wave < 0) {
+            int occ = 1;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b2_coltma_kernel<N, EPI, 0>, H::THREADS, H::SMEM) != cudaSuccess || occ < 1) {
+                cudaGetLastError();
+                occ = 1;
+            }
+            wave = occ * b2::sm_count();
+        }
+        PassParams q = p;
+        q.pf_ahead = 0;
+        const long long grid = nb < wave ? nb : wave;
+        if (p.swap_in)  // the selector takes this kernel only with swap_in == swap_out
+            b2_coltma_kernel<N, EPI, 1><<<(unsigned)grid, H::THREADS, H::SMEM, st>>>(tm, q, dst, b0, b0 + nb);
+        else
+            b2_coltma_kernel<N, EPI, 0><<<(unsigned)grid, H::THREADS, H::SMEM, st>>>(tm, q, dst, b0, b0 + nb);
+        return 0;
+    }
+    static size_t smem_for(int) { return H::SMEM; }
+    static void init() {
+        cudaFuncSetAttribute(b2_coltma_kernel<N, EPI, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, H::SMEM);
+        cudaFuncSetAttribute(b2_coltma_kernel<N, EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, H::SMEM);
+    }
+    static TileEntry entry() { return TileEntry{N, 16, MODE_COL, EPI, H::C, H::THREADS, (size_t)H::SMEM, &smem_for, &launch, &init, 2}; }
+};
+#endif
+
 // X(N, E, MODE, EPI, C): every instantiated tile kernel, in table order.
 // B2_TILE_LIST: the complex kernels (also the ones a chained launch can run);
 // B2_TILE_LIST_REAL: the variants with a real-transform prologue / epilogue (EPI 2, 3, 4).
@@ -171,12 +211,23 @@ struct TilePipeInst {
 #define B2_PIPE_LIST(P) B2_PIPE_EPIS(P, 512, 8, 8) B2_PIPE_EPIS(P, 1024, 8, 8)
 #endif
 
+// T(N, EPI): the TMA column kernels (fp32 CUDA build only); preferred over both older forms
+#if defined(B2_HAVE_COLTMA)
+#define B2_TMA_EPIS(T, N) T(N, 0) T(N, 1) T(N, 8)
+#define B2_TMA_LIST(T) B2_TMA_EPIS(T, 512) B2_TMA_EPIS(T, 1024) B2_TMA_EPIS(T, 2048)
+#else
+#define B2_TMA_LIST(T)
+#endif
+
 inline const std::vector<TileEntry> &b2_tile_table() {
 #define B2_X_ENTRY(N, E, MODE, EPI, C) TileInst<N, E, MODE, EPI, C>::entry(),
 #define B2_P_ENTRY(N, E, EPI, C) TilePipeInst<N, E, EPI, C>::entry(),
-    static const std::vector<TileEntry> tab = {B2_TILE_LIST(B2_X_ENTRY) B2_TILE_LIST_REAL(B2_X_ENTRY) B2_PIPE_LIST(B2_P_ENTRY)};
+#define B2_T_ENTRY(N, EPI) ColTmaInst<N, EPI>::entry(),
+    static const std::vector<TileEntry> tab = {B2_TILE_LIST(B2_X_ENTRY) B2_TILE_LIST_REAL(B2_X_ENTRY) B2_PIPE_LIST(B2_P_ENTRY)
+                                                   B2_TMA_LIST(B2_T_ENTRY)};
 #undef B2_X_ENTRY
 #undef B2_P_ENTRY
+#undef B2_T_ENTRY
     return tab;
 }
 
@@ -241,9 +292,22 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
     if (!getenv("FFTW_B200_PIPE_ALL") && (p.m < 1024 || p.s_axis * (long long)sizeof(real_t) >= (256ll << 10))) pipe_ok = false;
     if (const char *e = getenv("FFTW_B200_PIPE_MIN_N"))
         if (p.m < atoi(e)) pipe_ok = false;
-    for (int pass = pipe_ok ? 1 : 0; pass >= 0 && s.fast_id < 0; --pass)
+    // TMA column kernels (coltma_kernel.cuh): every stride a multiple of 16 bytes, plain tile loads, and the
+    // direction as one flag (plan_build.h gives every pass of a backward axis swap_in == swap_out).  The
+    // scattered store (slab exchange) stays on the older kernels unless FFTW_B200_TMA_SCATTER is set: a warp
+    // of this kernel stores 64-byte row segments, which is what made remote NVLink writes slow in round 1.
+    bool tma_ok = !getenv("FFTW_B200_NO_TMA") && sizeof(real_t) == 4 && p.fold_n == 0 && p.swap_in == p.swap_out &&
+                  p.nld <= 4 && s.outer.empty();
+    if (epi == 8 && !getenv("FFTW_B200_TMA_SCATTER")) tma_ok = false;
+    if (p.s_axis & 3) tma_ok = false;
+    for (int d = 1; d < p.nld; ++d)
+        if (p.ls[d] & 3) tma_ok = false;
+    if (const char *e = getenv("FFTW_B200_TMA_MIN_N"))
+        if (p.m < atoi(e)) tma_ok = false;
+    for (int pass = 2; pass >= 0 && s.fast_id < 0; --pass)
     for (size_t i = 0; i < tab.size(); ++i) {
         const TileEntry &e = tab[i];
+        if ((pass == 2 && !tma_ok) || (pass == 1 && !pipe_ok)) break;
         if (e.n != p.m || e.mode != mode || e.epi != epi || e.pipe != pass) continue;
         s.fast_id = (int)i;
         p.C = e.c;
@@ -263,7 +327,7 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         std::string rs;
         for (int i2 = 0; i2 < p.npass; ++i2) rs += (i2 ? "x" : "") + std::to_string(p.radix[i2]);
         snprintf(buf, sizeof buf, "%s n=%d tile-kernel[%s%s%s] E=%d regs-resident, tile=%dx%d ctas=%lld threads=%d smem=%zuB",
-                 real_half ? (epi == 3 ? "r2c" : "c2r") : "c2c", real_half ? p.n : p.m, mn[mode], e.pipe ? ", persistent, async-copy pipelined" : "", p.fold_n > 0 ? (p.swap_in ? "+hermitian unfold+twiddle" : "+hermitian fold") : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
+                 real_half ? (epi == 3 ? "r2c" : "c2r") : "c2c", real_half ? p.n : p.m, mn[mode], e.pipe == 2 ? ", persistent, TMA-fed, two line groups" : e.pipe ? ", persistent, async-copy pipelined" : "", p.fold_n > 0 ? (p.swap_in ? "+hermitian unfold+twiddle" : "+hermitian fold") : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
         s.desc = buf;
         return;
     }
