@@ -302,6 +302,10 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
     if (p.s_axis & 3) tma_ok = false;
     for (int d = 1; d < p.nld; ++d)
         if (p.ls[d] & 3) tma_ok = false;
+    // Measured on B200 (profiles/r2_col_probe.md): 512 points at a pitch of MiBs (the x axis of a 512^3 cube:
+    // every row of a tile in another 2 MiB page) is the one case where the round-1 kernel is faster (0.461 against
+    // 0.513 ms per GiB); 1024 / 2048 points at such pitches are equal or better with TMA
+    if (p.m <= 512 && p.s_axis * (long long)sizeof(real_t) >= (1ll << 20) && !getenv("FFTW_B200_TMA_ALL")) tma_ok = false;
     if (const char *e = getenv("FFTW_B200_TMA_MIN_N"))
         if (p.m < atoi(e)) tma_ok = false;
     for (int pass = 2; pass >= 0 && s.fast_id < 0; --pass)
