@@ -158,6 +158,23 @@ b2fft_comm *b2fft_comm_detached(int n_pes, int my_pe);
 /* device time (ms) of the last slab execute split into local FFT / exchange / local FFT */
 int b2fft_slab_last_times(const b2fft_plan *p, float *ms_fft1, float *ms_exchange, float *ms_fft2);
 
+/* ---- batched 1-D c2c that allocates nothing ----------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  A variant of the engine's
+ * two-pass (n = n1 * n2) long 1-D transform whose intermediate array and twiddle table live in a file-scope
+ * static __device__ array of the library (csrc/noalloc.cu) instead of plan-owned cudaMalloc'ed buffers.
+ * No plan, no cudaMalloc / cudaFree, no allocating library call; asynchronous on `cuda_stream`.
+ *   n        power of two, 64 <= n <= B2FFT_NOALLOC_MAX_N
+ *   howmany  contiguous transforms (dist n), n * howmany <= B2FFT_NOALLOC_MAX_POINTS, howmany <= 65535
+ *   in, out  DEVICE pointers to interleaved complex of the library's precision; in == out is allowed
+ *   sign     -1 forward, +1 backward (unnormalised, like fftw_execute)
+ * Returns 0, or non-zero with the reason in b2fft_last_error() (sizes beyond the maxima are rejected).
+ * Every call shares the one array (its previous contents are never read); calls that overlap on the GPU
+ * -- different streams without ordering -- race on it and must be serialised by the caller. */
+#define B2FFT_NOALLOC_MAX_POINTS (1 << 20)
+#define B2FFT_NOALLOC_MAX_N (1 << 16)
+int b2fft_c2c_1d_static_scratch(ptrdiff_t n, ptrdiff_t howmany, const void *in, void *out, int sign, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
