@@ -242,13 +242,38 @@ struct SlabPlan {
     // hybrid: the n1 pass stores the rows this rank owns straight into its own receive buffer and leaves
     // the others in place for the DMA, which then skips the local 1/P of the exchange
     bool hybrid = false;
+    // ---- round-2 schedule ("v2") for transposed-output c2c: chunks run along the CONTIGUOUS dimension ----
+    //   row pass over the whole slab, in -> W (W = the caller's output array: no send buffer at all), then per
+    //   chunk k of v2_w consecutive columns:  n1 pass in place on W | exchange W -> R (one 3-D DMA per peer)
+    //   | cross-rank barrier | n0 pass R -> out.  The exchange of chunk k overlaps the n1 pass of chunk k+1
+    //   AND the n0 passes of the chunks before it (round 1 chunked along n0, so its last stage could only
+    //   start after the whole exchange; reference shape of the messages: fftw/mpi/transpose-alltoall.c:224-227).
+    bool v2 = false;
+    int v2_nch = 1, v2_lag = 2;
+    ptrdiff_t v2_w = 0;
+    b2fft_plan *v2_row[2] = {nullptr, nullptr};  // [0] out of place, [1] in place; built on first use
+    b2fft_plan *v2_n1 = nullptr, *v2_n0 = nullptr;
+    // the n1 pass stores the rows THIS rank owns straight into its own receive buffer (tile-kernel epilogue 8,
+    // self only); the copy engines then move the remote blocks only.  Measured (profiles/r2_peer_copy.md): a
+    // strided same-GPU copy runs at ~0.6 TB/s on a copy engine, slower than the NVLink copies beside it.
+    bool v2_hyb = false;
 #if B2_CUDA
     // DMA exchange: one stream per peer so that the copies to different peers run on different copy engines
     std::vector<cudaStream_t> sx;
     std::vector<cudaEvent_t> evx;
     cudaEvent_t evb = nullptr;
+    cudaStream_t sb = nullptr;               // v2: barriers run beside the copy stream
+    std::vector<cudaEvent_t> v2_e1, v2_ec, v2_e2;  // per chunk: n1 pass done, copies done, every rank's copies done
+    cudaEvent_t v2_eb = nullptr, v2_ta = nullptr, v2_tb = nullptr;
 #endif
 };
+
+// the send buffer of the round-1 schedule and of the staged API: allocated when first needed (the v2 schedule
+// works in the caller's output array instead, which is what lets 2048^3 run on one 180 GB GPU)
+static bool slab_ensure_S(SlabPlan &s) {
+    if (!s.S) s.S = (cpx_t *)dev_malloc(s.s_elems * sizeof(cpx_t));
+    return s.S != nullptr;
+}
 
 // switch the stage-1 plans to the scattered store; all-or-nothing
 static void slab_enable_fused(SlabPlan &s) {
@@ -277,6 +302,7 @@ static void slab_enable_fused(SlabPlan &s) {
 
 #if B2_CUDA
 static int slab_setup_p2p(SlabPlan &s);
+static bool slab_setup_v2(SlabPlan &s);
 #endif
 
 static b2fft_plan *make_stage1(const SlabPlan &s, ptrdiff_t planes) {
@@ -417,7 +443,17 @@ void b2_slab_destroy(b2fft_plan_s *p) {
     b2fft_plan_destroy(s->p2);
     b2fft_plan_destroy(s->pA);
     b2fft_plan_destroy(s->pB);
+    b2fft_plan_destroy(s->v2_row[0]);
+    b2fft_plan_destroy(s->v2_row[1]);
+    b2fft_plan_destroy(s->v2_n1);
+    b2fft_plan_destroy(s->v2_n0);
 #if B2_CUDA
+    for (std::vector<cudaEvent_t> *v : {&s->v2_e1, &s->v2_ec, &s->v2_e2})
+        for (cudaEvent_t e : *v)
+            if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : {s->v2_eb, s->v2_ta, s->v2_tb})
+        if (e) cudaEventDestroy(e);
+    if (s->sb) cudaStreamDestroy(s->sb);
     for (int q = 0; q < (int)s->peerS.size(); ++q)
         if (q != s->pe) {
             if (s->peerS[q]) cudaIpcCloseMemHandle(s->peerS[q]);
@@ -457,7 +493,9 @@ static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
              s->transposed_in ? (s->kind == B2FFT_C2C ? " (first two dims exchanged: FFTW_MPI_TRANSPOSED_IN)" : " (transposed input)") : "", s->hm, s->P, s->pe,
              s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
              s->nchunks, s->chunk,
-             s->fused ? "fused into the n1 pass: rows stored straight into their owner's receive buffer (peer memory over NVLink)"
+             s->v2 ? (s->v2_hyb ? "v2: chunks along the contiguous dimension; local block stored by the n1 pass, one 3-D DMA per peer and chunk into peer memory; the n0 passes overlap it"
+                                : "v2: chunks along the contiguous dimension, one 3-D DMA per owner and chunk, the n0 passes overlap it")
+             : s->fused ? "fused into the n1 pass: rows stored straight into their owner's receive buffer (peer memory over NVLink)"
              : s->hybrid ? "local block stored by the n1 pass, remote blocks by strided DMA into peer memory (CUDA IPC over NVLink), NCCL barrier"
              : s->P == 1 ? "local copy" : s->p2p ? "strided DMA into peer memory (CUDA IPC over NVLink), NCCL barrier"
                                                 : "ncclSend/ncclRecv per plane and peer",
@@ -606,10 +644,13 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
     }
     s->s_elems = (size_t)std::max<ptrdiff_t>(1, s->ln0 * n1 * n2);
     s->r_elems = (size_t)std::max<ptrdiff_t>(1, n0 * s->ln1 * n2);
+    // v2 schedule: transposed-output c2c (after the TRANSPOSED_IN swap above).  Every rank decides alike.
+    // (CUDA build only: the emulation build drives the stages one by one through b2fft_slab_stage)
+    s->v2 = B2_CUDA && kind == B2FFT_C2C && s->transposed_out && !getenv("B2FFT_SLAB_NO_V2");
     if (ok) {
-        s->S = (cpx_t *)dev_malloc(s->s_elems * sizeof(cpx_t));
+        if (!s->v2) ok = slab_ensure_S(*s);  // v2 works in the caller's output array
         s->R = (cpx_t *)dev_malloc(s->r_elems * sizeof(cpx_t));
-        ok = s->S && s->R;
+        ok = ok && s->R;
     }
 #if B2_CUDA
     if (ok) {
@@ -619,13 +660,17 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
         for (cudaEvent_t &e : s->ev) ok = ok && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
         for (cudaEvent_t *e : {&s->t0, &s->t1, &s->t2, &s->t3}) ok = ok && cudaEventCreate(e) == cudaSuccess;
         if (ok) ok = slab_setup_p2p(*s) == 0;
-        if (ok && s->p2p && kind != B2FFT_C2R) slab_enable_fused(*s);
+        if (s->v2 && s->P > 1 && !s->p2p) s->v2 = false;  // no peer mapping: grouped send / receive (round-1 schedule)
+        if (ok && s->p2p && kind != B2FFT_C2R && !s->v2) slab_enable_fused(*s);
     }
 #endif
     if (ok && s->P == 1 && kind != B2FFT_C2R) {  // one rank: the "exchange" is the scatter into this rank's own receive buffer
         s->peerR.assign(1, s->R);
-        slab_enable_fused(*s);
+        if (!s->v2) slab_enable_fused(*s);
     }
+#if B2_CUDA
+    if (ok && s->v2) ok = slab_setup_v2(*s);
+#endif
     if (!ok) {
         b2_slab_destroy(bp);
         delete bp;
@@ -636,6 +681,76 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
     slab_describe(*s, bp);
     return bp;
 }
+
+#if B2_CUDA
+static bool slab_setup_v2(SlabPlan &s) {
+    // chunk width: whole 128-byte segments, rows of >= 1 KiB for the copy engines; else fewer chunks
+    int nch = 8;
+    if (const char *e = getenv("B2FFT_SLAB_V2_CHUNKS")) nch = std::max(1, atoi(e));
+    while (nch > 1 && (s.n2 % nch != 0 || (s.n2 / nch) % 16 != 0 || s.n2 / nch < 128)) --nch;
+    s.v2_nch = nch;
+    s.v2_w = s.n2 / nch;
+    if (const char *e = getenv("B2FFT_SLAB_V2_LAG")) s.v2_lag = std::max(0, atoi(e));
+    b2fft_geom g;
+    if (s.ln0 > 0) {  // n1 pass of one chunk, in place on W[ln0][n1][n2]
+        memset(&g, 0, sizeof g);
+        g.kind = B2FFT_C2C;
+        g.sign = s.sign;
+        g.rank = 1;
+        g.dims[0] = b2fft_dim{s.n1, s.n2, s.n2};
+        g.vrank = 2;
+        g.vdims[0] = b2fft_dim{s.v2_w, 1, 1};
+        g.vdims[1] = b2fft_dim{s.ln0, s.n1 * s.n2, s.n1 * s.n2};
+        g.in_place = 1;
+        s.v2_n1 = b2fft_plan_create(&g);
+        if (!s.v2_n1) return false;
+        if (!getenv("B2FFT_SLAB_V2_NO_HYBRID") && s.P <= B2_MAXSCAT && (int)s.peerR.size() == s.P) {
+            std::vector<long long> ps(s.P);
+            for (int o = 0; o < s.P; ++o) ps[o] = (long long)blk_len(s.n1, s.b1, o) * s.n2 * 2;
+            s.v2_hyb = b2_plan_enable_scatter(s.v2_n1, s.P, (long long)s.b1, (long long)s.n1 * s.n2 * 2, ps.data(), s.pe) == 0;
+        }
+    }
+    if (s.ln1 > 0) {  // n0 pass of one chunk, R[n0][ln1][n2] -> out[ln1][n0][n2]
+        memset(&g, 0, sizeof g);
+        g.kind = B2FFT_C2C;
+        g.sign = s.sign;
+        g.rank = 1;
+        g.dims[0] = b2fft_dim{s.n0, s.ln1 * s.n2, s.n2};
+        g.vrank = 2;
+        g.vdims[0] = b2fft_dim{s.v2_w, 1, 1};
+        g.vdims[1] = b2fft_dim{s.ln1, s.n2, s.n0 * s.n2};
+        g.in_place = 0;
+        s.v2_n0 = b2fft_plan_create(&g);
+        if (!s.v2_n0) return false;
+    }
+    bool ok = cudaStreamCreateWithFlags(&s.sb, cudaStreamNonBlocking) == cudaSuccess;
+    for (std::vector<cudaEvent_t> *v : {&s.v2_e1, &s.v2_ec, &s.v2_e2}) {
+        v->assign(nch, nullptr);
+        for (cudaEvent_t &e : *v) ok = ok && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
+    }
+    ok = ok && cudaEventCreateWithFlags(&s.v2_eb, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreate(&s.v2_ta) == cudaSuccess && cudaEventCreate(&s.v2_tb) == cudaSuccess;
+    return ok;
+}
+// the row pass over the whole slab (contiguous dimension), in -> W; built on first use because in-placeness is
+// only known at execute time
+static b2fft_plan *slab_v2_row_plan(SlabPlan &s, bool inplace) {
+    b2fft_plan *&p = s.v2_row[inplace ? 1 : 0];
+    if (p || s.ln0 <= 0) return p;
+    b2fft_geom g;
+    memset(&g, 0, sizeof g);
+    g.kind = B2FFT_C2C;
+    g.sign = s.sign;
+    g.rank = 1;
+    g.dims[0] = b2fft_dim{s.n2f, s.hm, s.hm};
+    g.vrank = s.hm > 1 ? 2 : 1;
+    g.vdims[0] = b2fft_dim{s.ln0 * s.n1, s.n2, s.n2};
+    g.vdims[1] = b2fft_dim{s.hm, 1, 1};
+    g.in_place = inplace ? 1 : 0;
+    p = b2fft_plan_create(&g);
+    return p;
+}
+#endif
 
 // ------------------------------------------------------------------ exchange
 // forward: send from `sb` (stage-1 output layout) and receive into `rb` (recv layout);
@@ -704,11 +819,12 @@ static int slab_setup_p2p(SlabPlan &s) {
     B2_CK(cudaMemset(s.flag, 0, 256));
     struct H {
         cudaIpcMemHandle_t s, r;
-        int ok;
+        int ok, has_s;
     };
     H mine;
     memset(&mine, 0, sizeof mine);
-    mine.ok = !getenv("B2FFT_SLAB_SENDRECV") && cudaIpcGetMemHandle(&mine.s, s.S) == cudaSuccess &&
+    mine.has_s = s.S != nullptr;  // the v2 schedule has no send buffer
+    mine.ok = !getenv("B2FFT_SLAB_SENDRECV") && (!s.S || cudaIpcGetMemHandle(&mine.s, s.S) == cudaSuccess) &&
               cudaIpcGetMemHandle(&mine.r, s.R) == cudaSuccess;
     cudaGetLastError();
     H *dev = nullptr;
@@ -731,7 +847,7 @@ static int slab_setup_p2p(SlabPlan &s) {
                 s.peerR[p] = s.R;
                 continue;
             }
-            if (cudaIpcOpenMemHandle((void **)&s.peerS[p], all[p].s, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+            if ((all[p].has_s && cudaIpcOpenMemHandle((void **)&s.peerS[p], all[p].s, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ||
                 cudaIpcOpenMemHandle((void **)&s.peerR[p], all[p].r, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
                 cudaGetLastError();
                 good = 0.0f;
@@ -841,6 +957,7 @@ extern "C" int b2fft_slab_set_peer_recv(b2fft_plan *p, void *const *recv, int n)
 extern "C" int b2fft_slab_stage(b2fft_plan *p, int stage, void *in, void *out) {
     if (!p || !p->slab) return -1;
     SlabPlan &s = *p->slab;
+    if (!slab_ensure_S(s)) return -3;
     stream_t st = nullptr;
 #if B2_CUDA
     st = s.sc;
@@ -878,9 +995,91 @@ extern "C" int b2fft_slab_stage(b2fft_plan *p, int stage, void *in, void *out) {
 extern "C" void *b2fft_slab_buffer(b2fft_plan *p, int which, size_t *bytes) {
     if (!p || !p->slab) return nullptr;
     SlabPlan &s = *p->slab;
+    if (which == 0 && !slab_ensure_S(s)) return nullptr;
     if (bytes) *bytes = (which == 0 ? s.s_elems : s.r_elems) * sizeof(cpx_t);
     return which == 0 ? (void *)s.S : (void *)s.R;
 }
+
+#if B2_CUDA
+// v2 schedule (see SlabPlan): din / dout are device arrays, W = dout.
+//   compute stream sc :  row pass | n1(0) n1(1) [n0(0)] n1(2) [n0(1)] ...  (n0(k) is queued v2_lag chunks behind
+//                        n1(k) so that the stream does not stall on a chunk still in flight)
+//   copy stream sn    :  per chunk, one strided 3-D copy per peer straight into the peer's receive buffer at its
+//                        final position, peers in the shifted order pe + d (one sender per receiver at a time)
+//   barrier stream sb :  per chunk, "every rank's copies of this chunk have landed" (1-float NCCL all-reduce)
+static int slab_execute_v2(SlabPlan &s, cpx_t *din, cpx_t *dout) {
+    const size_t esz = sizeof(cpx_t);
+    const int nch = s.v2_nch;
+    cpx_t *W = dout;
+    B2_CK(cudaEventRecord(s.t0, s.sc));
+    // nobody may still be reading the receive buffer that this execute is about to overwrite
+    if (s.P > 1) {
+        int rc = slab_barrier(s, s.sb);
+        if (rc) return rc;
+        B2_CK(cudaEventRecord(s.v2_eb, s.sb));
+        B2_CK(cudaStreamWaitEvent(s.sn, s.v2_eb, 0));
+    }
+    if (s.ln0 > 0) {
+        b2fft_plan *row = slab_v2_row_plan(s, din == dout);
+        if (!row) return -6;
+        int rc = b2fft_execute_async(row, din, W, s.sc);
+        if (rc) return rc;
+    }
+    B2_CK(cudaEventRecord(s.v2_ta, s.sc));
+    auto n0_pass = [&](int k) -> int {
+        B2_CK(cudaStreamWaitEvent(s.sc, s.v2_e2[k], 0));
+        if (!s.v2_n0) return 0;
+        return b2fft_execute_async(s.v2_n0, s.R + (size_t)k * s.v2_w, dout + (size_t)k * s.v2_w, s.sc);
+    };
+    for (int k = 0; k < nch; ++k) {
+        if (s.v2_n1) {
+            cpx_t *wk = W + (size_t)k * s.v2_w;
+            int rc;
+            if (s.v2_hyb) {
+                real_t *bases[B2_MAXSCAT];
+                for (int o = 0; o < s.P; ++o) bases[o] = (real_t *)(s.peerR[o] + (size_t)k * s.v2_w);
+                rc = b2_plan_execute_scatter(s.v2_n1, wk, wk, bases, (long long)s.s0, s.sc);
+            } else
+                rc = b2fft_execute_async(s.v2_n1, wk, wk, s.sc);
+            if (rc) return rc;
+        }
+        B2_CK(cudaEventRecord(s.v2_e1[k], s.sc));
+        B2_CK(cudaStreamWaitEvent(s.sn, s.v2_e1[k], 0));
+        for (int d = 0; d < s.P && s.ln0 > 0; ++d) {
+            const int pe = (s.pe + d) % s.P;
+            const ptrdiff_t ln1p = blk_len(s.n1, s.b1, pe);
+            if (ln1p <= 0 || (s.v2_hyb && pe == s.pe)) continue;  // (hybrid: the n1 pass stored the local block itself)
+            cudaMemcpy3DParms q;
+            memset(&q, 0, sizeof q);
+            q.srcPtr = make_cudaPitchedPtr((void *)W, (size_t)s.n2 * esz, (size_t)s.n2 * esz, (size_t)s.n1);
+            q.srcPos = make_cudaPos((size_t)k * s.v2_w * esz, (size_t)(pe * s.b1), 0);
+            q.dstPtr = make_cudaPitchedPtr((void *)s.peerR[pe], (size_t)s.n2 * esz, (size_t)s.n2 * esz, (size_t)ln1p);
+            q.dstPos = make_cudaPos((size_t)k * s.v2_w * esz, 0, (size_t)s.s0);
+            q.extent = make_cudaExtent((size_t)s.v2_w * esz, (size_t)ln1p, (size_t)s.ln0);
+            q.kind = cudaMemcpyDeviceToDevice;
+            B2_CK(cudaMemcpy3DAsync(&q, s.sn));
+        }
+        B2_CK(cudaEventRecord(s.v2_ec[k], s.sn));
+        B2_CK(cudaStreamWaitEvent(s.sb, s.v2_ec[k], 0));
+        if (s.P > 1) {
+            int rc = slab_barrier(s, s.sb);
+            if (rc) return rc;
+        }
+        B2_CK(cudaEventRecord(s.v2_e2[k], s.sb));
+        if (k >= s.v2_lag) {
+            int rc = n0_pass(k - s.v2_lag);
+            if (rc) return rc;
+        }
+    }
+    B2_CK(cudaEventRecord(s.v2_tb, s.sc));
+    for (int k = std::max(0, nch - s.v2_lag); k < nch; ++k) {
+        int rc = n0_pass(k);
+        if (rc) return rc;
+    }
+    B2_CK(cudaEventRecord(s.t3, s.sc));
+    return 0;
+}
+#endif
 
 int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
     SlabPlan &s = *p->slab;
@@ -898,10 +1097,25 @@ int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
         B2_CK(cudaMemcpyAsync(din, in, in_b, cudaMemcpyHostToDevice, s.sc));
     }
     if (hout) {
-        if (!s.dev_out) s.dev_out = (cpx_t *)dev_malloc(std::max<size_t>(out_b, 16));
+        // (the v2 schedule also works in this array: it must hold the stage-1 layout too)
+        if (!s.dev_out) s.dev_out = (cpx_t *)dev_malloc(std::max<size_t>(std::max(out_b, s.v2 ? in_b : (size_t)0), 16));
         if (!s.dev_out) return -3;
         dout = s.dev_out;
     }
+    if (s.v2) {
+        int rc = slab_execute_v2(s, din, dout);
+        if (rc) return rc;
+        if (hout) B2_CK(cudaMemcpyAsync(out, dout, out_b, cudaMemcpyDeviceToHost, s.sc));
+        B2_CK(cudaStreamSynchronize(s.sc));
+        B2_CK(cudaStreamSynchronize(s.sn));
+        B2_CK(cudaStreamSynchronize(s.sb));
+        // row pass | pipelined n1 passes, exchange and n0 passes | the n0 passes left after the last n1 pass
+        cudaEventElapsedTime(&s.ms[0], s.t0, s.v2_ta);
+        cudaEventElapsedTime(&s.ms[1], s.v2_ta, s.v2_tb);
+        cudaEventElapsedTime(&s.ms[2], s.v2_tb, s.t3);
+        return 0;
+    }
+    if (!slab_ensure_S(s)) return -3;
     B2_CK(cudaEventRecord(s.t0, s.sc));
     if (s.kind == B2FFT_C2R) {
         int rc = 0;

@@ -294,11 +294,11 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         if (p.m < atoi(e)) pipe_ok = false;
     // TMA column kernels (coltma_kernel.cuh): every stride a multiple of 16 bytes, plain tile loads, and the
     // direction as one flag (plan_build.h gives every pass of a backward axis swap_in == swap_out).  The
-    // scattered store (slab exchange) stays on the older kernels unless FFTW_B200_TMA_SCATTER is set: a warp
-    // of this kernel stores 64-byte row segments, which is what made remote NVLink writes slow in round 1.
+    // store scattered to REMOTE owners (fused slab exchange) stays on the older kernels unless FFTW_B200_TMA_SCATTER
+    // is set: a warp of this kernel stores 64-byte row segments, which is what made remote NVLink writes slow in round 1.
     bool tma_ok = !getenv("FFTW_B200_NO_TMA") && sizeof(real_t) == 4 && p.fold_n == 0 && p.swap_in == p.swap_out &&
                   p.nld <= 4 && s.outer.empty();
-    if (epi == 8 && !getenv("FFTW_B200_TMA_SCATTER")) tma_ok = false;
+    if (epi == 8 && p.scat_self1 == 0 && !getenv("FFTW_B200_TMA_SCATTER")) tma_ok = false;  // (self-only scatter = local stores: fine)
     if (p.s_axis & 3) tma_ok = false;
     for (int d = 1; d < p.nld; ++d)
         if (p.ls[d] & 3) tma_ok = false;

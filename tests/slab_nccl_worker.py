@@ -69,6 +69,18 @@ def main():
             assert err < tol, (rank, transposed, sign, err)
             assert np.array_equal(x.cpu().numpy(), xin), "out-of-place slab transform must preserve its input"
             lib.destroy_plan(plan)
+            if transposed:  # in place on one alloc_local-sized array (how BASELINE config 5 is quoted)
+                z = torch.from_numpy(xin).cuda()
+                plan = L.fftw_mpi_plan_dft_3d(n0, n1, n2, z.data_ptr(), z.data_ptr(), comm, sign,
+                                              capi.FFTW_ESTIMATE | (1 << 30))
+                assert plan, L.b2fft_last_error()
+                lib.execute(plan)
+                torch.cuda.synchronize()
+                got = z.cpu().numpy()[:ref.size].reshape(ref.shape)
+                err = float(np.linalg.norm(got - ref) / np.linalg.norm(ref)) if ref.size else 0.0
+                worst = max(worst, err)
+                assert err < tol, (rank, "in place", sign, err)
+                lib.destroy_plan(plan)
     # ---- real data: r2c (natural / transposed output) and c2r back (natural / transposed input)
     for nm in ("fftw_mpi_plan_dft_r2c_3d", "fftw_mpi_plan_dft_c2r_3d"):
         f = getattr(L, nm)

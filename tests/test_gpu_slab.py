@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 @pytest.mark.parametrize("prec", ["fp32", "fp64"])
 @pytest.mark.parametrize("transposed", [True, False])
-@pytest.mark.parametrize("shape", [(64, 48, 32), (20, 64, 24), (6, 1024, 40)], ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("shape", [(64, 48, 32), (20, 64, 24), (6, 1024, 40), (8, 12, 512)], ids=lambda s: "x".join(map(str, s)))
 def test_single_rank_device_arrays(prec, transposed, shape):
     """n1 = 64 / 1024: the n1 pass scatters straight into this rank's own receive buffer (fused exchange);
     n1 = 48: staged copy"""
@@ -120,10 +120,12 @@ def test_single_rank_real_data(prec, shape):
         lib.destroy_plan(plan)
 
 
-@pytest.mark.parametrize("shape", [(48, 40, 32), (50, 30, 16), (24, 64, 32), (21, 512, 48)],
+@pytest.mark.parametrize("shape", [(48, 40, 32), (50, 30, 16), (24, 64, 32), (21, 512, 48), (10, 12, 512), (512, 16, 256)],
                          ids=lambda s: "x".join(map(str, s)))
 def test_two_ranks_over_nccl(shape):
-    """n1 = 64, 512: the exchange is fused into the n1 pass (stores into peer memory); 40, 30: DMA path"""
+    """transposed output: the round-2 schedule (chunks along the contiguous dimension: 1 chunk for n2 < 256, 2 at 256,
+    4 at 512; uneven blocks at n0 = 21, 50); natural output: n1 = 64, 512 fuse the exchange into the n1 pass
+    (stores into peer memory), 40, 30 take the DMA path"""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
