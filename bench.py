@@ -130,16 +130,27 @@ def reference_lib(prec):
     return capi.FFTW3Lib(path, prec == "fp32")
 
 
-def cpu_sample_of(w, budget_s=20.0):
-    """a bounded sample of the workload: same transform, fewer of them"""
+def cpu_sample_of(w, name=None):
+    """what the reference arm runs: the FULL workload where the host can hold it and a step stays around 0.1 s
+    (the headline config: 65536 transforms of 4096 points, 2 GiB in + 2 GiB out), else a bounded sample of it
+    (same transform, fewer of them); the record says which"""
     s = dict(w)
     N = int(np.prod(w["n"]))
+    if name == DEFAULT_WORKLOAD:
+        return s
     if w["howmany"] > 1:
         # ~1.5 GFLOP-conv per repetition keeps a rep well under a second on a few cores
         s["howmany"] = max(1, min(w["howmany"], int(1.5e9 / (5.0 * N * math.log2(N))) or 1))
     elif len(w["n"]) == 3 and N > 256 ** 3:
         s["n"] = [256, 256, 256]
     return s
+
+
+def fill_uniform(a, rng, chunk=1 << 24):
+    """uniform [-0.5, 0.5) per real component, in place, in chunks (no array-sized temporaries)"""
+    flat = a.reshape(-1).view(np.float32 if a.dtype in (np.complex64, np.float32) else np.float64)
+    for i in range(0, flat.size, chunk):
+        flat[i:i + chunk] = rng.random(min(chunk, flat.size - i), dtype=np.float32 if flat.dtype == np.float32 else np.float64) - 0.5
 
 
 def run_reference(w, steps, warmup, threads=None, measure=True):
@@ -162,17 +173,17 @@ def run_reference(w, steps, warmup, threads=None, measure=True):
         x = np.zeros((hm, N), dtype=lib.cplx)
         y = x if w.get("inplace") else np.zeros_like(x)
         p = lib.plan_many_dft(n, hm, x, None, 1, N, y, None, 1, N, capi.FFTW_FORWARD, flags)
-        x[:] = ((rng.random(x.shape) - 0.5) + 1j * (rng.random(x.shape) - 0.5)).astype(lib.cplx)
+        fill_uniform(x, rng)
     elif w["kind"] == "r2c":
         x = np.zeros((hm, N), dtype=lib.real)
         y = np.zeros((hm, N // n[-1] * (n[-1] // 2 + 1)), dtype=lib.cplx)
         p = lib.plan_many_dft_r2c(n, hm, x, None, 1, N, y, None, 1, y.shape[1], flags)
-        x[:] = (rng.random(x.shape) - 0.5).astype(lib.real)
+        fill_uniform(x, rng)
     else:
         y = np.zeros((hm, N), dtype=lib.real)
         x = np.zeros((hm, N // n[-1] * (n[-1] // 2 + 1)), dtype=lib.cplx)
         p = lib.plan_many_dft_c2r(n, hm, x, None, 1, x.shape[1], y, None, 1, N, flags)
-        x[:] = ((rng.random(x.shape) - 0.5) + 1j * (rng.random(x.shape) - 0.5)).astype(lib.cplx)
+        fill_uniform(x, rng)
     assert p, "reference plan is NULL"
     for _ in range(warmup):
         lib.execute(p)
@@ -185,7 +196,7 @@ def run_reference(w, steps, warmup, threads=None, measure=True):
     return {"value": flops / dt / 1e9, "unit": "GFLOP/s", "cores": cores, "kind": kind,
             "sample": f"{w['kind']} n={'x'.join(map(str, n))} howmany={hm} {w['prec']}, "
                       f"{'FFTW_MEASURE' if measure else 'FFTW_ESTIMATE'}, {cores} threads, AVX2",
-            "ms_per_step": dt * 1e3}
+            "ms_per_step": dt * 1e3, "howmany": hm, "n": list(n)}
 
 
 # ------------------------------------------------------------------------------- GPU arm
@@ -237,6 +248,165 @@ def fftw_plan_bp(plan):
     return C.cast(plan, C.POINTER(C.c_void_p))[0]
 
 
+def device_arrays(lib, w, seed):
+    """device-resident synthetic input (uniform [-0.5, 0.5), like the reference verifier) and output array"""
+    import torch
+    (ishape, idt), (oshape, odt) = io_shapes(lib, w)
+    tmap = {np.complex64: torch.complex64, np.complex128: torch.complex128, np.float32: torch.float32, np.float64: torch.float64}
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    rdt = torch.float32 if w["prec"] == "fp32" else torch.float64
+    if idt in (np.complex64, np.complex128):
+        x = torch.view_as_complex(torch.empty(ishape + (2,), device="cuda", dtype=rdt).uniform_(-0.5, 0.5, generator=g))
+    else:
+        x = torch.empty(ishape, device="cuda", dtype=rdt).uniform_(-0.5, 0.5, generator=g)
+    y = x if w.get("inplace") else torch.empty(oshape, device="cuda", dtype=tmap[odt])
+    return x, y
+
+
+def validate(lib, w, x, y, plan):
+    """the bench refuses to post a number for garbage: after the timed loop, the plan's output is compared with
+    numpy's double-precision FFT on sampled rows (batched 1-D) or, for a 3-D cube, with direct double-precision
+    summation at 64 sampled bins plus Parseval (the checker is numpy / torch arithmetic, never the timed path)"""
+    import torch
+    n, hm = w["n"], w["howmany"]
+    N = int(np.prod(n))
+    tol = (1e-6 if w["prec"] == "fp32" else 1e-14) * math.log2(N)
+    if w.get("inplace"):  # re-seed: the timed loop transformed the array over and over
+        x2, _ = device_arrays(lib, w, 1)
+        x.copy_(x2)
+        del x2
+    rows = sorted({0, hm // 2, hm - 1}) if len(n) == 1 else []
+    rows_in = {r: x[r].cpu().numpy() for r in rows}  # (before the execute: out-of-place c2r may destroy its input)
+    xin = x.clone() if (w.get("inplace") and len(n) > 1) else x
+    lib.execute(plan)
+    torch.cuda.synchronize()
+    errs = []
+    if len(n) == 1:
+        for r in rows:
+            a = rows_in[r]
+            got = y[r].cpu().numpy().astype(np.complex128 if w["kind"] != "c2r" else np.float64)
+            if w["kind"] == "c2c":
+                ref = np.fft.fft(a.astype(np.complex128))
+            elif w["kind"] == "r2c":
+                ref = np.fft.rfft(a.astype(np.float64))
+            else:
+                ref = np.fft.irfft(a.astype(np.complex128), n[0]) * n[0]
+            errs.append(float(np.linalg.norm(got - ref) / np.linalg.norm(ref)))
+    else:
+        xd = xin.reshape(n).to(torch.complex128)
+        ks = [sorted({0, 1, m // 2, m - 1}) for m in n]
+        Ws = [torch.polar(torch.ones(m, len(k), dtype=torch.float64, device="cuda"),
+                          -2.0 * math.pi * torch.remainder(torch.arange(m, device="cuda", dtype=torch.float64)[:, None]
+                                                           * torch.tensor(k, device="cuda", dtype=torch.float64)[None, :], m) / m)
+              for m, k in zip(n, ks)]
+        t = torch.einsum("abc,cz->abz", xd, Ws[2])
+        t = torch.einsum("abz,by->ayz", t, Ws[1])
+        ref = torch.einsum("ayz,ax->xyz", t, Ws[0])
+        got = y.reshape(n)[ks[0]][:, ks[1]][:, :, ks[2]].to(torch.complex128)
+        errs.append(float((torch.linalg.norm(got - ref) / torch.linalg.norm(ref)).item()))
+        sx = float((xd.real ** 2 + xd.imag ** 2).sum().item())
+        yd = y.reshape(n).to(torch.complex128)
+        errs.append(abs(float((yd.real ** 2 + yd.imag ** 2).sum().item()) / (N * sx) - 1.0))
+        del xd, yd, t
+    worst = max(errs)
+    assert worst < tol, f"bench output check failed for {w}: {errs} (tolerance {tol})"
+    return {"worst_rel_err": worst, "tolerance": tol,
+            "against": "numpy fp64 FFT of sampled rows" if len(n) == 1 else "fp64 direct summation at 64 sampled bins + Parseval"}
+
+
+def time_device(lib, w, plan, x, y, steps, warmup, world=1):
+    """device-resident timing with CUDA events on the launching stream.  Out of place: ONE bracket around exactly
+    `steps` steps.  In place (unnormalised transform applied to its own output): per-step event pairs with a
+    rescale between them, outside the pairs, so that the data stays finite."""
+    import torch
+    import torch.distributed as dist
+    bp = fftw_plan_bp(plan)
+    stream = torch.cuda.current_stream()
+    sp = C.c_void_p(stream.cuda_stream)
+    inplace = bool(w.get("inplace"))
+    inv = 1.0 / math.sqrt(float(np.prod(w["n"])))
+
+    def step():
+        rc = lib.lib.b2fft_execute_async(bp, x.data_ptr(), y.data_ptr(), sp)
+        assert rc == 0, lib.lib.b2fft_last_error()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, warmup)):
+        step()
+        if inplace:
+            x.mul_(inv)
+    barrier()
+    l0 = lib.lib.b2fft_launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * steps)]
+    with ClockSampler(torch.cuda.current_device()) as clk:
+        for i in range(steps):
+            ev[2 * i].record(stream)
+            step()
+            ev[2 * i + 1].record(stream)
+            if inplace:
+                x.mul_(inv)
+        barrier()
+    launches = int(lib.lib.b2fft_launch_count() - l0)
+    per = sorted(ev[2 * i].elapsed_time(ev[2 * i + 1]) for i in range(steps))
+    total_ms = sum(per) if inplace else ev[0].elapsed_time(ev[-1])
+    if world > 1:
+        t = torch.tensor([total_ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    return total_ms / steps, per, launches, clk.summary()
+
+
+def traffic_of(name):
+    """measured DRAM bytes per step of the workload's kernels (ncu --set full captures, profiles/traffic.json)"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f).get(name)
+        if t:
+            return t["dram_bytes_per_launch"], "%s, %s" % (t["kernel"], t["source"])
+    except (OSError, ValueError, KeyError):
+        pass
+    return None, None
+
+
+def config_record(name, steps, warmup):
+    """one compact, validated record per BASELINE config (device-resident arrays, this GPU)"""
+    import torch
+    w = WORKLOADS[name]
+    lib = engine_lib(w["prec"])
+    flops, nbytes = workload_numbers(w)
+    x, y = device_arrays(lib, w, 1)
+    plan = plan_for(lib, w, x, y)
+    assert plan, "plan is NULL: " + lib.lib.b2fft_last_error().decode()
+    ms, per, launches, _ = time_device(lib, w, plan, x, y, steps, warmup)
+    peak, _ = measured_peak_gbs()
+    rec = {"workload": name, "n": w["n"], "howmany": w["howmany"], "in_place": bool(w.get("inplace")),
+           "dtype": "f32" if w["prec"] == "fp32" else "f64", "ms_per_step": ms, "min_step_ms": per[0],
+           "gflops": flops / (ms * 1e-3) / 1e9, "global_passes": int(lib.lib.b2fft_plan_num_passes(fftw_plan_bp(plan))),
+           "algorithmic_bytes": nbytes, "hbm_frac": nbytes / (ms * 1e-3) / 1e9 / peak,
+           "timed_call": "b2fft_execute_async on torch's current stream, CUDA events",
+           "kernels_per_step": launches / steps, "traffic": traffic_of(name)[0]}
+    if name == "c2c_1d_1024_fp64":  # BASELINE configs[0]: one transform, latency-bound -- also through fftw_execute itself
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(200):
+            lib.execute_dft(plan, x, y)  # synchronous fftw_execute_dft on device arrays
+        rec["fftw_execute_sync_us"] = (time.perf_counter() - t0) / 200 * 1e6
+        rec["hbm_frac"] = None
+        rec["note"] = "32 KiB of traffic: launch-latency bound; fftw_execute_sync_us = wall time of one synchronous fftw_execute_dft call"
+    rec["check"] = validate(lib, w, x, y, plan)
+    lib.destroy_plan(plan)
+    del x, y
+    torch.cuda.empty_cache()
+    return rec
+
+
+CONFIG_SET = ["c2c_1d_1024_fp64", "r2c_1d_1048576x256_fp32", "c2r_1d_1048576x256_fp32", "c2c_3d_512_fp32", "c2c_3d_512_fp32_inplace"]
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -252,57 +422,25 @@ def run_gpu(args):
     lib.lib.b2fft_set_device(local)
     flops, nbytes = workload_numbers(w)
     (ishape, idt), (oshape, odt) = io_shapes(lib, w)
-    tmap = {np.complex64: torch.complex64, np.complex128: torch.complex128,
-            np.float32: torch.float32, np.float64: torch.float64}
-
-    # ---- device-resident arrays: synthetic uniform [-0.5, 0.5) like the reference verifier
-    g = torch.Generator(device="cuda").manual_seed(1 + rank)
-    rdt = torch.float32 if w["prec"] == "fp32" else torch.float64
-    if idt in (np.complex64, np.complex128):
-        x = torch.view_as_complex(torch.rand(ishape + (2,), device="cuda", dtype=rdt, generator=g) - 0.5)
-    else:
-        x = torch.rand(ishape, device="cuda", dtype=rdt, generator=g) - 0.5
     inplace = bool(w.get("inplace"))
-    y = x if inplace else torch.empty(oshape, device="cuda", dtype=tmap[odt])
+
+    # ---- headline: device-resident arrays, K steps in one CUDA-event bracket, max over ranks
+    x, y = device_arrays(lib, w, 1 + rank)
     plan = plan_for(lib, w, x, y)
     assert plan, "plan is NULL: " + lib.lib.b2fft_last_error().decode()
     bp = fftw_plan_bp(plan)
-    stream = torch.cuda.current_stream()
-    sp = C.c_void_p(stream.cuda_stream)
-
-    def step_dev():
-        rc = lib.lib.b2fft_execute_async(bp, x.data_ptr(), y.data_ptr(), sp)
-        assert rc == 0, lib.lib.b2fft_last_error()
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(3, args.warmup)):
-        step_dev()
-    barrier()
-    l0 = lib.lib.b2fft_launch_count()
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-    with ClockSampler(local) as clk:
-        ev[0].record(stream)
-        for i in range(args.steps):
-            step_dev()
-            ev[i + 1].record(stream)
-        barrier()
-    launches = int(lib.lib.b2fft_launch_count() - l0)
-    total_ms = ev[0].elapsed_time(ev[-1])
-    per = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps))
-    if world > 1:
-        t = torch.tensor([total_ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
-    ms_step = total_ms / args.steps
+    ms_step, per, launches, clocks = time_device(lib, w, plan, x, y, args.steps, args.warmup, world)
     value = world * flops / (ms_step * 1e-3) / 1e9
     npasses = lib.lib.b2fft_plan_num_passes(bp)
     peak, peak_src = measured_peak_gbs()
     achieved = nbytes / (ms_step * 1e-3) / 1e9
     plan_desc = lib.sprint_plan(plan)
+    check = validate(lib, w, x, y, plan)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
 
     # ---- end to end: host (pinned) arrays through fftw_execute, copies inside the timed region
     e2e = None
@@ -330,33 +468,68 @@ def run_gpu(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
         e2e = {"value": world * flops / dt / 1e9, "unit": "GFLOP/s", "h2d_bytes_per_step": ib,
-               "d2h_bytes_per_step": ob, "ms_per_step": dt * 1e3, "steps": esteps}
+               "d2h_bytes_per_step": ob, "ms_per_step": dt * 1e3, "steps": esteps,
+               "h2d_GBs_per_rank": ib / dt / 1e9, "d2h_GBs_per_rank": ob / dt / 1e9,
+               "timed_call": "fftw_execute on fftw_malloc (pinned host) arrays, host clock, max over ranks"}
         lib.destroy_plan(hplan)
         lib.free(hin)
         if not inplace:
             lib.free(hout)
     lib.destroy_plan(plan)
+    del x, y
+    torch.cuda.empty_cache()
 
+    # ---- the other single-GPU BASELINE configs, one compact validated record each (rank 0's GPU)
+    configs = None
+    if not args.no_configs and args.workload == DEFAULT_WORKLOAD:
+        if rank == 0:
+            configs = []
+            for name in CONFIG_SET:
+                try:
+                    configs.append(config_record(name, steps=10, warmup=3))
+                except Exception as e:  # a failing side record must not take the headline line with it
+                    configs.append({"workload": name, "error": repr(e)[:300]})
+        barrier()
+
+    # ---- BASELINE config 5: the slab-distributed cube over all ranks of this run (strong scaling)
+    slab = None
+    if not args.no_slab and args.workload == DEFAULT_WORKLOAD:
+        from fftw3_b200 import bench_slab
+        try:
+            free_b, _ = torch.cuda.mem_get_info()
+            if world > 1:
+                t = torch.tensor([float(free_b)], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MIN)  # every rank must pick the same cube
+                free_b = int(t.item())
+            cube = args.slab_n
+            # in place: the array + the plan's receive buffer, 2 x 8 N^3 / world bytes per GPU (+ check temporaries)
+            while cube > 256 and 2 * 8 * cube ** 3 / world + (6 << 30) > free_b:
+                cube //= 2
+            slab, st = bench_slab.run(lib, (cube, cube, cube), world, rank, steps=args.slab_steps, warmup=3, peak_gbs=peak)
+            if cube != args.slab_n:
+                slab["note"] = "%d^3 does not fit %d GPU(s) with %.0f GiB free each: ran %d^3" % (args.slab_n, world, free_b / GIB, cube)
+            slab["parity"] = None if args.no_slab_checks else bench_slab.checks(st)
+            del st
+        except Exception as e:
+            slab = {"workload": "c2c_3d_%d_slab_fp32" % args.slab_n, "error": repr(e)[:400]}
+        torch.cuda.empty_cache()
+
+    # ---- the reference's own CPU path on this box's host cores (rank 0; the other ranks wait)
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
-        s = cpu_sample_of(w)
-        cpu = run_reference(s, steps=3, warmup=1, measure=True)
+    if rank == 0 and not args.no_cpu:
+        cpu = run_reference(cpu_sample_of(w, args.workload), steps=3, warmup=1, measure=True)
         if cpu:
-            cpu.pop("ms_per_step", None)
+            for k in ("ms_per_step", "howmany", "n"):
+                cpu.pop(k, None)
     if rank == 0:
-        traffic = traffic_note = None
-        try:  # measured DRAM bytes per launch of the dominant kernel (one ncu --set full capture, profiles/)
-            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                t = json.load(f).get(args.workload)
-            if t:
-                traffic, traffic_note = t["dram_bytes_per_launch"], "%s, %s" % (t["kernel"], t["source"])
-        except (OSError, ValueError, KeyError):
-            pass
+        traffic, traffic_note = traffic_of(args.workload)
         line = {
-            "metric": "FFTW-convention GFLOP/s (5 N log2 N / t), fftw_execute",
+            "metric": "FFTW-convention GFLOP/s (5 N log2 N / t), fftw_plan_many_dft + execute",
             "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if w["prec"] == "fp32" else "f64", "data": "synthetic uniform[-0.5,0.5), seed 1",
+            "timed_call": "value: b2fft_execute_async (the engine entry fftw_execute calls) on torch's current stream, device "
+                          "arrays, CUDA events; e2e: fftw_execute itself on pinned host arrays",
             "config": {"workload": args.workload, "api": "fftw_plan_many_dft + fftw_execute" if w["kind"] == "c2c"
                        else f"fftw_plan_many_dft_{w['kind']} + fftw_execute",
                        "n": w["n"], "howmany_per_gpu": w["howmany"], "in_place": inplace,
@@ -367,7 +540,8 @@ def run_gpu(args):
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_note,
                          "peak_source": peak_src, "algorithmic_bytes_per_step": nbytes, "kernels_per_step": launches / args.steps,
                          "median_step_ms": per[len(per) // 2], "min_step_ms": per[0]},
-            "clocks": clk.summary(),
+            "output_check": check,
+            "clocks": clocks,
             "gpu_launches": launches,
             "plan": plan_desc.strip().split("\n"),
         }
@@ -375,15 +549,21 @@ def run_gpu(args):
             line["e2e"] = e2e
         if cpu:
             line["cpu_baseline"] = cpu
+        if configs is not None:
+            line["configs"] = configs
+        if slab is not None:
+            line["slab"] = slab
         print(json.dumps(line))
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
 def run_slab(args):
-    """3-D c2c split over the ranks by slabs: local 2-D FFTs, NCCL all-to-all, 1-D FFTs"""
+    """a slab workload on its own (--workload c2c_3d_*_slab_fp32): the slab record is the line"""
     import torch
     import torch.distributed as dist
+    from fftw3_b200 import bench_slab
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -393,90 +573,26 @@ def run_slab(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     w = WORKLOADS[args.workload]
     lib = engine_lib(w["prec"])
-    L = lib.lib
-    L.b2fft_set_device(local)
-    L.fftw_mpi_comm_from_nccl.restype = C.c_void_p
-    L.fftw_mpi_comm_from_nccl.argtypes = [C.c_void_p, C.c_int, C.c_int]
-    L.fftw_mpi_comm_self.restype = C.c_void_p
-    L.fftw_mpi_plan_dft_3d.restype = C.c_void_p
-    L.fftw_mpi_plan_dft_3d.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] * 3 + [C.c_int, C.c_uint]
-    L.fftw_mpi_local_size_3d_transposed.restype = C.c_ssize_t
-    L.fftw_mpi_local_size_3d_transposed.argtypes = [C.c_ssize_t] * 3 + [C.c_void_p] + [C.POINTER(C.c_ssize_t)] * 4
-    L.b2fft_slab_last_times.argtypes = [C.c_void_p] + [C.POINTER(C.c_float)] * 3
-    if world > 1:
-        idt = torch.zeros(128, dtype=torch.uint8)
-        if rank == 0:
-            buf = (C.c_char * 128)()
-            assert L.fftw_mpi_nccl_unique_id(buf) == 0, L.b2fft_last_error()
-            idt = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
-        idt = idt.cuda()
-        dist.broadcast(idt, 0)
-        idb = bytes(idt.cpu().numpy().tobytes())
-        comm = L.fftw_mpi_comm_from_nccl(idb, world, rank)
-    else:
-        comm = L.fftw_mpi_comm_self()
-    assert comm, L.b2fft_last_error()
-    n0, n1, n2 = w["n"]
-    v = [C.c_ssize_t() for _ in range(4)]
-    nalloc = L.fftw_mpi_local_size_3d_transposed(n0, n1, n2, comm, *[C.byref(t) for t in v])
-    ln0, s0, ln1, s1 = (t.value for t in v)
-    g = torch.Generator(device="cuda").manual_seed(1 + rank)
-    x = torch.view_as_complex(torch.rand((nalloc, 2), device="cuda", dtype=torch.float32, generator=g) - 0.5)
-    y = torch.empty_like(x)
-    plan = L.fftw_mpi_plan_dft_3d(n0, n1, n2, x.data_ptr(), y.data_ptr(), comm, capi.FFTW_FORWARD,
-                                  capi.FFTW_ESTIMATE | (1 << 30))
-    assert plan, L.b2fft_last_error()
-    bp = fftw_plan_bp(plan)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(3, args.warmup)):
-        lib.execute(plan)
-    barrier()
-    l0 = L.b2fft_launch_count()
-    stage = np.zeros(3)
-    with ClockSampler(local) as clk:
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            lib.execute(plan)  # synchronous on the plan's streams
-            a, b, c = C.c_float(), C.c_float(), C.c_float()
-            L.b2fft_slab_last_times(bp, C.byref(a), C.byref(b), C.byref(c))
-            stage += (a.value, b.value, c.value)
-        barrier()
-        dt = (time.perf_counter() - t0) / args.steps
-    launches = int(L.b2fft_launch_count() - l0)
-    stage /= args.steps
-    if world > 1:
-        t = torch.tensor([dt, *stage], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt, stage = float(t[0]), t[1:].cpu().numpy()
-    flops, nbytes = workload_numbers(w)
+    lib.lib.b2fft_set_device(local)
     peak, peak_src = measured_peak_gbs()
-    sent = (n0 * n1 * n2 * 8 / world) * (world - 1) / world  # bytes each GPU sends
+    with ClockSampler(local) as clk:
+        rec, st = bench_slab.run(lib, tuple(w["n"]), world, rank, steps=args.steps, warmup=args.warmup, peak_gbs=peak)
+    parity = None if args.no_slab_checks else bench_slab.checks(st)
     if rank == 0:
-        line = {
-            "metric": "FFTW-convention GFLOP/s (5 N log2 N / t), fftw_mpi_plan_dft_3d + fftw_execute",
-            "value": flops / dt / 1e9, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(3, args.warmup), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic uniform[-0.5,0.5)",
-            "config": {"workload": args.workload, "n": w["n"], "layout": "FFTW_MPI_TRANSPOSED_OUT, slabs over n0",
-                       "timing": "host clock around synchronous fftw_execute, barrier + max over ranks",
-                       "stage_ms": {"local_2d_ffts": float(stage[0]), "exposed_exchange": float(stage[1]),
-                                    "final_1d_ffts": float(stage[2])}},
-            "roofline": {"bound": "hbm", "achieved": nbytes / world / dt / 1e9, "peak": peak, "unit": "GB/s",
-                         "frac": nbytes / world / dt / 1e9 / peak, "traffic": None, "peak_source": peak_src,
-                         "note": "per GPU: algorithmic bytes of its slab / whole step",
-                         "nvlink_bytes_sent_per_gpu": sent,
-                         "nvlink_min_ms_at_770GBs": sent / 770e9 * 1e3},
-            "clocks": clk.summary(), "gpu_launches": launches,
-            "plan": lib.sprint_plan(plan).strip().split("\n"),
-        }
+        line = {"metric": "FFTW-convention GFLOP/s (5 N log2 N / t), fftw_mpi_plan_dft_3d + fftw_execute",
+                "value": rec["value"], "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+                "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic uniform[-0.5,0.5)",
+                "config": {"workload": args.workload, "n": w["n"], "layout": rec["layout"], "timing": rec["timing"],
+                           "stage_ms": rec["stage_ms"]},
+                "roofline": {"bound": "hbm", "achieved": rec["hbm_frac"] * peak, "peak": peak, "unit": "GB/s",
+                             "frac": rec["hbm_frac"], "traffic": None, "peak_source": peak_src, "note": rec["hbm_note"],
+                             "nvlink_bytes_sent_per_gpu": rec["nvlink_bytes_sent_per_gpu"],
+                             "nvlink_frac_of_900GBs": rec["nvlink_frac_of_900GBs"]},
+                "slab": dict(rec, parity=parity), "clocks": clk.summary(), "gpu_launches": rec["gpu_launches"], "plan": rec["plan"]}
         print(json.dumps(line))
-    lib.destroy_plan(plan)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
@@ -485,7 +601,8 @@ def run_reference_arm(args):
     if rank != 0:
         return
     w = WORKLOADS[args.workload]
-    s = cpu_sample_of(w)
+    s = cpu_sample_of(w, args.workload)
+    same = s["howmany"] == w["howmany"] and list(s["n"]) == list(w["n"])
     r = run_reference(s, steps=max(1, args.steps), warmup=max(1, min(args.warmup, 3)), measure=True)
     if r is None:
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (run __graft_entry__.build() where /root/reference exists)"}))
@@ -495,7 +612,10 @@ def run_reference_arm(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if w["prec"] == "fp32" else "f64", "data": "synthetic uniform[-0.5,0.5), seed 1",
-            "config": {"workload": args.workload, "n": w["n"], "howmany_per_gpu": w["howmany"]},
+            "config": {"workload": args.workload, "n": r["n"], "howmany": r["howmany"], "howmany_of_the_config": w["howmany"],
+                       "same_config": same,
+                       "note": "the reference's own fftw_plan_many_dft + fftw_execute on the host cores, on the "
+                               + ("full config" if same else "bounded sample named in cpu_baseline.sample")},
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -511,6 +631,11 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-configs", action="store_true", help="skip the compact records of the other single-GPU configs")
+    ap.add_argument("--no-slab", action="store_true", help="skip the slab-distributed cube (BASELINE config 5)")
+    ap.add_argument("--no-slab-checks", action="store_true")
+    ap.add_argument("--slab-n", type=int, default=2048)
+    ap.add_argument("--slab-steps", type=int, default=6)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
