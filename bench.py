@@ -259,6 +259,9 @@ def device_arrays(lib, w, seed):
         x = torch.view_as_complex(torch.empty(ishape + (2,), device="cuda", dtype=rdt).uniform_(-0.5, 0.5, generator=g))
     else:
         x = torch.empty(ishape, device="cuda", dtype=rdt).uniform_(-0.5, 0.5, generator=g)
+    if w["kind"] == "c2r":  # a half-spectrum of REAL data: the DC and Nyquist bins are real
+        x[..., 0] = x[..., 0].real
+        x[..., -1] = x[..., -1].real
     y = x if w.get("inplace") else torch.empty(oshape, device="cuda", dtype=tmap[odt])
     return x, y
 

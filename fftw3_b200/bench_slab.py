@@ -204,6 +204,7 @@ def checks(st, tol_per_log2=1e-6):
             blk = t if blk is None else blk.add_(t)
         x3[a0:a0 + B] = blk
     del blk, t
+    torch.cuda.synchronize()  # (the fill above is asynchronous torch work)
     lib.execute(plan)
     torch.cuda.synchronize()
     y = x[:nout]
@@ -238,6 +239,7 @@ def checks(st, tol_per_log2=1e-6):
         acc += torch.einsum("bac,bz->zac", t1, W0[a0:a0 + B])
     del xb, t2, t1
     acc = allsum(acc, world)
+    torch.cuda.synchronize()
     lib.execute(plan)
     torch.cuda.synchronize()
     got = torch.zeros_like(acc)
@@ -257,6 +259,7 @@ def checks(st, tol_per_log2=1e-6):
     st["plan"] = None
     pb = L.fftw_mpi_plan_dft_3d(n0, n1, n2, x.data_ptr(), x.data_ptr(), comm, FFTW_BACKWARD, FFTW_ESTIMATE | TRANSPOSED_IN)
     assert pb, L.b2fft_last_error()
+    torch.cuda.synchronize()
     lib.execute(pb)
     torch.cuda.synchronize()
     lib.destroy_plan(pb)

@@ -265,6 +265,7 @@ struct SlabPlan {
     cudaStream_t sb = nullptr;               // v2: barriers run beside the copy stream
     std::vector<cudaEvent_t> v2_e1, v2_ec, v2_e2;  // per chunk: n1 pass done, copies done, every rank's copies done
     cudaEvent_t v2_eb = nullptr, v2_ta = nullptr, v2_tb = nullptr;
+    cudaEvent_t ev_in = nullptr;  // orders an execute after the caller's earlier work on the default stream
 #endif
 };
 
@@ -451,7 +452,7 @@ void b2_slab_destroy(b2fft_plan_s *p) {
     for (std::vector<cudaEvent_t> *v : {&s->v2_e1, &s->v2_ec, &s->v2_e2})
         for (cudaEvent_t e : *v)
             if (e) cudaEventDestroy(e);
-    for (cudaEvent_t e : {s->v2_eb, s->v2_ta, s->v2_tb})
+    for (cudaEvent_t e : {s->v2_eb, s->v2_ta, s->v2_tb, s->ev_in})
         if (e) cudaEventDestroy(e);
     if (s->sb) cudaStreamDestroy(s->sb);
     for (int q = 0; q < (int)s->peerS.size(); ++q)
@@ -1087,6 +1088,12 @@ int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
 #if B2_CUDA
     cpx_t *din = (cpx_t *)in, *dout = (cpx_t *)out;
     const bool hin = !is_device_ptr(in), hout = !is_device_ptr(out);
+    // The plan works on its own non-blocking streams.  A caller that filled its device arrays with work queued on
+    // the (legacy) default stream -- what ordinary plans run on, and what e.g. torch uses -- expects fftw_execute to
+    // see that data: order the plan's first stream after everything queued there so far.
+    if (!s.ev_in) B2_CK(cudaEventCreateWithFlags(&s.ev_in, cudaEventDisableTiming));
+    B2_CK(cudaEventRecord(s.ev_in, 0));
+    B2_CK(cudaStreamWaitEvent(s.sc, s.ev_in, 0));
     // (the padded real side of r2c / c2r has 2*n2 reals per row: the same bytes as n2 complex)
     const size_t in_b = (size_t)(s.c2r_tin ? s.ln1 * s.n0 : s.ln0 * s.n1) * s.n2 * sizeof(cpx_t);
     const size_t out_b = (size_t)(s.transposed_out && s.kind != B2FFT_C2R ? s.ln1 * s.n0 : s.ln0 * s.n1) * s.n2 * sizeof(cpx_t);
