@@ -393,7 +393,7 @@ template <int N, int EPI, int BWD> struct ColTma {
                 const unsigned k = (unsigned)(2 * t + (q & 1) + (q >> 1) * 2 * T);
                 const unsigned o = b2_fastdiv(k, p.scat_m, p.scat_s);
                 const long long r = (long long)(k - o * (unsigned)p.scat_blk);
-                cpx_t *po = reinterpret_cast<cpx_t *>(p.scat_base[o]) + (plane * p.scat_pstride[o] + r * p.d_axis) / 2 + loff;
+                cpx_t *po = reinterpret_cast<cpx_t *>(p.scat_base[o]) + (plane * p.scat_pstride[o] + r * p.scat_rstride[o]) / 2 + loff;
                 if (p.scat_self1 > 0 && (int)o != p.scat_self1 - 1)
                     po = cdst + ((long long)m.scoord * p.scat_lplane + (long long)k * p.d_axis) / 2 + loff;
                 *po = v[q];

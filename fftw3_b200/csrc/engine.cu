@@ -147,7 +147,7 @@ static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
 
 // ------------------------------------------------------------------------- scattered last step
 int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long long plane_stride, const long long *pstride,
-                           int self) {
+                           int self, const long long *rstride, int local) {
     if (!p || p->pc.steps.empty() || nowners < 1 || nowners > B2_MAXSCAT || blk < 1) return -1;
     if (p->chains && !p->chains->empty()) return -1;
     const StepPlan &last = p->pc.steps.back();
@@ -171,7 +171,11 @@ int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long lon
     q.scat_lplane = plane_stride;
     q.scat_blk = (int)blk;
     b2_fastdiv_make((unsigned long long)blk, q.scat_m, q.scat_s);
-    for (int o = 0; o < nowners; ++o) q.scat_pstride[o] = pstride[o];
+    for (int o = 0; o < nowners; ++o) {
+        q.scat_pstride[o] = pstride[o];
+        q.scat_rstride[o] = rstride ? rstride[o] : q.d_axis;
+    }
+    q.scat_local = local;
     b2_select_tile_kernel(*st);
     if (st->fast_id < 0 || b2_tile_table()[st->fast_id].epi != 8) {
         delete st;

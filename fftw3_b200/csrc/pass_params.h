@@ -78,6 +78,11 @@ struct PassParams {
     long long scat_lplane;
     real_t *scat_base[B2_MAXSCAT];
     long long scat_pstride[B2_MAXSCAT];
+    // distance (reals) between consecutive rows of owner o's block (d_axis unless the destination is laid out
+    // differently: the round-2 slab schedule stores chunk-major, rows of w columns); scat_local: every base is
+    // memory of THIS GPU (staging or its own receive buffer), so narrow row segments cost nothing
+    long long scat_rstride[B2_MAXSCAT];
+    int scat_local;
 };
 
 // Division by an invariant d for 0 <= n < 2^31 (Granlund-Montgomery): with l = ceil(log2 d) and

@@ -47,8 +47,10 @@ struct b2fft_plan_s {
 // dst stride (reals) of the line dim that numbers the planes; pstride[o] = owner o's plane stride.
 // Returns 0 when the step qualifies (tile kernel, column mode, no other epilogue).
 // self >= 0: hybrid form, only owner `self` is scattered, the other rows stay in place.
+// rstride (optional): per-owner distance between consecutive rows of the block, in reals (default: the step's own
+// axis stride); local: all bases are memory of this GPU.
 int b2_plan_enable_scatter(b2fft_plan_s *p, int nowners, long long blk, long long plane_stride, const long long *pstride,
-                           int self = -1);
+                           int self = -1, const long long *rstride = nullptr, int local = 0);
 int b2_plan_execute_scatter(b2fft_plan_s *p, void *in, void *out, real_t *const *bases, long long coord0,
                             b2::stream_t stream);
 void b2_slab_destroy(b2fft_plan_s *p);

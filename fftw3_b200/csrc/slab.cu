@@ -243,20 +243,23 @@ struct SlabPlan {
     // the others in place for the DMA, which then skips the local 1/P of the exchange
     bool hybrid = false;
     // ---- round-2 schedule ("v2") for transposed-output c2c: chunks run along the CONTIGUOUS dimension ----
-    //   row pass over the whole slab, in -> W (W = the caller's output array: no send buffer at all), then per
-    //   chunk k of v2_w consecutive columns:  n1 pass in place on W | exchange W -> R (one 3-D DMA per peer)
-    //   | cross-rank barrier | n0 pass R -> out.  The exchange of chunk k overlaps the n1 pass of chunk k+1
-    //   AND the n0 passes of the chunks before it (round 1 chunked along n0, so its last stage could only
-    //   start after the whole exchange; reference shape of the messages: fftw/mpi/transpose-alltoall.c:224-227).
+    // The planes of the slab are split into v2_ng groups, the rows into v2_nch chunks of v2_w columns.  Per group g:
+    //   row pass over the group's planes, in -> W (W = the caller's output array), then per chunk k:
+    //     n1 pass: reads W[i0][i1][chunk] and stores row k1 of plane i0 chunk-major (scatter epilogue, local stores):
+    //        rows this rank owns      -> its own receive buffer  R_k[s0 + i0][j1][w]
+    //        rows of the other ranks  -> staging                 S_k[i0][k1][w]
+    //     exchange: ONE 2-D copy per peer, runs of ln1 * w elements (512 KiB at 2048^3 on 8 GPUs) from S_k straight
+    //     into the peer's R_k at its final position (copy engines, peers in the shifted order pe + d)
+    //   after the last group's copies of chunk k: cross-rank barrier, then the n0 pass R_k[i0][j1][w] -> out[j1][k0][chunk].
+    // The exchange of a chunk overlaps the n1 passes that follow it, the NEXT group's row pass, and the n0 passes of the
+    // chunks before it; only the first group's row pass and the last n0 pass are exposed.  (Round 1 chunked along n0:
+    // its last stage could only start after the whole exchange.  Message shape of the reference:
+    // fftw/mpi/transpose-alltoall.c:224-227.)  One rank: every row is "owned", no staging, no copies.
     bool v2 = false;
-    int v2_nch = 1, v2_lag = 2;
-    ptrdiff_t v2_w = 0;
-    b2fft_plan *v2_row[2] = {nullptr, nullptr};  // [0] out of place, [1] in place; built on first use
+    int v2_nch = 1, v2_lag = 2, v2_ng = 1;
+    ptrdiff_t v2_w = 0, v2_gp = 0;               // chunk width (columns), planes per group
+    b2fft_plan *v2_row[2] = {nullptr, nullptr};  // one group's row pass: [0] out of place, [1] in place; built on first use
     b2fft_plan *v2_n1 = nullptr, *v2_n0 = nullptr;
-    // the n1 pass stores the rows THIS rank owns straight into its own receive buffer (tile-kernel epilogue 8,
-    // self only); the copy engines then move the remote blocks only.  Measured (profiles/r2_peer_copy.md): a
-    // strided same-GPU copy runs at ~0.6 TB/s on a copy engine, slower than the NVLink copies beside it.
-    bool v2_hyb = false;
 #if B2_CUDA
     // DMA exchange: one stream per peer so that the copies to different peers run on different copy engines
     std::vector<cudaStream_t> sx;
@@ -494,8 +497,7 @@ static void slab_describe(SlabPlan &sr, b2fft_plan *bp) {
              s->transposed_in ? (s->kind == B2FFT_C2C ? " (first two dims exchanged: FFTW_MPI_TRANSPOSED_IN)" : " (transposed input)") : "", s->hm, s->P, s->pe,
              s->s0, s->ln0, s->s1, s->ln1, s->transposed_out ? "transposed" : "natural",
              s->nchunks, s->chunk,
-             s->v2 ? (s->v2_hyb ? "v2: chunks along the contiguous dimension; local block stored by the n1 pass, one 3-D DMA per peer and chunk into peer memory; the n0 passes overlap it"
-                                : "v2: chunks along the contiguous dimension, one 3-D DMA per owner and chunk, the n0 passes overlap it")
+             s->v2 ? "v2: plane groups x chunks along the contiguous dimension; the n1 pass stores chunk-major (own rows -> receive buffer, others -> staging), one 2-D DMA per peer, group and chunk into peer memory; the next group's row pass and the n0 passes overlap it"
              : s->fused ? "fused into the n1 pass: rows stored straight into their owner's receive buffer (peer memory over NVLink)"
              : s->hybrid ? "local block stored by the n1 pass, remote blocks by strided DMA into peer memory (CUDA IPC over NVLink), NCCL barrier"
              : s->P == 1 ? "local copy" : s->p2p ? "strided DMA into peer memory (CUDA IPC over NVLink), NCCL barrier"
@@ -670,7 +672,15 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
         if (!s->v2) slab_enable_fused(*s);
     }
 #if B2_CUDA
-    if (ok && s->v2) ok = slab_setup_v2(*s);
+    if (ok && s->v2 && !slab_setup_v2(*s)) {
+        // not available for this geometry (e.g. n1 without a scattered-store tile kernel): round-1 schedule
+        s->v2 = false;
+        b2fft_plan_destroy(s->v2_n1);
+        b2fft_plan_destroy(s->v2_n0);
+        s->v2_n1 = s->v2_n0 = nullptr;
+        ok = slab_ensure_S(*s);
+        if (ok && (s->p2p || s->P == 1)) slab_enable_fused(*s);
+    }
 #endif
     if (!ok) {
         b2_slab_destroy(bp);
@@ -685,50 +695,60 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
 
 #if B2_CUDA
 static bool slab_setup_v2(SlabPlan &s) {
-    // chunk width: whole 128-byte segments, rows of >= 1 KiB for the copy engines; else fewer chunks
+    // chunk width: whole 128-byte segments and rows of >= 1 KiB; else fewer chunks
     int nch = 8;
     if (const char *e = getenv("B2FFT_SLAB_V2_CHUNKS")) nch = std::max(1, atoi(e));
     while (nch > 1 && (s.n2 % nch != 0 || (s.n2 / nch) % 16 != 0 || s.n2 / nch < 128)) --nch;
     s.v2_nch = nch;
     s.v2_w = s.n2 / nch;
     if (const char *e = getenv("B2FFT_SLAB_V2_LAG")) s.v2_lag = std::max(0, atoi(e));
+    // plane groups: the same split on every rank (even blocks only), groups of >= 8 planes
+    int ng = s.P > 1 ? 2 : 1;
+    if (const char *e = getenv("B2FFT_SLAB_V2_GROUPS")) ng = std::max(1, atoi(e));
+    if (s.n0 % s.P != 0) ng = 1;
+    while (ng > 1 && (s.b0 % ng != 0 || s.b0 / ng < 8)) --ng;
+    s.v2_ng = ng;
+    s.v2_gp = s.ln0 / ng;
+    if (s.P > B2_MAXSCAT || (int)s.peerR.size() != s.P) return false;
+    const ptrdiff_t w = s.v2_w;
     b2fft_geom g;
-    if (s.ln0 > 0) {  // n1 pass of one chunk, in place on W[ln0][n1][n2]
+    if (s.ln0 > 0) {  // n1 pass of one (group, chunk): reads W[gp][n1][n2], stores chunk-major into R_k / S_k
         memset(&g, 0, sizeof g);
         g.kind = B2FFT_C2C;
         g.sign = s.sign;
         g.rank = 1;
         g.dims[0] = b2fft_dim{s.n1, s.n2, s.n2};
         g.vrank = 2;
-        g.vdims[0] = b2fft_dim{s.v2_w, 1, 1};
-        g.vdims[1] = b2fft_dim{s.ln0, s.n1 * s.n2, s.n1 * s.n2};
+        g.vdims[0] = b2fft_dim{w, 1, 1};
+        g.vdims[1] = b2fft_dim{s.v2_gp, s.n1 * s.n2, s.n1 * s.n2};
         g.in_place = 1;
         s.v2_n1 = b2fft_plan_create(&g);
         if (!s.v2_n1) return false;
-        if (!getenv("B2FFT_SLAB_V2_NO_HYBRID") && s.P <= B2_MAXSCAT && (int)s.peerR.size() == s.P) {
-            std::vector<long long> ps(s.P);
-            for (int o = 0; o < s.P; ++o) ps[o] = (long long)blk_len(s.n1, s.b1, o) * s.n2 * 2;
-            s.v2_hyb = b2_plan_enable_scatter(s.v2_n1, s.P, (long long)s.b1, (long long)s.n1 * s.n2 * 2, ps.data(), s.pe) == 0;
-        }
+        std::vector<long long> ps(s.P), rs(s.P, (long long)w * 2);
+        for (int o = 0; o < s.P; ++o) ps[o] = (long long)(o == s.pe ? s.ln1 : s.n1) * w * 2;
+        if (b2_plan_enable_scatter(s.v2_n1, s.P, (long long)s.b1, (long long)s.n1 * s.n2 * 2, ps.data(), -1, rs.data(), 1) != 0)
+            return false;  // no tile kernel with the scattered store for this n1: round-1 schedule
     }
-    if (s.ln1 > 0) {  // n0 pass of one chunk, R[n0][ln1][n2] -> out[ln1][n0][n2]
+    if (s.ln1 > 0) {  // n0 pass of one chunk, R_k[n0][ln1][w] -> out[ln1][n0][n2]
         memset(&g, 0, sizeof g);
         g.kind = B2FFT_C2C;
         g.sign = s.sign;
         g.rank = 1;
-        g.dims[0] = b2fft_dim{s.n0, s.ln1 * s.n2, s.n2};
+        g.dims[0] = b2fft_dim{s.n0, s.ln1 * w, s.n2};
         g.vrank = 2;
-        g.vdims[0] = b2fft_dim{s.v2_w, 1, 1};
-        g.vdims[1] = b2fft_dim{s.ln1, s.n2, s.n0 * s.n2};
+        g.vdims[0] = b2fft_dim{w, 1, 1};
+        g.vdims[1] = b2fft_dim{s.ln1, w, s.n0 * s.n2};
         g.in_place = 0;
         s.v2_n0 = b2fft_plan_create(&g);
         if (!s.v2_n0) return false;
     }
+    if (s.P > 1 && !slab_ensure_S(s)) return false;
     bool ok = cudaStreamCreateWithFlags(&s.sb, cudaStreamNonBlocking) == cudaSuccess;
-    for (std::vector<cudaEvent_t> *v : {&s.v2_e1, &s.v2_ec, &s.v2_e2}) {
-        v->assign(nch, nullptr);
+    s.v2_e1.assign((size_t)nch * ng, nullptr);
+    s.v2_ec.assign(nch, nullptr);
+    s.v2_e2.assign(nch, nullptr);
+    for (std::vector<cudaEvent_t> *v : {&s.v2_e1, &s.v2_ec, &s.v2_e2})
         for (cudaEvent_t &e : *v) ok = ok && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
-    }
     ok = ok && cudaEventCreateWithFlags(&s.v2_eb, cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreate(&s.v2_ta) == cudaSuccess && cudaEventCreate(&s.v2_tb) == cudaSuccess;
     return ok;
@@ -745,7 +765,7 @@ static b2fft_plan *slab_v2_row_plan(SlabPlan &s, bool inplace) {
     g.rank = 1;
     g.dims[0] = b2fft_dim{s.n2f, s.hm, s.hm};
     g.vrank = s.hm > 1 ? 2 : 1;
-    g.vdims[0] = b2fft_dim{s.ln0 * s.n1, s.n2, s.n2};
+    g.vdims[0] = b2fft_dim{s.v2_gp * s.n1, s.n2, s.n2};  // one group of planes
     g.vdims[1] = b2fft_dim{s.hm, 1, 1};
     g.in_place = inplace ? 1 : 0;
     p = b2fft_plan_create(&g);
@@ -1003,14 +1023,15 @@ extern "C" void *b2fft_slab_buffer(b2fft_plan *p, int which, size_t *bytes) {
 
 #if B2_CUDA
 // v2 schedule (see SlabPlan): din / dout are device arrays, W = dout.
-//   compute stream sc :  row pass | n1(0) n1(1) [n0(0)] n1(2) [n0(1)] ...  (n0(k) is queued v2_lag chunks behind
-//                        n1(k) so that the stream does not stall on a chunk still in flight)
-//   copy stream sn    :  per chunk, one strided 3-D copy per peer straight into the peer's receive buffer at its
-//                        final position, peers in the shifted order pe + d (one sender per receiver at a time)
-//   barrier stream sb :  per chunk, "every rank's copies of this chunk have landed" (1-float NCCL all-reduce)
+//   compute stream sc :  row(g0) | n1(g0,0) .. n1(g0,nch-1) | row(g1) | n1(g1,0) n1(g1,1) [n0(0)] n1(g1,2) [n0(1)] ...
+//                        (n0(k) is queued v2_lag chunks behind the last group's n1(k) so that the stream does not
+//                        stall on a chunk still in flight)
+//   copy stream sn    :  per (group, chunk), one 2-D copy per peer straight into the peer's receive buffer
+//   barrier stream sb :  per chunk, after the last group's copies: "every rank's copies of this chunk have landed"
 static int slab_execute_v2(SlabPlan &s, cpx_t *din, cpx_t *dout) {
     const size_t esz = sizeof(cpx_t);
-    const int nch = s.v2_nch;
+    const int nch = s.v2_nch, ng = s.v2_ng;
+    const size_t w = (size_t)s.v2_w, gp = (size_t)s.v2_gp;
     cpx_t *W = dout;
     B2_CK(cudaEventRecord(s.t0, s.sc));
     // nobody may still be reading the receive buffer that this execute is about to overwrite
@@ -1020,56 +1041,55 @@ static int slab_execute_v2(SlabPlan &s, cpx_t *din, cpx_t *dout) {
         B2_CK(cudaEventRecord(s.v2_eb, s.sb));
         B2_CK(cudaStreamWaitEvent(s.sn, s.v2_eb, 0));
     }
-    if (s.ln0 > 0) {
-        b2fft_plan *row = slab_v2_row_plan(s, din == dout);
-        if (!row) return -6;
-        int rc = b2fft_execute_async(row, din, W, s.sc);
-        if (rc) return rc;
-    }
-    B2_CK(cudaEventRecord(s.v2_ta, s.sc));
+    b2fft_plan *row = s.ln0 > 0 ? slab_v2_row_plan(s, din == dout) : nullptr;
+    if (s.ln0 > 0 && !row) return -6;
     auto n0_pass = [&](int k) -> int {
         B2_CK(cudaStreamWaitEvent(s.sc, s.v2_e2[k], 0));
         if (!s.v2_n0) return 0;
-        return b2fft_execute_async(s.v2_n0, s.R + (size_t)k * s.v2_w, dout + (size_t)k * s.v2_w, s.sc);
+        return b2fft_execute_async(s.v2_n0, s.R + (size_t)k * s.n0 * s.ln1 * w, dout + (size_t)k * w, s.sc);
     };
-    for (int k = 0; k < nch; ++k) {
-        if (s.v2_n1) {
-            cpx_t *wk = W + (size_t)k * s.v2_w;
-            int rc;
-            if (s.v2_hyb) {
+    for (int g = 0; g < ng; ++g) {
+        const size_t p0 = (size_t)g * gp;  // first plane of the group
+        if (row) {
+            int rc = b2fft_execute_async(row, din + p0 * s.n1 * s.n2, W + p0 * s.n1 * s.n2, s.sc);
+            if (rc) return rc;
+        }
+        if (g == 0) B2_CK(cudaEventRecord(s.v2_ta, s.sc));
+        for (int k = 0; k < nch; ++k) {
+            cpx_t *Sk = s.S ? s.S + (size_t)k * s.ln0 * s.n1 * w + p0 * s.n1 * w : nullptr;
+            if (s.v2_n1) {
+                cpx_t *wk = W + p0 * s.n1 * s.n2 + (size_t)k * w;
                 real_t *bases[B2_MAXSCAT];
-                for (int o = 0; o < s.P; ++o) bases[o] = (real_t *)(s.peerR[o] + (size_t)k * s.v2_w);
-                rc = b2_plan_execute_scatter(s.v2_n1, wk, wk, bases, (long long)s.s0, s.sc);
-            } else
-                rc = b2fft_execute_async(s.v2_n1, wk, wk, s.sc);
-            if (rc) return rc;
-        }
-        B2_CK(cudaEventRecord(s.v2_e1[k], s.sc));
-        B2_CK(cudaStreamWaitEvent(s.sn, s.v2_e1[k], 0));
-        for (int d = 0; d < s.P && s.ln0 > 0; ++d) {
-            const int pe = (s.pe + d) % s.P;
-            const ptrdiff_t ln1p = blk_len(s.n1, s.b1, pe);
-            if (ln1p <= 0 || (s.v2_hyb && pe == s.pe)) continue;  // (hybrid: the n1 pass stored the local block itself)
-            cudaMemcpy3DParms q;
-            memset(&q, 0, sizeof q);
-            q.srcPtr = make_cudaPitchedPtr((void *)W, (size_t)s.n2 * esz, (size_t)s.n2 * esz, (size_t)s.n1);
-            q.srcPos = make_cudaPos((size_t)k * s.v2_w * esz, (size_t)(pe * s.b1), 0);
-            q.dstPtr = make_cudaPitchedPtr((void *)s.peerR[pe], (size_t)s.n2 * esz, (size_t)s.n2 * esz, (size_t)ln1p);
-            q.dstPos = make_cudaPos((size_t)k * s.v2_w * esz, 0, (size_t)s.s0);
-            q.extent = make_cudaExtent((size_t)s.v2_w * esz, (size_t)ln1p, (size_t)s.ln0);
-            q.kind = cudaMemcpyDeviceToDevice;
-            B2_CK(cudaMemcpy3DAsync(&q, s.sn));
-        }
-        B2_CK(cudaEventRecord(s.v2_ec[k], s.sn));
-        B2_CK(cudaStreamWaitEvent(s.sb, s.v2_ec[k], 0));
-        if (s.P > 1) {
-            int rc = slab_barrier(s, s.sb);
-            if (rc) return rc;
-        }
-        B2_CK(cudaEventRecord(s.v2_e2[k], s.sb));
-        if (k >= s.v2_lag) {
-            int rc = n0_pass(k - s.v2_lag);
-            if (rc) return rc;
+                for (int o = 0; o < s.P; ++o)
+                    bases[o] = o == s.pe ? (real_t *)(s.R + (size_t)k * s.n0 * s.ln1 * w + ((size_t)s.s0 + p0) * s.ln1 * w)
+                                         : (real_t *)(Sk + (size_t)o * s.b1 * w);
+                int rc = b2_plan_execute_scatter(s.v2_n1, wk, wk, bases, 0, s.sc);
+                if (rc) return rc;
+            }
+            cudaEvent_t e1 = s.v2_e1[(size_t)g * nch + k];
+            B2_CK(cudaEventRecord(e1, s.sc));
+            B2_CK(cudaStreamWaitEvent(s.sn, e1, 0));
+            for (int d = 1; d < s.P && s.ln0 > 0; ++d) {  // shifted order: one sender per receiver at a time
+                const int pe = (s.pe + d) % s.P;
+                const size_t ln1p = (size_t)blk_len(s.n1, s.b1, pe);
+                if (ln1p == 0) continue;
+                B2_CK(cudaMemcpy2DAsync(s.peerR[pe] + (size_t)k * s.n0 * ln1p * w + ((size_t)s.s0 + p0) * ln1p * w, ln1p * w * esz,
+                                        Sk + (size_t)pe * s.b1 * w, (size_t)s.n1 * w * esz, ln1p * w * esz, gp,
+                                        cudaMemcpyDeviceToDevice, s.sn));
+            }
+            if (g == ng - 1) {
+                B2_CK(cudaEventRecord(s.v2_ec[k], s.sn));
+                B2_CK(cudaStreamWaitEvent(s.sb, s.v2_ec[k], 0));
+                if (s.P > 1) {
+                    int rc = slab_barrier(s, s.sb);
+                    if (rc) return rc;
+                }
+                B2_CK(cudaEventRecord(s.v2_e2[k], s.sb));
+                if (k >= s.v2_lag) {
+                    int rc = n0_pass(k - s.v2_lag);
+                    if (rc) return rc;
+                }
+            }
         }
     }
     B2_CK(cudaEventRecord(s.v2_tb, s.sc));

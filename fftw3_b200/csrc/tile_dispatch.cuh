@@ -298,7 +298,7 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
     // is set: a warp of this kernel stores 64-byte row segments, which is what made remote NVLink writes slow in round 1.
     bool tma_ok = !getenv("FFTW_B200_NO_TMA") && sizeof(real_t) == 4 && p.fold_n == 0 && p.swap_in == p.swap_out &&
                   p.nld <= 4 && s.outer.empty();
-    if (epi == 8 && p.scat_self1 == 0 && !getenv("FFTW_B200_TMA_SCATTER")) tma_ok = false;  // (self-only scatter = local stores: fine)
+    if (epi == 8 && p.scat_self1 == 0 && !p.scat_local && !getenv("FFTW_B200_TMA_SCATTER")) tma_ok = false;  // (local stores are fine)
     if (p.s_axis & 3) tma_ok = false;
     for (int d = 1; d < p.nld; ++d)
         if (p.ls[d] & 3) tma_ok = false;

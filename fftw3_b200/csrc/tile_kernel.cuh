@@ -484,7 +484,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                 const unsigned o = b2_fastdiv(k, p.scat_m, p.scat_s);
                 const long long r = (long long)(k - o * (unsigned)p.scat_blk);
                 cpx_t *po = reinterpret_cast<cpx_t *>(p.scat_base[o]) +
-                            (plane * p.scat_pstride[o] + r * p.d_axis + loff) / 2;
+                            (plane * p.scat_pstride[o] + r * p.scat_rstride[o] + loff) / 2;
                 if (p.scat_self1 > 0 && (int)o != p.scat_self1 - 1)
                     po = cdst + ((long long)x.scoord * p.scat_lplane + (long long)k * p.d_axis + loff) / 2;
                 *po = v[q];
