@@ -22,6 +22,9 @@
 
 #include "b200fft.h"
 #include "device_rt.h"
+#if B2_CUDA
+#include <cuda.h>
+#endif
 
 using namespace b2;
 
@@ -269,6 +272,17 @@ struct SlabPlan {
     std::vector<cudaEvent_t> v2_e1, v2_ec, v2_e2;  // per chunk: n1 pass done, copies done, every rank's copies done
     cudaEvent_t v2_eb = nullptr, v2_ta = nullptr, v2_tb = nullptr;
     cudaEvent_t ev_in = nullptr;  // orders an execute after the caller's earlier work on the default stream
+    // v2 cross-rank signalling without kernels: word F[k*P + src] of MY flag array is set to the execute's epoch by
+    // rank `src` (a 4-byte copy behind its data copies of chunk k, on its copy stream); my n0 pass of chunk k waits
+    // for the P-1 words with cuStreamWaitValue32.  Row k = v2_nch holds "rank src has finished reading its receive
+    // buffer for this epoch".  (Round 1 and the fallback use a 1-float NCCL all-reduce as the barrier: a kernel that
+    // needs a free SM slot on every GPU at the same time, behind persistent FFT kernels that fill all of them.)
+    unsigned *F = nullptr, *epoch_dev = nullptr;
+    std::vector<unsigned *> peerF;
+    unsigned epoch = 0;
+    bool v2_flags = false;
+    cudaStream_t s2 = nullptr;  // v2: the n0 passes, so that a chunk still in flight never blocks the n1 passes
+    cudaEvent_t v2_e3 = nullptr;
 #endif
 };
 
@@ -307,6 +321,23 @@ static void slab_enable_fused(SlabPlan &s) {
 #if B2_CUDA
 static int slab_setup_p2p(SlabPlan &s);
 static bool slab_setup_v2(SlabPlan &s);
+#define B2_SLAB_FLAG_BYTES (65 * B2_MAXSCAT * sizeof(unsigned))  // <= 64 chunks + the "done" row, <= B2_MAXSCAT ranks
+// cuStreamWaitValue32 through the runtime (no link against libcuda); nullptr when the driver does not offer it
+typedef CUresult (*StreamWaitValueFn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static StreamWaitValueFn stream_wait_value() {
+    static StreamWaitValueFn f = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        cudaDriverEntryPointQueryResult q;
+        void *fp = nullptr;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fp, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            f = (StreamWaitValueFn)fp;
+        else
+            cudaGetLastError();
+    }
+    return f;
+}
 #endif
 
 static b2fft_plan *make_stage1(const SlabPlan &s, ptrdiff_t planes) {
@@ -458,6 +489,12 @@ void b2_slab_destroy(b2fft_plan_s *p) {
     for (cudaEvent_t e : {s->v2_eb, s->v2_ta, s->v2_tb, s->ev_in})
         if (e) cudaEventDestroy(e);
     if (s->sb) cudaStreamDestroy(s->sb);
+    if (s->s2) cudaStreamDestroy(s->s2);
+    if (s->v2_e3) cudaEventDestroy(s->v2_e3);
+    for (int q = 0; q < (int)s->peerF.size(); ++q)
+        if (q != s->pe && s->peerF[q]) cudaIpcCloseMemHandle(s->peerF[q]);
+    if (s->F) cudaFree(s->F);
+    if (s->epoch_dev) cudaFree(s->epoch_dev);
     for (int q = 0; q < (int)s->peerS.size(); ++q)
         if (q != s->pe) {
             if (s->peerS[q]) cudaIpcCloseMemHandle(s->peerS[q]);
@@ -744,6 +781,9 @@ static bool slab_setup_v2(SlabPlan &s) {
     }
     if (s.P > 1 && !slab_ensure_S(s)) return false;
     bool ok = cudaStreamCreateWithFlags(&s.sb, cudaStreamNonBlocking) == cudaSuccess;
+    if (!getenv("B2FFT_SLAB_V2_ONE_STREAM")) ok = ok && cudaStreamCreateWithFlags(&s.s2, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&s.v2_e3, cudaEventDisableTiming) == cudaSuccess;
+    if (nch > 64) s.v2_flags = false;
     s.v2_e1.assign((size_t)nch * ng, nullptr);
     s.v2_ec.assign(nch, nullptr);
     s.v2_e2.assign(nch, nullptr);
@@ -839,11 +879,15 @@ static int slab_setup_p2p(SlabPlan &s) {
     B2_CK(cudaMalloc(&s.flag, 256));
     B2_CK(cudaMemset(s.flag, 0, 256));
     struct H {
-        cudaIpcMemHandle_t s, r;
-        int ok, has_s;
+        cudaIpcMemHandle_t s, r, f;
+        int ok, has_s, has_f;
     };
     H mine;
     memset(&mine, 0, sizeof mine);
+    if (cudaMalloc(&s.F, B2_SLAB_FLAG_BYTES) == cudaSuccess && cudaMemset(s.F, 0, B2_SLAB_FLAG_BYTES) == cudaSuccess &&
+        cudaMalloc(&s.epoch_dev, 256) == cudaSuccess && cudaIpcGetMemHandle(&mine.f, s.F) == cudaSuccess)
+        mine.has_f = 1;
+    cudaGetLastError();
     mine.has_s = s.S != nullptr;  // the v2 schedule has no send buffer
     mine.ok = !getenv("B2FFT_SLAB_SENDRECV") && (!s.S || cudaIpcGetMemHandle(&mine.s, s.S) == cudaSuccess) &&
               cudaIpcGetMemHandle(&mine.r, s.R) == cudaSuccess;
@@ -860,13 +904,22 @@ static int slab_setup_p2p(SlabPlan &s) {
     for (int p = 0; p < s.P; ++p) ok = ok && all[p].ok;
     s.peerS.assign(s.P, nullptr);
     s.peerR.assign(s.P, nullptr);
+    s.peerF.assign(s.P, nullptr);
+    bool flags_ok = true;
+    for (int p = 0; p < s.P; ++p) flags_ok = flags_ok && all[p].has_f;
     float good = 1.0f;
     if (ok)
         for (int p = 0; p < s.P; ++p) {
             if (p == s.pe) {
                 s.peerS[p] = s.S;
                 s.peerR[p] = s.R;
+                s.peerF[p] = s.F;
                 continue;
+            }
+            if (flags_ok && cudaIpcOpenMemHandle((void **)&s.peerF[p], all[p].f, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                good = 0.0f;
+                break;
             }
             if ((all[p].has_s && cudaIpcOpenMemHandle((void **)&s.peerS[p], all[p].s, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ||
                 cudaIpcOpenMemHandle((void **)&s.peerR[p], all[p].r, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
@@ -885,6 +938,7 @@ static int slab_setup_p2p(SlabPlan &s) {
     B2_CK(cudaMemcpy(&bad, s.flag, sizeof(float), cudaMemcpyDeviceToHost));
     B2_CK(cudaMemset(s.flag, 0, 256));
     s.p2p = (bad == 0.0f);
+    s.v2_flags = s.p2p && flags_ok && stream_wait_value() != nullptr && !getenv("B2FFT_SLAB_V2_NCCL_BARRIER");
     // One stream per peer (copies to different peers on different copy engines) is opt-in: on 8 B200
     // (profiles/r1_slab_8gpu.md, 2048^3) the shifted schedule p = pe + d on ONE stream keeps every
     // receiver paired with one sender at a time and exposes 6.0 ms of exchange, seven concurrent
@@ -1023,19 +1077,39 @@ extern "C" void *b2fft_slab_buffer(b2fft_plan *p, int which, size_t *bytes) {
 
 #if B2_CUDA
 // v2 schedule (see SlabPlan): din / dout are device arrays, W = dout.
-//   compute stream sc :  row(g0) | n1(g0,0) .. n1(g0,nch-1) | row(g1) | n1(g1,0) n1(g1,1) [n0(0)] n1(g1,2) [n0(1)] ...
-//                        (n0(k) is queued v2_lag chunks behind the last group's n1(k) so that the stream does not
-//                        stall on a chunk still in flight)
-//   copy stream sn    :  per (group, chunk), one 2-D copy per peer straight into the peer's receive buffer
-//   barrier stream sb :  per chunk, after the last group's copies: "every rank's copies of this chunk have landed"
+//   compute stream sc :  row(g0) | n1(g0,0) .. n1(g0,nch-1) | row(g1) | n1(g1,0) .. n1(g1,nch-1)   (never waits for a peer)
+//   copy stream sn    :  per (group, chunk), one 2-D copy per peer straight into the peer's receive buffer; behind the
+//                        last group's copies of chunk k, one 4-byte copy per peer: "my part of chunk k has landed"
+//   n0 stream s2      :  per chunk: wait for the P-1 flag words (cuStreamWaitValue32) and for this rank's own rows,
+//                        then the n0 pass.  (B2FFT_SLAB_V2_ONE_STREAM: queued on sc instead, v2_lag chunks behind;
+//                        B2FFT_SLAB_V2_NCCL_BARRIER: a 1-float NCCL all-reduce per chunk on stream sb instead of flags.)
 static int slab_execute_v2(SlabPlan &s, cpx_t *din, cpx_t *dout) {
     const size_t esz = sizeof(cpx_t);
-    const int nch = s.v2_nch, ng = s.v2_ng;
+    const int nch = s.v2_nch, ng = s.v2_ng, P = s.P;
     const size_t w = (size_t)s.v2_w, gp = (size_t)s.v2_gp;
+    const bool flags = s.v2_flags && P > 1;
+    cudaStream_t sq = s.s2 ? s.s2 : s.sc;  // where the n0 passes run
+    StreamWaitValueFn wait_value = flags ? stream_wait_value() : nullptr;
+    auto wait_flag = [&](cudaStream_t st, size_t idx, unsigned value) -> int {
+        const CUresult r = wait_value((CUstream)st, (CUdeviceptr)(uintptr_t)(s.F + idx), value, CU_STREAM_WAIT_VALUE_GEQ);
+        if (r != CUDA_SUCCESS) {
+            set_error("cuStreamWaitValue32 failed (%d)", (int)r);
+            return 2000 + (int)r;
+        }
+        return 0;
+    };
     cpx_t *W = dout;
+    ++s.epoch;
     B2_CK(cudaEventRecord(s.t0, s.sc));
     // nobody may still be reading the receive buffer that this execute is about to overwrite
-    if (s.P > 1) {
+    if (P > 1 && flags) {
+        B2_CK(cudaMemcpyAsync(s.epoch_dev, &s.epoch, sizeof(unsigned), cudaMemcpyHostToDevice, s.sn));
+        for (int pe = 0; pe < P; ++pe)
+            if (pe != s.pe) {
+                int rc = wait_flag(s.sn, (size_t)nch * P + pe, s.epoch - 1);
+                if (rc) return rc;
+            }
+    } else if (P > 1) {
         int rc = slab_barrier(s, s.sb);
         if (rc) return rc;
         B2_CK(cudaEventRecord(s.v2_eb, s.sb));
@@ -1044,10 +1118,19 @@ static int slab_execute_v2(SlabPlan &s, cpx_t *din, cpx_t *dout) {
     b2fft_plan *row = s.ln0 > 0 ? slab_v2_row_plan(s, din == dout) : nullptr;
     if (s.ln0 > 0 && !row) return -6;
     auto n0_pass = [&](int k) -> int {
-        B2_CK(cudaStreamWaitEvent(s.sc, s.v2_e2[k], 0));
+        if (flags) {
+            B2_CK(cudaStreamWaitEvent(sq, s.v2_e1[(size_t)(ng - 1) * nch + k], 0));  // this rank's own rows of the chunk
+            for (int pe = 0; pe < P; ++pe)
+                if (pe != s.pe) {
+                    int rc = wait_flag(sq, (size_t)k * P + pe, s.epoch);
+                    if (rc) return rc;
+                }
+        } else
+            B2_CK(cudaStreamWaitEvent(sq, s.v2_e2[k], 0));
         if (!s.v2_n0) return 0;
-        return b2fft_execute_async(s.v2_n0, s.R + (size_t)k * s.n0 * s.ln1 * w, dout + (size_t)k * w, s.sc);
+        return b2fft_execute_async(s.v2_n0, s.R + (size_t)k * s.n0 * s.ln1 * w, dout + (size_t)k * w, sq);
     };
+    const int lag = s.s2 ? 0 : s.v2_lag;
     for (int g = 0; g < ng; ++g) {
         const size_t p0 = (size_t)g * gp;  // first plane of the group
         if (row) {
@@ -1060,7 +1143,7 @@ static int slab_execute_v2(SlabPlan &s, cpx_t *din, cpx_t *dout) {
             if (s.v2_n1) {
                 cpx_t *wk = W + p0 * s.n1 * s.n2 + (size_t)k * w;
                 real_t *bases[B2_MAXSCAT];
-                for (int o = 0; o < s.P; ++o)
+                for (int o = 0; o < P; ++o)
                     bases[o] = o == s.pe ? (real_t *)(s.R + (size_t)k * s.n0 * s.ln1 * w + ((size_t)s.s0 + p0) * s.ln1 * w)
                                          : (real_t *)(Sk + (size_t)o * s.b1 * w);
                 int rc = b2_plan_execute_scatter(s.v2_n1, wk, wk, bases, 0, s.sc);
@@ -1069,33 +1152,45 @@ static int slab_execute_v2(SlabPlan &s, cpx_t *din, cpx_t *dout) {
             cudaEvent_t e1 = s.v2_e1[(size_t)g * nch + k];
             B2_CK(cudaEventRecord(e1, s.sc));
             B2_CK(cudaStreamWaitEvent(s.sn, e1, 0));
-            for (int d = 1; d < s.P && s.ln0 > 0; ++d) {  // shifted order: one sender per receiver at a time
-                const int pe = (s.pe + d) % s.P;
+            for (int d = 1; d < P; ++d) {  // shifted order: one sender per receiver at a time
+                const int pe = (s.pe + d) % P;
                 const size_t ln1p = (size_t)blk_len(s.n1, s.b1, pe);
-                if (ln1p == 0) continue;
-                B2_CK(cudaMemcpy2DAsync(s.peerR[pe] + (size_t)k * s.n0 * ln1p * w + ((size_t)s.s0 + p0) * ln1p * w, ln1p * w * esz,
-                                        Sk + (size_t)pe * s.b1 * w, (size_t)s.n1 * w * esz, ln1p * w * esz, gp,
-                                        cudaMemcpyDeviceToDevice, s.sn));
+                if (ln1p > 0 && s.ln0 > 0)
+                    B2_CK(cudaMemcpy2DAsync(s.peerR[pe] + (size_t)k * s.n0 * ln1p * w + ((size_t)s.s0 + p0) * ln1p * w, ln1p * w * esz,
+                                            Sk + (size_t)pe * s.b1 * w, (size_t)s.n1 * w * esz, ln1p * w * esz, gp,
+                                            cudaMemcpyDeviceToDevice, s.sn));
+                if (flags && g == ng - 1)  // behind the data, same stream: "rank s.pe's part of chunk k is in your receive buffer"
+                    B2_CK(cudaMemcpyAsync(s.peerF[pe] + (size_t)k * P + s.pe, s.epoch_dev, sizeof(unsigned), cudaMemcpyDeviceToDevice, s.sn));
             }
             if (g == ng - 1) {
-                B2_CK(cudaEventRecord(s.v2_ec[k], s.sn));
-                B2_CK(cudaStreamWaitEvent(s.sb, s.v2_ec[k], 0));
-                if (s.P > 1) {
-                    int rc = slab_barrier(s, s.sb);
-                    if (rc) return rc;
+                if (!flags) {
+                    B2_CK(cudaEventRecord(s.v2_ec[k], s.sn));
+                    B2_CK(cudaStreamWaitEvent(s.sb, s.v2_ec[k], 0));
+                    if (P > 1) {
+                        int rc = slab_barrier(s, s.sb);
+                        if (rc) return rc;
+                    }
+                    B2_CK(cudaEventRecord(s.v2_e2[k], s.sb));
                 }
-                B2_CK(cudaEventRecord(s.v2_e2[k], s.sb));
-                if (k >= s.v2_lag) {
-                    int rc = n0_pass(k - s.v2_lag);
+                if (k >= lag) {
+                    int rc = n0_pass(k - lag);
                     if (rc) return rc;
                 }
             }
         }
     }
     B2_CK(cudaEventRecord(s.v2_tb, s.sc));
-    for (int k = std::max(0, nch - s.v2_lag); k < nch; ++k) {
+    for (int k = std::max(0, nch - lag); k < nch; ++k) {
         int rc = n0_pass(k);
         if (rc) return rc;
+    }
+    if (flags)  // "this rank has finished reading its receive buffer for this epoch"
+        for (int pe = 0; pe < P; ++pe)
+            if (pe != s.pe)
+                B2_CK(cudaMemcpyAsync(s.peerF[pe] + (size_t)nch * P + s.pe, s.epoch_dev, sizeof(unsigned), cudaMemcpyDeviceToDevice, sq));
+    if (sq != s.sc) {
+        B2_CK(cudaEventRecord(s.v2_e3, sq));
+        B2_CK(cudaStreamWaitEvent(s.sc, s.v2_e3, 0));
     }
     B2_CK(cudaEventRecord(s.t3, s.sc));
     return 0;
@@ -1136,6 +1231,7 @@ int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
         B2_CK(cudaStreamSynchronize(s.sc));
         B2_CK(cudaStreamSynchronize(s.sn));
         B2_CK(cudaStreamSynchronize(s.sb));
+        if (s.s2) B2_CK(cudaStreamSynchronize(s.s2));
         // row pass | pipelined n1 passes, exchange and n0 passes | the n0 passes left after the last n1 pass
         cudaEventElapsedTime(&s.ms[0], s.t0, s.v2_ta);
         cudaEventElapsedTime(&s.ms[1], s.v2_ta, s.v2_tb);
