@@ -733,7 +733,10 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
 #if B2_CUDA
 static bool slab_setup_v2(SlabPlan &s) {
     // chunk width: whole 128-byte segments and rows of >= 1 KiB; else fewer chunks
-    int nch = 8;
+    // measured on 2048^3 (profiles/r2_slab_8gpu.md): on 8 GPUs 4 chunks 16.6-16.9 ms, 8 chunks 18.7-19.8, 16 chunks 19.6-20.9
+    // (exchange-bound: every extra chunk adds a barrier and copy start-up on the critical path); on 2 GPUs the
+    // pipeline is compute-bound and 8 chunks are as good as 4
+    int nch = s.P > 2 ? 4 : 8;
     if (const char *e = getenv("B2FFT_SLAB_V2_CHUNKS")) nch = std::max(1, atoi(e));
     while (nch > 1 && (s.n2 % nch != 0 || (s.n2 / nch) % 16 != 0 || s.n2 / nch < 128)) --nch;
     s.v2_nch = nch;
@@ -781,7 +784,9 @@ static bool slab_setup_v2(SlabPlan &s) {
     }
     if (s.P > 1 && !slab_ensure_S(s)) return false;
     bool ok = cudaStreamCreateWithFlags(&s.sb, cudaStreamNonBlocking) == cudaSuccess;
-    if (!getenv("B2FFT_SLAB_V2_ONE_STREAM")) ok = ok && cudaStreamCreateWithFlags(&s.s2, cudaStreamNonBlocking) == cudaSuccess;
+    // opt-in: with the n0 passes on their own stream all n1 passes run first and compete with the whole exchange
+    // for HBM -- measured slower on 8 B200 (19.3 against 16.9 ms, profiles/r2_slab_8gpu.md)
+    if (getenv("B2FFT_SLAB_V2_SPLIT")) ok = ok && cudaStreamCreateWithFlags(&s.s2, cudaStreamNonBlocking) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&s.v2_e3, cudaEventDisableTiming) == cudaSuccess;
     if (nch > 64) s.v2_flags = false;
     s.v2_e1.assign((size_t)nch * ng, nullptr);
@@ -938,7 +943,8 @@ static int slab_setup_p2p(SlabPlan &s) {
     B2_CK(cudaMemcpy(&bad, s.flag, sizeof(float), cudaMemcpyDeviceToHost));
     B2_CK(cudaMemset(s.flag, 0, 256));
     s.p2p = (bad == 0.0f);
-    s.v2_flags = s.p2p && flags_ok && stream_wait_value() != nullptr && !getenv("B2FFT_SLAB_V2_NCCL_BARRIER");
+    // opt-in: measured slower on 8 B200 (profiles/r2_slab_8gpu.md: the 4-byte peer copies cost ~4 ms per execute)
+    s.v2_flags = s.p2p && flags_ok && stream_wait_value() != nullptr && getenv("B2FFT_SLAB_V2_FLAGS") != nullptr;
     // One stream per peer (copies to different peers on different copy engines) is opt-in: on 8 B200
     // (profiles/r1_slab_8gpu.md, 2048^3) the shifted schedule p = pe + d on ONE stream keeps every
     // receiver paired with one sender at a time and exposes 6.0 ms of exchange, seven concurrent
@@ -1080,9 +1086,10 @@ extern "C" void *b2fft_slab_buffer(b2fft_plan *p, int which, size_t *bytes) {
 //   compute stream sc :  row(g0) | n1(g0,0) .. n1(g0,nch-1) | row(g1) | n1(g1,0) .. n1(g1,nch-1)   (never waits for a peer)
 //   copy stream sn    :  per (group, chunk), one 2-D copy per peer straight into the peer's receive buffer; behind the
 //                        last group's copies of chunk k, one 4-byte copy per peer: "my part of chunk k has landed"
-//   n0 stream s2      :  per chunk: wait for the P-1 flag words (cuStreamWaitValue32) and for this rank's own rows,
-//                        then the n0 pass.  (B2FFT_SLAB_V2_ONE_STREAM: queued on sc instead, v2_lag chunks behind;
-//                        B2FFT_SLAB_V2_NCCL_BARRIER: a 1-float NCCL all-reduce per chunk on stream sb instead of flags.)
+//   barrier stream sb :  per chunk, after the last group's copies: "every rank's copies of this chunk have landed"
+//                        (1-float NCCL all-reduce); the n0 pass of chunk k is queued on sc v2_lag chunks behind n1(k)
+//   Opt-in variants, both measured slower on 8 GPUs: B2FFT_SLAB_V2_FLAGS (epoch flags in peer memory + cuStreamWaitValue32
+//   instead of the barrier kernels), B2FFT_SLAB_V2_SPLIT (n0 passes on their own stream s2).
 static int slab_execute_v2(SlabPlan &s, cpx_t *din, cpx_t *dout) {
     const size_t esz = sizeof(cpx_t);
     const int nch = s.v2_nch, ng = s.v2_ng, P = s.P;
