@@ -16,7 +16,8 @@
 using namespace b2;
 
 // ------------------------------------------------------------------------- launching
-static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream_t stream) {
+// bfirst / bcount: a sub-range of the step's blocks (grouped execution); bcount < 0: all of them
+static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream_t stream, long long bfirst = 0, long long bcount = -1) {
     // host loops over the line dims that did not fit in the kernel descriptor (almost never any)
     long long idx_store[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     std::vector<long long> idx_heap;
@@ -40,9 +41,10 @@ static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream
         PassParams pp = fast ? s.pp : s.gen_pp;
         if (!al_s) pp.vec_ld = 0;
         if (!al_d) pp.vec_st = 0;
-        const long long nblocks = (s.kind == SK_PASS && !fast) ? s.gen_nblocks : s.nblocks;
+        long long nblocks = (s.kind == SK_PASS && !fast) ? s.gen_nblocks : s.nblocks;
+        if (bcount >= 0) nblocks = std::min(nblocks, bfirst + bcount);
         const long long maxgrid = 1ll << 30;
-        for (long long b0 = 0; b0 < nblocks; b0 += maxgrid) {
+        for (long long b0 = bfirst; b0 < nblocks; b0 += maxgrid) {
             const long long nb = std::min(maxgrid, nblocks - b0);
             if (s.kind == SK_PASS && fast) {
                 int rc = b2_launch_tile_kernel(s.fast_id, pp, sp, dp, b0, nb, s.nthreads, s.smem, stream);
@@ -115,6 +117,29 @@ static int run_chain(b2fft_plan *p, const Chain &ch, real_t *const *buf, stream_
     return b2_launch_chain(cp, ch.threads, ch.smem, stream);
 }
 
+// Grouped execution (selector.h Step::grp_L).  Worth it only when the array between the two steps is much larger
+// than the L2; group size: FFTW_B200_GROUP_MIB (default 32 MiB of that array per group).
+// (the environment is read per call, but only for plans that have a groupable pair: tests lower the thresholds)
+static long long group_slabs(const b2fft_plan *p, const StepPlan &s) {
+    const char *e = getenv("FFTW_B200_GROUP_KIB");
+    const double group_bytes = e ? 1024.0 * std::max(1ll, atoll(e)) : 32.0 * (1 << 20);
+    const double total = (double)(s.dst == B_SCR ? p->pc.scr_reals : p->pc.out_reals) * sizeof(real_t);
+    const double slab = total / (double)s.grp_L;
+    return std::max<long long>(1, std::min<long long>(s.grp_L, (long long)(group_bytes / slab + 0.5)));
+}
+static bool group_pair_ok(const b2fft_plan *p, const StepPlan &s, const StepPlan &t) {
+    if (s.grp_L <= 1 || s.grp_L != t.grp_L || getenv("FFTW_B200_NO_GROUPS")) return false;
+    if (s.kind != SK_PASS || t.kind != SK_PASS || s.fast_id < 0 || t.fast_id < 0 || s.chain_id >= 0 || t.chain_id >= 0) return false;
+    if (!s.outer.empty() || !t.outer.empty() || s.dst != t.src) return false;
+    if (s.nblocks % s.grp_L || t.nblocks % t.grp_L) return false;  // a tile must not straddle two slabs
+    for (const StepPlan *q : {&s, &t})                             // (slab dim merged into the tile dim: whole tiles per slab)
+        if (q->pp.nld == 1 && (q->pp.ln[0] % q->grp_L || (q->pp.ln[0] / q->grp_L) % q->pp.C)) return false;
+    const double total = (double)(s.dst == B_SCR ? p->pc.scr_reals : p->pc.out_reals) * sizeof(real_t);
+    const char *e = getenv("FFTW_B200_GROUP_MIN_KIB");
+    if (total < (e ? 1024.0 * atoll(e) : 192.0 * (1 << 20))) return false;  // fits the L2 (or nearly): nothing to gain
+    return group_slabs(p, s) < s.grp_L;
+}
+
 static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
     real_t *buf[B_NBUF] = {in, out, p->scr, p->wrk};
     const bool aligned = ((uintptr_t)in % sizeof(cpx_t)) == 0 && ((uintptr_t)out % sizeof(cpx_t)) == 0;
@@ -132,6 +157,22 @@ static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
     const size_t ns = p->pc.steps.size();
     for (size_t i = 0; i < ns; ++i) {
         const StepPlan &s = p->pc.steps[i];
+        if (i + 1 < ns && aligned && group_pair_ok(p, s, p->pc.steps[i + 1])) {
+            // ---- grouped execution: steps i and i+1 slab group by slab group, the array between them stays in L2
+            const StepPlan &t = p->pc.steps[i + 1];
+            const long long L = s.grp_L, bs = s.nblocks / L, bt = t.nblocks / L;
+            const long long spg = group_slabs(p, s);
+            for (long long a = 0; a < L; a += spg) {
+                const long long cnt = std::min(spg, L - a);
+                // scratch between the two steps: every group sits at the start of the scratch (never written back)
+                const long long shift = (s.grp_slab > 0 && s.dst == B_SCR && t.src == B_SCR) ? a * s.grp_slab : 0;
+                int rc = launch_step(s, buf[s.src], buf[s.dst] - shift, stream, a * bs, cnt * bs);
+                if (!rc) rc = launch_step(t, buf[t.src] - shift, buf[t.dst], stream, a * bt, cnt * bt);
+                if (rc) return rc;
+            }
+            ++i;
+            continue;
+        }
         if (s.chain_id >= 0 && s.chain_pos == 0 && aligned && p->chains) {
             const Chain &ch = (*p->chains)[s.chain_id];
             int rc = run_chain(p, ch, buf, stream);

@@ -566,9 +566,11 @@ inline bool build_c2c(PlanCore &pc) {
         st.dst_allowed = fft_dst;
         pc.steps.push_back(st);
     }
+    std::vector<size_t> axis_first_step;
     for (size_t oi = 0; oi < order.size(); ++oi) {
         const int ax = order[oi];
         const bool first = (oi == 0), last = (oi + 1 == order.size());
+        axis_first_step.push_back(pc.steps.size());
         std::vector<LDim> lines;
         for (int i = 0; i < (int)T.size(); ++i)
             if (i != ax) lines.push_back(LDim{T[i].n, 2 * (first ? T[i].is : T[i].os), 2 * T[i].os, false});
@@ -577,6 +579,27 @@ inline bool build_c2c(PlanCore &pc) {
         (void)last;
         if (!add_c2c_axis(pc, T[ax].n, 2 * (first ? T[ax].is : T[ax].os), 2 * T[ax].os, lines, bwd, bwd, fft_dst))
             return false;
+    }
+    // Grouped execution of the first two axes (the reference walks the same slabs one after the other: rank>=2
+    // applies its child plan per leading index, rank_geq2_apply fftw/fftw_api.c:4435-4445): when every other
+    // dimension is outside the plane of the two axes in the output layout, the two passes can run plane group by
+    // plane group.  Single-kernel axes only.
+    axis_first_step.push_back(pc.steps.size());
+    if (order.size() >= 2 && !relayout && axis_first_step[1] - axis_first_step[0] == 1 && axis_first_step[2] - axis_first_step[1] == 1) {
+        std::vector<GDim> ds;
+        for (const GDim &d : all)
+            if (d.n > 1) ds.push_back(d);
+        std::sort(ds.begin(), ds.end(), [](const GDim &a, const GDim &b) { return a.os < b.os; });
+        bool nested = ds.size() >= 3 && ds[0].os == T[order[0]].os && ds[0].n == T[order[0]].n && ds[1].os == T[order[1]].os &&
+                      ds[1].n == T[order[1]].n;
+        long long L = 1;
+        for (size_t k = 0; nested && k + 1 < ds.size(); ++k)
+            if (ds[k + 1].os < ds[k].os * ds[k].n) nested = false;
+        for (size_t k = 2; nested && k < ds.size(); ++k) L *= ds[k].n;
+        if (nested && L > 1) {
+            pc.steps[axis_first_step[0]].grp_L = L;
+            pc.steps[axis_first_step[1]].grp_L = L;
+        }
     }
     if (relayout) {  // work array (output layout) -> the user's array
         AxisSpec a;

@@ -481,6 +481,11 @@ inline bool build_real(PlanCore &pc) {
                 st.dst_allowed = {B_OUT};
                 pc.steps.push_back(st);
             }
+            if (nz.size() == 1 && nz[0].n > 1) {  // one batch dim: the two passes can run transform group by transform group
+                StepPlan &a = pc.steps[pc.steps.size() - 2], &b = pc.steps.back();
+                a.grp_L = b.grp_L = nz[0].n;
+                a.grp_slab = b.grp_slab = cs2[0];  // the intermediate's stride per transform, in reals
+            }
             (void)first_real_step;
             if (!leading_axes(false)) return false;
             return assign_buffers(pc);

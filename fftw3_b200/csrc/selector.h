@@ -66,6 +66,12 @@ struct Step {
     size_t smem = 0;
     int fast_id = -1;           // >= 0: specialised tile kernel
     int chain_id = -1, chain_pos = 0;  // member of a chained launch (chain_build.h)
+    // Grouped execution (engine.cu run_steps): the step's tiles, in launch order, fall into grp_L equal slabs, and
+    // slab l of the step reads and writes only slab l of its arrays (planes of an N-D transform, transforms of a
+    // batch).  Two consecutive steps with the same grp_L > 1 are run group by group so that the array between
+    // them stays in the 126 MB L2.  grp_slab > 0: that array is plan scratch with this slab stride (reals): every
+    // group is placed at the start of the scratch, which then never has to be written back to HBM.
+    long long grp_L = 0, grp_slab = 0;
     std::vector<LDim> outer;    // extra line dims looped on the host
     std::string desc;
 };

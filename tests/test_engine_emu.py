@@ -144,3 +144,34 @@ def test_chained_launch_opt_in(lib):
 
 def test_two_pass_c2r_opt_in(lib):
     cases.check_two_pass_c2r(lib)
+
+
+@pytest.mark.parametrize("shape", [(6, 32, 128), (5, 3, 64, 256)], ids=lambda s: "x".join(map(str, s)))
+def test_grouped_execution_of_the_first_two_axes(lib, shape, monkeypatch):
+    """N-D c2c: the passes over the two innermost axes run plane group by plane group (engine.cu run_steps), forced
+    here at a size the emulation can run: groups of two planes, every plane larger than the 'fits the L2' threshold"""
+    monkeypatch.setenv("FFTW_B200_GROUP_MIN_KIB", "1")
+    monkeypatch.setenv("FFTW_B200_GROUP_KIB", str(2 * shape[-1] * shape[-2] * 2 * np.dtype(lib.real).itemsize // 1024))
+    cases.check_c2c(lib, shape)
+    monkeypatch.setenv("FFTW_B200_NO_GROUPS", "1")   # and the same plan without grouping agrees bit for bit
+    rng = np.random.default_rng(4)
+    x = cases.rand_c(rng, shape, lib)
+    a = lib.dft(x, -1)
+    monkeypatch.delenv("FFTW_B200_NO_GROUPS")
+    assert np.array_equal(a, lib.dft(x, -1))
+
+
+@pytest.mark.parametrize("shape", [(7, 2 ** 16), (4, 2 ** 17)], ids=lambda s: "x".join(map(str, s)))
+def test_grouped_execution_of_the_two_pass_real_transform(lib, shape, monkeypatch):
+    """batched two-pass r2c: both passes run transform group by transform group through the START of the scratch
+    array (three transforms per group here; 7 = 3 + 3 + 1 also covers the short last group)"""
+    monkeypatch.setenv("FFTW_B200_GROUP_MIN_KIB", "1")
+    monkeypatch.setenv("FFTW_B200_GROUP_KIB", str(3 * (shape[-1] + 2 * int(np.sqrt(shape[-1]))) * np.dtype(lib.real).itemsize // 1024))
+    x = np.zeros(shape, dtype=lib.real)
+    p = lib.plan_many_dft_r2c([shape[-1]], shape[0], x, None, 1, shape[-1], np.zeros((shape[0], shape[-1] // 2 + 1), dtype=lib.cplx),
+                              None, 1, shape[-1] // 2 + 1)
+    two_pass = "real-pair split" in lib.sprint_plan(p)
+    lib.destroy_plan(p)
+    if not two_pass:
+        pytest.skip("this precision does not take the two-pass real path at this length")
+    cases.check_r2c_c2r(lib, shape)
