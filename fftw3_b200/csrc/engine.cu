@@ -128,7 +128,10 @@ static long long group_slabs(const b2fft_plan *p, const StepPlan &s) {
     return std::max<long long>(1, std::min<long long>(s.grp_L, (long long)(group_bytes / slab + 0.5)));
 }
 static bool group_pair_ok(const b2fft_plan *p, const StepPlan &s, const StepPlan &t) {
-    if (s.grp_L <= 1 || s.grp_L != t.grp_L || getenv("FFTW_B200_NO_GROUPS")) return false;
+    // Opt-in (FFTW_B200_GROUPS=1): measured on B200 (profiles/r2_group_probe.md) every group size loses -- 512^3 1.39-2.02 ms
+    // against 1.19, r2c 2^20 x 256 1.56-1.93 against 1.21: ~6 us of ramp-up and tail per small launch outweigh the HBM
+    // traffic that the L2-resident intermediate saves.
+    if (s.grp_L <= 1 || s.grp_L != t.grp_L || !getenv("FFTW_B200_GROUPS") || getenv("FFTW_B200_NO_GROUPS")) return false;
     if (s.kind != SK_PASS || t.kind != SK_PASS || s.fast_id < 0 || t.fast_id < 0 || s.chain_id >= 0 || t.chain_id >= 0) return false;
     if (!s.outer.empty() || !t.outer.empty() || s.dst != t.src) return false;
     if (s.nblocks % s.grp_L || t.nblocks % t.grp_L) return false;  // a tile must not straddle two slabs

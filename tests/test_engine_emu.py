@@ -148,8 +148,9 @@ def test_two_pass_c2r_opt_in(lib):
 
 @pytest.mark.parametrize("shape", [(6, 32, 128), (5, 3, 64, 256)], ids=lambda s: "x".join(map(str, s)))
 def test_grouped_execution_of_the_first_two_axes(lib, shape, monkeypatch):
-    """N-D c2c: the passes over the two innermost axes run plane group by plane group (engine.cu run_steps), forced
+    """N-D c2c: the passes over the two innermost axes run plane group by plane group (engine.cu run_steps; opt-in), forced
     here at a size the emulation can run: groups of two planes, every plane larger than the 'fits the L2' threshold"""
+    monkeypatch.setenv("FFTW_B200_GROUPS", "1")
     monkeypatch.setenv("FFTW_B200_GROUP_MIN_KIB", "1")
     monkeypatch.setenv("FFTW_B200_GROUP_KIB", str(2 * shape[-1] * shape[-2] * 2 * np.dtype(lib.real).itemsize // 1024))
     cases.check_c2c(lib, shape)
@@ -165,6 +166,7 @@ def test_grouped_execution_of_the_first_two_axes(lib, shape, monkeypatch):
 def test_grouped_execution_of_the_two_pass_real_transform(lib, shape, monkeypatch):
     """batched two-pass r2c: both passes run transform group by transform group through the START of the scratch
     array (three transforms per group here; 7 = 3 + 3 + 1 also covers the short last group)"""
+    monkeypatch.setenv("FFTW_B200_GROUPS", "1")
     monkeypatch.setenv("FFTW_B200_GROUP_MIN_KIB", "1")
     monkeypatch.setenv("FFTW_B200_GROUP_KIB", str(3 * (shape[-1] + 2 * int(np.sqrt(shape[-1]))) * np.dtype(lib.real).itemsize // 1024))
     x = np.zeros(shape, dtype=lib.real)
