@@ -37,18 +37,23 @@ inline void host_fft_pow2(std::vector<std::complex<long double>> &a) {
 
 struct BlueTables {
     std::mutex mu;
-    std::map<unsigned long long, cpx_t *> chirps;
-    std::map<std::pair<unsigned long long, unsigned long long>, cpx_t *> bhats;
+    // keyed by device as well (see TwiddleCache); a failed upload is NOT remembered: the next plan tries again
+    std::map<std::pair<int, unsigned long long>, cpx_t *> chirps;
+    std::map<std::tuple<int, unsigned long long, unsigned long long>, cpx_t *> bhats;
 
     static cpx_t *upload(const std::vector<cpx_t> &h) {
         cpx_t *d = (cpx_t *)dev_malloc(h.size() * sizeof(cpx_t));
         if (!d) return nullptr;
-        if (dev_upload(d, h.data(), h.size() * sizeof(cpx_t)) != 0) return nullptr;
+        if (dev_upload(d, h.data(), h.size() * sizeof(cpx_t)) != 0) {
+            dev_free(d);
+            return nullptr;
+        }
         return d;
     }
     cpx_t *chirp(unsigned long long n) {
         std::lock_guard<std::mutex> lk(mu);
-        auto it = chirps.find(n);
+        const auto ckey = std::make_pair(current_device(), n);
+        auto it = chirps.find(ckey);
         if (it != chirps.end()) return it->second;
         std::vector<cpx_t> h(n);
         for (unsigned long long j = 0; j < n; ++j) {
@@ -57,11 +62,13 @@ struct BlueTables {
             h[j].x = (real_t)c;
             h[j].y = (real_t)s;
         }
-        return chirps[n] = upload(h);
+        cpx_t *d = upload(h);
+        if (d) chirps[ckey] = d;
+        return d;
     }
     cpx_t *bhat(unsigned long long n, unsigned long long M) {
         std::lock_guard<std::mutex> lk(mu);
-        auto key = std::make_pair(n, M);
+        auto key = std::make_tuple(current_device(), n, M);
         auto it = bhats.find(key);
         if (it != bhats.end()) return it->second;
         std::vector<std::complex<long double>> b(M, std::complex<long double>(0, 0));
@@ -78,7 +85,9 @@ struct BlueTables {
             h[k].x = (real_t)(b[k].real() / (long double)M);
             h[k].y = (real_t)(b[k].imag() / (long double)M);
         }
-        return bhats[key] = upload(h);
+        cpx_t *d = upload(h);
+        if (d) bhats[key] = d;
+        return d;
     }
     void clear() {
         std::lock_guard<std::mutex> lk(mu);

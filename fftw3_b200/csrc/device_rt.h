@@ -9,6 +9,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
+#include <mutex>
 #include <string>
 
 #include "b2_common.h"
@@ -50,20 +52,44 @@ inline int &device_ordinal() {
     static int d = -1;
     return d;
 }
-// 0 when a usable device is selected
+// Every extern "C" entry point opens one of these first: whatever device the engine makes current inside the call,
+// the CALLER's current device is what it was when the call returns (a host application on cuda:1 must not find
+// itself on cuda:0 after planning an FFT).
+struct DeviceScope {
+    int prev = -1;
+    DeviceScope() {
+        if (cudaGetDevice(&prev) != cudaSuccess) {
+            cudaGetLastError();
+            prev = -1;
+        }
+    }
+    ~DeviceScope() {
+        int cur = -1;
+        if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+    }
+    DeviceScope(const DeviceScope &) = delete;
+    DeviceScope &operator=(const DeviceScope &) = delete;
+};
+// 0 when a usable device is selected (and made current for the rest of the enclosing DeviceScope)
 inline int ensure_device() {
-    static int state = 0;  // 0 unknown, 1 ok, -1 none
-    if (state == 1) {
+    static std::atomic<int> state{0};  // 0 unknown, 1 ok, -1 none
+    static std::mutex init_mu;
+    if (state.load(std::memory_order_acquire) == 1) {
         cudaSetDevice(device_ordinal());
         return 0;
     }
-    if (state == -1) return -1;
+    std::lock_guard<std::mutex> lk(init_mu);
+    if (state.load() == 1) {
+        cudaSetDevice(device_ordinal());
+        return 0;
+    }
+    if (state.load() == -1) return -1;
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n <= 0) {
         set_error("no CUDA device available (%s): the B200 engine has no CPU fallback",
                   e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
-        state = -1;
+        state.store(-1);
         return -1;
     }
     int d = device_ordinal();
@@ -76,11 +102,28 @@ inline int ensure_device() {
     device_ordinal() = d;
     if (cudaSetDevice(d) != cudaSuccess) {
         set_error("cudaSetDevice(%d) failed", d);
-        state = -1;
+        state.store(-1);
         return -1;
     }
-    state = 1;
+    state.store(1, std::memory_order_release);
     return 0;
+}
+// a plan runs on the device it was created on, whatever the engine's device is by now (b2fft_set_device)
+inline int ensure_device_of(int dev) {
+    if (ensure_device() != 0) return -1;
+    if (dev >= 0 && dev != device_ordinal() && cudaSetDevice(dev) != cudaSuccess) {
+        set_error("cudaSetDevice(%d) failed: %s", dev, cudaGetErrorString(cudaGetLastError()));
+        return -1;
+    }
+    return 0;
+}
+inline int current_device() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess) {
+        cudaGetLastError();
+        d = 0;
+    }
+    return d;
 }
 inline void *dev_malloc(size_t bytes) {
     void *p = nullptr;
@@ -138,6 +181,9 @@ inline int sm_count() {
 }
 #else  // ---------------------------------------------------------------- emulation
 typedef void *stream_t;
+struct DeviceScope {};
+inline int ensure_device_of(int) { return 0; }
+inline int current_device() { return 0; }
 #define B2_CK(expr)                 \
     do {                            \
         int e_ = (expr);            \

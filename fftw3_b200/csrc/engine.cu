@@ -70,12 +70,8 @@ static int launch_step(const StepPlan &s, const real_t *src, real_t *dst, stream
                 for (long long b = 0; b < nb; ++b) b2_realpp_body(s.rp, s.kind == SK_RPOST, sp, dp, b0 + b, s.nthreads);
 #endif
             }
-            ++launch_counter();
-#if B2_CUDA
-            B2_CK(cudaGetLastError());
-#else
+            ++launch_counter();  // (launch errors are collected once per execute: run_steps / b2_plan_execute_scatter)
             (void)stream;
-#endif
         }
         size_t i = 0;
         for (; i < s.outer.size(); ++i) {
@@ -186,6 +182,9 @@ static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
         int rc = launch_step(s, buf[s.src], buf[s.dst], stream);
         if (rc) return rc;
     }
+#if B2_CUDA
+    B2_CK(cudaGetLastError());
+#endif
     return 0;
 }
 
@@ -243,7 +242,11 @@ int b2_plan_execute_scatter(b2fft_plan_s *p, void *in, void *out, real_t *const 
     StepPlan s = *p->scat;
     for (int o = 0; o < s.pp.scat_n; ++o) s.pp.scat_base[o] = bases[o];
     s.pp.scat_coord0 = coord0;
-    return launch_step(s, buf[s.src], buf[s.dst], stream);
+    int rc = launch_step(s, buf[s.src], buf[s.dst], stream);
+#if B2_CUDA
+    if (!rc) B2_CK(cudaGetLastError());
+#endif
+    return rc;
 }
 
 #if B2_CUDA
@@ -264,6 +267,7 @@ static void init_kernel_attrs() {
 
 extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
     if (!g) return nullptr;
+    DeviceScope caller;
     if (ensure_device() != 0) return nullptr;
 #if B2_CUDA
     init_kernel_attrs();
@@ -273,6 +277,7 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
         return nullptr;
     }
     b2fft_plan *p = new b2fft_plan_s();
+    p->device = current_device();
     p->pc.g = *g;
     p->pc.in_place = g->in_place != 0;
     auto build = [&]() {
@@ -345,6 +350,8 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
 
 extern "C" void b2fft_plan_destroy(b2fft_plan *p) {
     if (!p) return;
+    DeviceScope caller;
+    ensure_device_of(p->device);
     if (p->slab) b2_slab_destroy(p);
 #if B2_CUDA
     pipe_destroy(p);
@@ -452,23 +459,32 @@ static int pipe_execute(b2fft_plan *p, void *in, void *out) {
 extern "C" int b2fft_execute_async(b2fft_plan *p, void *in, void *out, void *stream) {
     if (!p) return -1;
     if (p->pc.empty) return 0;
-    if (ensure_device() != 0) return -1;
+    DeviceScope caller;
+    if (ensure_device_of(p->device) != 0) return -1;
     return run_steps(p, (real_t *)in, (real_t *)out, (stream_t)stream);
 }
 
 extern "C" int b2fft_execute(b2fft_plan *p, void *in, void *out) {
     if (!p) return -1;
     std::lock_guard<std::mutex> guard(p->exec_mutex);
+    DeviceScope caller;
     if (p->slab) return b2_slab_execute(p, in, out);
     if (p->pc.empty) return 0;
-    if (ensure_device() != 0) return -1;
+    if (ensure_device_of(p->device) != 0) return -1;
     const bool same = (in == out);
     if (same != p->pc.in_place) {
         set_error("execute: in-place-ness differs from the plan (reference contract, fftw_api.c:434-440)");
         return -2;
     }
 #if B2_CUDA
-    const bool din = is_device_ptr(in), dout = is_device_ptr(out);
+    if (!p->cls_valid || in != p->cls_in || out != p->cls_out) {
+        p->cls_din = is_device_ptr(in);
+        p->cls_dout = (out == in) ? p->cls_din : (bool)is_device_ptr(out);
+        p->cls_in = in;
+        p->cls_out = out;
+        p->cls_valid = true;
+    }
+    const bool din = p->cls_din, dout = p->cls_dout;
     if (!din && !dout) {
         if (!p->pipe) pipe_setup(p);
         if (p->pipe->state == 1) return pipe_execute(p, in, out);
@@ -517,9 +533,13 @@ extern "C" int b2fft_plan_describe(const b2fft_plan *p, char *buf, size_t n) {
 extern "C" double b2fft_plan_flops(const b2fft_plan *p) { return p ? p->pc.flops : 0.0; }
 extern "C" unsigned long long b2fft_launch_count(void) { return launch_counter(); }
 
-extern "C" void *b2fft_malloc(size_t n) { return host_malloc(n); }
+extern "C" void *b2fft_malloc(size_t n) {
+    DeviceScope caller;
+    return host_malloc(n);
+}
 extern "C" void b2fft_free(void *p) { host_free(p); }
 extern "C" void *b2fft_device_malloc(size_t n) {
+    DeviceScope caller;
     if (ensure_device() != 0) return nullptr;
     return dev_malloc(n);
 }
@@ -538,8 +558,15 @@ extern "C" int b2fft_device_count(void) {
 }
 extern "C" int b2fft_set_device(int d) {
 #if B2_CUDA
+    // selects the device of plans created from now on (existing plans keep theirs; the table caches are per
+    // device); the caller's own current device is left alone
+    DeviceScope caller;
+    if (cudaSetDevice(d) != cudaSuccess) {
+        cudaGetLastError();
+        return -1;
+    }
     device_ordinal() = d;
-    return cudaSetDevice(d) == cudaSuccess ? 0 : -1;
+    return 0;
 #else
     (void)d;
     return 0;

@@ -31,6 +31,11 @@ struct b2fft_plan_s {
     real_t *dev_in = nullptr, *dev_out = nullptr;
     b2::stream_t stream = nullptr;
     bool own_stream = false;
+    int device = -1;  // the device the plan (its tables, work arrays, streams) lives on; executes make it current
+    // host / device classification of the arrays of the last synchronous execute (fftw_execute passes the same
+    // two pointers every time: one cudaPointerGetAttributes pair per plan, not per call)
+    const void *cls_in = nullptr, *cls_out = nullptr;
+    bool cls_din = false, cls_dout = false, cls_valid = false;
     SlabPlan *slab = nullptr;
     HostPipe *pipe = nullptr;
     std::vector<b2::Chain> *chains = nullptr;

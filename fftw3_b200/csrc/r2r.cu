@@ -208,6 +208,7 @@ extern "C" void b2fft_r2r_plan_destroy(b2fft_r2r *r) {
 extern "C" b2fft_r2r *b2fft_r2r_plan_create(int rank, const b2fft_dim *dims, int vrank, const b2fft_dim *vdims,
                                             const int *kinds) {
     if (rank < 0 || rank > B2FFT_MAXRANK || vrank < 0 || vrank > B2FFT_MAXRANK || (rank > 0 && (!dims || !kinds))) return nullptr;
+    DeviceScope caller;
     if (ensure_device() != 0) return nullptr;
     b2fft_r2r *r = new b2fft_r2r_s();
     // dense order: batch dims outermost, then the transform dims
@@ -297,6 +298,7 @@ extern "C" b2fft_r2r *b2fft_r2r_plan_create(int rank, const b2fft_dim *dims, int
 extern "C" int b2fft_r2r_execute(b2fft_r2r *r, void *in_, void *out_) {
     if (!r) return -1;
     std::lock_guard<std::mutex> guard(r->exec_mutex);
+    DeviceScope caller;
     if (ensure_device() != 0) return -1;
     if (r->total <= 0) return 0;
     real_t *in = (real_t *)in_, *out = (real_t *)out_;

@@ -139,6 +139,7 @@ struct b2fft_comm_s {
 extern "C" int b2fft_nccl_unique_id(void *id128) {
     NcclApi *a = nccl();
     if (!a) return -1;
+    DeviceScope caller;
     if (ensure_device() != 0) return -1;
     nccl_uid_t id;
     B2_NCCL(a->GetUniqueId(&id));
@@ -150,6 +151,7 @@ extern "C" b2fft_comm *b2fft_comm_create(const void *id128, int n_pes, int my_pe
         set_error("bad communicator shape");
         return nullptr;
     }
+    DeviceScope caller;
     if (ensure_device() != 0) return nullptr;
     b2fft_comm *c = new b2fft_comm_s();
     c->rank = my_pe;
@@ -608,6 +610,7 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
         set_error("slab plan: howmany must be positive");
         return nullptr;
     }
+    DeviceScope caller;
     if (ensure_device() != 0) return nullptr;
     SlabPlan *s = new SlabPlan();
     // FFTW_MPI_TRANSPOSED_IN: the input is [local_n1][n0][n2], block-distributed over n1 -- that is the
@@ -657,6 +660,7 @@ static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
     s->chunk = (maxl0 + s->nchunks - 1) / s->nchunks;
     s->nchunks = (int)((maxl0 + s->chunk - 1) / s->chunk);
     b2fft_plan *bp = new b2fft_plan_s();
+    bp->device = current_device();
     bp->slab = s;
     bool ok = true;
     if (kind == B2FFT_C2R) {
@@ -1037,6 +1041,8 @@ extern "C" int b2fft_slab_set_peer_recv(b2fft_plan *p, void *const *recv, int n)
 //   stage 3: natural output only: exchange recv -> out
 extern "C" int b2fft_slab_stage(b2fft_plan *p, int stage, void *in, void *out) {
     if (!p || !p->slab) return -1;
+    DeviceScope caller;
+    if (ensure_device_of(p->device) != 0) return -1;
     SlabPlan &s = *p->slab;
     if (!slab_ensure_S(s)) return -3;
     stream_t st = nullptr;
@@ -1206,7 +1212,7 @@ static int slab_execute_v2(SlabPlan &s, cpx_t *din, cpx_t *dout) {
 
 int b2_slab_execute(b2fft_plan_s *p, void *in, void *out) {
     SlabPlan &s = *p->slab;
-    if (ensure_device() != 0) return -1;
+    if (ensure_device_of(p->device) != 0) return -1;
 #if B2_CUDA
     cpx_t *din = (cpx_t *)in, *dout = (cpx_t *)out;
     const bool hin = !is_device_ptr(in), hout = !is_device_ptr(out);

@@ -130,6 +130,7 @@ static bool split_nest(const b2fft_geom &g, bool input_side, bool half, SplitCop
 
 extern "C" b2fft_split *b2fft_split_plan_create(const b2fft_geom *gu) {
     if (!gu || gu->rank < 0 || gu->rank > B2FFT_MAXRANK || gu->vrank < 0 || gu->vrank > B2FFT_MAXRANK) return nullptr;
+    DeviceScope caller;
     if (ensure_device() != 0) return nullptr;
     for (int i = 0; i < gu->rank; ++i)
         if (gu->dims[i].n <= 0) return nullptr;
@@ -218,6 +219,7 @@ static int split_unstage(real_t *dev, real_t *user, long long extent) {
 extern "C" int b2fft_split_execute(b2fft_split *s, void *ri_, void *ii_, void *ro_, void *io_) {
     if (!s) return -1;
     std::lock_guard<std::mutex> guard(s->exec_mutex);
+    DeviceScope caller;
     if (ensure_device() != 0) return -1;
     real_t *ri = (real_t *)ri_, *ii = (real_t *)ii_, *ro = (real_t *)ro_, *io = (real_t *)io_;
     int rc = 0;

@@ -39,12 +39,13 @@ inline void unit_root(unsigned long long num, unsigned long long den, long doubl
 
 struct TwiddleCache {
     std::mutex mu;
-    std::map<std::tuple<unsigned long long, unsigned long long, unsigned long long>, cpx_t *> tabs;
+    // keyed by the device the table lives on as well: a table cudaMalloc'ed on one GPU is not addressable from another
+    std::map<std::tuple<int, unsigned long long, unsigned long long, unsigned long long>, cpx_t *> tabs;
 
     // count entries w_den^(j*mult), j < count
     cpx_t *get(unsigned long long den, unsigned long long count, unsigned long long mult) {
         std::lock_guard<std::mutex> lk(mu);
-        auto key = std::make_tuple(den, count, mult);
+        auto key = std::make_tuple(current_device(), den, count, mult);
         auto it = tabs.find(key);
         if (it != tabs.end()) return it->second;
         std::vector<cpx_t> h(count ? count : 1);
@@ -56,7 +57,10 @@ struct TwiddleCache {
         }
         cpx_t *d = (cpx_t *)dev_malloc(h.size() * sizeof(cpx_t));
         if (!d) return nullptr;
-        if (dev_upload(d, h.data(), h.size() * sizeof(cpx_t)) != 0) return nullptr;
+        if (dev_upload(d, h.data(), h.size() * sizeof(cpx_t)) != 0) {
+            dev_free(d);
+            return nullptr;
+        }
         tabs[key] = d;
         return d;
     }

@@ -301,3 +301,54 @@ def test_chained_launch_opt_in(lib):
 
 def test_two_pass_c2r_opt_in(lib):
     cases.check_two_pass_c2r(lib)
+
+
+def test_engine_calls_leave_the_callers_current_device_alone(lib):
+    """the engine made its own device current on every call and never restored it.  Planning and
+    executing must leave the caller's current device as it was; with two GPUs a plan keeps running on the device it
+    was created on after b2fft_set_device selects another one, and the table caches are per device."""
+    import torch
+    L = lib.lib
+    ndev = torch.cuda.device_count()
+    caller = ndev - 1            # the caller works on the LAST device, the engine (so far) on device 0
+    rng = np.random.default_rng(21)
+    xh = cases.rand_c(rng, (4, 1000), lib)   # 1000 = 8 x 125: twiddle tables; 1009 below: Bluestein tables
+    ref = np.stack([np.fft.fft(r.astype(np.complex128)) for r in xh])
+    try:
+        L.b2fft_set_device(0)
+        torch.cuda.set_device(caller)
+        x0 = torch.from_numpy(xh).to("cuda:0")
+        y0 = torch.empty_like(x0)
+        p0 = lib.plan_many_dft([1000], 4, x0, None, 1, 1000, y0, None, 1, 1000, -1)
+        assert p0 and torch.cuda.current_device() == caller
+        lib.execute(p0)
+        assert torch.cuda.current_device() == caller
+        torch.cuda.synchronize(0)
+        assert cases.rel_l2(y0.cpu().numpy(), ref) < cases.tol(lib, 1000)
+        if ndev >= 2:
+            assert L.b2fft_set_device(1) == 0 and torch.cuda.current_device() == caller
+            x1 = torch.from_numpy(xh).to("cuda:1")
+            y1 = torch.empty_like(x1)
+            p1 = lib.plan_many_dft([1000], 4, x1, None, 1, 1000, y1, None, 1, 1000, -1)   # same length: its own tables on device 1
+            assert p1
+            lib.execute(p1)
+            y0.zero_()
+            lib.execute(p0)   # still on device 0
+            torch.cuda.synchronize(0)
+            torch.cuda.synchronize(1)
+            assert torch.cuda.current_device() == caller
+            assert cases.rel_l2(y1.cpu().numpy(), ref) < cases.tol(lib, 1000)
+            assert cases.rel_l2(y0.cpu().numpy(), ref) < cases.tol(lib, 1000)
+            xb = torch.from_numpy(cases.rand_c(rng, (2, 1009), lib)).to("cuda:1")
+            yb = torch.empty_like(xb)
+            pb = lib.plan_many_dft([1009], 2, xb, None, 1, 1009, yb, None, 1, 1009, -1)
+            lib.execute(pb)
+            torch.cuda.synchronize(1)
+            refb = np.stack([np.fft.fft(r.astype(np.complex128)) for r in xb.cpu().numpy()])
+            assert cases.rel_l2(yb.cpu().numpy(), refb) < cases.tol(lib, 1009)
+            for p in (p1, pb):
+                lib.destroy_plan(p)
+        lib.destroy_plan(p0)
+    finally:
+        L.b2fft_set_device(0)
+        torch.cuda.set_device(0)
