@@ -140,7 +140,8 @@ static bool group_pair_ok(const b2fft_plan *p, const StepPlan &s, const StepPlan
 }
 
 static int run_steps(b2fft_plan *p, real_t *in, real_t *out, stream_t stream) {
-    real_t *buf[B_NBUF] = {in, out, p->scr, p->wrk};
+    const long long woff = p->pc.neg ? p->pc.out_off : 0;  // work arrays in the output layout: element 0 sits woff reals in
+    real_t *buf[B_NBUF] = {in, out, p->scr ? p->scr + woff : nullptr, p->wrk ? p->wrk + woff : nullptr};
     const bool aligned = ((uintptr_t)in % sizeof(cpx_t)) == 0 && ((uintptr_t)out % sizeof(cpx_t)) == 0;
     if (!aligned && p->needs_aligned) {
         // arrays that are not aligned to a complex element: the same problem planned without the
@@ -395,7 +396,7 @@ static void pipe_setup(b2fft_plan *p) {
     hp->state = -1;
     const PlanCore &pc = p->pc;
     const b2fft_geom &g = pc.g;
-    if (getenv("FFTW_B200_NO_PIPELINE")) return;
+    if (getenv("FFTW_B200_NO_PIPELINE") || pc.neg) return;
     // dense arrays only: a chunk of the batch must be one contiguous range on both sides
     if (pc.in_dense != pc.in_reals || pc.out_dense != pc.out_reals) return;
     int v = -1;
@@ -491,12 +492,16 @@ extern "C" int b2fft_execute(b2fft_plan *p, void *in, void *out) {
     }
     real_t *ri = (real_t *)in, *ro = (real_t *)out;
     const size_t ib = (size_t)p->pc.in_reals * sizeof(real_t), ob = (size_t)p->pc.out_reals * sizeof(real_t);
+    // (negative strides: the host spans start in_off / out_off reals BELOW the pointers; in place both are equal)
+    const long long ioff = p->pc.in_off, ooff = p->pc.out_off;
+    const real_t *hin = (const real_t *)in - ioff;
+    real_t *hout = (real_t *)out - ooff;
     if (!dout) {
         if (!p->dev_out) p->dev_out = (real_t *)dev_malloc(std::max(ob, same ? ib : (size_t)0));
         if (!p->dev_out) return -3;
-        ro = p->dev_out;
+        ro = p->dev_out + ooff;
         // keep whatever lives in the gaps of a strided / embedded output
-        if (!same && p->pc.out_dense != p->pc.out_reals) B2_CK(cudaMemcpyAsync(ro, out, ob, cudaMemcpyHostToDevice, 0));
+        if (!same && p->pc.out_dense != p->pc.out_reals) B2_CK(cudaMemcpyAsync(p->dev_out, hout, ob, cudaMemcpyHostToDevice, 0));
     }
     if (!din) {
         if (same)
@@ -504,14 +509,14 @@ extern "C" int b2fft_execute(b2fft_plan *p, void *in, void *out) {
         else {
             if (!p->dev_in) p->dev_in = (real_t *)dev_malloc(ib);
             if (!p->dev_in) return -3;
-            ri = p->dev_in;
+            ri = p->dev_in + ioff;
         }
-        B2_CK(cudaMemcpyAsync(ri, in, ib, cudaMemcpyHostToDevice, 0));
+        B2_CK(cudaMemcpyAsync(ri - ioff, hin, ib, cudaMemcpyHostToDevice, 0));
     } else if (same)
         ri = ro;
     int rc = run_steps(p, ri, ro, 0);
     if (rc) return rc;
-    if (!dout) B2_CK(cudaMemcpyAsync(out, ro, std::max(ob, same ? ib : (size_t)0), cudaMemcpyDeviceToHost, 0));
+    if (!dout) B2_CK(cudaMemcpyAsync(hout, ro - ooff, std::max(ob, same ? ib : (size_t)0), cudaMemcpyDeviceToHost, 0));
     B2_CK(cudaStreamSynchronize(0));
     return 0;
 #else

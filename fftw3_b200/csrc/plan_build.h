@@ -39,6 +39,12 @@ struct PlanCore {
     long long in_dense = 0, out_dense = 0;  // reals actually touched
     long long scr_reals = 0;
     long long wrk_reals = 0;    // second plan-owned work array (Bluestein rows)
+    // Negative strides (the reference's tensors carry signed strides, fftw/fftw_api.h:472-487): the caller's pointer is
+    // element 0, which is then not the lowest address.  in_off / out_off = distance (reals) from the lowest address
+    // touched to the pointer; in_reals / out_reals stay the extent of the whole span.  Such geometries run on the
+    // generic kernel (signed 64-bit offsets throughout); work arrays in the output layout get the same offset.
+    bool neg = false;
+    long long in_off = 0, out_off = 0;
     double flops = 0;
     std::string desc;
 };
@@ -472,13 +478,16 @@ inline bool assign_buffers(PlanCore &pc) {
     return true;
 }
 
-inline long long extent_of(const std::vector<GDim> &dims, bool in, long long unit) {
-    long long e = 1;
+// extent of the span the dims address, in units; *below = how far the span reaches below element 0 (negative strides)
+inline long long extent_of(const std::vector<GDim> &dims, bool in, long long unit, long long *below = nullptr) {
+    long long hi = 0, lo = 0;
     for (const GDim &d : dims) {
         if (d.n == 0) return 0;
-        e += (d.n - 1) * (in ? d.is : d.os);
+        const long long reach = (d.n - 1) * (in ? d.is : d.os);
+        (reach >= 0 ? hi : lo) += reach;
     }
-    return e * unit;
+    if (below) *below = -lo * unit;
+    return (hi - lo + 1) * unit;
 }
 
 inline bool build_c2c(PlanCore &pc) {
@@ -503,19 +512,21 @@ inline bool build_c2c(PlanCore &pc) {
     }
     std::vector<GDim> all = T;
     all.insert(all.end(), V.begin(), V.end());
-    pc.in_reals = extent_of(all, true, 2);
-    pc.out_reals = extent_of(all, false, 2);
+    pc.in_reals = extent_of(all, true, 2, &pc.in_off);
+    pc.out_reals = extent_of(all, false, 2, &pc.out_off);
+    pc.neg = pc.in_off > 0 || pc.out_off > 0;
     pc.in_dense = pc.out_dense = (long long)(N * H * 2);
     pc.flops = 5.0 * N * (N > 1 ? log2(N) : 0) * H;
     if (H == 0) {
         pc.empty = true;
         return true;
     }
-    for (const GDim &d : all)
-        if (d.is < 0 || d.os < 0) {
-            set_error("negative strides are not supported");
-            return false;
-        }
+    if (pc.neg && pc.in_place)
+        for (const GDim &d : all)
+            if (d.n > 1 && d.is != d.os) {  // (the location-set comparison below assumes positive strides)
+                set_error("in-place transform with negative strides needs identical input and output strides");
+                return false;
+            }
     // In place with different input and output strides (e.g. a batched transform written back transposed):
     // solvable when both stride sets address the same locations (reference: fftw_tensor_inplace_locations
     // fftw_api.c:17298, checked in fftw_mkproblem_dft :4090-4094).  The transform then runs through the
@@ -611,7 +622,13 @@ inline bool build_c2c(PlanCore &pc) {
         st.dst_allowed = {B_OUT};
         pc.steps.push_back(st);
     }
-    return assign_buffers(pc);
+    if (!assign_buffers(pc)) return false;
+    if (pc.neg)  // work arrays share the output layout: the same span, the same offset to element 0
+        for (const StepPlan &st : pc.steps) {
+            if (st.dst == B_SCR) pc.scr_reals = std::max(pc.scr_reals, pc.out_reals);
+            if (st.dst == B_WRK) pc.wrk_reals = std::max(pc.wrk_reals, pc.out_reals);
+        }
+    return true;
 }
 
 }  // namespace b2

@@ -174,19 +174,19 @@ inline bool make_pass_step(Step &st, const AxisSpec &a) {
     std::vector<LDim> L;
     for (const LDim &d : a.lines)
         if (d.n > 1) L.push_back(d);
-    const bool src_row = a.s_axis <= 2, dst_row = a.d_axis <= 2;
+    const bool src_row = a.s_axis > 0 && a.s_axis <= 2, dst_row = a.d_axis > 0 && a.d_axis <= 2;
     int tile = -1;
     if (!dst_row) {
         for (size_t i = 0; i < L.size(); ++i)
-            if (L[i].d <= 2 && (tile < 0 || L[i].d < L[tile].d)) tile = (int)i;
+            if (L[i].d > 0 && L[i].d <= 2 && (tile < 0 || L[i].d < L[tile].d)) tile = (int)i;
         if (tile >= 0) p.st_col = 1;
     }
     if (tile < 0 && !src_row) {
         for (size_t i = 0; i < L.size(); ++i)
-            if (L[i].s <= 2 && (tile < 0 || L[i].s < L[tile].s)) tile = (int)i;
+            if (L[i].s > 0 && L[i].s <= 2 && (tile < 0 || L[i].s < L[tile].s)) tile = (int)i;
         if (tile >= 0) p.ld_col = 1;
     }
-    if (tile >= 0 && p.st_col && !src_row && L[tile].s <= 2) p.ld_col = 1;
+    if (tile >= 0 && p.st_col && !src_row && L[tile].s > 0 && L[tile].s <= 2) p.ld_col = 1;
     if (tile < 0)
         for (size_t i = 0; i < L.size(); ++i)
             if (tile < 0 || L[i].d < L[tile].d) tile = (int)i;

@@ -253,8 +253,11 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
     if (p.rmode != RM_C2C && !real_half) return;
     if (real_half && (p.s_axis != 2 || p.d_axis != 2 || p.s_pair != 1 || p.d_pair != 1)) return;
     if ((p.s_axis | p.d_axis) & 1) return;
+    if (p.s_axis < 0 || p.d_axis < 0) return;  // negative strides: generic kernel (signed offsets throughout)
     for (int d = 0; d < p.nld; ++d)
-        if ((p.ls[d] | p.ld[d]) & 1) return;
+        if (((p.ls[d] | p.ld[d]) & 1) || p.ls[d] < 0 || p.ld[d] < 0) return;
+    for (const b2::LDim &o : s.outer)
+        if (o.s < 0 || o.d < 0) return;
     for (const b2::LDim &o : s.outer)
         if ((o.s | o.d) & 1) return;
     int mode;

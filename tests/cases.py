@@ -566,6 +566,58 @@ def check_split_interleaved_host(lib):
     lib.destroy_plan(p)
 
 
+def check_negative_strides(lib, device=False):
+    """guru c2c with negative strides (the reference's tensors carry signed strides, fftw_api.h:472-487; guru entry
+    fftw_api.c:1172-1517): the pointers address element 0, which is then not the lowest address of the array.
+    Reversed input, reversed output rows, a batch walked backwards on both sides, in place with equal strides."""
+    rng = np.random.default_rng(31)
+    esz = np.dtype(lib.cplx).itemsize
+    if device:
+        import torch
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        down = lambda t: t.cpu().numpy()
+        addr = lambda t, off: t.data_ptr() + off * esz
+    else:
+        up = lambda a: np.array(a, copy=True, order="C")  # (a copy: case 3 transforms in place)
+        down = lambda a: a
+        addr = lambda a, off: a.ctypes.data + off * esz
+    # 1. batched 1-D, input read backwards (is = -1), output forwards
+    n, hm = 48, 3
+    x = rand_c(rng, (hm, n), lib)
+    dx, dy = up(x), up(np.zeros((hm, n), lib.cplx))
+    p = lib.plan_guru_dft([(n, -1, 1)], [(hm, n, n)], addr(dx, n - 1), addr(dy, 0), -1)
+    assert p, "plan with a negative input stride is NULL"
+    lib.execute(p)
+    lib.destroy_plan(p)
+    ref = np.stack([orc.dft(np.ascontiguousarray(x[b][::-1]), -1) for b in range(hm)])
+    assert rel_l2(down(dy), ref) < tol(lib, n)
+    # 2. 2-D 6 x 20, output rows stored in reverse order (os0 < 0), batch of 4 walked backwards on both sides
+    n0, n1, hm = 6, 20, 4
+    x = rand_c(rng, (hm, n0, n1), lib)
+    dx, dy = up(x), up(np.full((hm, n0, n1), 3, lib.cplx))
+    p = lib.plan_guru_dft([(n0, n1, -n1), (n1, 1, 1)], [(hm, -n0 * n1, -n0 * n1)],
+                          addr(dx, (hm - 1) * n0 * n1), addr(dy, (hm - 1) * n0 * n1 + (n0 - 1) * n1), -1)
+    assert p, "plan with negative output / batch strides is NULL"
+    lib.execute(p)
+    lib.destroy_plan(p)
+    got = down(dy)
+    for b in range(hm):  # batch element k sits at block hm-1-k on both sides; its output row r at row n0-1-r
+        ref = orc.dft(np.ascontiguousarray(x[hm - 1 - b]), -1)
+        assert rel_l2(got[hm - 1 - b][::-1], ref) < tol(lib, n0 * n1), b
+    # 3. in place, the same negative stride on both sides (4096 points: two passes with a work array on the GPU)
+    n = 4096 * 4
+    x = rand_c(rng, (n,), lib)
+    dz = up(x)
+    p = lib.plan_guru_dft([(n, -1, -1)], [], addr(dz, n - 1), addr(dz, n - 1), +1)
+    assert p, "in-place plan with negative strides is NULL"
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(down(dz)[::-1], orc.dft(np.ascontiguousarray(x[::-1]), +1)) < tol(lib, n)
+    # in place with DIFFERENT signs cannot address the same locations: NULL, as in the reference
+    dz = up(x)
+    assert not lib.plan_guru_dft([(n, -1, 1)], [], addr(dz, n - 1), addr(dz, n - 1), -1)
+
+
 R2R_SIZES = [2, 3, 4, 5, 8, 9, 16, 30, 64, 100, 255, 1024]
 
 

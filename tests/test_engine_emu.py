@@ -116,6 +116,10 @@ def test_r2r_kinds(lib, r2r_golden):
     cases.check_r2r(lib, r2r_golden)
 
 
+def test_negative_strides(lib):
+    cases.check_negative_strides(lib)
+
+
 def test_threads_share_a_plan_and_the_planner(lib):
     cases.check_threads(lib)
 

@@ -87,6 +87,11 @@ def test_split_array_guru_interfaces(lib):
     cases.check_split_interleaved_host(lib)
 
 
+def test_negative_strides(lib):
+    cases.check_negative_strides(lib)
+    cases.check_negative_strides(lib, device=True)
+
+
 def test_r2r_kinds(lib, r2r_golden):
     cases.check_r2r(lib, r2r_golden)
     cases.check_r2r(lib, r2r_golden, device=True)
