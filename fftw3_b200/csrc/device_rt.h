@@ -31,6 +31,20 @@ inline void set_error(const char *fmt, ...) {
     if (getenv("FFTW_B200_VERBOSE")) fprintf(stderr, "[b200fft] %s\n", buf);
 }
 
+// Experiment switches that FFTW_MEASURE is allowed to toggle per candidate plan: opt(name) answers like getenv(name)
+// unless the calling thread is building a candidate with that switch forced on or off (b2fft_plan_create_tuned).
+enum { B2_CFG_NO_TMA = 1, B2_CFG_NO_PIPE = 2, B2_CFG_NO_PREFER3 = 4, B2_CFG_THREE_PASS_REAL = 8, B2_CFG_NO_TWO_PASS_REAL = 16,
+       B2_CFG_TWO_PASS_C2R = 32, B2_CFG_ALL = 63 };
+inline int &cfg_override() {
+    static thread_local int v = -1;  // -1: the environment decides; >= 0: bit mask of switches that are ON (all others OFF)
+    return v;
+}
+inline const char *opt(const char *name, int bit) {
+    const int c = cfg_override();
+    if (c >= 0) return (c & bit) ? "1" : nullptr;
+    return getenv(name);
+}
+
 inline unsigned long long &launch_counter() {
     static unsigned long long n = 0;
     return n;

@@ -3,6 +3,7 @@
 // pointers.  Compiled by nvcc for the product; compiled by g++ -DB2_EMULATE (-x c++) into the
 // test-only emulation library.  There is deliberately no CPU execution path in the product
 // build: without a CUDA device b2fft_plan_create returns NULL.
+#include <chrono>
 #include <mutex>
 
 #include "b200fft.h"
@@ -348,6 +349,117 @@ extern "C" b2fft_plan *b2fft_plan_create(const b2fft_geom *g) {
     p->pc.desc = d;
     return p;
 }
+
+// ------------------------------------------------------------------------- FFTW_MEASURE
+static const char *cfg_name(int bit) {
+    switch (bit) {
+    case B2_CFG_NO_TMA: return "round-1 column kernels instead of TMA";
+    case B2_CFG_NO_PIPE: return "no async-copy pipelined column kernels";
+    case B2_CFG_NO_PREFER3: return "two passes instead of three for a long axis";
+    case B2_CFG_THREE_PASS_REAL: return "three-pass real transform";
+    case B2_CFG_NO_TWO_PASS_REAL: return "no two-pass real transform";
+    case B2_CFG_TWO_PASS_C2R: return "two-pass c2r";
+    }
+    return "?";
+}
+static b2fft_plan *create_with_cfg(const b2fft_geom *g, int cfg) {
+    const int saved = cfg_override();
+    cfg_override() = cfg;
+    b2fft_plan *p = b2fft_plan_create(g);
+    cfg_override() = saved;
+    if (p) p->cfg = cfg;
+    return p;
+}
+// average time of one execute on device arrays, in ms; < 0: could not be measured
+static double time_plan(b2fft_plan *p, real_t *in, real_t *out) {
+    real_t *ri = in + p->pc.in_off, *ro = (p->pc.in_place ? in : out) + p->pc.out_off;
+    const int reps = 3;
+#if B2_CUDA
+    cudaEvent_t e0, e1;
+    if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) return -1;
+    float ms = -1;
+    if (run_steps(p, ri, ro, 0) == 0 && cudaEventRecord(e0, 0) == cudaSuccess) {
+        bool ok = true;
+        for (int i = 0; i < reps && ok; ++i) ok = run_steps(p, ri, ro, 0) == 0;
+        ok = ok && cudaEventRecord(e1, 0) == cudaSuccess && cudaEventSynchronize(e1) == cudaSuccess &&
+             cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess;
+        if (!ok) ms = -1;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaGetLastError();
+    return ms < 0 ? -1 : ms / reps;
+#else
+    if (run_steps(p, ri, ro, nullptr) != 0) return -1;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < reps; ++i)
+        if (run_steps(p, ri, ro, nullptr) != 0) return -1;
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() / reps;
+#endif
+}
+
+extern "C" b2fft_plan *b2fft_plan_create_tuned(const b2fft_geom *g, int cfg) {
+    if (!g) return nullptr;
+    if (cfg == B2FFT_CFG_DEFAULT) return b2fft_plan_create(g);
+    DeviceScope caller;
+    if (cfg >= 0) return create_with_cfg(g, cfg & B2_CFG_ALL);  // replay (wisdom): that configuration, unmeasured
+    // ---- measure: the default plus every single switch that changes the plan for this geometry
+    b2fft_plan *best = create_with_cfg(g, 0);
+    if (!best || best->pc.empty) return best;
+    std::vector<b2fft_plan *> cand{best};
+    for (int bit = 1; bit <= B2_CFG_ALL; bit <<= 1) {
+        b2fft_plan *q = create_with_cfg(g, bit);
+        if (q && q->pc.desc != best->pc.desc)
+            cand.push_back(q);
+        else
+            b2fft_plan_destroy(q);
+    }
+    std::string note = "  measured (FFTW_MEASURE):";
+    if (cand.size() > 1) {
+        // zero-filled plan-owned arrays: the cost of an FFT does not depend on the data (the reference's own speed
+        // test transforms zeros, libbench2/speed.c:42-53) and the caller's arrays stay untouched
+        const size_t ib = (size_t)best->pc.in_reals * sizeof(real_t), ob = (size_t)best->pc.out_reals * sizeof(real_t);
+        real_t *din = (real_t *)dev_malloc(std::max(ib, (size_t)16)), *dout = best->pc.in_place ? din : (real_t *)dev_malloc(std::max(ob, (size_t)16));
+        bool ok = din && dout;
+#if B2_CUDA
+        ok = ok && cudaMemset(din, 0, ib) == cudaSuccess && (dout == din || cudaMemset(dout, 0, ob) == cudaSuccess);
+#else
+        if (ok) {
+            memset(din, 0, ib);
+            if (dout != din) memset(dout, 0, ob);
+        }
+#endif
+        double tbest = 1e300;
+        size_t ibest = 0;
+        for (size_t i = 0; ok && i < cand.size(); ++i) {
+            const double t = time_plan(cand[i], din, dout);
+            char buf[160];
+            snprintf(buf, sizeof buf, " [%s: %.4f ms]", cand[i]->cfg ? cfg_name(cand[i]->cfg) : "default", t);
+            note += buf;
+            if (t >= 0 && t < tbest) {
+                tbest = t;
+                ibest = i;
+            }
+        }
+        if (dout != din) dev_free(dout);
+        dev_free(din);
+        if (!ok) {
+            set_error("");
+            note += " work arrays for the measurement could not be allocated: default configuration";
+        }
+        for (size_t i = 0; i < cand.size(); ++i)
+            if (i != ibest) b2fft_plan_destroy(cand[i]);
+        best = cand[ibest];
+        best->measured = ok;
+    } else {
+        note += " no alternative configuration for this geometry";
+        best->measured = true;
+    }
+    best->pc.desc += note + "\n";
+    return best;
+}
+extern "C" int b2fft_plan_config(const b2fft_plan *p) { return p ? p->cfg : 0; }
+extern "C" int b2fft_plan_measured(const b2fft_plan *p) { return p && p->measured ? 1 : 0; }
 
 extern "C" void b2fft_plan_destroy(b2fft_plan *p) {
     if (!p) return;

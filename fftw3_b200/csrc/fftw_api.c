@@ -37,13 +37,15 @@ static pthread_mutex_t planner_lock = PTHREAD_MUTEX_INITIALIZER;
 #define PLANNER_LOCK() pthread_mutex_lock(&planner_lock)
 #define PLANNER_UNLOCK() pthread_mutex_unlock(&planner_lock)
 
-/* ---- wisdom: the set of problems planned (or imported) so far.  The selector is deterministic, so a
- * wisdom entry carries no plan, only the problem's signature; what it preserves of the reference's
- * contract is FFTW_WISDOM_ONLY (NULL unless the problem is in the accumulated wisdom,
- * fftw_api.c:332-337) and a round-trippable export / import / forget (fftw_api.c:895-1168). */
-#define WIS_MAX 4096
-static uint64_t wis_key[WIS_MAX];
-static int wis_n = 0;
+/* ---- wisdom: the set of problems planned (or imported) so far: the problem's signature and, once a plan for
+ * it was made with FFTW_MEASURE or more, the configuration that won the timing (b2fft_plan_create_tuned), which
+ * later plans for the same problem replay without measuring again -- the reference's "wisdom = remembered winner"
+ * (fftw_api.c:332-337, 15300-15426).  FFTW_WISDOM_ONLY gives NULL unless the problem is in the accumulated wisdom;
+ * export / import / forget round-trip (fftw_api.c:895-1168).  All accesses under the planner lock. */
+#define WIS_UNMEASURED 0xffffffffu
+static uint64_t *wis_key = 0;
+static unsigned *wis_cfg = 0;
+static int wis_n = 0, wis_cap = 0;
 static uint64_t wis_hash(const b2fft_geom *g) {
     uint64_t h = 1469598103934665603ull;
     int i;
@@ -67,14 +69,33 @@ static uint64_t wis_hash(const b2fft_geom *g) {
 #undef WIS_MIX
     return h;
 }
-static int wis_has(uint64_t k) {
+static int wis_find(uint64_t k) {
     int i;
     for (i = 0; i < wis_n; ++i)
-        if (wis_key[i] == k) return 1;
-    return 0;
+        if (wis_key[i] == k) return i;
+    return -1;
 }
-static void wis_add(uint64_t k) {
-    if (!wis_has(k) && wis_n < WIS_MAX) wis_key[wis_n++] = k;
+static int wis_has(uint64_t k) { return wis_find(k) >= 0; }
+/* cfg: the measured configuration, or WIS_UNMEASURED (which never replaces a measured one) */
+static void wis_add(uint64_t k, unsigned cfg) {
+    int i = wis_find(k);
+    if (i < 0) {
+        if (wis_n == wis_cap) {
+            int cap = wis_cap ? 2 * wis_cap : 256;
+            uint64_t *nk = (uint64_t *)realloc(wis_key, (size_t)cap * sizeof *nk);
+            unsigned *nc;
+            if (!nk) return;
+            wis_key = nk;
+            nc = (unsigned *)realloc(wis_cfg, (size_t)cap * sizeof *nc);
+            if (!nc) return;
+            wis_cfg = nc;
+            wis_cap = cap;
+        }
+        i = wis_n++;
+        wis_key[i] = k;
+        wis_cfg[i] = WIS_UNMEASURED;
+    }
+    if (cfg != WIS_UNMEASURED) wis_cfg[i] = cfg;
 }
 
 static fftw_plan finish_locked(b2fft_geom *g, void *in, void *out, unsigned flags);
@@ -88,13 +109,20 @@ static fftw_plan finish(b2fft_geom *g, void *in, void *out, unsigned flags) {
 static fftw_plan finish_locked(b2fft_geom *g, void *in, void *out, unsigned flags) {
     fftw_plan p;
     b2fft_plan *bp;
+    int wi;
     g->in_place = (in == out);
     /* the reference answers WISDOM_ONLY with NULL when it has no wisdom for the problem
      * (fftw_api.c:332-337) */
-    if ((flags & FFTW_WISDOM_ONLY) && !wis_has(wis_hash(g))) return 0;
+    wi = wis_find(wis_hash(g));
+    if ((flags & FFTW_WISDOM_ONLY) && wi < 0) return 0;
     g->flags = flags;
     g->in_place = (in == out);
-    bp = b2fft_plan_create(g);
+    if (wi >= 0 && wis_cfg[wi] != WIS_UNMEASURED)
+        bp = b2fft_plan_create_tuned(g, (int)wis_cfg[wi]);           /* replay the winner remembered in wisdom */
+    else if (!(flags & (FFTW_ESTIMATE | FFTW_WISDOM_ONLY)))
+        bp = b2fft_plan_create_tuned(g, B2FFT_CFG_MEASURE);          /* FFTW_MEASURE (0), PATIENT, EXHAUSTIVE: time the candidates */
+    else
+        bp = b2fft_plan_create(g);
     if (!bp) return 0;
     p = (fftw_plan)malloc(sizeof *p);
     if (!p) {
@@ -107,7 +135,7 @@ static fftw_plan finish_locked(b2fft_geom *g, void *in, void *out, unsigned flag
     p->out = out;
     p->kind = g->kind;
     p->g = *g;
-    wis_add(wis_hash(g));
+    wis_add(wis_hash(g), b2fft_plan_measured(bp) ? (unsigned)b2fft_plan_config(bp) : WIS_UNMEASURED);
     return p;
 }
 
@@ -557,13 +585,21 @@ void fftw_make_planner_thread_safe(void) {}
 /* wisdom I/O: "(b200fft_wisdom-1 <hex signature> ...)" */
 static const char wis_head[] = "(b200fft_wisdom-1";
 char *fftw_export_wisdom_to_string(void) {
-    size_t cap = sizeof wis_head + (size_t)wis_n * 18 + 32, len;
-    char *s = (char *)malloc(cap);
+    size_t cap, len;
+    char *s;
     int i;
-    if (!s) return 0;
-    PLANNER_LOCK();
+    PLANNER_LOCK(); /* (before wis_n is read: a concurrent planner must not truncate the export) */
+    cap = sizeof wis_head + (size_t)wis_n * 28 + 32;
+    s = (char *)malloc(cap);
+    if (!s) {
+        PLANNER_UNLOCK();
+        return 0;
+    }
     len = (size_t)sprintf(s, "%s", wis_head);
-    for (i = 0; i < wis_n && len + 24 < cap; ++i) len += (size_t)sprintf(s + len, " %016llx", (unsigned long long)wis_key[i]);
+    for (i = 0; i < wis_n && len + 32 < cap; ++i) {
+        len += (size_t)sprintf(s + len, " %016llx", (unsigned long long)wis_key[i]);
+        if (wis_cfg[i] != WIS_UNMEASURED) len += (size_t)sprintf(s + len, ":%x", wis_cfg[i]); /* the measured winner */
+    }
     PLANNER_UNLOCK();
     sprintf(s + len, ")\n");
     return s;
@@ -596,24 +632,50 @@ int fftw_import_wisdom_from_string(const char *s) {
     for (;;) {
         char *end;
         unsigned long long k;
+        unsigned cfg = WIS_UNMEASURED;
         while (*c == ' ' || *c == '\n' || *c == '\t') ++c;
         if (*c == ')') return 1;
         if (!*c) return 0;
         k = strtoull(c, &end, 16);
         if (end == c) return 0;
+        if (*end == ':') {
+            char *e2;
+            cfg = (unsigned)strtoul(end + 1, &e2, 16);
+            if (e2 == end + 1) return 0;
+            end = e2;
+        }
         PLANNER_LOCK();
-        wis_add((uint64_t)k);
+        wis_add((uint64_t)k, cfg);
         PLANNER_UNLOCK();
         c = end;
     }
 }
-int fftw_import_wisdom_from_file(FILE *f) {
-    char buf[WIS_MAX * 18 + 64];
-    size_t n;
-    if (!f) return 0;
-    n = fread(buf, 1, sizeof buf - 1, f);
+/* reads characters until get() says EOF into a growing buffer and imports them */
+static int import_stream(int (*get)(void *), void *data) {
+    size_t cap = 4096, n = 0;
+    char *buf = (char *)malloc(cap), *nb;
+    int c, ok;
+    if (!buf) return 0;
+    while ((c = get(data)) != EOF) {
+        if (n + 2 > cap) {
+            nb = (char *)realloc(buf, cap *= 2);
+            if (!nb) {
+                free(buf);
+                return 0;
+            }
+            buf = nb;
+        }
+        buf[n++] = (char)c;
+    }
     buf[n] = 0;
-    return fftw_import_wisdom_from_string(buf);
+    ok = fftw_import_wisdom_from_string(buf);
+    free(buf);
+    return ok;
+}
+static int get_from_file(void *f) { return fgetc((FILE *)f); }
+int fftw_import_wisdom_from_file(FILE *f) {
+    if (!f) return 0;
+    return import_stream(get_from_file, f);
 }
 int fftw_import_wisdom_from_filename(const char *filename) {
     FILE *f = fopen(filename, "r");
@@ -624,13 +686,8 @@ int fftw_import_wisdom_from_filename(const char *filename) {
     return ok;
 }
 int fftw_import_wisdom(fftw_read_char_func read_char, void *data) {
-    char buf[WIS_MAX * 18 + 64];
-    size_t n = 0;
-    int c;
     if (!read_char) return 0;
-    while (n + 1 < sizeof buf && (c = read_char(data)) != EOF) buf[n++] = (char)c;
-    buf[n] = 0;
-    return fftw_import_wisdom_from_string(buf);
+    return import_stream(read_char, data);
 }
 
 /* plan printing: the selected kernel configurations (reference prints its solver tree,

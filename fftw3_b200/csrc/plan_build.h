@@ -307,7 +307,7 @@ inline bool add_c2c_axis(PlanCore &pc, long long n, long long s_axis, long long 
     }
     long long n1, n2;
     bool two_pass = split_four_step(n, &n1, &n2);
-    if (two_pass && !getenv("FFTW_B200_NO_PREFER3")) {
+    if (two_pass && !opt("FFTW_B200_NO_PREFER3", B2_CFG_NO_PREFER3)) {
         // Measured on B200 (profiles/r1_long1d_probe.md): three passes through the 128..256-point kernels
         // (4 CTAs per SM, ~0.35 ms per GiB pass) beat two passes through the 2048-point (fp32) or
         // 1024-point (fp64) kernels, which run one CTA per SM: fp32 2^22 1.31 ms in two passes against

@@ -377,8 +377,8 @@ inline bool build_real(PlanCore &pc) {
         // 256-point kernels' bandwidth.  So: default only where no two-pass split exists (n > 2^22 fp32 /
         // 2^20 fp64, where it replaces four passes), FFTW_B200_THREE_PASS_REAL=1 forces it from 2^19 on.
         long long u1 = 0, u2 = 0;
-        const bool want3 = getenv("FFTW_B200_THREE_PASS_REAL") ? nl >= (1ll << 19) : !split_two_pass_real(nl, &u1, &u2);
-        if (r2c && !no_two_pass_real() && !getenv("FFTW_B200_NO_TWO_PASS_REAL") && !getenv("FFTW_B200_NO_THREE_PASS_REAL") &&
+        const bool want3 = opt("FFTW_B200_THREE_PASS_REAL", B2_CFG_THREE_PASS_REAL) ? nl >= (1ll << 19) : !split_two_pass_real(nl, &u1, &u2);
+        if (r2c && !no_two_pass_real() && !opt("FFTW_B200_NO_TWO_PASS_REAL", B2_CFG_NO_TWO_PASS_REAL) && !getenv("FFTW_B200_NO_THREE_PASS_REAL") &&
             want3 && nl < (1ll << 31) && (nl & (nl - 1)) == 0 && T[L].is == 1 && T[L].os == 1 && evens_src && evens_dst &&
             split_three_pass_real(nl, &t1, &t2, &t3)) {
             const long long rows = t1 / 2 + 1, Q = t2 * t3;
@@ -445,7 +445,7 @@ inline bool build_real(PlanCore &pc) {
             if (!leading_axes(false)) return false;
             return assign_buffers(pc);
         }
-        if (r2c && !no_two_pass_real() && !getenv("FFTW_B200_NO_TWO_PASS_REAL") && (nl & (nl - 1)) == 0 &&
+        if (r2c && !no_two_pass_real() && !opt("FFTW_B200_NO_TWO_PASS_REAL", B2_CFG_NO_TWO_PASS_REAL) && (nl & (nl - 1)) == 0 &&
             T[L].is == 1 && T[L].os == 1 && evens_src && evens_dst && split_two_pass_real(nl, &q1, &q2)) {
             // ---- two passes: real column pairs (FFT + split + twiddle), then rows with a Hermitian fold
             const long long rows = q1 / 2 + 1;
@@ -493,7 +493,7 @@ inline bool build_real(PlanCore &pc) {
         // (c2r: opt-in.  Measured on B200, 2^20 x 256: 1.56 ms against 1.33 ms for merge + two passes --
         // the unfold + twiddle column pass runs 1744 instructions per thread at one 1024-thread CTA
         // per SM; 2^16 x 4096: 1.01 against 1.07 ms.)
-        if (!r2c && getenv("FFTW_B200_TWO_PASS_C2R") && !no_two_pass_real() && (nl & (nl - 1)) == 0 &&
+        if (!r2c && opt("FFTW_B200_TWO_PASS_C2R", B2_CFG_TWO_PASS_C2R) && !no_two_pass_real() && (nl & (nl - 1)) == 0 &&
             T[L].is == 1 && T[L].os == 1 && evens_src && evens_dst && split_two_pass_real(nl, &q1, &q2, false)) {
             // ---- two passes, the mirror image of the r2c pair: columns k1 <= q1/2 of the Hermitian-
             // unfolded spectrum (backward FFT over k2 + twiddle), then per pair of output columns a

@@ -31,6 +31,8 @@ struct b2fft_plan_s {
     real_t *dev_in = nullptr, *dev_out = nullptr;
     b2::stream_t stream = nullptr;
     bool own_stream = false;
+    int cfg = 0;            // configuration bit mask the plan was built with (B2_CFG_*), 0 = the selector's default
+    bool measured = false;  // chosen by timing (FFTW_MEASURE)
     int device = -1;  // the device the plan (its tables, work arrays, streams) lives on; executes make it current
     // host / device classification of the arrays of the last synchronous execute (fftw_execute passes the same
     // two pointers every time: one cudaPointerGetAttributes pair per plan, not per call)

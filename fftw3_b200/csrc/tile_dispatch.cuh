@@ -280,7 +280,7 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
     if (p.fold_n > 0 && p.swap_in && (p.ls[0] != 2 || p.fold_n >= (1ll << 30))) return;  // unfold load: unit stride, 32-bit indices
     const std::vector<TileEntry> &tab = b2_tile_table();
     // pipelined column kernels: 16-byte async copies -> every stride a multiple of 16 bytes
-    bool pipe_ok = !getenv("FFTW_B200_NO_PIPE");
+    bool pipe_ok = !b2::opt("FFTW_B200_NO_PIPE", b2::B2_CFG_NO_PIPE);
     if (sizeof(real_t) == 4) {
         if (p.s_axis & 3) pipe_ok = false;
         for (int d = 1; d < p.nld; ++d)
@@ -299,7 +299,7 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
     // direction as one flag (plan_build.h gives every pass of a backward axis swap_in == swap_out).  The
     // store scattered to REMOTE owners (fused slab exchange) stays on the older kernels unless FFTW_B200_TMA_SCATTER
     // is set: a warp of this kernel stores 64-byte row segments, which is what made remote NVLink writes slow in round 1.
-    bool tma_ok = !getenv("FFTW_B200_NO_TMA") && sizeof(real_t) == 4 && p.fold_n == 0 && p.swap_in == p.swap_out &&
+    bool tma_ok = !b2::opt("FFTW_B200_NO_TMA", b2::B2_CFG_NO_TMA) && sizeof(real_t) == 4 && p.fold_n == 0 && p.swap_in == p.swap_out &&
                   p.nld <= 4 && s.outer.empty();
     if (epi == 8 && p.scat_self1 == 0 && !p.scat_local && !getenv("FFTW_B200_TMA_SCATTER")) tma_ok = false;  // (local stores are fine)
     if (p.s_axis & 3) tma_ok = false;

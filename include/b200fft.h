@@ -54,6 +54,18 @@ typedef struct b2fft_plan_s b2fft_plan;
 b2fft_plan *b2fft_plan_create(const b2fft_geom *g);
 void        b2fft_plan_destroy(b2fft_plan *p);
 
+/* FFTW_MEASURE / PATIENT / EXHAUSTIVE (reference: patience loop fftw/fftw_api.c:351-376, cost by time :15106-15153).
+ * cfg = B2FFT_CFG_MEASURE: build the default plan and every alternative configuration the selector knows for this
+ * geometry (TMA or round-1 column kernels, pipelined or not, two or three passes of a long axis, the real-transform
+ * variants), time each on plan-owned zero-filled device arrays and keep the fastest; cfg >= 0: that configuration,
+ * unmeasured (what wisdom replays); cfg = B2FFT_CFG_DEFAULT: b2fft_plan_create.  b2fft_plan_config = the
+ * configuration of a plan (a bit mask; 0 = the selector's default), b2fft_plan_measured = 1 when it was timed. */
+#define B2FFT_CFG_DEFAULT (-1)
+#define B2FFT_CFG_MEASURE (-2)
+b2fft_plan *b2fft_plan_create_tuned(const b2fft_geom *g, int cfg);
+int         b2fft_plan_config(const b2fft_plan *p);
+int         b2fft_plan_measured(const b2fft_plan *p);
+
 /* Synchronous execute.  in/out may each be a host pointer (copied over PCIe inside the call)
  * or a device/managed pointer (transformed in HBM).  Returns 0, or a CUDA error code. */
 int b2fft_execute(b2fft_plan *p, void *in, void *out);

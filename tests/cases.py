@@ -618,6 +618,65 @@ def check_negative_strides(lib, device=False):
     assert not lib.plan_guru_dft([(n, -1, 1)], [], addr(dz, n - 1), addr(dz, n - 1), -1)
 
 
+def check_measure_and_wisdom(lib, device=False):
+    """FFTW_MEASURE (flags = 0) times the candidate configurations of the selector and keeps the fastest (reference:
+    patience loop fftw_api.c:351-376, cost by time :15106-15153); the winner goes into wisdom, is exported with the
+    problem's signature and is replayed, unmeasured, by later plans for the same problem (also FFTW_WISDOM_ONLY
+    after forget + import).  A 3-D transform whose middle axis has 1024 points has at least one alternative."""
+    import ctypes as C
+    L = lib.lib
+    L.fftw_export_wisdom_to_string.restype = C.c_void_p
+    L.fftw_import_wisdom_from_string.argtypes = [C.c_char_p]
+    L.fftw_forget_wisdom()
+    rng = np.random.default_rng(41)
+    shape = (3, 1024, 32)
+    x = rand_c(rng, shape, lib)
+    if device:
+        import torch
+        dx = torch.from_numpy(x).cuda()
+        dy = torch.empty_like(dx)
+        get = lambda: dy.cpu().numpy()
+    else:
+        dx, dy = x.copy(), np.zeros(shape, lib.cplx)
+        get = lambda: dy
+    ref = orc.dft(x, -1)
+    p = lib.plan_dft(list(shape), dx, dy, -1, capi.FFTW_MEASURE)
+    assert p, "FFTW_MEASURE plan is NULL"
+    d1 = lib.sprint_plan(p)
+    assert "measured (FFTW_MEASURE):" in d1 and "default:" in d1 and " ms]" in d1, d1
+    if device:
+        dx.copy_(torch.from_numpy(x))  # (planning with MEASURE may overwrite the arrays in the reference; here it does not)
+    lib.execute(p)
+    assert rel_l2(get(), ref) < tol(lib, int(np.prod(shape)))
+    lib.destroy_plan(p)
+    sp = L.fftw_export_wisdom_to_string()
+    text = C.string_at(sp)
+    lib.free_string(sp) if hasattr(lib, "free_string") else None
+    assert b":" in text, text  # "<signature>:<configuration>" for the measured problem
+    # the same problem again, FFTW_ESTIMATE: the remembered winner is replayed, nothing is timed
+    p = lib.plan_dft(list(shape), dx, dy, -1, capi.FFTW_ESTIMATE)
+    d2 = lib.sprint_plan(p)
+    assert "measured" not in d2
+    assert [l for l in d2.split("\n") if "pass " in l] == [l for l in d1.split("\n") if "pass " in l]
+    lib.destroy_plan(p)
+    # forget, import, WISDOM_ONLY
+    L.fftw_forget_wisdom()
+    assert not lib.plan_dft(list(shape), dx, dy, -1, capi.FFTW_ESTIMATE | capi.FFTW_WISDOM_ONLY)
+    assert L.fftw_import_wisdom_from_string(text) == 1
+    p = lib.plan_dft(list(shape), dx, dy, -1, capi.FFTW_ESTIMATE | capi.FFTW_WISDOM_ONLY)
+    assert p, "imported wisdom must answer FFTW_WISDOM_ONLY"
+    assert [l for l in lib.sprint_plan(p).split("\n") if "pass " in l] == [l for l in d1.split("\n") if "pass " in l]
+    lib.execute(p)
+    assert rel_l2(get(), ref) < tol(lib, int(np.prod(shape)))
+    lib.destroy_plan(p)
+    # a geometry without alternatives still plans under FFTW_MEASURE
+    y = np.zeros(64, lib.cplx)
+    p = lib.plan_dft([64], y.copy(), y, -1, capi.FFTW_MEASURE)
+    assert p and "no alternative configuration" in lib.sprint_plan(p)
+    lib.destroy_plan(p)
+    L.fftw_forget_wisdom()
+
+
 R2R_SIZES = [2, 3, 4, 5, 8, 9, 16, 30, 64, 100, 255, 1024]
 
 

@@ -120,6 +120,10 @@ def test_negative_strides(lib):
     cases.check_negative_strides(lib)
 
 
+def test_measure_and_wisdom(lib):
+    cases.check_measure_and_wisdom(lib)
+
+
 def test_threads_share_a_plan_and_the_planner(lib):
     cases.check_threads(lib)
 

@@ -87,6 +87,11 @@ def test_split_array_guru_interfaces(lib):
     cases.check_split_interleaved_host(lib)
 
 
+def test_measure_and_wisdom(lib):
+    cases.check_measure_and_wisdom(lib)
+    cases.check_measure_and_wisdom(lib, device=True)
+
+
 def test_negative_strides(lib):
     cases.check_negative_strides(lib)
     cases.check_negative_strides(lib, device=True)
