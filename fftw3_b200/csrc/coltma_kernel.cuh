@@ -116,7 +116,8 @@ template <int N> struct ColTmaShape {
 };
 
 // ---- PART 2: the kernel body ----
-// EPI: 0 plain, 1 four-step twiddle on the way out, 8 rows scattered to their owners (slab exchange)
+// EPI: 0 plain, 1 four-step twiddle on the way out, 2 split of a pair of real columns + twiddle (first pass of the
+//      two-pass r2c), 8 rows scattered to their owners (slab exchange)
 // BWD: backward transform = swap re/im on the way in and out (compile time: the swap is pure register renaming)
 template <int N, int EPI, int BWD> struct ColTma {
     typedef ColTmaShape<N> H;
@@ -280,7 +281,27 @@ template <int N, int EPI, int BWD> struct ColTma {
                 g, false, [&] { store_pass<1>(Xl, t, v); }, [&] { load_next<2>(Xl, t, v); });
             // ---- last pass: pair ownership, v[2k+e] = output 2t + e + k*2T ----
             twiddle_butterflies<2>(TW, t, v);
-            if (c < m.nlines) store_tile(p, m, cdst, ds, lds0, c, t, v);
+            if (EPI == 2) {
+                // real-pair split: X_a, X_b of output k1 need Z[k1] AND Z[N-k1], which another thread of the line holds:
+                // one more exchange through X (natural order), then every thread pairs its own k1 < N/2 with the mirror
+                cpx_t zb[E / 2];
+                exchange(
+                    g, false,
+                    [&] {
+                        Pair *o = reinterpret_cast<Pair *>(Xl + 2 * t);
+#pragma unroll
+                        for (int k = 0; k < E / 2; ++k) o[k * T] = Pair{v[2 * k], v[2 * k + 1]};
+                    },
+                    [&] {
+#pragma unroll
+                        for (int q = 0; q < E / 2; ++q) {
+                            const int k1 = 2 * t + (q & 1) + (q >> 1) * 2 * T;  // q = 2k + e, k < E/4: k1 < N/2
+                            zb[q] = Xl[(N - k1) & (N - 1)];
+                        }
+                    });
+                if (c < m.nlines) rsplit_store(p, m, cdst, ds, c, t, v, zb);
+            } else if (c < m.nlines)
+                store_tile(p, m, cdst, ds, lds0, c, t, v);
         }
         if (g == 0 && !first_use) b2tma::bar_sync<4, THREADS>();  // pairs group B's last arrive
     }
@@ -362,6 +383,46 @@ template <int N, int EPI, int BWD> struct ColTma {
             cpx_t *o = Xl + (t - jm) * R + jm;
 #pragma unroll
             for (int k = 0; k < R; ++k) o[k * NS] = v[k];
+        }
+    }
+
+    // EPI 2, first pass of the two-pass real transform (same arithmetic as TileFFT::rsplit_exit, tile_kernel.cuh).  The line
+    // is the complex FFT Z of a pair of real columns x_a + i x_b; per k1 <= N/2
+    //   X_a = (Z[k1] + conj Z[N-k1]) / 2,   X_b = -i (Z[k1] - conj Z[N-k1]) / 2,
+    // times the four-step twiddles w_n^(k1*j2), w_n^(k1*(j2+1)) of their columns j2 = 2*line, j2 + 1, stored as one 16-byte
+    // vector at row k1 of the [N/2+1][n2] intermediate.  v[2k+e] = Z[k1], zb[2k+e] = Z[N-k1] for k1 = 2t + e + k*2T, k < E/4;
+    // thread t = 0 also stores row N/2 (it holds Z[N/2] = v[E/2]).  Reference: the hc2c step of rdft2-ct
+    // (ct_hc2c_direct_apply fftw/fftw_api.c:5831-5845) applied to column pairs.
+    static __device__ __forceinline__ void rsplit_store(const PassParams &p, const ColTmaMeta &m, cpx_t *cdst, long long ds, int c,
+                                                        int t, const cpx_t *v, const cpx_t *zb) {
+        const unsigned long long j2 = 2ull * (unsigned long long)(m.l0 + c);  // even column of the pair
+        Pair *row0 = reinterpret_cast<Pair *>(cdst + m.dbase / 2) + (m.l0 + c);  // (two complex per line in the intermediate)
+        const long long dsp = ds / 2;                                            // row pitch in Pairs
+        // wa(k1) = w^(j2*k1) = A_e * S^k,  w1(k1) = w^k1 = B_e * U^k   with k1 = 2t + e + k*2T
+        const cpx_t S = epi_root(p, j2 * (unsigned long long)(2 * T)), U = epi_root(p, (unsigned long long)(2 * T));
+        cpx_t Sk[E / 4], Uk[E / 4];
+        Sk[0] = Uk[0] = cpx_t{1, 0};
+        b2_twiddle_powers<E / 4>(S, Sk);
+        b2_twiddle_powers<E / 4>(U, Uk);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const cpx_t A = epi_root(p, j2 * (unsigned long long)(2 * t + e)), B = epi_root(p, (unsigned long long)(2 * t + e));
+#pragma unroll
+            for (int k = 0; k < E / 4; ++k) {
+                const int k1 = 2 * t + e + k * 2 * T;
+                const cpx_t za = v[2 * k + e], zc = cconj(zb[2 * k + e]);
+                const cpx_t xa = cscale(cadd(za, zc), (real_t)0.5);
+                const cpx_t xb = cmul_mi(cscale(csub(za, zc), (real_t)0.5));
+                const cpx_t wa = k ? cmul(A, Sk[k]) : A;
+                const cpx_t w1 = k ? cmul(B, Uk[k]) : B;
+                row0[(long long)k1 * dsp] = Pair{cmul(xa, wa), cmul(xb, cmul(wa, w1))};
+            }
+        }
+        if (t == 0) {  // k1 = N/2 pairs with itself
+            const int k1 = N / 2;
+            const cpx_t za = v[E / 2];
+            const cpx_t wa = epi_root(p, j2 * (unsigned long long)k1);
+            row0[(long long)k1 * dsp] = Pair{cmul(cpx_t{za.x, 0}, wa), cmul(cpx_t{za.y, 0}, cmul(wa, epi_root(p, (unsigned long long)k1)))};
         }
     }
 

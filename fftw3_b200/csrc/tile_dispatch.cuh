@@ -213,7 +213,7 @@ struct ColTmaInst {
 
 // T(N, EPI): the TMA column kernels (fp32 CUDA build only); preferred over both older forms
 #if defined(B2_HAVE_COLTMA)
-#define B2_TMA_EPIS(T, N) T(N, 0) T(N, 1) T(N, 8)
+#define B2_TMA_EPIS(T, N) T(N, 0) T(N, 1) T(N, 2) T(N, 8)
 #define B2_TMA_LIST(T) B2_TMA_EPIS(T, 512) B2_TMA_EPIS(T, 1024) B2_TMA_EPIS(T, 2048)
 #else
 #define B2_TMA_LIST(T)
