@@ -109,10 +109,11 @@ inline int b2_launch_chain(const ChainParams &cp, int threads, size_t smem, b2::
     const long long slots = cp.G + (long long)cp.lag * (cp.nsteps - 1);
     const long long nblocks = slots * cp.bpg;
 #if B2_CUDA
-    static size_t smem_set = 0;  // the opt-in only ever grows
-    if (smem > smem_set) {
+    static size_t smem_set[64] = {0};  // per device (function attributes are); the opt-in only ever grows
+    const int dv = b2::current_device() & 63;
+    if (smem > smem_set[dv]) {
         B2_CK(cudaFuncSetAttribute(b2_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set = smem;
+        smem_set[dv] = smem;
     }
     B2_CK(cudaMemsetAsync(cp.counters, 0, sizeof(unsigned) * (size_t)cp.nsteps * cp.G, st));
     const long long maxgrid = 1ll << 30;

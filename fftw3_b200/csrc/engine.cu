@@ -257,13 +257,16 @@ static void pipe_destroy(b2fft_plan *p);
 
 // ------------------------------------------------------------------------- plan create
 #if B2_CUDA
+// function attributes (opt-in dynamic shared memory) are per DEVICE: once per device a plan is created on
 static void init_kernel_attrs() {
-    static std::once_flag once;
-    std::call_once(once, [] {
-        cudaFuncSetAttribute(b2_generic_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             max_smem_optin());
-        b2_init_tile_kernels();
-    });
+    static std::mutex mu;
+    static bool done[64] = {false};
+    const int d = current_device();
+    std::lock_guard<std::mutex> lk(mu);
+    if (d >= 0 && d < 64 && done[d]) return;
+    cudaFuncSetAttribute(b2_generic_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_optin());
+    b2_init_tile_kernels();
+    if (d >= 0 && d < 64) done[d] = true;
 }
 #endif
 
