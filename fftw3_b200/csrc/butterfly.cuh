@@ -191,3 +191,76 @@ template <typename T> struct Bf<5, T> : BfPrime<5, T> {};
 template <typename T> struct Bf<7, T> : BfPrime<7, T> {};
 template <typename T> struct Bf<11, T> : BfPrime<11, T> {};
 template <typename T> struct Bf<13, T> : BfPrime<13, T> {};
+
+// Composite radices with coprime factors R = R1 * R2 (Good-Thomas / prime-factor form: no twiddles between
+// the two stages).  With a = R2^-1 mod R1, b = R1^-1 mod R2:
+//   input index  j = (R2*j1 + R1*j2) mod R,   output index  k = (R2*a*k1 + R1*b*k2) mod R,
+//   X[k] = sum_{j1,j2} x[j] w_R1^(j1 k1) w_R2^(j2 k2).
+// Every index is a compile-time constant after unrolling.  These stand where the reference has the generated
+// codelets n1_6, n1_10, n1_12, n1_15, n1_20 (fftw/dft_scalar/codelets/codlist.c:57-109), which the generator
+// derives the same way.
+constexpr int b2_inv_mod(int a, int m) {
+    for (int x = 1; x < m; ++x)
+        if ((a * x) % m == 1) return x;
+    return 0;
+}
+template <int R1, int R2, typename T> struct BfPFA {
+    static constexpr int R = R1 * R2;
+    static constexpr int A = R2 * b2_inv_mod(R2 % R1, R1), B = R1 * b2_inv_mod(R1 % R2, R2);
+    static_assert(A % R1 == 1 % R1 && B % R2 == 1 % R2, "the factors must be coprime");
+    static B2_HD void run(cpx<T> *v) {
+        cpx<T> b[R2][R1];  // b[j2][k1]
+#pragma unroll
+        for (int j2 = 0; j2 < R2; ++j2) {
+#pragma unroll
+            for (int j1 = 0; j1 < R1; ++j1) b[j2][j1] = v[(R2 * j1 + R1 * j2) % R];
+            Bf<R1, T>::run(b[j2]);
+        }
+#pragma unroll
+        for (int k1 = 0; k1 < R1; ++k1) {
+            cpx<T> r[R2];
+#pragma unroll
+            for (int j2 = 0; j2 < R2; ++j2) r[j2] = b[j2][k1];
+            Bf<R2, T>::run(r);
+#pragma unroll
+            for (int k2 = 0; k2 < R2; ++k2) v[(A * k1 + B * k2) % R] = r[k2];
+        }
+    }
+};
+template <typename T> struct Bf<6, T> : BfPFA<3, 2, T> {};
+template <typename T> struct Bf<10, T> : BfPFA<5, 2, T> {};
+template <typename T> struct Bf<12, T> : BfPFA<4, 3, T> {};
+template <typename T> struct Bf<15, T> : BfPFA<5, 3, T> {};
+template <typename T> struct Bf<20, T> : BfPFA<4, 5, T> {};
+template <typename T> struct Bf<24, T> : BfPFA<8, 3, T> {};
+template <typename T> struct Bf<30, T> : BfPFA<5, 6, T> {};
+
+// 9 = 3 x 3 (Cooley-Tukey: x[3 j1 + j2] -> three radix-3 butterflies over j1, twiddles w9^(j2 k1), three over
+// j2 -> X[k1 + 3 k2]).  Reference codelet: n1_9.
+template <typename T> struct Bf<9, T> {
+    static B2_HD void run(cpx<T> *v) {
+        const T c1 = (T)0.76604444311897803520, s1 = (T)0.64278760968653932632;   // 2 pi / 9
+        const T c2 = (T)0.17364817766693034885, s2 = (T)0.98480775301220805937;   // 4 pi / 9
+        const T c4 = (T)-0.93969262078590838405, s4 = (T)0.34202014332566873304;  // 8 pi / 9
+        cpx<T> b[3][3];  // b[j2][k1]
+#pragma unroll
+        for (int j2 = 0; j2 < 3; ++j2) {
+            b[j2][0] = v[j2];
+            b[j2][1] = v[3 + j2];
+            b[j2][2] = v[6 + j2];
+            Bf<3, T>::run(b[j2]);
+        }
+        b[1][1] = cmul(b[1][1], cpx<T>{c1, -s1});
+        b[1][2] = cmul(b[1][2], cpx<T>{c2, -s2});
+        b[2][1] = cmul(b[2][1], cpx<T>{c2, -s2});
+        b[2][2] = cmul(b[2][2], cpx<T>{c4, -s4});
+#pragma unroll
+        for (int k1 = 0; k1 < 3; ++k1) {
+            cpx<T> r[3] = {b[0][k1], b[1][k1], b[2][k1]};
+            Bf<3, T>::run(r);
+            v[k1] = r[0];
+            v[k1 + 3] = r[1];
+            v[k1 + 6] = r[2];
+        }
+    }
+};

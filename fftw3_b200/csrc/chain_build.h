@@ -113,7 +113,8 @@ inline void chain_candidates(const StepPlan &s, std::vector<long long> &out) {
 
 inline bool chainable_step(const StepPlan &s) {
     if (!s.outer.empty()) return false;
-    if (s.kind == SK_PASS) return s.fast_id >= 0 && !s.needs_tile_kernel && b2_tile_table()[s.fast_id].epi <= 1;
+    if (s.kind == SK_PASS)  // (the chain kernel dispatches over the power-of-two list only: no mixed-radix rows)
+        return s.fast_id >= 0 && !s.needs_tile_kernel && b2_tile_table()[s.fast_id].epi <= 1 && b2_tile_table()[s.fast_id].pipe != 3;
     return s.kind == SK_RPOST || s.kind == SK_RPRE;
 }
 

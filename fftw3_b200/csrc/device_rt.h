@@ -39,7 +39,7 @@ inline void set_error(const char *fmt, ...) {
 // Experiment switches that FFTW_MEASURE is allowed to toggle per candidate plan: opt(name) answers like getenv(name)
 // unless the calling thread is building a candidate with that switch forced on or off (b2fft_plan_create_tuned).
 enum { B2_CFG_NO_TMA = 1, B2_CFG_NO_PIPE = 2, B2_CFG_NO_PREFER3 = 4, B2_CFG_THREE_PASS_REAL = 8, B2_CFG_NO_TWO_PASS_REAL = 16,
-       B2_CFG_TWO_PASS_C2R = 32, B2_CFG_ALL = 63 };
+       B2_CFG_TWO_PASS_C2R = 32, B2_CFG_NO_MIX = 64, B2_CFG_ALL = 127 };
 inline int &cfg_override() {
     static thread_local int v = -1;  // -1: the environment decides; >= 0: bit mask of switches that are ON (all others OFF)
     return v;

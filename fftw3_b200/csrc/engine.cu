@@ -362,6 +362,7 @@ static const char *cfg_name(int bit) {
     case B2_CFG_THREE_PASS_REAL: return "three-pass real transform";
     case B2_CFG_NO_TWO_PASS_REAL: return "no two-pass real transform";
     case B2_CFG_TWO_PASS_C2R: return "two-pass c2r";
+    case B2_CFG_NO_MIX: return "generic kernel instead of the mixed-radix tile kernels";
     }
     return "?";
 }

@@ -13,6 +13,7 @@
 struct b2fft_comm_s;
 
 inline bool b2_have_tile_kernel(int n, int mode, int epi);  // tile_dispatch.cuh
+inline bool b2_have_any_tile_kernel(int n, int mode, int epi);  // the same, mixed-radix kernels included
 
 namespace b2 {
 
@@ -64,6 +65,11 @@ inline bool split_four_step(long long n, long long *n1o, long long *n2o) {
         long long b = n / a;
         if (b > c.col || !factorable(a) || !factorable(b)) continue;
         double d = fabs(log((double)a) - log((double)b));
+        // a factor pair that runs on tile kernels beats a better balanced one that does not (for a power of two
+        // every pair in range has them, so nothing changes there): larger factor = column pass + twiddle, smaller
+        // = row -> column pass
+        const long long hi = a > b ? a : b, lo = a > b ? b : a;
+        d += 100.0 * ((b2_have_any_tile_kernel((int)hi, 1, 1) ? 0 : 1) + (b2_have_any_tile_kernel((int)lo, 2, 0) ? 0 : 1));
         if (d < bestd) {
             bestd = d;
             best = a;

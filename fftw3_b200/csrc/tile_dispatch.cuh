@@ -3,19 +3,11 @@
 #pragma once
 #include "colpipe_kernel.cuh"
 #include "coltma_kernel.cuh"
+#include "tile_entry.h"
 
 #ifndef B2_MINB256
 #define B2_MINB256 4
 #endif
-struct TileEntry {
-    int n, e, mode, epi, c, threads;
-    size_t smem;
-    size_t (*smem_for)(int C);
-    int (*launch)(const PassParams &, const real_t *, real_t *, long long, long long, int, size_t, b2::stream_t);
-    void (*init)();
-    int pipe;  // 1: persistent, software-pipelined column kernel (colpipe_kernel.cuh); 2: TMA column kernel (coltma_kernel.cuh)
-};
-
 template <int N, int E, int MODE, int EPI, int C>
 struct TileInst {
     static constexpr int THREADS = C * (N / E);
@@ -223,8 +215,14 @@ inline const std::vector<TileEntry> &b2_tile_table() {
 #define B2_X_ENTRY(N, E, MODE, EPI, C) TileInst<N, E, MODE, EPI, C>::entry(),
 #define B2_P_ENTRY(N, E, EPI, C) TilePipeInst<N, E, EPI, C>::entry(),
 #define B2_T_ENTRY(N, EPI) ColTmaInst<N, EPI>::entry(),
-    static const std::vector<TileEntry> tab = {B2_TILE_LIST(B2_X_ENTRY) B2_TILE_LIST_REAL(B2_X_ENTRY) B2_PIPE_LIST(B2_P_ENTRY)
-                                                   B2_TMA_LIST(B2_T_ENTRY)};
+    static const std::vector<TileEntry> tab = [] {
+        std::vector<TileEntry> t = {B2_TILE_LIST(B2_X_ENTRY) B2_TILE_LIST_REAL(B2_X_ENTRY) B2_PIPE_LIST(B2_P_ENTRY)
+                                        B2_TMA_LIST(B2_T_ENTRY)};
+        int nmix = 0;
+        const TileEntry *mix = b2::mix_entries(&nmix);  // lengths that are not powers of two (mixtile.cu)
+        t.insert(t.end(), mix, mix + nmix);
+        return t;
+    }();
 #undef B2_X_ENTRY
 #undef B2_P_ENTRY
 #undef B2_T_ENTRY
@@ -236,7 +234,14 @@ inline const std::vector<TileEntry> &b2_tile_table() {
 inline bool b2_have_tile_kernel(int n, int mode, int epi) {
     if (getenv("FFTW_B200_GENERIC_ONLY")) return false;
     for (const TileEntry &e : b2_tile_table())
-        if (e.n == n && e.mode == mode && e.epi == epi) return true;
+        if (e.n == n && e.mode == mode && e.epi == epi && e.pipe != 3) return true;
+    return false;
+}
+
+inline bool b2_have_any_tile_kernel(int n, int mode, int epi) {
+    if (getenv("FFTW_B200_GENERIC_ONLY")) return false;
+    for (const TileEntry &e : b2_tile_table())
+        if (e.n == n && e.mode == mode && e.epi == epi && (e.pipe != 3 || !b2::opt("FFTW_B200_NO_MIX", b2::B2_CFG_NO_MIX))) return true;
     return false;
 }
 
@@ -311,10 +316,12 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
     if (p.m <= 512 && p.s_axis * (long long)sizeof(real_t) >= (1ll << 20) && !getenv("FFTW_B200_TMA_ALL")) tma_ok = false;
     if (const char *e = getenv("FFTW_B200_TMA_MIN_N"))
         if (p.m < atoi(e)) tma_ok = false;
-    for (int pass = 2; pass >= 0 && s.fast_id < 0; --pass)
+    // mixed-radix kernels (mixtile.cu): plain complex passes only (their lengths never meet the real-transform epilogues)
+    const bool mix_ok = !b2::opt("FFTW_B200_NO_MIX", b2::B2_CFG_NO_MIX) && p.fold_n == 0;
+    for (int pass = 3; pass >= 0 && s.fast_id < 0; --pass)
     for (size_t i = 0; i < tab.size(); ++i) {
         const TileEntry &e = tab[i];
-        if ((pass == 2 && !tma_ok) || (pass == 1 && !pipe_ok)) break;
+        if ((pass == 3 && !mix_ok) || (pass == 2 && !tma_ok) || (pass == 1 && !pipe_ok)) break;
         if (e.n != p.m || e.mode != mode || e.epi != epi || e.pipe != pass) continue;
         s.fast_id = (int)i;
         p.C = e.c;
@@ -334,8 +341,9 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         std::string rs;
         for (int i2 = 0; i2 < p.npass; ++i2) rs += (i2 ? "x" : "") + std::to_string(p.radix[i2]);
         snprintf(buf, sizeof buf, "%s n=%d tile-kernel[%s%s%s] E=%d regs-resident, tile=%dx%d ctas=%lld threads=%d smem=%zuB",
-                 real_half ? (epi == 3 ? "r2c" : "c2r") : "c2c", real_half ? p.n : p.m, mn[mode], e.pipe == 2 ? ", persistent, TMA-fed, two line groups" : e.pipe ? ", persistent, async-copy pipelined" : "", p.fold_n > 0 ? (p.swap_in ? "+hermitian unfold+twiddle" : "+hermitian fold") : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
+                 real_half ? (epi == 3 ? "r2c" : "c2r") : "c2c", real_half ? p.n : p.m, mn[mode], e.pipe == 3 ? ", mixed radix" : e.pipe == 2 ? ", persistent, TMA-fed, two line groups" : e.pipe ? ", persistent, async-copy pipelined" : "", p.fold_n > 0 ? (p.swap_in ? "+hermitian unfold+twiddle" : "+hermitian fold") : en[epi], e.e, p.C, p.m, nb, e.threads, e.smem);
         s.desc = buf;
+        if (e.pipe == 3 && e.sched) s.desc += std::string(" radices ") + e.sched;
         return;
     }
 }

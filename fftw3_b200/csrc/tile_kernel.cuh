@@ -32,6 +32,31 @@ template <int N, int E> struct TileSched {
     static constexpr int bits(int i) { return (LOGN + (NP - 1 - i)) / NP; }
     static constexpr int radix(int i) { return 1 << bits(i); }
     static constexpr int ns(int i) { return i == 0 ? 1 : ns(i - 1) * radix(i - 1); }
+    static constexpr int PER = -1;  // shared-memory padding period: the precision's default
+};
+
+// Mixed-radix schedule for a length that is not a power of two: N = R0 * R1 * ..., every radix divides E
+// (a thread holds E points and runs E / R butterflies of radix R in a pass).  Radices: whatever Bf<R>
+// exists for (butterfly.cuh: 2 3 4 5 7 8 16 and the composites 6 9 10 12 20 24 25 30).
+template <int... RS> struct MixRadices {
+    static constexpr int NP = sizeof...(RS);
+    static constexpr int get(int i) {
+        constexpr int r[] = {RS...};
+        return r[i];
+    }
+    static constexpr int prod(int i) { return i == 0 ? 1 : prod(i - 1) * get(i - 1); }  // of the first i radices
+    static constexpr bool all_divide(int e, int i) { return i == NP ? true : (e % get(i) == 0 && all_divide(e, i + 1)); }
+};
+template <int N, int E, int... RS> struct MixSched {
+    typedef MixRadices<RS...> RR;
+    static constexpr int NP = RR::NP;
+    static constexpr int radix(int i) { return RR::get(i); }
+    static constexpr int ns(int i) { return RR::prod(i); }
+    static_assert(RR::prod(NP) == N, "the radices must multiply to N");
+    static_assert(N % E == 0 && RR::all_divide(E, 0), "every radix must divide E, and E must divide N");
+    // the first pass writes R0 neighbouring points per butterfly, butterflies of neighbouring threads R0 apart:
+    // one pad element per R0 makes that stride odd (an odd R0 needs none)
+    static constexpr int PER = (RR::get(0) % 2 == 0) ? RR::get(0) : 0;
 };
 
 #if B2_CUDA
@@ -55,7 +80,12 @@ struct TileCtx {
     int nthreads;
 };
 
-template <int PADSHIFT> B2_HD int b2_pad(int o) { return o + (o >> PADSHIFT); }
+// index -> padded index, one pad element per PER (0: no padding)
+template <int PER> B2_HD int b2_pad(int o) {
+    if (PER == 0) return o;
+    if ((PER & (PER - 1)) == 0) return o + (o >> b2_ilog2(PER > 0 ? PER : 1));
+    return o + (int)((unsigned)o / (unsigned)(PER > 0 ? PER : 1));
+}
 
 // Streaming data is read through L2 only (ld.global.cg): it is never reused from L1, and when
 // passes are chained inside one launch the producer may be another SM, whose writes a stale L1
@@ -96,25 +126,25 @@ template <int R> B2_D void b2_twiddle_powers(cpx_t w1, cpx_t *w) {
 }
 
 // EPI: 0 none, 1 four-step twiddle on the way out, 2 split of a pair of real columns + twiddle
-template <int N, int E, int MODE, int EPI> struct TileFFT {
-    typedef TileSched<N, E> S;
+template <int N, int E, int MODE, int EPI, class SCHED = TileSched<N, E>> struct TileFFT {
+    typedef SCHED S;
     static constexpr int T = N / E;  // threads per line
-    static constexpr int PADSHIFT = sizeof(real_t) == 4 ? 4 : 3;
+    static constexpr int PER = S::PER < 0 ? (sizeof(real_t) == 4 ? 16 : 8) : S::PER;  // padding period (0: none)
+    static constexpr int PERD = PER > 0 ? PER : 1;
     static constexpr bool COLMAP = (MODE == MODE_COL);
     // smem line stride (complex): row-mapped passes pad inside the line; any kernel that walks
     // neighbouring lines with neighbouring lanes needs an odd stride
-    static constexpr int LSRAW = COLMAP ? N : (N + (N >> PADSHIFT));
+    static constexpr int LSRAW = (COLMAP || PER == 0) ? N : (N + N / PERD);
     static constexpr int LS = (MODE == MODE_ROW) ? LSRAW : (LSRAW | 1);
 
-    static B2_HD int phys(int o) { return COLMAP ? o : b2_pad<PADSHIFT>(o); }
+    static B2_HD int phys(int o) { return COLMAP ? o : b2_pad<PER>(o); }
     // phys(o + k*STEP) for k = 0..: when STEP is a multiple of the padding period (or the whole
     // run stays inside one period) the padding separates and k*STEP' becomes an immediate offset
     template <int STEP, int SPAN> static B2_HD int phys_k(int o, int po, int k) {
-        constexpr int PER = 1 << PADSHIFT;
-        if (COLMAP) return o + k * STEP;
-        if (STEP % PER == 0) return po + k * (STEP + STEP / PER);
-        if (SPAN > 0 && STEP * SPAN <= PER && (PER % (STEP * (SPAN > 0 ? SPAN : 1))) == 0) return po + k * STEP;  // o is a multiple of STEP*SPAN
-        return b2_pad<PADSHIFT>(o + k * STEP);
+        if (COLMAP || PER == 0) return o + k * STEP;
+        if (STEP % PERD == 0) return po + k * (STEP + STEP / PERD);
+        if (SPAN > 0 && STEP * SPAN <= PER && (PERD % (STEP * (SPAN > 0 ? SPAN : 1))) == 0) return po + k * STEP;  // o is a multiple of STEP*SPAN
+        return b2_pad<PER>(o + k * STEP);
     }
     static B2_HD size_t smem_bytes(int C) { return (size_t)C * LS * sizeof(cpx_t); }
 
@@ -171,7 +201,7 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
             cpx_t a[R];
 #pragma unroll
             for (int k = 0; k < R; ++k) a[k] = v[m + k * NB];
-            const int jm = j & (NS - 1);
+            const int jm = (NS & (NS - 1)) == 0 ? (j & (NS - 1)) : (int)((unsigned)j % (unsigned)NS);
             if (NS > 1) {
                 cpx_t w[R];
                 b2_twiddle_powers<R>(tw[jm * (N / (NS * R))], w);
@@ -680,12 +710,12 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                     const int pk = phys(k0);
                     cpx_t *ps = cdst + (base + (long long)c * lstep + (long long)k0 * ds);
                     const long long step = (long long)T * ds;
-                    constexpr int H = E / 2;  // two half batches: 16 values in flight would spill
+                    constexpr int H = (E + 1) / 2;  // two half batches: 16 values in flight would spill
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
                         cpx_t a[H];
 #pragma unroll
-                        for (int q = 0; q < H; ++q) a[q] = sp[phys_k<T, 0>(k0, pk, h * H + q)];
+                        for (int q = 0; q < H; ++q) a[q] = (h * H + q < E) ? sp[phys_k<T, 0>(k0, pk, h * H + q)] : cpx_t{0, 0};
                         if (p.swap_out) {
 #pragma unroll
                             for (int q = 0; q < H; ++q) a[q] = cswap(a[q]);
@@ -696,13 +726,13 @@ template <int N, int E, int MODE, int EPI> struct TileFFT {
                             for (int q = 0; q < H; ++q) {
                                 long long idx;
                                 bool cj;
-                                if (fold_target(p, x.l0 + c, k0 + (h * H + q) * T, x.fcoord, idx, cj))
+                                if (h * H + q < E && fold_target(p, x.l0 + c, k0 + (h * H + q) * T, x.fcoord, idx, cj))
                                     fb[idx * lstep] = cj ? cconj(a[q]) : a[q];
                             }
                         } else {
 #pragma unroll
                             for (int q = 0; q < H; ++q) {
-                                *ps = a[q];
+                                if (h * H + q < E) *ps = a[q];
                                 ps += step;
                             }
                         }

@@ -820,3 +820,77 @@ def check_inplace_relayout(lib, device=False):
     assert rel_l2(down(buf).reshape(20, 12), orc.dft(x, +1).T) < tol(lib, 240)
     y = up(np.zeros(64, dtype=lib.cplx))
     assert not lib.plan_many_dft([8], 2, y, None, 1, 8, y, None, 2, 20, capi.FFTW_FORWARD)
+
+
+# lengths with a mixed-radix tile kernel (csrc/mixtile.cu): (n, has the column forms)
+MIX_LENGTHS = [(96, True), (192, True), (384, True), (768, True), (1536, True), (3072, False), (100, True), (200, True),
+               (250, True), (400, True), (500, True), (1000, True), (2000, False), (3000, False), (4000, False),
+               (81, True), (243, True), (729, True), (2187, False), (125, True), (625, False), (3125, False),
+               (49, True), (343, True), (2401, False), (1080, False)]
+MIX_LENGTHS_FP32_ONLY = [(5000, False), (6144, False), (6561, False)]
+
+
+def check_mixed_radix(lib, n, cols, seed=0):
+    """Compile-time mixed-radix tile kernels for lengths that are not powers of two: every form the selector can pick
+    (row; column, column + four-step twiddle and row -> column for the lengths that have them), full and ragged
+    tiles, both directions, against numpy fp64.  The plan text must name the kernel, so a silent fall back to the
+    generic kernel fails the test.  Reference: the n1_* / t1_* codelets for radices 3 5 6 7 9 10 12 15 20
+    (fftw/dft_scalar/codelets/codlist.c:57-109)."""
+    rng = np.random.default_rng(seed + n)
+    # ---- row form: batched contiguous lines, a batch that is not a multiple of any tile width
+    hm = 67 if n <= 512 else (9 if n <= 2048 else 3)
+    x = rand_c(rng, (hm, n), lib)
+    for sign in (capi.FFTW_FORWARD, capi.FFTW_BACKWARD):
+        y = np.zeros_like(x)
+        p = lib.plan_many_dft([n], hm, x, None, 1, n, y, None, 1, n, sign)
+        assert p
+        txt = lib.sprint_plan(p)
+        assert "mixed radix" in txt and "tile-kernel[row" in txt, txt
+        lib.execute(p)
+        lib.destroy_plan(p)
+        ref = np.fft.fft(x.astype(np.complex128), axis=1) if sign < 0 else n * np.fft.ifft(x.astype(np.complex128), axis=1)
+        assert rel_l2(y, ref) < tol(lib, n), (n, "row", sign)
+    if not cols or n > (2048 if lib.single else 1024):  # (the column cap, csrc/selector.h caps())
+        return
+    # ---- column form: the first axis of a 2-D array (ragged: 20 columns; full: 64)
+    for w in (20, 64):
+        x = rand_c(rng, (n, w), lib)
+        y = np.zeros_like(x)
+        p = lib.plan_many_dft([n], w, x, None, w, 1, y, None, w, 1, capi.FFTW_FORWARD)
+        assert p
+        txt = lib.sprint_plan(p)
+        assert "mixed radix" in txt and "tile-kernel[col" in txt, txt
+        lib.execute(p)
+        lib.destroy_plan(p)
+        assert rel_l2(y, np.fft.fft(x.astype(np.complex128), axis=0)) < tol(lib, n), (n, "col", w)
+    # ---- inside an N-D transform (column pass in place after the row pass), backward
+    x = rand_c(rng, (n, 24), lib)
+    y = lib.dft(x, capi.FFTW_BACKWARD)
+    assert rel_l2(y, x.size * np.fft.ifft2(x.astype(np.complex128))) < tol(lib, x.size), (n, "2-D")
+
+
+def check_mixed_radix_long(lib):
+    """Long 1-D lengths whose two passes are mixed-radix kernels: column + four-step twiddle, then row -> column."""
+    import os
+    rng = np.random.default_rng(5)
+    old = os.environ.get("FFTW_B200_ROW_CAP")
+    os.environ["FFTW_B200_ROW_CAP"] = "1024"  # make the two-pass split reachable at test sizes
+    try:
+        for n, hm in ((100000, 2), (24576, 3), (1000 * 96, 1), (243 * 250, 2), (400 * 400, 1), (3 * 2 ** 17, 1)):
+            x = rand_c(rng, (hm, n), lib)
+            for sign in (capi.FFTW_FORWARD, capi.FFTW_BACKWARD):
+                y = np.zeros_like(x)
+                p = lib.plan_many_dft([n], hm, x, None, 1, n, y, None, 1, n, sign)
+                assert p
+                txt = lib.sprint_plan(p)
+                assert "mixed radix" in txt, txt
+                lib.execute(p)
+                lib.destroy_plan(p)
+                xd = x.astype(np.complex128)
+                ref = np.fft.fft(xd, axis=1) if sign < 0 else n * np.fft.ifft(xd, axis=1)
+                assert rel_l2(y, ref) < tol(lib, n), (n, sign, txt)
+    finally:
+        if old is None:
+            os.environ.pop("FFTW_B200_ROW_CAP", None)
+        else:
+            os.environ["FFTW_B200_ROW_CAP"] = old

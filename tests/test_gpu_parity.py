@@ -87,6 +87,17 @@ def test_split_array_guru_interfaces(lib):
     cases.check_split_interleaved_host(lib)
 
 
+@pytest.mark.parametrize("n,cols", cases.MIX_LENGTHS + cases.MIX_LENGTHS_FP32_ONLY, ids=lambda v: str(v))
+def test_mixed_radix_tile_kernels(lib, n, cols):
+    if not lib.single and (n, cols) in cases.MIX_LENGTHS_FP32_ONLY:
+        pytest.skip("beyond the fp64 row cap")
+    cases.check_mixed_radix(lib, n, cols)
+
+
+def test_mixed_radix_long_lengths(lib):
+    cases.check_mixed_radix_long(lib)
+
+
 def test_measure_and_wisdom(lib):
     cases.check_measure_and_wisdom(lib)
     cases.check_measure_and_wisdom(lib, device=True)
