@@ -87,6 +87,13 @@ struct MixInst {
     MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_COL, 1, CCOL>::entry(#__VA_ARGS__),     \
     MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_ROW2COL, 0, CCOL>::entry(#__VA_ARGS__),
 
+// the three column forms alone (a second shape for a length: the selector takes the FIRST row of the table that fits,
+// FFTW_B200_MIX_ALT=1 the last)
+#define B2_MIX_COLS(N, E, CCOL, ...)                                                       \
+    MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_COL, 0, CCOL>::entry(#__VA_ARGS__),     \
+    MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_COL, 1, CCOL>::entry(#__VA_ARGS__),     \
+    MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_ROW2COL, 0, CCOL>::entry(#__VA_ARGS__),
+
 #if defined(FFTW_SINGLE)
 #define B2_CC(c32, c64) c32
 #define B2_MIX_ALL32(N, E, CROW, CCOL, ...) B2_MIX_ALL(N, E, CROW, CCOL, __VA_ARGS__)
@@ -132,6 +139,16 @@ const TileEntry *mix_entries(int *count) {
         B2_MIX_ROW(5000, 10, 1, 10, 10, 10, 5)
         B2_MIX_ROW(6144, 24, 1, 12, 8, 8, 8)
         B2_MIX_ROW(6561, 27, 1, 9, 9, 9, 9)
+        // second shapes (see B2_MIX_COLS): wider column tiles / more points per thread, other row shapes
+        B2_MIX_COLS(250, 10, 16, 10, 5, 5)
+        B2_MIX_COLS(500, 20, 16, 10, 10, 5)
+        B2_MIX_COLS(1000, 20, 16, 10, 10, 10)
+        B2_MIX_COLS(243, 27, 16, 9, 9, 3)
+        B2_MIX_COLS(729, 27, 16, 9, 9, 9)
+        B2_MIX_ROW(5000, 20, 1, 10, 10, 10, 5)
+        B2_MIX_ROW(6561, 9, 1, 9, 9, 9, 9)
+        B2_MIX_ROW(625, 5, 2, 5, 5, 5, 5)
+        B2_MIX_ROW(3125, 5, 1, 5, 5, 5, 5, 5)
 #endif
     };
     *count = (int)(sizeof tab / sizeof tab[0]);

@@ -318,11 +318,21 @@ inline void b2_select_tile_kernel(b2::StepPlan &s) {
         if (p.m < atoi(e)) tma_ok = false;
     // mixed-radix kernels (mixtile.cu): plain complex passes only (their lengths never meet the real-transform epilogues)
     const bool mix_ok = !b2::opt("FFTW_B200_NO_MIX", b2::B2_CFG_NO_MIX) && p.fold_n == 0;
+    const bool mix_alt = getenv("FFTW_B200_MIX_ALT") != nullptr;
     for (int pass = 3; pass >= 0 && s.fast_id < 0; --pass)
     for (size_t i = 0; i < tab.size(); ++i) {
         const TileEntry &e = tab[i];
         if ((pass == 3 && !mix_ok) || (pass == 2 && !tma_ok) || (pass == 1 && !pipe_ok)) break;
         if (e.n != p.m || e.mode != mode || e.epi != epi || e.pipe != pass) continue;
+        if (pass == 3 && mix_alt) {  // experiments: the LAST shape listed for this length instead of the first
+            size_t j = i;
+            for (size_t k = i + 1; k < tab.size(); ++k)
+                if (tab[k].n == e.n && tab[k].mode == e.mode && tab[k].epi == e.epi && tab[k].pipe == 3) j = k;
+            if (j != i) {
+                i = j - 1;
+                continue;
+            }
+        }
         s.fast_id = (int)i;
         p.C = e.c;
         p.tiles0 = (p.ln[0] + p.C - 1) / p.C;

@@ -894,3 +894,17 @@ def check_mixed_radix_long(lib):
             os.environ.pop("FFTW_B200_ROW_CAP", None)
         else:
             os.environ["FFTW_B200_ROW_CAP"] = old
+
+
+# lengths with a second kernel shape in the table (csrc/mixtile.cu, FFTW_B200_MIX_ALT=1 selects it)
+MIX_SECOND_SHAPES = [(250, True), (500, True), (1000, True), (243, True), (729, True), (625, False), (3125, False)]
+MIX_SECOND_SHAPES_FP32_ONLY = [(5000, False), (6561, False)]
+
+
+def check_mixed_radix_second_shapes(lib, n, cols):
+    import os
+    os.environ["FFTW_B200_MIX_ALT"] = "1"
+    try:
+        check_mixed_radix(lib, n, cols, seed=3)
+    finally:
+        os.environ.pop("FFTW_B200_MIX_ALT", None)

@@ -127,6 +127,13 @@ def test_mixed_radix_tile_kernels(lib, n, cols):
     cases.check_mixed_radix(lib, n, cols)
 
 
+@pytest.mark.parametrize("n,cols", cases.MIX_SECOND_SHAPES + cases.MIX_SECOND_SHAPES_FP32_ONLY, ids=lambda v: str(v))
+def test_mixed_radix_second_shapes(lib, n, cols):
+    if not lib.single:
+        pytest.skip("second shapes exist in the fp32 library only")
+    cases.check_mixed_radix_second_shapes(lib, n, cols)
+
+
 def test_mixed_radix_long_lengths(lib):
     cases.check_mixed_radix_long(lib)
 
