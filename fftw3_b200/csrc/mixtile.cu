@@ -87,8 +87,9 @@ struct MixInst {
     MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_COL, 1, CCOL>::entry(#__VA_ARGS__),     \
     MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_ROW2COL, 0, CCOL>::entry(#__VA_ARGS__),
 
-// the three column forms alone (a second shape for a length: the selector takes the FIRST row of the table that fits,
-// FFTW_B200_MIX_ALT=1 the last)
+#define B2_MIX_ONE(N, E, MODE, EPI, C, ...) MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE, EPI, C>::entry(#__VA_ARGS__),
+// the three column forms alone (a length may be listed with several shapes: the selector takes the FIRST row of the
+// table that fits, FFTW_B200_MIX_ALT=1 the last)
 #define B2_MIX_COLS(N, E, CCOL, ...)                                                       \
     MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_COL, 0, CCOL>::entry(#__VA_ARGS__),     \
     MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_COL, 1, CCOL>::entry(#__VA_ARGS__),     \
@@ -105,6 +106,16 @@ struct MixInst {
 namespace b2 {
 const TileEntry *mix_entries(int *count) {
     static const TileEntry tab[] = {
+#if defined(FFTW_SINGLE)
+        // Shapes that measured faster than the ones in the main list below (profiles/r2_mix_probe.md: 64-byte column
+        // segments and 9/10 points per thread are what holds a column kernel back): listed first, so they are chosen.
+        B2_MIX_COLS(250, 10, 16, 10, 5, 5)         // 0.727 -> 0.466 ms per GiB pass
+        B2_MIX_COLS(1000, 20, 16, 10, 10, 10)      // 0.788 -> 0.598
+        B2_MIX_ONE(243, 27, MODE_COL, 0, 16, 9, 9, 3)  // 0.727 -> 0.438 (the twiddle / row->column forms stay at E = 9)
+        B2_MIX_COLS(729, 27, 16, 9, 9, 9)          // 0.849 -> 0.657
+        B2_MIX_ROW(5000, 20, 1, 10, 10, 10, 5)     // 0.642 -> 0.545
+        B2_MIX_ROW(625, 5, 2, 5, 5, 5, 5)          // 0.626 -> 0.444
+#endif
         // 3 * 2^k
         B2_MIX_ALL(96, 24, 64, B2_CC(64, 32), 12, 8)
         B2_MIX_ALL(192, 24, 32, B2_CC(32, 16), 24, 8)
@@ -139,15 +150,12 @@ const TileEntry *mix_entries(int *count) {
         B2_MIX_ROW(5000, 10, 1, 10, 10, 10, 5)
         B2_MIX_ROW(6144, 24, 1, 12, 8, 8, 8)
         B2_MIX_ROW(6561, 27, 1, 9, 9, 9, 9)
-        // second shapes (see B2_MIX_COLS): wider column tiles / more points per thread, other row shapes
-        B2_MIX_COLS(250, 10, 16, 10, 5, 5)
+        // shapes that measured equal or slower than the ones above (kept selectable with FFTW_B200_MIX_ALT=1, which
+        // takes the LAST row listed for a length: scripts/gpu_mix_alt_probe.py)
         B2_MIX_COLS(500, 20, 16, 10, 10, 5)
-        B2_MIX_COLS(1000, 20, 16, 10, 10, 10)
-        B2_MIX_COLS(243, 27, 16, 9, 9, 3)
-        B2_MIX_COLS(729, 27, 16, 9, 9, 9)
-        B2_MIX_ROW(5000, 20, 1, 10, 10, 10, 5)
+        B2_MIX_ONE(243, 27, MODE_COL, 1, 16, 9, 9, 3)
+        B2_MIX_ONE(243, 27, MODE_ROW2COL, 0, 16, 9, 9, 3)
         B2_MIX_ROW(6561, 9, 1, 9, 9, 9, 9)
-        B2_MIX_ROW(625, 5, 2, 5, 5, 5, 5)
         B2_MIX_ROW(3125, 5, 1, 5, 5, 5, 5, 5)
 #endif
     };
