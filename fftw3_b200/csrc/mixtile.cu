@@ -107,14 +107,17 @@ namespace b2 {
 const TileEntry *mix_entries(int *count) {
     static const TileEntry tab[] = {
 #if defined(FFTW_SINGLE)
-        // Shapes that measured faster than the ones in the main list below (profiles/r2_mix_probe.md: 64-byte column
-        // segments and 9/10 points per thread are what holds a column kernel back): listed first, so they are chosen.
-        B2_MIX_COLS(250, 10, 16, 10, 5, 5)         // 0.727 -> 0.466 ms per GiB pass
-        B2_MIX_COLS(1000, 20, 16, 10, 10, 10)      // 0.788 -> 0.598
-        B2_MIX_ONE(243, 27, MODE_COL, 0, 16, 9, 9, 3)  // 0.727 -> 0.438 (the twiddle / row->column forms stay at E = 9)
-        B2_MIX_COLS(729, 27, 16, 9, 9, 9)          // 0.849 -> 0.657
-        B2_MIX_ROW(5000, 20, 1, 10, 10, 10, 5)     // 0.642 -> 0.545
-        B2_MIX_ROW(625, 5, 2, 5, 5, 5, 5)          // 0.626 -> 0.444
+        // Shapes that measured faster than the ones in the main list below, form by form (profiles/r2_mix_probe.md): listed
+        // first, so they are chosen.  Column forms want 128-byte row segments (16 lines) and 20+ points per thread; the
+        // row -> column form wants many small CTAs, so it mostly stays with the main list's shape.
+        B2_MIX_ONE(250, 10, MODE_COL, 0, 16, 10, 5, 5)   // 0.727 -> 0.466 ms per GiB pass
+        B2_MIX_COLS(1000, 20, 16, 10, 10, 10)            // 0.788 -> 0.598; as the passes of n = 10^6: 1.556 -> 1.330
+        B2_MIX_ONE(243, 27, MODE_COL, 0, 16, 9, 9, 3)    // 0.727 -> 0.438
+        B2_MIX_ONE(243, 27, MODE_COL, 1, 16, 9, 9, 3)    // n = 243 * 128: 0.966 -> 0.920
+        B2_MIX_ONE(729, 27, MODE_COL, 0, 16, 9, 9, 9)    // 0.849 -> 0.657
+        B2_MIX_ONE(729, 27, MODE_COL, 1, 16, 9, 9, 9)    // n = 729 * 512: 1.383 -> 1.122
+        B2_MIX_ROW(5000, 20, 1, 10, 10, 10, 5)           // 0.642 -> 0.545
+        B2_MIX_ROW(625, 5, 2, 5, 5, 5, 5)                // 0.626 -> 0.444
 #endif
         // 3 * 2^k
         B2_MIX_ALL(96, 24, 64, B2_CC(64, 32), 12, 8)
@@ -151,10 +154,12 @@ const TileEntry *mix_entries(int *count) {
         B2_MIX_ROW(6144, 24, 1, 12, 8, 8, 8)
         B2_MIX_ROW(6561, 27, 1, 9, 9, 9, 9)
         // shapes that measured equal or slower than the ones above (kept selectable with FFTW_B200_MIX_ALT=1, which
-        // takes the LAST row listed for a length: scripts/gpu_mix_alt_probe.py)
+        // takes the LAST row listed for a length and form: scripts/gpu_mix_alt_probe.py, gpu_mix_form_probe.py)
         B2_MIX_COLS(500, 20, 16, 10, 10, 5)
-        B2_MIX_ONE(243, 27, MODE_COL, 1, 16, 9, 9, 3)
+        B2_MIX_ONE(250, 10, MODE_COL, 1, 16, 10, 5, 5)
+        B2_MIX_ONE(250, 10, MODE_ROW2COL, 0, 16, 10, 5, 5)
         B2_MIX_ONE(243, 27, MODE_ROW2COL, 0, 16, 9, 9, 3)
+        B2_MIX_ONE(729, 27, MODE_ROW2COL, 0, 16, 9, 9, 9)
         B2_MIX_ROW(6561, 9, 1, 9, 9, 9, 9)
         B2_MIX_ROW(3125, 5, 1, 5, 5, 5, 5, 5)
 #endif
