@@ -33,7 +33,31 @@ template <int N, int E> struct TileSched {
     static constexpr int radix(int i) { return 1 << bits(i); }
     static constexpr int ns(int i) { return i == 0 ? 1 : ns(i - 1) * radix(i - 1); }
     static constexpr int PER = -1;  // shared-memory padding period: the precision's default
+    static constexpr bool MIXED = false;
+    static constexpr int xp(int) { return 0; }  // (per-exchange layouts are a MixSched matter)
+    static constexpr int xa(int) { return 0; }
+    static constexpr int xls(int) { return -1; }
 };
+
+// Per-exchange shared-memory layouts of a mixed-radix schedule.  The exchange between radix passes X and X+1 is written
+// by one access pattern (R points NS apart per butterfly) and read by another (E points T apart per thread), both known
+// at compile time, and the buffer is rewritten in every exchange -- so every exchange may have its own layout
+//   f(o) = o + (o / P) * A   with line stride LS,
+// chosen to minimise bank conflicts.  The table (mix_layouts.h) is produced by scripts/analysis/smem_conflicts.py, an
+// exact enumeration of the kernel's shared-memory accesses calibrated against ncu's conflict counters.
+template <int N, int E> struct MixLayout {
+    static constexpr int NX = 0;
+    static constexpr int get(int, int) { return 0; }
+};
+#define B2_MIX_LAYOUT(N, E, NXV, ...)                \
+    template <> struct MixLayout<N, E> {             \
+        static constexpr int NX = NXV;               \
+        static constexpr int get(int x, int f) {     \
+            constexpr int t[NXV][3] = {__VA_ARGS__}; \
+            return t[x][f];                          \
+        }                                            \
+    };
+#include "mix_layouts.h"
 
 // Mixed-radix schedule for a length that is not a power of two: N = R0 * R1 * ..., every radix divides E
 // (a thread holds E points and runs E / R butterflies of radix R in a pass).  Radices: whatever Bf<R>
@@ -57,6 +81,12 @@ template <int N, int E, int... RS> struct MixSched {
     // the first pass writes R0 neighbouring points per butterfly, butterflies of neighbouring threads R0 apart:
     // one pad element per R0 makes that stride odd (an odd R0 needs none)
     static constexpr int PER = (RR::get(0) % 2 == 0) ? RR::get(0) : 0;
+    static constexpr bool MIXED = true;
+    typedef MixLayout<N, E> ML;
+    static constexpr bool TABLE = ML::NX == NP - 1 && NP > 1;
+    static constexpr int xp(int X) { return TABLE ? ML::get(X, 0) : PER; }
+    static constexpr int xa(int X) { return TABLE ? ML::get(X, 1) : (PER ? 1 : 0); }
+    static constexpr int xls(int X) { return TABLE ? ML::get(X, 2) : -1; }  // -1: the kernel's default line stride
 };
 
 #if B2_CUDA
@@ -146,7 +176,26 @@ template <int N, int E, int MODE, int EPI, class SCHED = TileSched<N, E>> struct
         if (SPAN > 0 && STEP * SPAN <= PER && (PERD % (STEP * (SPAN > 0 ? SPAN : 1))) == 0) return po + k * STEP;  // o is a multiple of STEP*SPAN
         return b2_pad<PER>(o + k * STEP);
     }
-    static B2_HD size_t smem_bytes(int C) { return (size_t)C * LS * sizeof(cpx_t); }
+    // ---- exchange X (between radix passes X and X+1): its own layout for mixed-radix schedules, the one above otherwise
+    static constexpr int xper(int X) { return S::MIXED ? S::xp(X) : PER; }
+    static constexpr int xadd(int X) { return S::MIXED ? S::xa(X) : (PER ? 1 : 0); }
+    static constexpr int xls(int X) { return (COLMAP || !S::MIXED || S::xls(X) < 0) ? LS : S::xls(X); }
+    static constexpr int xls_max(int X) { return X < 0 ? LS : (xls(X) > xls_max(X - 1) ? xls(X) : xls_max(X - 1)); }
+    template <int X> static B2_HD int physx(int o) {
+        constexpr int P = xper(X), A = xadd(X), PD = P > 0 ? P : 1;
+        if (COLMAP || P == 0) return o;
+        if (A == 1) return b2_pad<P>(o);
+        if ((P & (P - 1)) == 0) return o + (o >> b2_ilog2(PD)) * A;
+        return o + (int)((unsigned)o / (unsigned)PD) * A;
+    }
+    template <int X, int STEP, int SPAN> static B2_HD int physx_k(int o, int po, int k) {
+        constexpr int P = xper(X), A = xadd(X), PD = P > 0 ? P : 1;
+        if (COLMAP || P == 0) return o + k * STEP;
+        if (STEP % PD == 0) return po + k * (STEP + STEP / PD * A);
+        if (SPAN > 0 && STEP * SPAN <= P && (PD % (STEP * (SPAN > 0 ? SPAN : 1))) == 0) return po + k * STEP;  // the run stays inside one period
+        return physx<X>(o + k * STEP);
+    }
+    static B2_HD size_t smem_bytes(int C) { return (size_t)C * xls_max(S::NP - 2) * sizeof(cpx_t); }
 
     // thread -> (line c, slot t).  Every thread of the CTA owns a slot: a chained launch, whose
     // CTAs have the thread count of the widest step, retires its surplus warps before it gets here
@@ -193,8 +242,9 @@ template <int N, int E, int MODE, int EPI, class SCHED = TileSched<N, E>> struct
     template <int P> static B2_D void butterflies(const TileCtx &x, cpx_t *v, int c, int t, bool active) {
         constexpr int R = S::radix(P), NS = S::ns(P), NB = E / R;
         constexpr bool LAST = (P == S::NP - 1);
+        constexpr int X = LAST ? 0 : P;  // the exchange this pass writes (none after the last pass)
         const cpx_t *tw = x.p->tw;
-        cpx_t *line = x.sm + (size_t)c * LS;
+        cpx_t *line = x.sm + (size_t)c * xls(X);
 #pragma unroll
         for (int m = 0; m < NB; ++m) {
             const int j = t + m * T;
@@ -214,9 +264,12 @@ template <int N, int E, int MODE, int EPI, class SCHED = TileSched<N, E>> struct
                 for (int k = 0; k < R; ++k) v[m + k * NB] = a[k];
             } else if (active) {
                 const int o = (j - jm) * R + jm;  // (j / NS) * NS * R + jm
-                const int po = phys(o);
+                const int po = physx<X>(o);
+                // (mixed radix: the R points of a butterfly lie inside one block of NS*R, so a period that is a multiple
+                // of NS*R leaves their offsets immediate)
 #pragma unroll
-                for (int k = 0; k < R; ++k) line[NS == 1 ? phys_k<1, R>(o, po, k) : phys_k<NS, 0>(o, po, k)] = a[k];
+                for (int k = 0; k < R; ++k)
+                    line[NS == 1 ? physx_k<X, 1, R>(o, po, k) : physx_k<X, NS, (S::MIXED ? R : 0)>(o, po, k)] = a[k];
             }
         }
     }
@@ -230,10 +283,10 @@ template <int N, int E, int MODE, int EPI, class SCHED = TileSched<N, E>> struct
             cpx_t *v = B2_TREGS(x);
             int c, t;
             if (map(tid, x.p->C, x.p->lgC, c, t)) {
-                const cpx_t *line = x.sm + (size_t)c * LS;
-                const int pt = phys(t);
+                const cpx_t *line = x.sm + (size_t)c * xls(P - 1);
+                const int pt = physx<P - 1>(t);
 #pragma unroll
-                for (int q = 0; q < E; ++q) v[q] = line[phys_k<T, 0>(t, pt, q)];
+                for (int q = 0; q < E; ++q) v[q] = line[physx_k<P - 1, T, 0>(t, pt, q)];
             }
         }
         if (P < S::NP - 1) B2_SYNC();  // the next write must not overtake a neighbour's read
