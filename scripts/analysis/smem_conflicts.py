@@ -256,6 +256,11 @@ def search_cost(N, E, radices, C, esz):
     return out
 
 
+# searched layouts that measured SLOWER than the default rule on B200 (profiles/r2_mix_probe.md: the cost model overrates the
+# price of a recomputed address for these): (element size, N, E) keep the default
+KEEP_DEFAULT = {(8, 1536, 24), (8, 200, 20), (8, 500, 10), (8, 729, 9), (8, 2187, 9), (8, 1080, 30),
+                (16, 1536, 24), (16, 4000, 20), (16, 500, 10), (16, 625, 5)}
+
 ALL_ROW_SHAPES = SCHEDULES + [(5000, 10, 1, (10, 10, 10, 5)), (6561, 9, 1, (9, 9, 9, 9)), (625, 25, 10, (5, 5, 5, 5)), (3125, 5, 1, (5, 5, 5, 5, 5))]
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "emit":
@@ -276,7 +281,9 @@ if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "emit":
             cost_new = sum(b[0][0] for b in res)
             conf_new = sum(b[4] + b[5] for b in res)
             body = ", ".join("{%d, %d, %d}" % (b[1], b[2], b[3]) for b in res)
-            if cost_new < cost_cur:
+            if (esz, N, E) in KEEP_DEFAULT:
+                lines.append(f"// {N} E={E}: the default layout stays (the searched one measured slower on B200, profiles/r2_mix_probe.md): B2_MIX_LAYOUT({N}, {E}, {len(res)}, {body})")
+            elif cost_new < cost_cur:
                 lines.append(f"B2_MIX_LAYOUT({N}, {E}, {len(res)}, {body})  // bank conflicts per CTA {conf_cur} -> {conf_new} (cost {cost_cur:.0f} -> {cost_new:.0f})")
             else:
                 lines.append(f"// {N} E={E}: the default layout stays (conflicts per CTA {conf_cur}, cost {cost_cur:.0f}; best found {cost_new:.0f})")
