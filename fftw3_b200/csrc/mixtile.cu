@@ -87,6 +87,11 @@ struct MixInst {
     MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_COL, 1, CCOL>::entry(#__VA_ARGS__),     \
     MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_ROW2COL, 0, CCOL>::entry(#__VA_ARGS__),
 
+// r2c / c2r rows of 2N reals: the N-point row kernel with the Hermitian split on the way out (EPI 3) / merge on the way in
+// (EPI 4) -- tile_kernel.cuh r2c_row_exit / c2r_row_enter pair k with N-k inside the line's shared memory; E must be even
+#define B2_MIX_REAL(N, E, CROW, ...)                                                       \
+    MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_ROW, 3, CROW>::entry(#__VA_ARGS__),     \
+    MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE_ROW, 4, CROW>::entry(#__VA_ARGS__),
 #define B2_MIX_ONE(N, E, MODE, EPI, C, ...) MixInst<MixSched<N, E, __VA_ARGS__>, N, E, MODE, EPI, C>::entry(#__VA_ARGS__),
 // the three column forms alone (a length may be listed with several shapes: the selector takes the FIRST row of the
 // table that fits, FFTW_B200_MIX_ALT=1 the last)
@@ -153,6 +158,27 @@ const TileEntry *mix_entries(int *count) {
         B2_MIX_ROW(5000, 10, 1, 10, 10, 10, 5)
         B2_MIX_ROW(6144, 24, 1, 12, 8, 8, 8)
         B2_MIX_ROW(6561, 27, 1, 9, 9, 9, 9)
+#endif
+        // real transforms of 2N points on the N-point row shapes with an even E (same shape as the complex row form)
+        B2_MIX_REAL(96, 24, 64, 12, 8)
+        B2_MIX_REAL(192, 24, 32, 24, 8)
+        B2_MIX_REAL(384, 24, 16, 8, 8, 6)
+        B2_MIX_REAL(768, 24, 8, 12, 8, 8)
+        B2_MIX_REAL(1536, 24, 4, 24, 8, 8)
+        B2_MIX_REAL(3072, 24, 2, 8, 8, 8, 6)
+        B2_MIX_REAL(100, 10, 24, 10, 10)
+        B2_MIX_REAL(200, 20, 24, 20, 10)
+        B2_MIX_REAL(250, 10, 10, 10, 5, 5)
+        B2_MIX_REAL(400, 20, 12, 20, 20)
+        B2_MIX_REAL(500, 10, 5, 10, 10, 5)
+        B2_MIX_REAL(1000, 10, 2, 10, 10, 10)
+        B2_MIX_REAL(2000, 20, 2, 20, 10, 10)
+        B2_MIX_REAL(3000, 30, 2, 30, 10, 10)
+        B2_MIX_REAL(4000, 20, 1, 20, 20, 10)
+        B2_MIX_REAL(1080, 30, 7, 30, 6, 6)
+#if defined(FFTW_SINGLE)
+        B2_MIX_REAL(5000, 20, 1, 10, 10, 10, 5)
+        B2_MIX_REAL(6144, 24, 1, 12, 8, 8, 8)
         // shapes that measured equal or slower than the ones above (kept selectable with FFTW_B200_MIX_ALT=1, which
         // takes the LAST row listed for a length and form: scripts/gpu_mix_alt_probe.py, gpu_mix_form_probe.py)
         B2_MIX_COLS(500, 20, 16, 10, 10, 5)

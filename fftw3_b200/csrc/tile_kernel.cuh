@@ -409,7 +409,7 @@ template <int N, int E, int MODE, int EPI, class SCHED = TileSched<N, E>> struct
                 for (int q = 0; q < HQ; ++q) {
                     const int k = t + q * T;
                     zk[q] = line[phys(k)];
-                    zc[q] = cconj(line[phys((N - k) & (N - 1))]);
+                    zc[q] = cconj(line[phys((N & (N - 1)) == 0 ? ((N - k) & (N - 1)) : (k ? N - k : 0))]);
                     w[q] = p.twr[k];
                 }
 #pragma unroll

@@ -908,3 +908,49 @@ def check_mixed_radix_second_shapes(lib, n, cols):
         check_mixed_radix(lib, n, cols, seed=3)
     finally:
         os.environ.pop("FFTW_B200_MIX_ALT", None)
+
+
+# lengths N whose row shape has an even E: r2c / c2r of 2N reals run on the mixed-radix kernel with the Hermitian split / merge fused
+MIX_REAL_HALF = [96, 192, 384, 768, 1536, 3072, 100, 200, 250, 400, 500, 1000, 2000, 3000, 4000, 1080]
+MIX_REAL_HALF_FP32_ONLY = [5000, 6144]
+
+
+def check_mixed_radix_real(lib, N, seed=0):
+    """r2c / c2r rows of n = 2N reals for N with a mixed-radix row kernel (csrc/mixtile.cu B2_MIX_REAL): ragged batch, out of
+    place and in place (padded rows), and as the last axis of a 2-D real transform; against numpy fp64.  Reference: rdft2 via
+    hc2c (ct_hc2c_direct_apply fftw/fftw_api.c:5831-5845)."""
+    rng = np.random.default_rng(seed + N)
+    n = 2 * N
+    hm = 37 if N <= 512 else (7 if N <= 2048 else 3)
+    x = rand_r(rng, (hm, n), lib)
+    X = np.zeros((hm, N + 1), dtype=lib.cplx)
+    p = lib.plan_many_dft_r2c([n], hm, x, None, 1, n, X, None, 1, N + 1)
+    assert p
+    txt = lib.sprint_plan(p)
+    assert "mixed radix" in txt and "r2c" in txt, txt
+    lib.execute(p)
+    lib.destroy_plan(p)
+    ref = np.fft.rfft(x.astype(np.float64), axis=1)
+    assert rel_l2(X, ref) < tol(lib, n), (N, "r2c")
+    y = np.zeros_like(x)
+    Xc = X.copy()
+    p = lib.plan_many_dft_c2r([n], hm, Xc, None, 1, N + 1, y, None, 1, n)
+    assert p
+    txt = lib.sprint_plan(p)
+    assert "mixed radix" in txt and "c2r" in txt, txt
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(y, n * x.astype(np.float64)) < 2 * tol(lib, n), (N, "c2r")
+    # in place, rows padded to 2(N+1) reals
+    buf = np.zeros((hm, 2 * (N + 1)), dtype=lib.real)
+    buf[:, :n] = x
+    p = lib.plan_many_dft_r2c([n], hm, buf, None, 1, 2 * (N + 1), buf, None, 1, N + 1)
+    assert p
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(buf.view(lib.cplx), ref) < tol(lib, n), (N, "r2c in place")
+    # last axis of a 2-D real transform
+    if N <= 1536:
+        x2 = rand_r(rng, (12, n), lib)
+        Y = lib.r2c(x2)
+        assert rel_l2(Y, np.fft.rfft2(x2.astype(np.float64))) < tol(lib, x2.size), (N, "2-D r2c")

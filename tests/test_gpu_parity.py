@@ -101,6 +101,13 @@ def test_mixed_radix_second_shapes(lib, n, cols):
     cases.check_mixed_radix_second_shapes(lib, n, cols)
 
 
+@pytest.mark.parametrize("N", cases.MIX_REAL_HALF + cases.MIX_REAL_HALF_FP32_ONLY)
+def test_mixed_radix_real_rows(lib, N):
+    if not lib.single and N in cases.MIX_REAL_HALF_FP32_ONLY:
+        pytest.skip("beyond the fp64 row cap")
+    cases.check_mixed_radix_real(lib, N)
+
+
 def test_mixed_radix_long_lengths(lib):
     cases.check_mixed_radix_long(lib)
 
