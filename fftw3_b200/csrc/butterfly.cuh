@@ -234,6 +234,9 @@ template <typename T> struct Bf<15, T> : BfPFA<5, 3, T> {};
 template <typename T> struct Bf<20, T> : BfPFA<4, 5, T> {};
 template <typename T> struct Bf<24, T> : BfPFA<8, 3, T> {};
 template <typename T> struct Bf<30, T> : BfPFA<5, 6, T> {};
+template <typename T> struct Bf<14, T> : BfPFA<7, 2, T> {};
+template <typename T> struct Bf<21, T> : BfPFA<7, 3, T> {};
+template <typename T> struct Bf<28, T> : BfPFA<7, 4, T> {};
 
 // 9 = 3 x 3 (Cooley-Tukey: x[3 j1 + j2] -> three radix-3 butterflies over j1, twiddles w9^(j2 k1), three over
 // j2 -> X[k1 + 3 k2]).  Reference codelet: n1_9.

@@ -221,6 +221,8 @@ inline const std::vector<TileEntry> &b2_tile_table() {
         int nmix = 0;
         const TileEntry *mix = b2::mix_entries(&nmix);  // lengths that are not powers of two (mixtile.cu)
         t.insert(t.end(), mix, mix + nmix);
+        mix = b2::mix_entries_more(&nmix);
+        t.insert(t.end(), mix, mix + nmix);
         return t;
     }();
 #undef B2_X_ENTRY

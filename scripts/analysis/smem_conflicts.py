@@ -290,3 +290,51 @@ if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "emit":
             print(lines[-1], file=sys.stderr, flush=True)
     lines.append("#endif")
     print("\n".join(lines))
+
+
+MORE_ROW_SHAPES = [  # csrc/mixtile2.cu (not individually measured on the GPU)
+    (144, 12, 21, (12, 12)), (288, 24, 21, (24, 12)), (576, 24, 10, (24, 24)), (1152, 24, 5, (24, 8, 6)), (2304, 24, 2, (24, 12, 8)),
+    (4608, 24, 1, (24, 24, 8)), (1296, 12, 2, (6, 6, 6, 6)), (1728, 24, 3, (12, 12, 12)), (216, 12, 14, (6, 6, 6)), (432, 24, 14, (24, 6, 3)),
+    (864, 24, 7, (24, 12, 3)), (320, 20, 16, (20, 4, 4)), (640, 20, 8, (20, 4, 4, 2)), (1280, 20, 4, (20, 4, 4, 4)), (800, 20, 6, (20, 10, 4)),
+    (1600, 20, 3, (20, 20, 4)), (3200, 20, 1, (20, 20, 4, 2)), (8000, 20, 1, (20, 20, 20)), (162, 18, 28, (6, 9, 3)), (486, 18, 9, (6, 9, 9)),
+    (1458, 18, 3, (6, 9, 9, 3)), (150, 30, 50, (30, 5)), (300, 30, 25, (30, 10)), (450, 30, 17, (30, 15)), (600, 30, 12, (10, 10, 6)),
+    (750, 30, 10, (30, 5, 5)), (900, 30, 8, (30, 30)), (1500, 30, 5, (30, 10, 5)), (1800, 30, 4, (30, 10, 6)), (2700, 30, 2, (30, 30, 3)),
+    (4500, 30, 1, (30, 30, 5)), (6000, 30, 1, (30, 10, 10, 2)), (7500, 30, 1, (30, 10, 5, 5)), (1250, 10, 2, (10, 5, 5, 5)), (2500, 10, 1, (10, 10, 5, 5)),
+    (6250, 10, 1, (10, 5, 5, 5, 5)), (360, 30, 21, (6, 6, 10)), (540, 30, 14, (30, 6, 3)), (720, 30, 10, (6, 6, 10, 2)), (196, 14, 18, (14, 14)),
+    (392, 14, 9, (14, 14, 2)), (686, 14, 5, (14, 7, 7)), (1372, 14, 2, (14, 14, 7)), (2744, 14, 1, (14, 14, 14)), (448, 28, 16, (28, 4, 4)),
+    (896, 28, 8, (28, 4, 4, 2)), (1792, 28, 4, (28, 4, 4, 4)), (441, 21, 12, (21, 21)), (121, 11, 23, (11, 11)), (1331, 11, 2, (11, 11, 11)),
+    (169, 13, 19, (13, 13)), (2197, 13, 1, (13, 13, 13)),
+]
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "emit_more":
+    # Unmeasured shapes: a searched layout is adopted only where the measured first list says it pays -- the default rule
+    # has at least 1.2 conflicts per request and the search removes at least 60 % of them.
+    fp32_only = {4608, 8000, 4500, 6000, 7500, 6250}
+    lines = []
+    for esz, guard in ((8, "#if defined(FFTW_SINGLE)"), (16, "#else")):
+        lines.append(guard)
+        for N, E, C, rad in MORE_ROW_SHAPES:
+            if esz == 16 and N in fp32_only:
+                continue
+            cur = current_per(rad)
+            conf_cur = req = 0
+            LS0 = N if cur == 0 else N + N // cur
+            warps = (C * (N // E) + 31) // 32
+            for X in range(len(rad) - 1):
+                sc, lc = exchange_conflicts(N, E, rad, C, X, cur, 1 if cur else 0, LS0, esz)
+                conf_cur += sc + lc
+                req += 2 * E * warps
+            if conf_cur < 1.2 * req:
+                lines.append(f"// {N} E={E}: the default layout stays ({conf_cur} conflicts on {req} requests per CTA)")
+            else:
+                res = search_cost(N, E, rad, C, esz)
+                conf_new = sum(b[4] + b[5] for b in res)
+                body = ", ".join("{%d, %d, %d}" % (b[1], b[2], b[3]) for b in res)
+                if conf_new <= 0.4 * conf_cur:
+                    lines.append(f"B2_MIX_LAYOUT({N}, {E}, {len(res)}, {body})  // bank conflicts per CTA {conf_cur} -> {conf_new} on {req} requests")
+                else:
+                    lines.append(f"// {N} E={E}: the default layout stays ({conf_cur} conflicts on {req} requests per CTA; best found {conf_new})")
+            print(lines[-1], file=sys.stderr, flush=True)
+    lines.append("#endif")
+    print("\n".join(lines))

@@ -141,6 +141,18 @@ def test_mixed_radix_real_rows(lib, N):
     cases.check_mixed_radix_real(lib, N)
 
 
+@pytest.mark.parametrize("n,cols", cases.MIX_MORE + cases.MIX_MORE_FP32_ONLY, ids=lambda v: str(v))
+def test_mixed_radix_second_list(lib, n, cols):
+    if not lib.single and (n, cols) in cases.MIX_MORE_FP32_ONLY:
+        pytest.skip("beyond the fp64 row cap")
+    cases.check_mixed_radix(lib, n, cols)
+
+
+@pytest.mark.parametrize("N", cases.MIX_MORE_REAL_HALF)
+def test_mixed_radix_second_list_real_rows(lib, N):
+    cases.check_mixed_radix_real(lib, N)
+
+
 def test_mixed_radix_long_lengths(lib):
     cases.check_mixed_radix_long(lib)
 
