@@ -35,7 +35,7 @@ struct MixInst {
     typedef TileFFT<N, E, MODE, EPI, S> F;
     static constexpr int THREADS = C * (N / E);
     // registers a thread should get: its E points plus a butterfly's temporaries and addressing
-    static constexpr int NEED = (2 * E * (int)(sizeof(real_t) / 4) + (sizeof(real_t) == 4 ? 40 : 56) + 7) / 8 * 8;
+    static constexpr int NEED = (2 * E * (int)(sizeof(real_t) / 4) + (E >= 40 ? 112 : sizeof(real_t) == 4 ? 40 : 56) + 7) / 8 * 8;
     static constexpr int TW = (THREADS + 31) / 32 * 32;
     static constexpr int MINB0 = 65536 / (TW * NEED);
     static constexpr int MINB = MINB0 < 1 ? 1 : MINB0 > 8 ? 8 : MINB0;

@@ -338,3 +338,35 @@ if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "emit_more":
             print(lines[-1], file=sys.stderr, flush=True)
     lines.append("#endif")
     print("\n".join(lines))
+
+
+E60_ROW_SHAPES = [  # csrc/mixtile2.cu, fp32 only
+    (240, 60, 32, (20, 12)), (480, 60, 16, (30, 4, 4)), (960, 60, 8, (20, 12, 4)), (1920, 60, 4, (30, 4, 4, 4)), (3840, 60, 2, (20, 12, 4, 4)),
+    (1200, 60, 6, (30, 10, 4)), (2400, 60, 3, (30, 20, 4)), (1440, 60, 5, (30, 12, 4)), (2880, 60, 2, (20, 12, 12)), (3600, 60, 2, (30, 30, 4)),
+    (4800, 60, 1, (30, 10, 4, 4)), (5760, 60, 1, (20, 12, 12, 2)), (7200, 60, 1, (30, 20, 12)), (7680, 60, 1, (20, 12, 4, 4, 2)),
+]
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "emit_e60":
+    lines = ["#if defined(FFTW_SINGLE)"]
+    for N, E, C, rad in E60_ROW_SHAPES:
+        cur = current_per(rad)
+        conf_cur = req = 0
+        LS0 = N if cur == 0 else N + N // cur
+        warps = (C * (N // E) + 31) // 32
+        for X in range(len(rad) - 1):
+            sc, lc = exchange_conflicts(N, E, rad, C, X, cur, 1 if cur else 0, LS0, 8)
+            conf_cur += sc + lc
+            req += 2 * E * warps
+        if conf_cur < 1.2 * req:
+            lines.append(f"// {N} E={E}: the default layout stays ({conf_cur} conflicts on {req} requests per CTA)")
+        else:
+            res = search_cost(N, E, rad, C, 8)
+            conf_new = sum(b[4] + b[5] for b in res)
+            body = ", ".join("{%d, %d, %d}" % (b[1], b[2], b[3]) for b in res)
+            if conf_new <= 0.4 * conf_cur:
+                lines.append(f"B2_MIX_LAYOUT({N}, {E}, {len(res)}, {body})  // bank conflicts per CTA {conf_cur} -> {conf_new} on {req} requests")
+            else:
+                lines.append(f"// {N} E={E}: the default layout stays ({conf_cur} conflicts on {req} requests per CTA; best found {conf_new})")
+        print(lines[-1], file=sys.stderr, flush=True)
+    lines.append("#endif")
+    print("\n".join(lines))

@@ -960,3 +960,6 @@ def check_mixed_radix_real(lib, N, seed=0):
 MIX_MORE = [(144, False), (288, False), (576, False), (1152, False), (2304, False), (1296, False), (1728, False), (216, False), (432, False), (864, False), (320, False), (640, False), (1280, False), (800, False), (1600, False), (3200, False), (162, False), (486, False), (1458, False), (150, False), (300, False), (450, False), (600, False), (750, False), (900, False), (1500, False), (1800, False), (2700, False), (1250, False), (2500, False), (360, False), (540, False), (720, False), (196, False), (392, False), (686, False), (1372, False), (2744, False), (448, False), (896, False), (1792, False), (441, False), (121, False), (1331, False), (169, False), (2197, False)]
 MIX_MORE_FP32_ONLY = [(4608, False), (8000, False), (4500, False), (6000, False), (7500, False), (6250, False)]
 MIX_MORE_REAL_HALF = [144, 288, 576, 1152, 2304, 1296, 1728, 216, 432, 864, 320, 640, 1280, 800, 1600, 3200, 300, 600, 900, 1500, 1800, 1250, 2500, 360, 720]
+
+# 60 points per thread, fp32 library only (csrc/mixtile2.cu): video widths and multiples of 240; complex rows and r2c / c2r rows
+MIX_E60 = [240, 480, 960, 1920, 3840, 1200, 2400, 1440, 2880, 3600, 4800, 5760, 7200, 7680]

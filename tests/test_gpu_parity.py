@@ -120,6 +120,15 @@ def test_mixed_radix_second_list_real_rows(lib, N):
     cases.check_mixed_radix_real(lib, N)
 
 
+@pytest.mark.parametrize("n", cases.MIX_E60)
+def test_mixed_radix_sixty_points_per_thread(lib, n):
+    if not lib.single:
+        pytest.skip("60 points per thread do not fit the register file in double precision")
+    cases.check_mixed_radix(lib, n, False)
+    if 2 * n <= 8192 * 2:
+        cases.check_mixed_radix_real(lib, n)
+
+
 def test_mixed_radix_long_lengths(lib):
     cases.check_mixed_radix_long(lib)
 
