@@ -22,7 +22,7 @@ LIBDIR = os.path.join(HERE, "lib")
 EMUDIR = os.path.join(ROOT, "tests", "_emu")
 OBJDIR = os.path.join(HERE, "lib", "_obj")
 
-CU_SOURCES = ["engine.cu", "mixtile.cu", "mixtile2.cu", "slab.cu", "split.cu", "r2r.cu", "noalloc.cu"]
+CU_SOURCES = ["engine.cu", "mixtile.cu", "mixtile2.cu", "mixtile3.cu", "slab.cu", "split.cu", "r2r.cu", "noalloc.cu"]
 C_SOURCES = ["fftw_api.c", "fftw_mpi_api.c"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 

@@ -223,6 +223,8 @@ inline const std::vector<TileEntry> &b2_tile_table() {
         t.insert(t.end(), mix, mix + nmix);
         mix = b2::mix_entries_more(&nmix);
         t.insert(t.end(), mix, mix + nmix);
+        mix = b2::mix_entries_cols(&nmix);
+        t.insert(t.end(), mix, mix + nmix);
         return t;
     }();
 #undef B2_X_ENTRY

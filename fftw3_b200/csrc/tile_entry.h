@@ -19,4 +19,5 @@ struct TileEntry {
 namespace b2 {
 const TileEntry *mix_entries(int *count);       // the mixed-radix rows (mixtile.cu)
 const TileEntry *mix_entries_more(int *count);  // ... and mixtile2.cu
+const TileEntry *mix_entries_cols(int *count);  // ... and mixtile3.cu
 }

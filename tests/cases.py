@@ -963,3 +963,49 @@ MIX_MORE_REAL_HALF = [144, 288, 576, 1152, 2304, 1296, 1728, 216, 432, 864, 320,
 
 # 60 points per thread, fp32 library only (csrc/mixtile2.cu): video widths and multiples of 240; complex rows and r2c / c2r rows
 MIX_E60 = [240, 480, 960, 1920, 3840, 1200, 2400, 1440, 2880, 3600, 4800, 5760, 7200, 7680]
+
+# second-list lengths with column forms (csrc/mixtile3.cu); in double precision only those within the column cap of 1024
+MIX_MORE_COLS = [144, 288, 576, 1152, 320, 640, 1280, 800, 1600, 300, 600, 900, 1500, 1800, 360, 720, 1080, 216, 432, 864, 1296, 1728]
+
+
+def check_mixed_radix_frames(lib):
+    """N-D transforms whose axes all have mixed-radix kernels: rows on the row form, the other axes on the column forms
+    (a 1080 x 1920 frame in single precision, a 144 x 96 x 100 box, a 720 x 1280 real frame), and long 1-D products of the
+    third list's lengths."""
+    import os
+    rng = np.random.default_rng(9)
+    shapes = [(144, 96, 100), (360, 600)] + ([(1080, 1920)] if lib.single else [(720, 1000)])
+    for shape in shapes:
+        x = rand_c(rng, shape, lib)
+        y = np.zeros_like(x)
+        p = lib.plan_dft(list(shape), x, y, capi.FFTW_FORWARD)
+        assert p
+        txt = lib.sprint_plan(p)
+        passes = [l for l in txt.split("\n") if l.strip().startswith("pass ")]
+        assert len(passes) == len(shape) and all("mixed radix" in l for l in passes), txt
+        lib.execute(p)
+        lib.destroy_plan(p)
+        assert rel_l2(y, np.fft.fftn(x.astype(np.complex128))) < tol(lib, x.size), shape
+    # real frame: r2c rows of 1280 reals (N = 640), then 720-point columns over the 641 half-spectrum columns
+    xr = rand_r(rng, (720, 1280), lib)
+    Y = lib.r2c(xr)
+    assert rel_l2(Y, np.fft.rfft2(xr.astype(np.float64))) < tol(lib, xr.size)
+    old = os.environ.get("FFTW_B200_ROW_CAP")
+    os.environ["FFTW_B200_ROW_CAP"] = "1024"
+    try:
+        for n in (144 * 144, 720 * 720, 600 * 360):
+            x = rand_c(rng, (2, n), lib)
+            y = np.zeros_like(x)
+            p = lib.plan_many_dft([n], 2, x, None, 1, n, y, None, 1, n, capi.FFTW_BACKWARD)
+            assert p
+            txt = lib.sprint_plan(p)
+            passes = [l for l in txt.split("\n") if l.strip().startswith("pass ")]
+            assert len(passes) == 2 and all("mixed radix" in l for l in passes), txt
+            lib.execute(p)
+            lib.destroy_plan(p)
+            assert rel_l2(y, n * np.fft.ifft(x.astype(np.complex128), axis=1)) < tol(lib, n), n
+    finally:
+        if old is None:
+            os.environ.pop("FFTW_B200_ROW_CAP", None)
+        else:
+            os.environ["FFTW_B200_ROW_CAP"] = old

@@ -129,6 +129,15 @@ def test_mixed_radix_sixty_points_per_thread(lib, n):
         cases.check_mixed_radix_real(lib, n)
 
 
+@pytest.mark.parametrize("n", cases.MIX_MORE_COLS)
+def test_mixed_radix_third_list_column_forms(lib, n):
+    cases.check_mixed_radix(lib, n, True)
+
+
+def test_mixed_radix_frames_and_boxes(lib):
+    cases.check_mixed_radix_frames(lib)
+
+
 def test_mixed_radix_long_lengths(lib):
     cases.check_mixed_radix_long(lib)
 
