@@ -1,4 +1,5 @@
-// csrc/tile_kernel.cuh -- specialised tile kernels for power-of-two lengths: the hot path.
+// csrc/tile_kernel.cuh -- specialised tile kernels: the hot path.  Instantiated for power-of-two lengths with TileSched
+// (tile_dispatch.cuh) and for 95 other smooth lengths with mixed-radix schedules (MixSched; mixtile*.cu).
 //
 // One CTA transforms a tile of C lines of N points.  Each thread keeps E points of one line
 // in registers across ALL radix passes (compile-time schedule, radices <= E); between passes
