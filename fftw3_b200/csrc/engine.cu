@@ -266,6 +266,7 @@ static void init_kernel_attrs() {
     if (d >= 0 && d < 64 && done[d]) return;
     cudaFuncSetAttribute(b2_generic_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem_optin());
     b2_init_tile_kernels();
+    cudaGetLastError();  // an attribute a device refuses shows up as that kernel's launch error, not as the next execute's
     if (d >= 0 && d < 64) done[d] = true;
 }
 #endif
