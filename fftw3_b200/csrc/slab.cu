@@ -576,6 +576,26 @@ extern "C" b2fft_plan *b2fft_slab_plan_many_rdft_3d(int kind, ptrdiff_t n0, ptrd
     }
     return slab_plan_create(kind, n0, n1, n2, howmany, c, kind == B2FFT_R2C ? -1 : +1, transposed_in, transposed_out);
 }
+// the same with explicit block sizes: block0 over n0 (the dimension the REAL array is distributed over), block1 over n1 (the
+// dimension the transposed complex array is distributed over); 0 = default (fftw_mpi_plan_many_dft_r2c / _c2r iblock / oblock,
+// reference fftw/mpi/api.c:790-858)
+extern "C" b2fft_plan *b2fft_slab_plan_many_rdft_3d_blocks(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2,
+                                                           ptrdiff_t howmany, ptrdiff_t block0, ptrdiff_t block1,
+                                                           b2fft_comm *c, int transposed_in, int transposed_out,
+                                                           unsigned flags) {
+    (void)flags;
+    if (kind != B2FFT_R2C && kind != B2FFT_C2R) return nullptr;
+    if ((kind == B2FFT_R2C && transposed_in) || (kind == B2FFT_C2R && transposed_out)) {
+        set_error("slab real transform: a transposed REAL array is not supported");
+        return nullptr;
+    }
+    if (block0 < 0 || block1 < 0) {
+        set_error("slab real transform: negative block size");
+        return nullptr;
+    }
+    return slab_plan_create(kind, n0, n1, n2, howmany, c, kind == B2FFT_R2C ? -1 : +1, transposed_in, transposed_out, block0,
+                            block1);
+}
 extern "C" b2fft_plan *b2fft_slab_plan_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, b2fft_comm *c,
                                                int transposed_in, int transposed_out, unsigned flags) {
     (void)flags;

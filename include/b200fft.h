@@ -155,6 +155,12 @@ b2fft_plan *b2fft_slab_plan_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdif
 /* the same with `howmany` interleaved transforms (tuples of howmany reals / complex per element) */
 b2fft_plan *b2fft_slab_plan_many_rdft_3d(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
                                          b2fft_comm *c, int transposed_in, int transposed_out, unsigned flags);
+/* ... and with explicit block sizes: block0 over n0 (the distribution of the REAL array and of a natural complex array), block1
+ * over n1 (the distribution of the TRANSPOSED complex array); 0 = default.  Replaces the iblock / oblock arguments of
+ * fftw_mpi_plan_many_dft_r2c / _c2r (reference fftw/mpi/api.c:790-858). */
+b2fft_plan *b2fft_slab_plan_many_rdft_3d_blocks(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
+                                                ptrdiff_t block0, ptrdiff_t block1, b2fft_comm *c, int transposed_in,
+                                                int transposed_out, unsigned flags);
 /* 2-D real data (fftw_mpi_plan_dft_r2c_2d / _c2r_2d): real [local_n0][2(n1/2+1)], complex [local_n0][n1/2+1] or,
  * transposed, [local_n1c][n0] with the n1/2+1 complex columns block-distributed. */
 b2fft_plan *b2fft_slab_plan_rdft_2d(int kind, ptrdiff_t n0, ptrdiff_t n1, b2fft_comm *c, int transposed_in,

@@ -809,3 +809,146 @@ def test_two_processes_over_gloo():
         assert not isinstance(err, str), err
         assert err < 1e-13
         assert tmax == 2.0
+
+
+def _many_real_api(lib):
+    L = lib.lib
+    for nm in ("fftw_mpi_plan_many_dft_r2c", "fftw_mpi_plan_many_dft_c2r"):
+        f = getattr(L, nm)
+        f.restype = C.c_void_p
+        f.argtypes = [C.c_int, C.POINTER(C.c_ssize_t), C.c_ssize_t, C.c_ssize_t, C.c_ssize_t, C.c_void_p, C.c_void_p,
+                      C.c_void_p, C.c_uint]
+    L.fftw_mpi_local_size_many_transposed.restype = C.c_ssize_t
+    L.fftw_mpi_local_size_many_transposed.argtypes = [C.c_int, C.POINTER(C.c_ssize_t), C.c_ssize_t, C.c_ssize_t,
+                                                      C.c_ssize_t, C.c_void_p] + [C.POINTER(C.c_ssize_t)] * 4
+    return L
+
+
+def _block_sizes(L, shape_c, b_n0, b_n1, comm):
+    v = [C.c_ssize_t() for _ in range(4)]
+    nn = (C.c_ssize_t * 3)(*shape_c)
+    N = L.fftw_mpi_local_size_many_transposed(3, nn, 1, b_n0, b_n1, comm, *[C.byref(t) for t in v])
+    return (N,) + tuple(t.value for t in v)
+
+
+@pytest.mark.parametrize("transposed", [True, False], ids=["transposed_out", "natural_out"])
+@pytest.mark.parametrize("shape,P,b_n0,b_n1", [((10, 12, 6), 4, 4, 5), ((9, 32, 7), 3, 5, 16), ((8, 6, 10), 2, 6, 3)],
+                         ids=["10x12x6", "9x32x7", "8x6x10"])
+def test_real_to_complex_slab_with_explicit_block_sizes(shape, P, b_n0, b_n1, transposed):
+    """fftw_mpi_plan_many_dft_r2c with iblock / oblock other than ceil(n/P) (fftw/mpi/api.c:790-812: iblock over the input's
+    distributed dimension n0, oblock over the output's -- n1 with FFTW_MPI_TRANSPOSED_OUT, else n0 again): uneven and empty
+    ranks; a natural-output plan whose oblock differs from its iblock is refused (NULL)."""
+    lib = load()
+    L = _many_real_api(lib)
+    n0, n1, n2 = shape
+    n2c = n2 // 2 + 1
+    rng = np.random.default_rng(51 + P)
+    x = (rng.random(shape) - 0.5).astype(lib.real)
+    Y = orc.r2c(x)
+    nn = (C.c_ssize_t * 3)(*shape)
+    ranks = []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        # (natural output: the distribution over n1 in the middle of the plan is the plan's own business -- default blocks)
+        N, ln0, s0, ln1, s1 = _block_sizes(L, (n0, n1, n2c), b_n0, b_n1 if transposed else 0, comm)
+        assert ln0 == max(0, min(b_n0, n0 - pe * b_n0)) and (not transposed or ln1 == max(0, min(b_n1, n1 - pe * b_n1)))
+        xin = np.zeros(2 * max(N, 1), dtype=lib.real)
+        pad = np.zeros((ln0, n1, 2 * n2c), dtype=lib.real)
+        pad[:, :, :n2] = x[s0:s0 + ln0]
+        xin[:pad.size] = pad.ravel()
+        out = np.zeros(max(N, 1), dtype=lib.cplx)
+        plan = L.fftw_mpi_plan_many_dft_r2c(3, nn, 1, b_n0, b_n1 if transposed else b_n0, xin.ctypes.data, out.ctypes.data,
+                                            comm, capi.FFTW_ESTIMATE | (TRANSPOSED_OUT if transposed else 0))
+        assert plan, "slab r2c plan with explicit blocks is NULL"
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        ranks.append(dict(comm=comm, la=ln0, sa=s0, lb=ln1, sb=s1, xin=xin, out=out, plan=plan, bp=bp, S=S, R=R))
+    if not transposed:  # different blocks on the two sides of a natural-output plan cannot be served
+        assert not L.fftw_mpi_plan_many_dft_r2c(3, nn, 1, b_n0, b_n0 + 1, ranks[0]["xin"].ctypes.data,
+                                                ranks[0]["out"].ctypes.data, ranks[0]["comm"], capi.FFTW_ESTIMATE)
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 0, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    if "fused into" not in lib.sprint_plan(ranks[0]["plan"]):
+        _exchange(ranks, n0, n1, n2c)
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 2, r["xin"].ctypes.data, r["out"].ctypes.data) == 0
+    if not transposed:
+        for src in ranks:
+            if src["lb"] == 0:
+                continue
+            Rv = src["R"][:n0 * src["lb"] * n2c].reshape(n0, src["lb"], n2c)
+            for dst in ranks:
+                if dst["la"] == 0:
+                    continue
+                Ov = dst["out"][:dst["la"] * n1 * n2c].reshape(dst["la"], n1, n2c)
+                Ov[:, src["sb"]:src["sb"] + src["lb"], :] = Rv[dst["sa"]:dst["sa"] + dst["la"]]
+    for r in ranks:
+        ref = Y.transpose(1, 0, 2)[r["sb"]:r["sb"] + r["lb"]] if transposed else Y[r["sa"]:r["sa"] + r["la"]]
+        got = r["out"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+        lib.destroy_plan(r["plan"])
+        L.b2fft_comm_destroy(r["comm"])
+
+
+@pytest.mark.parametrize("tin", [True, False], ids=["transposed_in", "natural_in"])
+@pytest.mark.parametrize("shape,P,b_n0,b_n1", [((10, 12, 6), 4, 4, 5), ((9, 32, 7), 3, 5, 16), ((8, 6, 10), 2, 6, 3)],
+                         ids=["10x12x6", "9x32x7", "8x6x10"])
+def test_complex_to_real_slab_with_explicit_block_sizes(shape, P, b_n0, b_n1, tin):
+    """fftw_mpi_plan_many_dft_c2r with explicit blocks (fftw/mpi/api.c:814-836): iblock over the complex input's distributed
+    dimension (n1 with FFTW_MPI_TRANSPOSED_IN, else n0), oblock over n0 of the real output."""
+    lib = load()
+    L = _many_real_api(lib)
+    n0, n1, n2 = shape
+    n2c = n2 // 2 + 1
+    rng = np.random.default_rng(61 + P)
+    x = (rng.random(shape) - 0.5).astype(lib.real)
+    Y = orc.r2c(x)
+    YT = np.ascontiguousarray(Y.transpose(1, 0, 2))
+    nn = (C.c_ssize_t * 3)(*shape)
+    ranks = []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        N, ln0, s0, ln1, s1 = _block_sizes(L, (n0, n1, n2c), b_n0, b_n1 if tin else 0, comm)
+        cin = np.zeros(max(N, 1), dtype=lib.cplx)
+        if tin:
+            cin[:ln1 * n0 * n2c] = YT[s1:s1 + ln1].ravel()
+        else:
+            cin[:ln0 * n1 * n2c] = Y[s0:s0 + ln0].ravel()
+        out = np.zeros(2 * max(N, 1), dtype=lib.real)
+        plan = L.fftw_mpi_plan_many_dft_c2r(3, nn, 1, b_n1 if tin else b_n0, b_n0, cin.ctypes.data, out.ctypes.data, comm,
+                                            capi.FFTW_ESTIMATE | (TRANSPOSED_IN if tin else 0))
+        assert plan, "slab c2r plan with explicit blocks is NULL"
+        S, bp = buffer_view(lib, plan, 0, lib.cplx)
+        R, _ = buffer_view(lib, plan, 1, lib.cplx)
+        ranks.append(dict(comm=comm, la=ln0, sa=s0, lb=ln1, sb=s1, cin=cin, out=out, plan=plan, bp=bp, S=S, R=R))
+    if not tin:  # forward exchange of the natural input straight into the receive layout
+        for src in ranks:
+            if src["la"] == 0:
+                continue
+            Iv = src["cin"][:src["la"] * n1 * n2c].reshape(src["la"], n1, n2c)
+            for dst in ranks:
+                if dst["lb"] == 0:
+                    continue
+                Rv = dst["R"][:n0 * dst["lb"] * n2c].reshape(n0, dst["lb"], n2c)
+                Rv[src["sa"]:src["sa"] + src["la"]] = Iv[:, dst["sb"]:dst["sb"] + dst["lb"], :]
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 1, r["cin"].ctypes.data, r["out"].ctypes.data) == 0
+    for src in ranks:  # reverse exchange: receive layout -> [la][n1][n2c]
+        if src["lb"] == 0:
+            continue
+        Rv = src["R"][:n0 * src["lb"] * n2c].reshape(n0, src["lb"], n2c)
+        for dst in ranks:
+            if dst["la"] == 0:
+                continue
+            Sv = dst["S"][:dst["la"] * n1 * n2c].reshape(dst["la"], n1, n2c)
+            Sv[:, src["sb"]:src["sb"] + src["lb"], :] = Rv[dst["sa"]:dst["sa"] + dst["la"]]
+    for r in ranks:
+        assert L.b2fft_slab_stage(r["bp"], 3, r["cin"].ctypes.data, r["out"].ctypes.data) == 0
+    for r in ranks:
+        ref = x[r["sa"]:r["sa"] + r["la"]] * (n0 * n1 * n2)
+        got = r["out"][:r["la"] * n1 * 2 * n2c].reshape(r["la"], n1, 2 * n2c)[:, :, :n2]
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+        lib.destroy_plan(r["plan"])
+        L.b2fft_comm_destroy(r["comm"])
