@@ -146,6 +146,15 @@ class FFTW3Lib:
         d, h = arr(dims), arr(howmany_dims)
         return f(len(dims), C.cast(d, _vp), len(howmany_dims), C.cast(h, _vp), _ptr(inp), _ptr(out), sign, flags)
 
+    def plan_guru_real(self, kind, dims, howmany_dims, inp, out, flags=FFTW_ESTIMATE):
+        """fftw_plan_guru_dft_r2c / _c2r: dims / howmany_dims = lists of (n, is, os), strides in elements of the respective
+        array (reals on the real side, complex on the other); n of the last dim is the logical real length"""
+        f = self.lib.fftw_plan_guru_dft_r2c if kind == "r2c" else self.lib.fftw_plan_guru_dft_c2r
+        f.restype = _vp
+        f.argtypes = [C.c_int, _vp, C.c_int, _vp, _vp, _vp, C.c_uint]
+        d, h = self._iodims(dims), self._iodims(howmany_dims)
+        return f(len(dims), C.cast(d, _vp), len(howmany_dims), C.cast(h, _vp), _ptr(inp), _ptr(out), flags)
+
     def _iodims(self, ds):
         class IoDim(C.Structure):
             _fields_ = [("n", C.c_int), ("is_", C.c_int), ("os", C.c_int)]

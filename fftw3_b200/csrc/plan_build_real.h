@@ -142,44 +142,53 @@ inline bool build_real(PlanCore &pc) {
     const long long nl = T[L].n, hc = nl / 2 + 1;
     const long long ru = 1, cu = 2;                // reals per element of a real / complex array
     const long long iu = r2c ? ru : cu, ou = r2c ? cu : ru;
-    {   // extents: the last dim holds nl reals on the real side and hc complex on the other
-        long long ei = 1, eo = 1, di = 1, dn = 1;
+    {   // extents: the last dim holds nl reals on the real side and hc complex on the other.  Strides are signed (the
+        // pointer is element 0): hi / lo = how far the span reaches above / below it, in elements
+        long long hi_i = 0, lo_i = 0, hi_o = 0, lo_o = 0, di = 1, dn = 1;
+        auto reach = [](long long n, long long st, long long &hi, long long &lo) {
+            const long long r = (n - 1) * st;
+            (r >= 0 ? hi : lo) += r;
+        };
         for (int i = 0; i < g.rank; ++i) {
             long long ni = (i == L) ? (r2c ? nl : hc) : T[i].n;
             long long no = (i == L) ? (r2c ? hc : nl) : T[i].n;
-            ei += (ni - 1) * T[i].is;
-            eo += (no - 1) * T[i].os;
+            reach(ni, T[i].is, hi_i, lo_i);
+            reach(no, T[i].os, hi_o, lo_o);
             di *= ni;
             dn *= no;
         }
         bool zero = false;
         for (const GDim &d : V) {
-            if (d.n == 0) zero = true;
-            ei += (d.n - 1) * d.is;
-            eo += (d.n - 1) * d.os;
+            if (d.n == 0) {
+                zero = true;
+                continue;
+            }
+            reach(d.n, d.is, hi_i, lo_i);
+            reach(d.n, d.os, hi_o, lo_o);
             di *= d.n;
             dn *= d.n;
         }
-        pc.in_reals = zero ? 0 : ei * iu;
-        pc.out_reals = zero ? 0 : eo * ou;
-        pc.in_dense = di * iu;
-        pc.out_dense = dn * ou;
+        pc.in_reals = zero ? 0 : (hi_i - lo_i + 1) * iu;
+        pc.out_reals = zero ? 0 : (hi_o - lo_o + 1) * ou;
+        pc.in_off = zero ? 0 : -lo_i * iu;
+        pc.out_off = zero ? 0 : -lo_o * ou;
+        pc.neg = pc.in_off > 0 || pc.out_off > 0;
+        pc.in_dense = (zero ? 0 : di) * iu;
+        pc.out_dense = (zero ? 0 : dn) * ou;
     }
     pc.flops = 2.5 * N * (N > 1 ? log2(N) : 0) * H;
     if (H == 0) {
         pc.empty = true;
         return true;
     }
+    // Negative strides (guru interfaces; the reference's tensors are signed, fftw/fftw_api.h:472-487): served where the real
+    // transform is ONE real step plus complex passes over the leading dimensions, all on the generic kernel (signed offsets
+    // throughout) and in place in the caller's arrays; the long multi-pass and Bluestein real paths keep positive strides.
+    bool any_neg = false;
     for (const GDim &d : T)
-        if (d.is < 0 || d.os < 0) {
-            set_error("negative strides are not supported");
-            return false;
-        }
+        if (d.n > 1 && (d.is < 0 || d.os < 0)) any_neg = true;
     for (const GDim &d : V)
-        if (d.is < 0 || d.os < 0) {
-            set_error("negative strides are not supported");
-            return false;
-        }
+        if (d.n > 1 && (d.is < 0 || d.os < 0)) any_neg = true;
     if (pc.in_place) {
         // same bytes: stride in reals on the real side == 2 * stride in complex on the other
         bool ok = true;
@@ -233,6 +242,7 @@ inline bool build_real(PlanCore &pc) {
             }
             const bool bwd = !r2c;
             std::vector<int> allowed = on_input ? std::vector<int>{B_IN, B_SCR} : std::vector<int>{B_OUT, B_SCR};
+            if (any_neg) allowed.pop_back();  // (a work array would need this side's span and offset: stay in the caller's array)
             if (!add_c2c_axis(pc, T[ax].n, st_of(ax), st_of(ax), lines, bwd, bwd, allowed))
                 return false;
         }
@@ -245,6 +255,10 @@ inline bool build_real(PlanCore &pc) {
     // lengths the radix kernels cannot do (a prime factor > 13, or odd and longer than one CTA's
     // line): Bluestein on the full length, reading the real / Hermitian-half line directly
     const bool direct_ok = even ? axis_direct_ok(m, unit_rows) : (nl <= cap && factorable(nl));
+    if (any_neg && !(direct_ok && (even ? m <= cap : true))) {
+        set_error("negative strides: real transforms of this length (more than one pass, or Bluestein) need positive strides");
+        return false;
+    }
     if (!direct_ok) {
         BlueSpec b;
         b.n = nl;

@@ -1009,3 +1009,60 @@ def check_mixed_radix_frames(lib):
             os.environ.pop("FFTW_B200_ROW_CAP", None)
         else:
             os.environ["FFTW_B200_ROW_CAP"] = old
+
+
+def check_negative_strides_real(lib, device=False):
+    """guru r2c / c2r with negative strides, where the engine serves them (one real step + complex leading passes): the real
+    input read backwards, the batch walked backwards on both sides, output rows of a 2-D r2c stored in reverse order, c2r
+    writing its real output backwards; and the documented refusals (a length that needs several passes)."""
+    rng = np.random.default_rng(37)
+    rsz, csz = np.dtype(lib.real).itemsize, np.dtype(lib.cplx).itemsize
+    if device:
+        import torch
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        down = lambda t: t.cpu().numpy()
+        addr = lambda t, off, sz: t.data_ptr() + off * sz
+    else:
+        up = lambda a: np.array(a, copy=True, order="C")
+        down = lambda a: a
+        addr = lambda a, off, sz: a.ctypes.data + off * sz
+    # 1. batched 1-D r2c: input read backwards (is = -1), batch walked backwards on the output side
+    n, hm = 60, 4
+    hc = n // 2 + 1
+    x = rand_r(rng, (hm, n), lib)
+    dx, dy = up(x), up(np.zeros((hm, hc), lib.cplx))
+    p = lib.plan_guru_real("r2c", [(n, -1, 1)], [(hm, n, -hc)], addr(dx, n - 1, rsz), addr(dy, (hm - 1) * hc, csz))
+    assert p, "r2c plan with negative strides is NULL"
+    lib.execute(p)
+    lib.destroy_plan(p)
+    got = down(dy)
+    for b in range(hm):
+        ref = np.fft.rfft(x[b][::-1].astype(np.float64))
+        assert rel_l2(got[hm - 1 - b], ref) < tol(lib, n), b
+    # 2. 2-D r2c 6 x 20, output rows in reverse order (os0 < 0)
+    n0, n1 = 6, 20
+    h1 = n1 // 2 + 1
+    x = rand_r(rng, (n0, n1), lib)
+    dx, dy = up(x), up(np.zeros((n0, h1), lib.cplx))
+    p = lib.plan_guru_real("r2c", [(n0, n1, -h1), (n1, 1, 1)], [], addr(dx, 0, rsz), addr(dy, (n0 - 1) * h1, csz))
+    assert p, "2-D r2c plan with a negative output stride is NULL"
+    lib.execute(p)
+    lib.destroy_plan(p)
+    assert rel_l2(down(dy)[::-1], np.fft.rfft2(x.astype(np.float64))) < tol(lib, n0 * n1)
+    # 3. batched c2r: real output written backwards (os = -1), input batch walked backwards
+    n, hm = 64, 3
+    hc = n // 2 + 1
+    x = rand_r(rng, (hm, n), lib)
+    X = np.fft.rfft(x.astype(np.float64), axis=1).astype(lib.cplx)
+    dX, dz = up(X), up(np.zeros((hm, n), lib.real))
+    p = lib.plan_guru_real("c2r", [(n, 1, -1)], [(hm, -hc, n)], addr(dX, (hm - 1) * hc, csz), addr(dz, n - 1, rsz))
+    assert p, "c2r plan with negative strides is NULL"
+    lib.execute(p)
+    lib.destroy_plan(p)
+    got = down(dz)
+    for b in range(hm):  # batch element b reads X[hm-1-b] and writes row b backwards
+        assert rel_l2(got[b][::-1], n * x[hm - 1 - b].astype(np.float64)) < 2 * tol(lib, n), b
+    # refused: a real length that needs more than one pass with a negative stride
+    big = 1 << 16
+    dx, dy = up(np.zeros(big, lib.real)), up(np.zeros(big // 2 + 1, lib.cplx))
+    assert not lib.plan_guru_real("r2c", [(big, -1, 1)], [], addr(dx, big - 1, rsz), addr(dy, 0, csz))

@@ -142,6 +142,11 @@ def test_mixed_radix_long_lengths(lib):
     cases.check_mixed_radix_long(lib)
 
 
+def test_negative_strides_real_transforms(lib):
+    cases.check_negative_strides_real(lib)
+    cases.check_negative_strides_real(lib, device=True)
+
+
 def test_measure_and_wisdom(lib):
     cases.check_measure_and_wisdom(lib)
     cases.check_measure_and_wisdom(lib, device=True)
