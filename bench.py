@@ -49,8 +49,20 @@ WORKLOADS = {
     "c2c_3d_2048_slab_fp32": dict(kind="slab", n=[2048, 2048, 2048], howmany=1, prec="fp32"),
     "c2c_3d_1024_slab_fp32": dict(kind="slab", n=[1024, 1024, 1024], howmany=1, prec="fp32"),
     "c2c_3d_512_slab_fp32": dict(kind="slab", n=[512, 512, 512], howmany=1, prec="fp32"),
+    # lengths that are not powers of two (mixed-radix tile kernels, csrc/mixtile*.cu): not BASELINE configs -- side records
+    # ("smooth_lengths" in the JSON line), about 1 GiB of data each
+    "c2c_1d_1000x134217_fp32": dict(kind="c2c", n=[1000], howmany=134217, prec="fp32"),
+    "c2c_1d_3072x43690_fp32": dict(kind="c2c", n=[3072], howmany=43690, prec="fp32"),
+    "c2c_1d_1152x116508_fp32": dict(kind="c2c", n=[1152], howmany=116508, prec="fp32"),
+    "c2c_1d_1920x69905_fp32": dict(kind="c2c", n=[1920], howmany=69905, prec="fp32"),
+    "c2c_1d_100000x1342_fp32": dict(kind="c2c", n=[100000], howmany=1342, prec="fp32"),
+    "c2c_1d_1000x67108_fp64": dict(kind="c2c", n=[1000], howmany=67108, prec="fp64"),
+    "r2c_1d_2000x134217_fp32": dict(kind="r2c", n=[2000], howmany=134217, prec="fp32"),
+    "r2c_1d_3840x69905_fp32": dict(kind="r2c", n=[3840], howmany=69905, prec="fp32"),
 }
 DEFAULT_WORKLOAD = "c2c_1d_4096x65536_fp32"
+SMOOTH_SET = ["c2c_1d_1000x134217_fp32", "c2c_1d_3072x43690_fp32", "c2c_1d_1152x116508_fp32", "c2c_1d_1920x69905_fp32",
+              "c2c_1d_100000x1342_fp32", "c2c_1d_1000x67108_fp64", "r2c_1d_2000x134217_fp32", "r2c_1d_3840x69905_fp32"]
 
 
 def workload_numbers(w):
@@ -401,6 +413,7 @@ def config_record(name, steps, warmup):
         rec["hbm_frac"] = None
         rec["note"] = "32 KiB of traffic: launch-latency bound; fftw_execute_sync_us = wall time of one synchronous fftw_execute_dft call"
     rec["check"] = validate(lib, w, x, y, plan)
+    rec["plan"] = [l.strip()[:160] for l in lib.sprint_plan(plan).strip().split("\n")[1:]]
     lib.destroy_plan(plan)
     del x, y
     torch.cuda.empty_cache()
@@ -517,6 +530,20 @@ def run_gpu(args):
             slab = {"workload": "c2c_3d_%d_slab_fp32" % args.slab_n, "error": repr(e)[:400]}
         torch.cuda.empty_cache()
 
+    # ---- lengths that are not powers of two: side records, LAST of the GPU work so that whatever happens here cannot touch
+    # the headline, the BASELINE configs or the slab record above
+    smooth = None
+    if not args.no_configs and args.workload == DEFAULT_WORKLOAD:
+        if rank == 0:
+            smooth = []
+            for name in SMOOTH_SET:
+                try:
+                    smooth.append(config_record(name, steps=10, warmup=3))
+                except Exception as e:
+                    smooth.append({"workload": name, "error": repr(e)[:300]})
+            torch.cuda.empty_cache()
+        barrier()
+
     # ---- the reference's own CPU path on this box's host cores (rank 0; the other ranks wait)
     cpu = None
     if rank == 0 and not args.no_cpu:
@@ -556,6 +583,8 @@ def run_gpu(args):
             line["configs"] = configs
         if slab is not None:
             line["slab"] = slab
+        if smooth is not None:
+            line["smooth_lengths"] = smooth
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
