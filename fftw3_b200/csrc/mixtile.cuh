@@ -1,5 +1,6 @@
 // csrc/mixtile.cuh -- tile kernels for the common lengths that are NOT powers of two: kernel, instance wrapper and list macros
-// (the lists themselves are in mixtile.cu and mixtile2.cu, two translation units so that they compile side by side).
+// (the lists themselves are in mixtile.cu, mixtile2.cu and mixtile3.cu, separate translation units so that they compile side by
+// side with engine.cu instead of after it).
 //
 // Same kernel body as the power-of-two tile kernels (tile_kernel.cuh TileFFT: a thread keeps E points of a line in
 // registers across all radix passes, one exchange through padded shared memory between passes, global memory touched
@@ -13,9 +14,8 @@
 // and t1_* for such lengths (fftw/dft_scalar/codelets/codlist.c:57-109; drivers direct_apply fftw/fftw_api.c:3183-3187,
 // dftw_direct_apply :2315-2324).
 //
-// A separate translation unit so that it compiles next to engine.cu, not after it.  Row form for every listed length;
-// column / column+twiddle / row->column forms (what the other axes of an N-D transform and the two passes of a long
-// 1-D transform need) for the lengths that have a column tile width.
+// Row form for every listed length; r2c / c2r row forms where E is even; column / column+twiddle / row->column forms (what the
+// other axes of an N-D transform and the two passes of a long 1-D transform need) for the lengths that have a column tile width.
 #pragma once
 #include "tile_entry.h"
 #include "tile_kernel.cuh"
