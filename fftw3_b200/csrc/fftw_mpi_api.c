@@ -97,7 +97,7 @@ fftw_plan fftw_mpi_plan_dft_3d(ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, FFTW_CO
     return fftw_mpi_plan_many_dft(3, n, 1, FFTW_MPI_DEFAULT_BLOCK, FFTW_MPI_DEFAULT_BLOCK, in, out, comm, sign, flags);
 }
 
-/* real data (reference fftw/mpi/api.c:751-858): rank 3 with any howmany and explicit block sizes, rank 2 with default blocks */
+/* real data (reference fftw/mpi/api.c:751-858): rank 3 with any howmany, rank 2 with howmany 1; explicit block sizes for both */
 static fftw_plan mpi_rdft(int kind, int rnk, const ptrdiff_t *n, ptrdiff_t howmany, ptrdiff_t iblock,
                           ptrdiff_t oblock, void *in, void *out, MPI_Comm comm, unsigned flags) {
     fftw_plan p;
@@ -107,15 +107,11 @@ static fftw_plan mpi_rdft(int kind, int rnk, const ptrdiff_t *n, ptrdiff_t howma
     if ((rnk != 3 && rnk != 2) || !n || !comm || howmany < 1 || (rnk == 2 && howmany != 1)) return 0;
     if (iblock < 0 || oblock < 0) return 0;
     P = b2fft_comm_size(comm);
-    if (rnk == 2) { /* default blocks only; the distributed "dimension 1" is the n1/2+1 complex columns */
-        const ptrdiff_t d1 = n[1] / 2 + 1;
-        if (iblock != FFTW_MPI_DEFAULT_BLOCK && iblock != ((tin ? d1 : n[0]) + P - 1) / P) return 0;
-        if (oblock != FFTW_MPI_DEFAULT_BLOCK && oblock != ((tout ? d1 : n[0]) + P - 1) / P) return 0;
-        bp = b2fft_slab_plan_rdft_2d(kind, n[0], n[1], comm, tin, tout, flags);
-    } else {
+    {
         /* iblock = block size of the distributed INPUT dimension, oblock = of the distributed OUTPUT dimension.  The real
-         * array is always distributed over n0; the complex one over n1 when it is the transposed side, else over n0 too --
-         * and then both sides must use the same block (as in fftw_mpi_plan_many_dft above). */
+         * array is always distributed over n0; the complex one over dimension 1 (n1 in 3-D, the n1/2+1 complex columns in
+         * 2-D) when it is the transposed side, else over n0 too -- and then both sides must use the same block (as in
+         * fftw_mpi_plan_many_dft above). */
         const ptrdiff_t rblock = kind == B2FFT_R2C ? iblock : oblock; /* of the real side: over n0 */
         const ptrdiff_t cblock = kind == B2FFT_R2C ? oblock : iblock; /* of the complex side */
         const int ctrans = kind == B2FFT_R2C ? tout : tin;
@@ -125,7 +121,8 @@ static fftw_plan mpi_rdft(int kind, int rnk, const ptrdiff_t *n, ptrdiff_t howma
             if (br != bc) return 0;
             b1 = 0;
         }
-        bp = b2fft_slab_plan_many_rdft_3d_blocks(kind, n[0], n[1], n[2], howmany, rblock, b1, comm, tin, tout, flags);
+        bp = rnk == 3 ? b2fft_slab_plan_many_rdft_3d_blocks(kind, n[0], n[1], n[2], howmany, rblock, b1, comm, tin, tout, flags)
+                      : b2fft_slab_plan_rdft_2d_blocks(kind, n[0], n[1], rblock, b1, comm, tin, tout, flags);
     }
     if (!bp) return 0;
     p = (fftw_plan)malloc(sizeof *p);

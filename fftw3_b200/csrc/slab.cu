@@ -618,6 +618,21 @@ extern "C" b2fft_plan *b2fft_slab_plan_rdft_2d(int kind, ptrdiff_t n0, ptrdiff_t
     }
     return slab_plan_create(kind, n0, n1, 1, 1, c, kind == B2FFT_R2C ? -1 : +1, transposed_in, transposed_out, 0, 0, true);
 }
+// ... with explicit block sizes: block0 over n0, block1 over the n1/2+1 complex columns; 0 = default
+extern "C" b2fft_plan *b2fft_slab_plan_rdft_2d_blocks(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t block0, ptrdiff_t block1,
+                                                      b2fft_comm *c, int transposed_in, int transposed_out, unsigned flags) {
+    (void)flags;
+    if (kind != B2FFT_R2C && kind != B2FFT_C2R) return nullptr;
+    if ((kind == B2FFT_R2C && transposed_in) || (kind == B2FFT_C2R && transposed_out)) {
+        set_error("slab real transform: a transposed REAL array is not supported");
+        return nullptr;
+    }
+    if (block0 < 0 || block1 < 0) {
+        set_error("slab real transform: negative block size");
+        return nullptr;
+    }
+    return slab_plan_create(kind, n0, n1, 1, 1, c, kind == B2FFT_R2C ? -1 : +1, transposed_in, transposed_out, block0, block1, true);
+}
 
 static b2fft_plan *slab_plan_create(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t n2, ptrdiff_t howmany,
                                     b2fft_comm *c, int sign, int transposed_in, int transposed_out,

@@ -165,6 +165,10 @@ b2fft_plan *b2fft_slab_plan_many_rdft_3d_blocks(int kind, ptrdiff_t n0, ptrdiff_
  * transposed, [local_n1c][n0] with the n1/2+1 complex columns block-distributed. */
 b2fft_plan *b2fft_slab_plan_rdft_2d(int kind, ptrdiff_t n0, ptrdiff_t n1, b2fft_comm *c, int transposed_in,
                                     int transposed_out, unsigned flags);
+/* ... with explicit block sizes: block0 over n0, block1 over the n1/2+1 complex columns; 0 = default (the iblock / oblock of
+ * fftw_mpi_plan_many_dft_r2c / _c2r with rnk = 2, reference fftw/mpi/api.c:790-836) */
+b2fft_plan *b2fft_slab_plan_rdft_2d_blocks(int kind, ptrdiff_t n0, ptrdiff_t n1, ptrdiff_t block0, ptrdiff_t block1, b2fft_comm *c,
+                                           int transposed_in, int transposed_out, unsigned flags);
 /* Staged execution, for callers that bring their own transport and for the CPU tests of the
  * multi-rank path: stage 0 local (n1 x n2) FFTs in -> send buffer; 1 exchange (NCCL); 2 length-n0
  * FFTs recv buffer -> out; 3 (natural-order output only) exchange back (c2r plans: 0 forward exchange

@@ -952,3 +952,93 @@ def test_complex_to_real_slab_with_explicit_block_sizes(shape, P, b_n0, b_n1, ti
             assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
         lib.destroy_plan(r["plan"])
         L.b2fft_comm_destroy(r["comm"])
+
+
+@pytest.mark.parametrize("transposed", [True, False], ids=["transposed", "natural"])
+@pytest.mark.parametrize("shape,P,b_n0,b_n1c", [((10, 22), 4, 4, 5), ((9, 62), 3, 5, 16), ((8, 10), 2, 6, 3)],
+                         ids=["10x22", "9x62", "8x10"])
+def test_two_dimensional_real_slab_with_explicit_block_sizes(shape, P, b_n0, b_n1c, transposed):
+    """fftw_mpi_plan_many_dft_r2c / _c2r with rnk = 2 and explicit iblock / oblock: block over n0 on the real side, over the
+    n1/2+1 complex columns on a transposed complex side (fftw/mpi/api.c:790-836); r2c forward, then c2r back from that layout."""
+    lib = load()
+    L = _many_real_api(lib)
+    n0, n1 = shape
+    n1c = n1 // 2 + 1
+    assert (n1c + b_n1c - 1) // b_n1c <= P
+    rng = np.random.default_rng(71 + P)
+    x = (rng.random(shape) - 0.5).astype(lib.real)
+    Y = orc.r2c(x)
+    nn = (C.c_ssize_t * 2)(n0, n1)
+    nc = (C.c_ssize_t * 2)(n0, n1c)
+    fwd, bwd = [], []
+    for pe in range(P):
+        comm = L.b2fft_comm_detached(P, pe)
+        v = [C.c_ssize_t() for _ in range(4)]
+        N = L.fftw_mpi_local_size_many_transposed(2, nc, 1, b_n0, b_n1c if transposed else 0, comm, *[C.byref(t) for t in v])
+        ln0, s0, ln1, s1 = (t.value for t in v)
+        assert ln0 == max(0, min(b_n0, n0 - pe * b_n0))
+        rin = np.zeros(2 * max(N, 1), dtype=lib.real)
+        pad = np.zeros((ln0, 2 * n1c), dtype=lib.real)
+        pad[:, :n1] = x[s0:s0 + ln0]
+        rin[:pad.size] = pad.ravel()
+        cbuf = np.zeros(max(N, 1), dtype=lib.cplx)
+        rout = np.zeros(2 * max(N, 1), dtype=lib.real)
+        cb = b_n1c if transposed else b_n0
+        pf = L.fftw_mpi_plan_many_dft_r2c(2, nn, 1, b_n0, cb, rin.ctypes.data, cbuf.ctypes.data, comm,
+                                          capi.FFTW_ESTIMATE | (TRANSPOSED_OUT if transposed else 0))
+        pb = L.fftw_mpi_plan_many_dft_c2r(2, nn, 1, cb, b_n0, cbuf.ctypes.data, rout.ctypes.data, comm,
+                                          capi.FFTW_ESTIMATE | (TRANSPOSED_IN if transposed else 0))
+        assert pf and pb, "2-D real slab plan with explicit blocks is NULL"
+        geo = dict(comm=comm, la=ln0, sa=s0, lb=ln1, sb=s1, rin=rin, cbuf=cbuf, rout=rout)
+        for plan, lst in ((pf, fwd), (pb, bwd)):
+            S, bp = buffer_view(lib, plan, 0, lib.cplx)
+            R, _ = buffer_view(lib, plan, 1, lib.cplx)
+            lst.append(dict(plan=plan, bp=bp, S=S, R=R, **geo))
+
+    def reverse_exchange(ranks, dst_key):  # receive layout [n0][lb] -> [la][n1c] rows
+        for src in ranks:
+            if src["lb"] == 0:
+                continue
+            Rv = src["R"][:n0 * src["lb"]].reshape(n0, src["lb"])
+            for dst in ranks:
+                if dst["la"] == 0:
+                    continue
+                Dv = dst[dst_key][:dst["la"] * n1c].reshape(dst["la"], n1c)
+                Dv[:, src["sb"]:src["sb"] + src["lb"]] = Rv[dst["sa"]:dst["sa"] + dst["la"]]
+
+    for r in fwd:
+        assert L.b2fft_slab_stage(r["bp"], 0, r["rin"].ctypes.data, r["cbuf"].ctypes.data) == 0
+    _exchange(fwd, n0, n1c, 1)
+    for r in fwd:
+        assert L.b2fft_slab_stage(r["bp"], 2, r["rin"].ctypes.data, r["cbuf"].ctypes.data) == 0
+    if not transposed:
+        reverse_exchange(fwd, "cbuf")
+    for r in fwd:
+        ref = Y.T[r["sb"]:r["sb"] + r["lb"]] if transposed else Y[r["sa"]:r["sa"] + r["la"]]
+        got = r["cbuf"][:ref.size].reshape(ref.shape)
+        if ref.size:
+            assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-13
+    if not transposed:
+        for src in bwd:
+            if src["la"] == 0:
+                continue
+            Iv = src["cbuf"][:src["la"] * n1c].reshape(src["la"], n1c)
+            for dst in bwd:
+                if dst["lb"] == 0:
+                    continue
+                Rv = dst["R"][:n0 * dst["lb"]].reshape(n0, dst["lb"])
+                Rv[src["sa"]:src["sa"] + src["la"]] = Iv[:, dst["sb"]:dst["sb"] + dst["lb"]]
+    for r in bwd:
+        assert L.b2fft_slab_stage(r["bp"], 1, r["cbuf"].ctypes.data, r["rout"].ctypes.data) == 0
+    reverse_exchange(bwd, "S")
+    for r in bwd:
+        assert L.b2fft_slab_stage(r["bp"], 3, r["cbuf"].ctypes.data, r["rout"].ctypes.data) == 0
+        want = x[r["sa"]:r["sa"] + r["la"]] * (n0 * n1)
+        got = r["rout"][:r["la"] * 2 * n1c].reshape(r["la"], 2 * n1c)[:, :n1]
+        if want.size:
+            assert np.linalg.norm(got - want) / np.linalg.norm(want) < 1e-13
+    for lst in (fwd, bwd):
+        for r in lst:
+            lib.destroy_plan(r["plan"])
+    for r in fwd:
+        L.b2fft_comm_destroy(r["comm"])
