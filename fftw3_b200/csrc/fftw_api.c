@@ -733,6 +733,10 @@ void fftw_flops(const fftw_plan p, double *add, double *mul, double *fmas) {
     if (mul) *mul = 0.4 * f;
     if (fmas) *fmas = 0.0;
 }
-double fftw_estimate_cost(const fftw_plan p) { return p ? b2fft_plan_flops(p->bp) : 0.0; }
-double fftw_cost(const fftw_plan p) { return p ? b2fft_plan_flops(p->bp) : 0.0; }
+/* cost = the plan's flop count, whatever kind of plan it is (r2r and split-array plans keep theirs in their own objects) */
+static double plan_cost(const fftw_plan p) {
+    return !p ? 0.0 : p->rr ? b2fft_r2r_flops(p->rr) : p->sp ? b2fft_split_flops(p->sp) : b2fft_plan_flops(p->bp);
+}
+double fftw_estimate_cost(const fftw_plan p) { return plan_cost(p); }
+double fftw_cost(const fftw_plan p) { return plan_cost(p); }
 int fftw_alignment_of(FFTW_REAL_TYPE *p) { return (int)(((uintptr_t)p) % 16); } /* fftw_api.c:14530 */

@@ -76,6 +76,30 @@ def test_plan_description_and_flops(lib):
     lib.destroy_plan(p)
 
 
+def test_cost_is_the_flop_count_for_every_kind_of_plan(lib):
+    """fftw_cost / fftw_estimate_cost (reference fftw_api.c: cost of the plan's operation counts): c2c, r2r and split-array
+    plans all report the flop count fftw_flops reports -- r2r and split plans keep theirs in their own objects"""
+    import ctypes as C
+    L = lib.lib
+    L.fftw_cost.restype = C.c_double
+    L.fftw_cost.argtypes = [C.c_void_p]
+    L.fftw_estimate_cost.restype = C.c_double
+    L.fftw_estimate_cost.argtypes = [C.c_void_p]
+    x = np.zeros((4, 96), dtype=lib.cplx)
+    y = x.copy()
+    plans = [lib.plan_many_dft([96], 4, x, None, 1, 96, y, None, 1, 96, -1)]
+    r = np.zeros(64, dtype=lib.real)
+    r2 = r.copy()
+    plans.append(lib.plan_r2r([64], r, r2, [3]))  # REDFT00
+    ri, ii, ro, io = (np.zeros(48, dtype=lib.real) for _ in range(4))
+    plans.append(lib.plan_guru_split("c2c", [(48, 1, 1)], [], ri, ii, ro, io))
+    for p in plans:
+        assert p
+        f = sum(lib.flops(p))
+        assert f > 0 and abs(L.fftw_cost(p) - f) < 1e-6 and abs(L.fftw_estimate_cost(p) - f) < 1e-6
+        lib.destroy_plan(p)
+
+
 def test_long_column_axes_take_the_pipelined_kernel(lib):
     x = np.zeros((1024, 64), dtype=lib.cplx)
     p = lib.plan_dft([1024, 64], x, x.copy(), -1)
